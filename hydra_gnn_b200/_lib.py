@@ -1,0 +1,133 @@
+"""ctypes binding of ``libhydra_gnn_b200.so`` (the C ABI in ``include/hydra_gnn_b200.h``).
+
+The library is the ONLY compute path of this package: there is no CPU or eager-PyTorch
+fallback.  ``lib()`` raises ``RuntimeError`` when the shared object has not been built
+(``python __graft_entry__.py`` / ``make -C hydra_gnn_b200/csrc``) or when no CUDA device
+is usable.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+HG_MAX_RELATIONS = 8
+HG_MAX_SEGMENTS = 8
+HG_MAX_PLAN_RELATIONS = 16
+
+REDUCE = {"sum": 0, "add": 0, "mean": 1, "max": 2}
+ACT = {None: 0, "none": 0, "relu": 1, "elu": 2}
+GROUP = {"sum": 0, "mean": 1}
+PREC = {"fp32": 0, "tf32x3": 1}
+
+_SO_NAME = "libhydra_gnn_b200.so"
+SO_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), _SO_NAME)
+
+vp, i32, i64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
+
+
+class PlanRel(C.Structure):
+    _fields_ = [("src", vp), ("dst", vp), ("n_edges", i64), ("n_src", i32), ("n_dst", i32),
+                ("self_loops", i32), ("reserved", i32), ("rowptr", vp), ("col", vp), ("perm", vp),
+                ("inv_sqrt_deg", vp)]
+
+
+class SegArgs(C.Structure):
+    _fields_ = [("x", vp), ("ldx", i64), ("rowptr", vp), ("col", vp), ("src_scale", vp), ("dst_scale", vp),
+                ("row_map", vp), ("x_self", vp), ("ldself", i64), ("self_coef_ptr", vp), ("self_coef_add", f32),
+                ("bias", vp), ("out", vp), ("ldout", i64), ("n_out", i32), ("F", i32), ("op", i32), ("act", i32)]
+
+
+class GatRel(C.Structure):
+    _fields_ = [("xs", vp), ("ldxs", i64), ("a_src", vp), ("lda_src", i64), ("a_dst", vp), ("lda_dst", i64),
+                ("a_edge", vp), ("rowptr", vp), ("col", vp), ("bias", vp)]
+
+
+class GatArgs(C.Structure):
+    _fields_ = [("rel", GatRel * HG_MAX_RELATIONS), ("n_rel", i32), ("n_dst", i32), ("H", i32), ("C", i32),
+                ("concat", i32), ("group", i32), ("act", i32), ("neg_slope", f32), ("out", vp), ("ldout", i64),
+                ("alpha_saved", vp * HG_MAX_RELATIONS)]
+
+
+class LinSeg(C.Structure):
+    _fields_ = [("x", vp), ("ldx", i64), ("w", vp), ("ldw", i64), ("K", i32), ("reserved", i32)]
+
+
+class LinearArgs(C.Structure):
+    _fields_ = [("seg", LinSeg * HG_MAX_SEGMENTS), ("n_seg", i32), ("M", i32), ("N", i32), ("bias", vp),
+                ("scale", vp), ("shift", vp), ("act", i32), ("precision", i32), ("y", vp), ("ldy", i64)]
+
+
+_STRUCTS = [PlanRel, SegArgs, GatRel, GatArgs, LinSeg, LinearArgs]
+
+# name -> (restype, argtypes); every symbol declared in include/hydra_gnn_b200.h
+SYMBOLS = {
+    "hg_strerror": (C.c_char_p, [C.c_int]),
+    "hg_abi_version": (C.c_int, []),
+    "hg_last_cuda_error": (C.c_int, []),
+    "hg_device_sm_count": (C.c_int, []),
+    "hg_sizeof": (C.c_int, [C.c_int]),
+    "hg_plan_workspace_bytes": (C.c_size_t, [C.POINTER(PlanRel), C.c_int]),
+    "hg_plan_build": (C.c_int, [C.POINTER(PlanRel), C.c_int, vp, vp, C.c_size_t, vp]),
+    "hg_seg_reduce": (C.c_int, [C.POINTER(SegArgs), vp]),
+    "hg_gat_fused": (C.c_int, [C.POINTER(GatArgs), vp]),
+    "hg_linear_workspace_bytes": (C.c_size_t, [C.POINTER(LinearArgs)]),
+    "hg_linear": (C.c_int, [C.POINTER(LinearArgs), vp, C.c_size_t, vp]),
+    "hg_edge_logits": (C.c_int, [vp, i64, i32, vp, vp, i64, vp, vp, i32, vp, vp]),
+    "hg_relative_pos": (C.c_int, [vp, vp, vp, vp, i64, vp, vp]),
+}
+
+_lock = threading.Lock()
+_handle = None
+launch_count = 0  # kernels-launching ABI calls made through this binding (bench's gpu_launches bookkeeping)
+
+
+def load_shared_object():
+    """dlopen + prototype every symbol + verify struct layouts.  Needs no GPU."""
+    global _handle
+    with _lock:
+        if _handle is not None:
+            return _handle
+        if not os.path.exists(SO_PATH):
+            raise RuntimeError(
+                f"{_SO_NAME} is not built ({SO_PATH} missing). hydra_gnn_b200 has no CPU / eager fallback: "
+                "build it with `python -c 'import __graft_entry__ as g; g.build()'` or "
+                "`make -C hydra_gnn_b200/csrc`.")
+        h = C.CDLL(SO_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(h, name)  # AttributeError if the symbol is not exported
+            fn.restype, fn.argtypes = res, args
+        for which, st in enumerate(_STRUCTS):
+            if h.hg_sizeof(which) != C.sizeof(st):
+                raise RuntimeError(f"ABI mismatch: sizeof({st.__name__}) python={C.sizeof(st)} C={h.hg_sizeof(which)}")
+        _handle = h
+        return h
+
+
+def lib():
+    """The loaded library, after checking that a CUDA device is usable."""
+    h = load_shared_object()
+    import torch
+
+    if not torch.cuda.is_available():
+        raise RuntimeError("hydra_gnn_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    return h
+
+
+def check(code: int, what: str):
+    if code != 0:
+        h = load_shared_object()
+        msg = h.hg_strerror(code).decode()
+        extra = f" (cudaError {h.hg_last_cuda_error()})" if code == -4 else ""
+        raise RuntimeError(f"{what}: {msg}{extra}")
+
+
+def ptr(t):
+    """Device pointer of a tensor (or NULL)."""
+    return None if t is None else t.data_ptr()
+
+
+def stream_ptr():
+    import torch
+
+    return torch.cuda.current_stream().cuda_stream

@@ -1,0 +1,72 @@
+// Edge-attribute helpers of the GAT_edge path (integer gathers + exact fp32 subtraction).
+#include "hg_common.cuh"
+
+namespace hg {
+namespace {
+
+constexpr int kThreads = 256;
+
+// a_edge[p, h] = perm[p] >= 0 ? <edge_attr[perm[p], :D], v[h, :D]> : <fill, v[h]>, p < E' = *n_entries
+__global__ void __launch_bounds__(kThreads)
+k_edge_logits(const float* __restrict__ attr, int64_t ld, int D, const int32_t* __restrict__ perm,
+              const int32_t* __restrict__ n_entries, int64_t cap, const float* __restrict__ v,
+              const float* __restrict__ fill, int H, float* __restrict__ out) {
+    const int64_t total = min(static_cast<int64_t>(__ldg(n_entries)), cap) * H;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += stride) {
+        const int64_t p = t / H;
+        const int h = static_cast<int>(t % H);
+        const int32_t e = __ldg(perm + p);
+        float acc = 0.f;
+        if (e >= 0) {
+            for (int d = 0; d < D; ++d) acc = fmaf(__ldg(attr + e * ld + d), __ldg(v + h * D + d), acc);
+        } else if (fill) {
+            for (int d = 0; d < D; ++d) acc = fmaf(__ldg(fill + d), __ldg(v + h * D + d), acc);
+        }
+        out[t] = acc;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_relative_pos(const float* __restrict__ ps, const float* __restrict__ pd, const int64_t* __restrict__ src,
+               const int64_t* __restrict__ dst, int64_t E, float* __restrict__ out) {
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; e < E; e += stride) {
+        const int64_t s = src[e], d = dst[e];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) out[e * 3 + c] = __ldg(pd + d * 3 + c) - __ldg(ps + s * 3 + c);
+    }
+}
+
+unsigned grid_for(int64_t n) {
+    const int sms = sm_count() > 0 ? sm_count() : 148;
+    int64_t g = ceil_div<int64_t>(n > 0 ? n : 1, kThreads);
+    const int64_t cap = static_cast<int64_t>(sms) * 8 * 8;
+    return static_cast<unsigned>(g < cap ? g : cap);
+}
+
+}  // namespace
+}  // namespace hg
+
+extern "C" int hg_edge_logits(const float* edge_attr, int64_t ld_attr, int32_t D, const int32_t* perm,
+                              const int32_t* rowptr_last, int64_t cap, const float* v, const float* fill, int32_t H,
+                              float* a_edge, void* stream_) {
+    using namespace hg;
+    if (cap < 0 || D < 0 || H < 1) return HG_EINVAL;
+    if (cap == 0) return HG_OK;
+    if (!perm || !rowptr_last || !v || !a_edge || (D > 0 && !edge_attr)) return HG_EINVAL;
+    k_edge_logits<<<grid_for(cap * H), kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(
+        edge_attr, ld_attr, D, perm, rowptr_last, cap, v, fill, H, a_edge);
+    return check_launch();
+}
+
+extern "C" int hg_relative_pos(const float* pos_src, const float* pos_dst, const int64_t* src, const int64_t* dst,
+                               int64_t E, float* edge_attr, void* stream_) {
+    using namespace hg;
+    if (E < 0) return HG_EINVAL;
+    if (E == 0) return HG_OK;
+    if (!pos_src || !pos_dst || !src || !dst || !edge_attr) return HG_EINVAL;
+    k_relative_pos<<<grid_for(E), kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(pos_src, pos_dst, src, dst, E,
+                                                                                      edge_attr);
+    return check_launch();
+}

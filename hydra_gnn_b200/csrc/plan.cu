@@ -1,0 +1,273 @@
+// K1 -- graph plan: CSR-by-destination for up to 16 relations in six launches.
+//
+// Integer work, bit-exact with a stable sort by destination of the (self-loop adjusted) edge
+// list.  Stability without a radix sort: count -> scan -> unordered atomic fill of edge ids
+// -> every edge ranks itself inside its (short) row.  All relations of a batch share each
+// launch (blockIdx.y = relation) so a 4-relation DSG plan or a 15-relation H-tree plan costs
+// the same number of launches.  HBM-bound: 16 B/edge in, 8 B/edge + 4 B/row out.
+#include "hg_common.cuh"
+
+namespace hg {
+namespace {
+
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 8;
+constexpr int kScanTile = kScanThreads * kScanItems;  // rows per scan block
+constexpr int kEdgeThreads = 256;
+
+struct RelDev {
+    const int64_t* src;
+    const int64_t* dst;
+    int64_t n_edges;
+    int32_t n_src, n_dst, self_loops, n_loop;
+    int32_t* rowptr;
+    int32_t* col;
+    int32_t* perm;
+    float* inv_sqrt_deg;
+    int32_t* cnt;      // [n_dst]  histogram, then fill cursor
+    int32_t* ids_tmp;  // [E + n_loop] edge ids, row-bucketed, unordered inside a row
+    int32_t* bsum;     // [n_scan_blocks]
+    int32_t n_scan_blocks;
+    int32_t pad;
+};
+
+struct PlanParams {
+    RelDev r[HG_MAX_PLAN_RELATIONS];
+    int32_t* status;
+};
+
+__device__ __forceinline__ bool edge_kept(const RelDev& R, int64_t e, int32_t& s, int32_t& d, int32_t* status) {
+    const int64_t s64 = R.src[e], d64 = R.dst[e];
+    if (s64 < 0 || s64 >= R.n_src || d64 < 0 || d64 >= R.n_dst) {
+        if (status) atomicAdd(status, 1);
+        return false;
+    }
+    s = static_cast<int32_t>(s64);
+    d = static_cast<int32_t>(d64);
+    return !(R.self_loops && s == d);
+}
+
+__global__ void __launch_bounds__(kEdgeThreads) k_count(const __grid_constant__ PlanParams P) {
+    const RelDev& R = P.r[blockIdx.y];
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; e < R.n_edges; e += stride) {
+        int32_t s, d;
+        if (edge_kept(R, e, s, d, P.status)) atomicAdd(&R.cnt[d], 1);
+    }
+}
+
+__device__ __forceinline__ int32_t row_count(const RelDev& R, int32_t k) {
+    return k < R.n_dst ? R.cnt[k] + (k < R.n_loop ? 1 : 0) : 0;
+}
+
+// Block-wide exclusive scan of one int per thread; returns the exclusive prefix, total in `total`.
+__device__ __forceinline__ int32_t block_exclusive_scan(int32_t v, int32_t& total) {
+    __shared__ int32_t warp_tot[kScanThreads / kWarp];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) warp_tot[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        int32_t w = lane < kScanThreads / kWarp ? warp_tot[lane] : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int32_t t = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += t;
+        }
+        if (lane < kScanThreads / kWarp) warp_tot[lane] = w;  // inclusive over warps
+    }
+    __syncthreads();
+    const int32_t warp_off = wid == 0 ? 0 : warp_tot[wid - 1];
+    total = warp_tot[kScanThreads / kWarp - 1];
+    __syncthreads();
+    return warp_off + inc - v;
+}
+
+__global__ void __launch_bounds__(kScanThreads) k_scan_a(const __grid_constant__ PlanParams P) {
+    const RelDev& R = P.r[blockIdx.y];
+    if (static_cast<int>(blockIdx.x) >= R.n_scan_blocks) return;
+    const int32_t base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+    int32_t v = 0;
+#pragma unroll
+    for (int t = 0; t < kScanItems; ++t) v += row_count(R, base + t);
+    int32_t total;
+    block_exclusive_scan(v, total);
+    if (threadIdx.x == 0) R.bsum[blockIdx.x] = total;
+}
+
+// One block per relation: in-place exclusive scan of the per-block sums.
+__global__ void __launch_bounds__(kScanThreads) k_scan_b(const __grid_constant__ PlanParams P) {
+    const RelDev& R = P.r[blockIdx.x];
+    int32_t carry = 0;
+    for (int32_t b0 = 0; b0 < R.n_scan_blocks; b0 += kScanThreads) {
+        const int32_t b = b0 + threadIdx.x;
+        const int32_t v = b < R.n_scan_blocks ? R.bsum[b] : 0;
+        int32_t total;
+        const int32_t ex = block_exclusive_scan(v, total);
+        if (b < R.n_scan_blocks) R.bsum[b] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) R.rowptr[R.n_dst] = carry;  // E'
+}
+
+__global__ void __launch_bounds__(kScanThreads) k_scan_c(const __grid_constant__ PlanParams P) {
+    const RelDev& R = P.r[blockIdx.y];
+    if (static_cast<int>(blockIdx.x) >= R.n_scan_blocks) return;
+    const int32_t base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+    int32_t c[kScanItems];
+    int32_t v = 0;
+#pragma unroll
+    for (int t = 0; t < kScanItems; ++t) {
+        c[t] = row_count(R, base + t);
+        v += c[t];
+    }
+    int32_t total;
+    int32_t run = block_exclusive_scan(v, total) + R.bsum[blockIdx.x];
+#pragma unroll
+    for (int t = 0; t < kScanItems; ++t) {
+        const int32_t k = base + t;
+        if (k < R.n_dst) {
+            R.rowptr[k] = run;
+            R.cnt[k] = 0;  // becomes the fill cursor
+            if (R.inv_sqrt_deg) R.inv_sqrt_deg[k] = c[t] > 0 ? 1.0f / sqrtf(static_cast<float>(c[t])) : 0.f;
+        }
+        run += c[t];
+    }
+}
+
+__global__ void __launch_bounds__(kEdgeThreads) k_fill(const __grid_constant__ PlanParams P) {
+    const RelDev& R = P.r[blockIdx.y];
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; e < R.n_edges; e += stride) {
+        int32_t s, d;
+        if (edge_kept(R, e, s, d, nullptr)) {
+            const int32_t slot = R.rowptr[d] + atomicAdd(&R.cnt[d], 1);
+            R.ids_tmp[slot] = static_cast<int32_t>(e);
+        }
+    }
+}
+
+// Every kept edge ranks itself among the edge ids of its row => stable order; loops go last.
+__global__ void __launch_bounds__(kEdgeThreads) k_rank(const __grid_constant__ PlanParams P) {
+    const RelDev& R = P.r[blockIdx.y];
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    const int64_t total = R.n_edges + R.n_loop;
+    for (int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; e < total; e += stride) {
+        if (e >= R.n_edges) {  // appended self loop (k, k)
+            const int32_t k = static_cast<int32_t>(e - R.n_edges);
+            const int32_t pos = R.rowptr[k + 1] - 1;
+            R.col[pos] = k;
+            if (R.perm) R.perm[pos] = -1;
+            continue;
+        }
+        int32_t s, d;
+        if (!edge_kept(R, e, s, d, nullptr)) continue;
+        const int32_t base = R.rowptr[d];
+        const int32_t n_real = R.rowptr[d + 1] - base - (d < R.n_loop ? 1 : 0);
+        const int32_t me = static_cast<int32_t>(e);
+        int32_t rank = 0;
+        for (int32_t t = 0; t < n_real; ++t) rank += (R.ids_tmp[base + t] < me) ? 1 : 0;
+        R.col[base + rank] = s;
+        if (R.perm) R.perm[base + rank] = me;
+    }
+}
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct WsLayout {
+    size_t cnt_off[HG_MAX_PLAN_RELATIONS], ids_off[HG_MAX_PLAN_RELATIONS], bsum_off[HG_MAX_PLAN_RELATIONS];
+    size_t cnt_total;  // bytes of the leading region that must be zeroed
+    size_t total;
+};
+
+int layout(const hg_plan_rel* rels, int n_rel, WsLayout& L) {
+    if (!rels || n_rel < 0 || n_rel > HG_MAX_PLAN_RELATIONS) return HG_EINVAL;
+    size_t off = 0;
+    for (int r = 0; r < n_rel; ++r) {
+        if (rels[r].n_edges < 0 || rels[r].n_src < 0 || rels[r].n_dst < 0) return HG_EINVAL;
+        const int64_t loops = rels[r].self_loops ? (rels[r].n_src < rels[r].n_dst ? rels[r].n_src : rels[r].n_dst) : 0;
+        if (rels[r].n_edges + loops >= (int64_t(1) << 31)) return HG_ERANGE;
+        L.cnt_off[r] = off;
+        off = align_up(off + sizeof(int32_t) * static_cast<size_t>(rels[r].n_dst), 256);
+    }
+    L.cnt_total = off;
+    for (int r = 0; r < n_rel; ++r) {
+        const int64_t loops = rels[r].self_loops ? (rels[r].n_src < rels[r].n_dst ? rels[r].n_src : rels[r].n_dst) : 0;
+        L.ids_off[r] = off;
+        off = align_up(off + sizeof(int32_t) * static_cast<size_t>(rels[r].n_edges + loops), 256);
+        L.bsum_off[r] = off;
+        off = align_up(off + sizeof(int32_t) * static_cast<size_t>(ceil_div<int64_t>(rels[r].n_dst, kScanTile) + 1), 256);
+    }
+    L.total = off;
+    return HG_OK;
+}
+
+}  // namespace
+}  // namespace hg
+
+extern "C" size_t hg_plan_workspace_bytes(const hg_plan_rel* rels, int n_rel) {
+    hg::WsLayout L;
+    if (hg::layout(rels, n_rel, L) != HG_OK) return 0;
+    return L.total + 256;
+}
+
+extern "C" int hg_plan_build(const hg_plan_rel* rels, int n_rel, int32_t* status, void* workspace,
+                             size_t workspace_bytes, void* stream_) {
+    using namespace hg;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    WsLayout L;
+    int rc = layout(rels, n_rel, L);
+    if (rc != HG_OK) return rc;
+    if (n_rel == 0) return HG_OK;
+    if (!status) return HG_EINVAL;
+    if (!workspace || workspace_bytes < L.total) return HG_EWORKSPACE;
+    if (!aligned(workspace, 256)) return HG_EALIGN;
+    char* ws = static_cast<char*>(workspace);
+
+    PlanParams P;
+    P.status = status;
+    int64_t max_edges = 0, max_total = 0;
+    int32_t max_blocks = 0;
+    for (int r = 0; r < n_rel; ++r) {
+        const hg_plan_rel& h = rels[r];
+        if (h.n_edges > 0 && (!h.src || !h.dst)) return HG_EINVAL;
+        if (!h.rowptr || (!h.col && (h.n_edges > 0 || h.self_loops))) return HG_EINVAL;
+        RelDev& d = P.r[r];
+        d.src = h.src; d.dst = h.dst; d.n_edges = h.n_edges;
+        d.n_src = h.n_src; d.n_dst = h.n_dst; d.self_loops = h.self_loops ? 1 : 0;
+        d.n_loop = h.self_loops ? (h.n_src < h.n_dst ? h.n_src : h.n_dst) : 0;
+        d.rowptr = h.rowptr; d.col = h.col; d.perm = h.perm; d.inv_sqrt_deg = h.inv_sqrt_deg;
+        d.cnt = reinterpret_cast<int32_t*>(ws + L.cnt_off[r]);
+        d.ids_tmp = reinterpret_cast<int32_t*>(ws + L.ids_off[r]);
+        d.bsum = reinterpret_cast<int32_t*>(ws + L.bsum_off[r]);
+        d.n_scan_blocks = static_cast<int32_t>(ceil_div<int64_t>(h.n_dst, kScanTile));
+        d.pad = 0;
+        max_edges = h.n_edges > max_edges ? h.n_edges : max_edges;
+        max_total = h.n_edges + d.n_loop > max_total ? h.n_edges + d.n_loop : max_total;
+        max_blocks = d.n_scan_blocks > max_blocks ? d.n_scan_blocks : max_blocks;
+    }
+    for (int r = n_rel; r < HG_MAX_PLAN_RELATIONS; ++r) P.r[r] = RelDev{};
+
+    HG_CUDA_TRY(cudaMemsetAsync(ws, 0, L.cnt_total, stream));
+    HG_CUDA_TRY(cudaMemsetAsync(status, 0, sizeof(int32_t), stream));
+
+    // Edge passes: grid-stride, capped at 8 waves of 148 SMs x 8 resident CTAs.
+    const int sms = sm_count() > 0 ? sm_count() : 148;
+    auto edge_grid = [&](int64_t n) {
+        int64_t g = ceil_div<int64_t>(n > 0 ? n : 1, kEdgeThreads);
+        const int64_t cap = static_cast<int64_t>(sms) * 8 * 8;
+        return static_cast<unsigned>(g < cap ? g : cap);
+    };
+    if (max_edges > 0) k_count<<<dim3(edge_grid(max_edges), n_rel), kEdgeThreads, 0, stream>>>(P);
+    if (max_blocks > 0) k_scan_a<<<dim3(max_blocks, n_rel), kScanThreads, 0, stream>>>(P);
+    k_scan_b<<<dim3(n_rel), kScanThreads, 0, stream>>>(P);
+    if (max_blocks > 0) k_scan_c<<<dim3(max_blocks, n_rel), kScanThreads, 0, stream>>>(P);
+    if (max_edges > 0) k_fill<<<dim3(edge_grid(max_edges), n_rel), kEdgeThreads, 0, stream>>>(P);
+    if (max_total > 0) k_rank<<<dim3(edge_grid(max_total), n_rel), kEdgeThreads, 0, stream>>>(P);
+    return check_launch();
+}

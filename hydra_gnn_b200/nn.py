@@ -1,0 +1,518 @@
+"""Message-passing layers with PyG-compatible parameter names, executed by the CUDA library.
+
+These modules stand where the reference constructs ``torch_geometric.nn`` layers
+(models/utils.py:9-140; heterogeneous_neural_tree_network.py:18-31,93-103;
+homogeneous_neural_tree_network.py:63-70).  Their parameter / buffer names equal PyG 2.3.x's
+(SURVEY.md section 8b), so a checkpoint trained with the reference loads with
+``load_state_dict``.  Arithmetic is NOT done here: a layer is executed as
+
+    one fused projection (``ops.linear``; all relations leaving a node type share one GEMM,
+    attention logits are extra folded columns)  ->  one fused aggregation per destination
+    type (``ops.gat_fused`` / ``ops.seg_reduce``; cross-relation sum, bias and the model's
+    activation in the epilogue),
+
+on a per-batch :class:`GraphPlan` (CSR per relation, built once by ``ops.build_csr``).
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.nn as nn
+from torch import Tensor
+
+from . import ops
+from .ops import CSR, CSRSpec, GatRelation
+
+EdgeType = Tuple[str, str, str]
+
+
+def _glorot(t: Optional[Tensor]):
+    if t is not None:
+        a = math.sqrt(6.0 / (t.size(-2) + t.size(-1)))
+        with torch.no_grad():
+            t.uniform_(-a, a)
+
+
+class Linear(nn.Module):
+    """Parameter holder named like ``torch_geometric.nn.dense.linear.Linear`` (``weight [out, in]``)."""
+
+    def __init__(self, in_channels: int, out_channels: int, bias: bool = True, weight_initializer: str = None):
+        super().__init__()
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.weight = nn.Parameter(torch.empty(out_channels, in_channels))
+        if bias:
+            self.bias = nn.Parameter(torch.empty(out_channels))
+        else:
+            self.register_parameter("bias", None)
+        if weight_initializer == "glorot":
+            _glorot(self.weight)
+        else:
+            nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
+        if bias:
+            bound = 1.0 / math.sqrt(in_channels) if in_channels > 0 else 0.0
+            nn.init.uniform_(self.bias, -bound, bound)
+
+    def forward(self, x: Tensor, act: str = None) -> Tensor:
+        return ops.linear([(x, self.weight)], self.out_channels, bias=self.bias, act=act)
+
+
+# =============================================================================== graph plan
+class GraphPlan:
+    """CSR variants of the relations of ONE batch, keyed ``(relation key, self_loops)``."""
+
+    def __init__(self):
+        self.csr: Dict[Tuple[object, bool], CSR] = {}
+        self.status: Optional[Tensor] = None
+        self.extra: Dict[str, Tensor] = {}
+
+    def __getitem__(self, key) -> CSR:
+        return self.csr[key]
+
+    def check(self):
+        """Synchronising: raises if any edge endpoint was out of range."""
+        if self.status is not None and int(self.status.item()) != 0:
+            raise IndexError(f"{int(self.status.item())} edges have endpoints outside [0, num_nodes)")
+
+
+class PlanRequest:
+    __slots__ = ("key", "edge_index", "n_src", "n_dst", "self_loops", "want_perm", "want_norm")
+
+    def __init__(self, key, edge_index, n_src, n_dst, self_loops=False, want_perm=False, want_norm=False):
+        self.key, self.edge_index, self.n_src, self.n_dst = key, edge_index, int(n_src), int(n_dst)
+        self.self_loops, self.want_perm, self.want_norm = bool(self_loops), bool(want_perm), bool(want_norm)
+
+    def signature(self):
+        ei = self.edge_index
+        return (self.key, ei.data_ptr(), tuple(ei.shape), ei._version, self.n_src, self.n_dst, self.self_loops,
+                self.want_perm, self.want_norm)
+
+
+class PlanCache:
+    """Keeps the plan of the most recent batch (all layers of a forward, and repeated forwards
+    of the same batch object, share it).  ``enabled = False`` rebuilds on every call."""
+
+    def __init__(self):
+        self.enabled = True
+        self._sig = None
+        self._plan: Optional[GraphPlan] = None
+
+    def clear(self):
+        self._sig, self._plan = None, None
+
+    def get(self, requests: Sequence[PlanRequest]) -> GraphPlan:
+        sig = tuple(r.signature() for r in requests)
+        if self.enabled and sig == self._sig and self._plan is not None:
+            return self._plan
+        plan = GraphPlan()
+        specs = [CSRSpec(r.edge_index, r.n_src, r.n_dst, r.self_loops, r.want_perm, r.want_norm) for r in requests]
+        csrs, plan.status = ops.build_csr(specs)
+        for r, c in zip(requests, csrs):
+            plan.csr[(r.key, r.self_loops)] = c
+        self._sig, self._plan = (sig, plan) if self.enabled else (None, None)
+        return plan
+
+
+def _param_signature(params: Sequence[Optional[Tensor]]):
+    return tuple((p.data_ptr(), p._version) if p is not None else None for p in params)
+
+
+# =============================================================================== GAT
+class GATConv(nn.Module):
+    """Parameters of PyG ``GATConv``: ``lin_src``/``lin_dst`` ([H*C, in];
+    one shared module for an int ``in_channels``), ``att_src``/``att_dst`` [1,H,C], optional
+    ``lin_edge``/``att_edge``, ``bias`` [H*C] (concat) or [C]."""
+
+    def __init__(self, in_channels, out_channels: int, heads: int = 1, concat: bool = True,
+                 negative_slope: float = 0.2, dropout: float = 0.0, add_self_loops: bool = True, edge_dim=None,
+                 fill_value="mean", bias: bool = True, **kwargs):
+        super().__init__()
+        self.in_channels, self.out_channels, self.heads = in_channels, out_channels, heads
+        self.concat, self.negative_slope, self.dropout = concat, negative_slope, dropout
+        self.add_self_loops, self.edge_dim, self.fill_value = add_self_loops, edge_dim, fill_value
+        H, C = heads, out_channels
+        if isinstance(in_channels, int):
+            self.lin_src = Linear(in_channels, H * C, bias=False, weight_initializer="glorot")
+            self.lin_dst = self.lin_src
+        else:
+            self.lin_src = Linear(in_channels[0], H * C, bias=False, weight_initializer="glorot")
+            self.lin_dst = Linear(in_channels[1], H * C, bias=False, weight_initializer="glorot")
+        self.att_src = nn.Parameter(torch.empty(1, H, C))
+        self.att_dst = nn.Parameter(torch.empty(1, H, C))
+        if edge_dim is not None:
+            self.lin_edge = Linear(edge_dim, H * C, bias=False, weight_initializer="glorot")
+            self.att_edge = nn.Parameter(torch.empty(1, H, C))
+        else:
+            self.lin_edge = None
+            self.register_parameter("att_edge", None)
+        if bias:
+            self.bias = nn.Parameter(torch.zeros(H * C if concat else C))
+        else:
+            self.register_parameter("bias", None)
+        _glorot(self.att_src)
+        _glorot(self.att_dst)
+        _glorot(self.att_edge)
+        self._plans = PlanCache()
+        self._pack = None
+
+    @staticmethod
+    def fold(att: Tensor, weight: Tensor, H: int, C: int) -> Tensor:
+        """``(x W^T).view(H,C) . att`` == ``x (W^T att)``: the [H, in] rows appended to the projection."""
+        return (att.reshape(H, C, 1) * weight.reshape(H, C, -1)).sum(dim=1)
+
+    def fill_vector(self, device) -> Optional[Tensor]:
+        """Edge attribute given to added self loops (None = zeros)."""
+        fv = self.fill_value
+        if self.edge_dim is None or fv is None:
+            return None
+        if isinstance(fv, Tensor):
+            v = fv.to(device=device, dtype=torch.float32).reshape(-1)
+            return v if bool((v != 0).any()) else None
+        if isinstance(fv, (int, float)):
+            return torch.full((self.edge_dim,), float(fv), device=device) if fv != 0 else None
+        raise NotImplementedError(
+            f"GATConv(edge_dim, fill_value={fv!r}): only constant / tensor fill values are supported "
+            "(the reference uses zeros(3), models/utils.py:125-126)")
+
+    def forward(self, x, edge_index: Tensor, edge_attr: Tensor = None, act: str = None) -> Tensor:
+        """Stand-alone call (single relation).  ``x``: Tensor or ``(x_src, x_dst)``."""
+        single = isinstance(x, Tensor)
+        x_src, x_dst = (x, x) if single else x
+        key = "_"
+        req = [PlanRequest(key, edge_index, x_src.size(0), x_dst.size(0), self.add_self_loops,
+                           want_perm=self.lin_edge is not None and edge_attr is not None)]
+        plan = self._plans.get(req)
+        types = {"s": x_src} if single else {"s": x_src, "d": x_dst}
+        et = ("s", key, "s" if single else "d")
+        out = run_gat_layer({et: self}, [et], types, {et: plan[(key, self.add_self_loops)]}, act=act,
+                            edge_attr={et: edge_attr} if edge_attr is not None else None, owner=self)
+        return out[et[2]]
+
+
+def _pad4(n: int) -> int:
+    return (n + 3) // 4 * 4
+
+
+class _GatPack:
+    """Packed projection weights of one GAT layer: per node type one ``[cols, in]`` matrix whose
+    rows are, in order: the ``lin_src`` blocks of every relation leaving the type (each padded
+    to a multiple of 4 rows), the folded ``att_src`` rows of those relations, the folded
+    ``att_dst`` rows of every relation entering the type."""
+
+    def __init__(self, convs: Dict[EdgeType, GATConv], rels: Sequence[EdgeType], in_dims: Dict[str, int]):
+        self.W: Dict[str, Tensor] = {}
+        self.xs_off: Dict[EdgeType, int] = {}
+        self.as_off: Dict[EdgeType, int] = {}
+        self.ad_off: Dict[EdgeType, int] = {}
+        self.v_edge: Dict[EdgeType, Tensor] = {}
+        types: List[str] = []
+        for s, _, d in rels:
+            for t in (s, d):
+                if t not in types:
+                    types.append(t)
+        for T in types:
+            blocks, col = [], 0
+            for et in rels:
+                if et[0] != T:
+                    continue
+                c = convs[et]
+                W = c.lin_src.weight
+                rows = c.heads * c.out_channels
+                blocks.append(W)
+                if _pad4(rows) != rows:
+                    blocks.append(W.new_zeros(_pad4(rows) - rows, W.size(1)))
+                self.xs_off[et] = col
+                col += _pad4(rows)
+            for et in rels:
+                if et[0] != T:
+                    continue
+                c = convs[et]
+                blocks.append(GATConv.fold(c.att_src, c.lin_src.weight, c.heads, c.out_channels))
+                self.as_off[et] = col
+                col += c.heads
+            for et in rels:
+                if et[2] != T:
+                    continue
+                c = convs[et]
+                Wd = c.lin_src.weight if et[0] == et[2] else c.lin_dst.weight
+                blocks.append(GATConv.fold(c.att_dst, Wd, c.heads, c.out_channels))
+                self.ad_off[et] = col
+                col += c.heads
+            if _pad4(col) != col:
+                blocks.append(blocks[0].new_zeros(_pad4(col) - col, in_dims[T]))
+            self.W[T] = torch.cat(blocks, dim=0).contiguous()
+        for et in rels:
+            c = convs[et]
+            if c.lin_edge is not None:
+                self.v_edge[et] = GATConv.fold(c.att_edge, c.lin_edge.weight, c.heads, c.out_channels).contiguous()
+
+
+def _gat_pack(owner: nn.Module, convs: Dict[EdgeType, GATConv], rels: Sequence[EdgeType],
+              x: Dict[str, Tensor]) -> _GatPack:
+    params: List[Optional[Tensor]] = []
+    for et in rels:
+        c = convs[et]
+        params += [c.lin_src.weight, c.lin_dst.weight, c.att_src, c.att_dst, c.att_edge,
+                   c.lin_edge.weight if c.lin_edge is not None else None]
+    sig = (tuple(rels), _param_signature(params))
+    cached = getattr(owner, "_pack", None)
+    if cached is not None and cached[0] == sig:
+        return cached[1]
+    with torch.no_grad():
+        pack = _GatPack(convs, rels, {t: v.size(1) for t, v in x.items()})
+    owner._pack = (sig, pack)
+    return pack
+
+
+def run_gat_layer(convs: Dict[EdgeType, GATConv], rels: Sequence[EdgeType], x: Dict[str, Tensor],
+                  csr: Dict[EdgeType, CSR], *, act: str = None, group: str = "sum",
+                  edge_attr: Dict[EdgeType, Tensor] = None, owner: nn.Module = None,
+                  only_dst: Sequence[str] = None) -> Dict[str, Tensor]:
+    """One GAT layer over ``rels`` (HeteroConv semantics; a homogeneous layer is the 1-relation case)."""
+    if only_dst is not None:
+        rels = [et for et in rels if et[2] in only_dst]
+    pack = _gat_pack(owner, convs, rels, x)
+    Y = {T: ops.linear([(x[T], W)], W.size(0)) for T, W in pack.W.items()}
+    out: Dict[str, Tensor] = {}
+    for T in dict.fromkeys(et[2] for et in rels):
+        grp: List[GatRelation] = []
+        H = C = concat = slope = None
+        for et in rels:
+            if et[2] != T:
+                continue
+            c = convs[et]
+            if H is None:
+                H, C, concat, slope = c.heads, c.out_channels, c.concat, c.negative_slope
+            elif (H, C, concat, slope) != (c.heads, c.out_channels, c.concat, c.negative_slope):
+                raise NotImplementedError("relations targeting one node type must share heads/channels/concat")
+            if c.training and c.dropout > 0:
+                raise NotImplementedError("attention dropout (training mode) is not implemented; call model.eval()")
+            ys, yd = Y[et[0]], Y[T]
+            xo, ao, do = pack.xs_off[et], pack.as_off[et], pack.ad_off[et]
+            a_edge = None
+            if c.lin_edge is not None and edge_attr is not None and edge_attr.get(et) is not None:
+                a_edge = ops.edge_logits(edge_attr[et], csr[et], pack.v_edge[et], H, fill=c.fill_vector(ys.device))
+            grp.append(GatRelation(ys[:, xo: xo + H * C], ys[:, ao: ao + H], yd[:, do: do + H], csr[et], c.bias, a_edge))
+        out[T] = ops.gat_fused(grp, x[T].size(0), H, C, concat, group=group, act=act, neg_slope=slope)
+    return out
+
+
+# =============================================================================== SAGE / GCN / GIN
+class SAGEConv(nn.Module):
+    """PyG ``SAGEConv(normalize=False, root_weight=True)``: ``lin_l`` (bias) on the mean of the
+    neighbours, ``lin_r`` (no bias) on the node itself."""
+
+    def __init__(self, in_channels, out_channels: int, aggr: str = "mean", normalize: bool = False,
+                 root_weight: bool = True, bias: bool = True, **kwargs):
+        super().__init__()
+        if normalize or aggr != "mean" or not root_weight:
+            raise NotImplementedError("only SAGEConv(aggr='mean', normalize=False, root_weight=True) is on the path")
+        if isinstance(in_channels, int):
+            in_channels = (in_channels, in_channels)
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.lin_l = Linear(in_channels[0], out_channels, bias=bias)
+        self.lin_r = Linear(in_channels[1], out_channels, bias=False)
+        self._plans = PlanCache()
+
+    def forward(self, x, edge_index: Tensor, act: str = None) -> Tensor:
+        single = isinstance(x, Tensor)
+        x_src, x_dst = (x, x) if single else x
+        plan = self._plans.get([PlanRequest("_", edge_index, x_src.size(0), x_dst.size(0))])
+        return run_sage(self, x_src, x_dst, plan[("_", False)], act=act)
+
+
+def run_sage(conv: SAGEConv, x_src: Tensor, x_dst: Tensor, csr: CSR, act: str = None) -> Tensor:
+    """Homogeneous / single-relation SAGE.  Aggregate-first when in <= out (fewer gathered bytes),
+    project-first otherwise (``lin_l(mean x) = mean(x W_l^T) + b``: same value, 1e-7 rounding)."""
+    d_in, d_out = conv.in_channels[0], conv.out_channels
+    if d_in <= d_out or x_src is not x_dst:
+        mean = ops.seg_reduce(x_src, csr, "mean")
+        return ops.linear([(mean, conv.lin_l.weight), (x_dst, conv.lin_r.weight)], d_out, bias=conv.lin_l.bias, act=act)
+    W = torch.cat([conv.lin_l.weight, conv.lin_r.weight], dim=0)
+    Y = ops.linear([(x_src, W)], 2 * d_out)
+    return ops.seg_reduce(Y[:, :d_out], csr, "mean", x_self=Y[:, d_out:], self_coef_add=1.0, bias=conv.lin_l.bias,
+                          act=act)
+
+
+def run_hetero_sage(convs: Dict[EdgeType, SAGEConv], rels: Sequence[EdgeType], x: Dict[str, Tensor],
+                    csr: Dict[EdgeType, CSR], *, act: str = None, group: str = "sum", owner: nn.Module = None,
+                    only_dst: Sequence[str] = None) -> Dict[str, Tensor]:
+    """HeteroConv of SAGEConvs: per destination type ONE projection whose K dimension is the
+    concatenation [mean_r1 | mean_r2 | ... | x_dst] (root weights and biases pre-summed)."""
+    if only_dst is not None:
+        rels = [et for et in rels if et[2] in only_dst]
+    out: Dict[str, Tensor] = {}
+    for T in dict.fromkeys(et[2] for et in rels):
+        mine = [et for et in rels if et[2] == T]
+        params = [p for et in mine for p in (convs[et].lin_r.weight, convs[et].lin_l.bias)]
+        sig = (tuple(mine), _param_signature(params))
+        cache = owner.__dict__.setdefault("_sage_pack", {})
+        if T not in cache or cache[T][0] != sig:
+            with torch.no_grad():
+                scale = 1.0 / len(mine) if group == "mean" else 1.0
+                w_root = sum(convs[et].lin_r.weight for et in mine) * scale
+                biases = [convs[et].lin_l.bias for et in mine if convs[et].lin_l.bias is not None]
+                bias = (sum(biases) * scale) if biases else None
+                w_l = [convs[et].lin_l.weight * scale if scale != 1.0 else convs[et].lin_l.weight for et in mine]
+            cache[T] = (sig, (w_root.contiguous(), bias, w_l))
+        w_root, bias, w_l = cache[T][1]
+        segs = [(ops.seg_reduce(x[et[0]], csr[et], "mean"), w) for et, w in zip(mine, w_l)]
+        segs.append((x[T], w_root))
+        out[T] = ops.linear(segs, convs[mine[0]].out_channels, bias=bias, act=act)
+    return out
+
+
+class GCNConv(nn.Module):
+    """PyG ``GCNConv(add_self_loops=True, normalize=True)``: ``lin`` (no bias) + ``bias``
+    (SURVEY.md section 9.4).  The normalisation ``deg^-1/2`` comes with the plan (K1)."""
+
+    def __init__(self, in_channels: int, out_channels: int, add_self_loops: bool = True, bias: bool = True, **kwargs):
+        super().__init__()
+        if not isinstance(in_channels, int):
+            raise ValueError("GCNConv is not bipartite")
+        if not add_self_loops:
+            raise NotImplementedError("GCNConv(add_self_loops=False) is not on the reference's path")
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.lin = Linear(in_channels, out_channels, bias=False, weight_initializer="glorot")
+        if bias:
+            self.bias = nn.Parameter(torch.zeros(out_channels))
+        else:
+            self.register_parameter("bias", None)
+        self._plans = PlanCache()
+
+    def forward(self, x: Tensor, edge_index: Tensor, act: str = None) -> Tensor:
+        plan = self._plans.get([PlanRequest("_", edge_index, x.size(0), x.size(0), True, want_norm=True)])
+        return run_gcn(self, x, plan[("_", True)], act=act)
+
+
+def run_gcn(conv: GCNConv, x: Tensor, csr: CSR, act: str = None) -> Tensor:
+    y = ops.linear([(x, conv.lin.weight)], conv.out_channels)
+    return ops.seg_reduce(y, csr, "sum", src_scale=csr.inv_sqrt_deg, dst_scale=csr.inv_sqrt_deg, bias=conv.bias, act=act)
+
+
+class GINConv(nn.Module):
+    """PyG ``GINConv(nn, eps, train_eps)``: ``out = nn((1 + eps) x_i + sum_j x_j)`` (section 9.5)."""
+
+    def __init__(self, nn_module: nn.Module, eps: float = 0.0, train_eps: bool = False, **kwargs):
+        super().__init__()
+        self.nn = nn_module
+        if train_eps:
+            self.eps = nn.Parameter(torch.tensor([float(eps)]))
+        else:
+            self.register_buffer("eps", torch.tensor([float(eps)]))
+        self._plans = PlanCache()
+
+    def forward(self, x: Tensor, edge_index: Tensor, act: str = None, bn: "BatchNorm" = None) -> Tensor:
+        plan = self._plans.get([PlanRequest("_", edge_index, x.size(0), x.size(0))])
+        return run_gin(self, x, plan[("_", False)], act=act, bn=bn)
+
+
+def run_gin(conv: GINConv, x: Tensor, csr: CSR, act: str = None, bn: "BatchNorm" = None) -> Tensor:
+    h = ops.seg_reduce(x, csr, "sum", x_self=x, self_coef=conv.eps, self_coef_add=1.0)
+    layers = list(conv.nn)
+    lin_idx = [k for k, m in enumerate(layers) if isinstance(m, nn.Linear)]
+    for k, m in enumerate(layers):
+        if isinstance(m, nn.Linear):
+            last = k == lin_idx[-1]
+            fuse_relu = (not last) and k + 1 < len(layers) and isinstance(layers[k + 1], nn.ReLU)
+            scale = shift = None
+            if last and bn is not None:
+                scale, shift = bn.affine()
+            h = ops.linear([(h, m.weight)], m.out_features, bias=m.bias, scale=scale, shift=shift,
+                           act="relu" if fuse_relu else (act if last else None))
+        elif isinstance(m, nn.ReLU):
+            continue  # fused into the preceding projection
+        else:
+            raise NotImplementedError(f"GINConv.nn may hold Linear / ReLU only, got {type(m).__name__}")
+    return h
+
+
+class BatchNorm(nn.Module):
+    """PyG ``BatchNorm`` wrapper (parameters under ``.module.``).  Eval mode only: folded into
+    the epilogue of the preceding projection as a per-channel scale/shift."""
+
+    def __init__(self, in_channels: int, eps: float = 1e-5, momentum: float = 0.1, affine: bool = True,
+                 track_running_stats: bool = True, **kwargs):
+        super().__init__()
+        self.module = nn.BatchNorm1d(in_channels, eps, momentum, affine, track_running_stats)
+
+    def affine(self):
+        m = self.module
+        if m.training or m.running_mean is None:
+            raise NotImplementedError("BatchNorm with batch statistics (training mode) is not implemented; "
+                                      "call model.eval()")
+        with torch.no_grad():
+            scale = torch.rsqrt(m.running_var + m.eps)
+            if m.weight is not None:
+                scale = scale * m.weight
+            shift = -m.running_mean * scale
+            if m.bias is not None:
+                shift = shift + m.bias
+        return scale.contiguous(), shift.contiguous()
+
+
+# =============================================================================== HeteroConv / LeafPool
+class HeteroConv(nn.Module):
+    """PyG 2.3.x ``HeteroConv``: ``convs`` keyed ``'__'.join(edge_type)``; relations are taken in
+    ``edge_index_dict`` order, those without a registered conv are skipped, outputs are grouped
+    per destination type with ``aggr``.  Executed fused (see module doc)."""
+
+    def __init__(self, convs: Dict[EdgeType, nn.Module], aggr: str = "sum"):
+        super().__init__()
+        if aggr not in ("sum", "mean"):
+            raise NotImplementedError("HeteroConv aggr must be 'sum' or 'mean'")
+        self.convs = nn.ModuleDict({"__".join(k): v for k, v in convs.items()})
+        self.aggr = aggr
+        self._edge_types = list(convs.keys())
+        self._plans = PlanCache()
+        self._pack = None
+
+    def conv_of(self, et: EdgeType):
+        return self.convs["__".join(et)]
+
+    def relations(self, x_dict, edge_index_dict) -> List[EdgeType]:
+        return [et for et in edge_index_dict if "__".join(et) in self.convs]
+
+    def plan_requests(self, x_dict, edge_index_dict) -> List[PlanRequest]:
+        reqs = []
+        for et in self.relations(x_dict, edge_index_dict):
+            c = self.conv_of(et)
+            loops = bool(getattr(c, "add_self_loops", False)) and isinstance(c, GATConv)
+            perm = isinstance(c, GATConv) and c.lin_edge is not None
+            reqs.append(PlanRequest(et, edge_index_dict[et], x_dict[et[0]].size(0), x_dict[et[2]].size(0), loops, perm))
+        return reqs
+
+    def run(self, x_dict, edge_index_dict, plan: GraphPlan, *, act: str = None, edge_attr_dict=None,
+            only_dst: Sequence[str] = None) -> Dict[str, Tensor]:
+        rels = self.relations(x_dict, edge_index_dict)
+        convs = {et: self.conv_of(et) for et in rels}
+        kinds = {type(c) for c in convs.values()}
+        if kinds == {GATConv}:
+            csr = {et: plan[(et, convs[et].add_self_loops)] for et in rels}
+            return run_gat_layer(convs, rels, x_dict, csr, act=act, group=self.aggr, edge_attr=edge_attr_dict,
+                                 owner=self, only_dst=only_dst)
+        if kinds == {SAGEConv}:
+            csr = {et: plan[(et, False)] for et in rels}
+            return run_hetero_sage(convs, rels, x_dict, csr, act=act, group=self.aggr, owner=self, only_dst=only_dst)
+        raise NotImplementedError(f"HeteroConv over {sorted(k.__name__ for k in kinds)} is not on the reference's path")
+
+    def forward(self, x_dict, edge_index_dict, edge_attr_dict=None, act: str = None):
+        plan = self._plans.get(self.plan_requests(x_dict, edge_index_dict))
+        return self.run(x_dict, edge_index_dict, plan, act=act, edge_attr_dict=edge_attr_dict)
+
+
+class LeafPool(nn.Module):
+    """heterogeneous_neural_tree_network.py:18-31: identity message, mean aggregation.  A
+    single-Tensor ``x`` makes PyG return ``x.size(0)`` rows; callers keep only the virtual-node
+    rows, so ``num_out`` / ``row_map`` compute just those."""
+
+    def __init__(self, aggr: str = "mean"):
+        super().__init__()
+        self.aggr = aggr
+        self._plans = PlanCache()
+
+    def forward(self, x: Tensor, edge_index: Tensor, num_out: int = None) -> Tensor:
+        n = x.size(0) if num_out is None else num_out
+        plan = self._plans.get([PlanRequest("_", edge_index, x.size(0), n)])
+        return ops.seg_reduce(x, plan[("_", False)], self.aggr)

@@ -1,0 +1,283 @@
+"""Thin tensor-level wrappers over the C ABI (``include/hydra_gnn_b200.h``).
+
+Every function launches hand-written sm_100a kernels on the current torch stream; torch
+is used only to own device memory.  No function here has a CPU or eager fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import torch
+from torch import Tensor
+
+from . import _lib
+from ._lib import ACT, GROUP, PREC, REDUCE, check, lib, ptr, stream_ptr
+
+DEFAULT_PRECISION = "fp32"
+
+
+def _require_no_grad(*tensors):
+    if torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors):
+        raise NotImplementedError(
+            "hydra_gnn_b200 kernels are forward-only in this build; call under torch.no_grad() "
+            "(backward kernels belong to the training config, see DESIGN.md)")
+
+
+def _f32(t: Tensor, name: str) -> Tensor:
+    if t.dtype != torch.float32:
+        raise TypeError(f"{name}: expected float32, got {t.dtype} (fp64 mode of the reference is not supported)")
+    if not t.is_cuda:
+        raise RuntimeError(f"{name}: expected a CUDA tensor; hydra_gnn_b200 has no CPU path")
+    return t
+
+
+def _rows(t: Tensor, name: str) -> Tensor:
+    """2-D, unit stride along features (an arbitrary row stride is the leading dimension)."""
+    _f32(t, name)
+    if t.dim() != 2:
+        raise ValueError(f"{name}: expected a 2-D tensor")
+    if t.size(1) > 0 and t.stride(1) != 1:
+        t = t.contiguous()
+    return t
+
+
+def _ld(t: Tensor) -> int:
+    """Leading dimension in floats (any value works for a single row; keep it vector friendly)."""
+    return t.stride(0) if t.size(0) > 1 else max((t.size(1) + 3) // 4 * 4, 4)
+
+
+# ------------------------------------------------------------------------------ workspace
+_workspaces = {}
+
+
+def _workspace(device, nbytes: int) -> Tensor:
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+# ------------------------------------------------------------------------------ K1 plan
+@dataclass
+class CSR:
+    """Destination-sorted adjacency of one relation (device int32)."""
+    rowptr: Tensor
+    col: Tensor
+    perm: Optional[Tensor]
+    inv_sqrt_deg: Optional[Tensor]
+    n_src: int
+    n_dst: int
+    cap: int  # allocated entries; the live count is rowptr[-1] (kept on the device)
+    self_loops: bool
+
+
+@dataclass
+class CSRSpec:
+    edge_index: Tensor  # int64 [2, E] (row 0 = source, row 1 = target)
+    n_src: int
+    n_dst: int
+    self_loops: bool = False
+    want_perm: bool = False
+    want_norm: bool = False
+    transpose: bool = False  # build the CSR of the reversed relation (rows = sources)
+
+
+def build_csr(specs: Sequence[CSRSpec]):
+    """All relations of a batch in one ``hg_plan_build`` call (six launches in total).
+
+    Returns (list of CSR, status) -- ``status`` is a device int32[1] counting edges whose
+    endpoints were outside [0, n) (skipped, never dereferenced); read it with
+    ``int(status)`` only when a sync is acceptable.
+    """
+    h = lib()
+    out: List[CSR] = []
+    if len(specs) == 0:
+        return out, None
+    device = specs[0].edge_index.device
+    status = torch.empty(1, dtype=torch.int32, device=device)
+    for lo in range(0, len(specs), _lib.HG_MAX_PLAN_RELATIONS):
+        chunk = specs[lo: lo + _lib.HG_MAX_PLAN_RELATIONS]
+        rels = (_lib.PlanRel * len(chunk))()
+        keep = []
+        for k, s in enumerate(chunk):
+            ei = s.edge_index
+            if ei.dtype != torch.int64 or ei.dim() != 2 or ei.size(0) != 2:
+                raise TypeError("edge_index must be int64 [2, E]")
+            if not ei.is_cuda:
+                raise RuntimeError("edge_index must be a CUDA tensor; hydra_gnn_b200 has no CPU path")
+            if not ei.is_contiguous():
+                ei = ei.contiguous()
+            E = ei.size(1)
+            n_src, n_dst = (s.n_dst, s.n_src) if s.transpose else (s.n_src, s.n_dst)
+            loops = min(n_src, n_dst) if s.self_loops else 0
+            cap = E + loops
+            rowptr = torch.empty(n_dst + 1, dtype=torch.int32, device=device)
+            col = torch.empty(max(cap, 1), dtype=torch.int32, device=device)
+            perm = torch.empty(max(cap, 1), dtype=torch.int32, device=device) if s.want_perm else None
+            norm = torch.empty(max(n_dst, 1), dtype=torch.float32, device=device) if s.want_norm else None
+            r = rels[k]
+            src_row, dst_row = (1, 0) if s.transpose else (0, 1)
+            r.src = ei.data_ptr() + src_row * E * 8
+            r.dst = ei.data_ptr() + dst_row * E * 8
+            r.n_edges, r.n_src, r.n_dst, r.self_loops = E, n_src, n_dst, int(s.self_loops)
+            r.rowptr, r.col, r.perm, r.inv_sqrt_deg = ptr(rowptr), ptr(col), ptr(perm), ptr(norm)
+            keep.append(ei)
+            out.append(CSR(rowptr, col, perm, norm, n_src, n_dst, cap, s.self_loops))
+        nbytes = h.hg_plan_workspace_bytes(rels, len(chunk))
+        if nbytes == 0:
+            raise RuntimeError("hg_plan_workspace_bytes rejected the plan (sizes out of int32 range?)")
+        ws = _workspace(device, nbytes)
+        st = status if lo == 0 else torch.empty(1, dtype=torch.int32, device=device)
+        check(h.hg_plan_build(rels, len(chunk), ptr(st), ptr(ws), ws.numel(), stream_ptr()), "hg_plan_build")
+        _lib.launch_count += 6
+        if lo != 0:
+            status += st
+    return out, status
+
+
+# ------------------------------------------------------------------------------ K2 / K5
+def seg_reduce(x: Tensor, csr: CSR, op: str = "sum", *, src_scale: Tensor = None, dst_scale: Tensor = None,
+               row_map: Tensor = None, x_self: Tensor = None, self_coef: Tensor = None, self_coef_add: float = 0.0,
+               bias: Tensor = None, act: str = None, out: Tensor = None) -> Tensor:
+    _require_no_grad(x, x_self, bias)
+    h = lib()
+    x = _rows(x, "x")
+    F = x.size(1)
+    n_out = csr.n_dst if row_map is None else row_map.numel()
+    if out is None:
+        out = torch.empty(n_out, F, dtype=torch.float32, device=x.device)
+    a = _lib.SegArgs()
+    a.x, a.ldx = ptr(x), _ld(x)
+    a.rowptr, a.col = ptr(csr.rowptr), ptr(csr.col)
+    a.src_scale, a.dst_scale = ptr(src_scale), ptr(dst_scale)
+    if row_map is not None and row_map.dtype != torch.int32:
+        raise TypeError("row_map must be int32")
+    a.row_map = ptr(row_map)
+    if x_self is not None:
+        x_self = _rows(x_self, "x_self")
+        if x_self.size(1) != F:
+            raise ValueError("x_self width mismatch")
+        a.x_self, a.ldself = ptr(x_self), _ld(x_self)
+        a.self_coef_ptr = ptr(self_coef)
+        a.self_coef_add = float(self_coef_add)
+    a.bias = ptr(bias)
+    a.out, a.ldout = ptr(out), _ld(out)
+    a.n_out, a.F = n_out, F
+    a.op, a.act = REDUCE[op], ACT[act]
+    check(h.hg_seg_reduce(C.byref(a), stream_ptr()), "hg_seg_reduce")
+    _lib.launch_count += 1
+    return out
+
+
+# ------------------------------------------------------------------------------ K3 + K4
+@dataclass
+class GatRelation:
+    xs: Tensor            # [n_src, H*C] view (may be a column slice of the projection output)
+    a_src: Tensor         # [n_src, H] view
+    a_dst: Tensor         # [n_dst, H] view
+    csr: CSR
+    bias: Optional[Tensor] = None
+    a_edge: Optional[Tensor] = None  # [cap, H] contiguous, CSR order
+    alpha_out: Optional[Tensor] = None
+
+
+def gat_fused(rels: Sequence[GatRelation], n_dst: int, H: int, Cc: int, concat: bool, *, group: str = "sum",
+              act: str = None, neg_slope: float = 0.2, out: Tensor = None) -> Tensor:
+    h = lib()
+    if not 1 <= len(rels) <= _lib.HG_MAX_RELATIONS:
+        raise ValueError("1..8 relations per destination type")
+    device = rels[0].xs.device
+    width = H * Cc if concat else Cc
+    if out is None:
+        out = torch.empty(n_dst, width, dtype=torch.float32, device=device)
+    a = _lib.GatArgs()
+    for k, r in enumerate(rels):
+        _require_no_grad(r.xs, r.a_src, r.a_dst, r.bias)
+        for t, nm in ((r.xs, "xs"), (r.a_src, "a_src"), (r.a_dst, "a_dst")):
+            _f32(t, nm)
+            if t.dim() != 2 or (t.size(1) > 1 and t.stride(1) != 1):
+                raise ValueError(f"{nm}: expected 2-D with unit feature stride")
+        if r.xs.size(1) != H * Cc or r.a_src.size(1) != H or r.a_dst.size(1) != H:
+            raise ValueError("GAT operand widths do not match H, C")
+        if r.csr.n_dst != n_dst:
+            raise ValueError("relation CSR has a different destination count")
+        g = a.rel[k]
+        g.xs, g.ldxs = ptr(r.xs), _ld(r.xs)
+        g.a_src, g.lda_src = ptr(r.a_src), _ld(r.a_src)
+        g.a_dst, g.lda_dst = ptr(r.a_dst), _ld(r.a_dst)
+        g.a_edge = ptr(r.a_edge)
+        g.rowptr, g.col, g.bias = ptr(r.csr.rowptr), ptr(r.csr.col), ptr(r.bias)
+        a.alpha_saved[k] = ptr(r.alpha_out)
+    a.n_rel, a.n_dst, a.H, a.C = len(rels), n_dst, H, Cc
+    a.concat, a.group, a.act, a.neg_slope = int(concat), GROUP[group], ACT[act], float(neg_slope)
+    a.out, a.ldout = ptr(out), _ld(out)
+    check(h.hg_gat_fused(C.byref(a), stream_ptr()), "hg_gat_fused")
+    _lib.launch_count += 1
+    return out
+
+
+# ------------------------------------------------------------------------------ K6
+def linear(segments: Sequence, N: int, *, bias: Tensor = None, scale: Tensor = None, shift: Tensor = None,
+           act: str = None, precision: str = None, out: Tensor = None) -> Tensor:
+    """``y = act((sum_s x_s @ W_s^T + bias) * scale + shift)``; ``segments`` = [(x_s, W_s), ...]."""
+    h = lib()
+    if not 1 <= len(segments) <= _lib.HG_MAX_SEGMENTS:
+        raise ValueError("1..8 K-segments")
+    a = _lib.LinearArgs()
+    M = segments[0][0].size(0)
+    device = segments[0][0].device
+    keep = []
+    for k, (x, w) in enumerate(segments):
+        _require_no_grad(x, w)
+        x, w = _rows(x, "x"), _rows(w, "W")
+        if x.size(0) != M or w.size(0) != N or x.size(1) != w.size(1):
+            raise ValueError(f"segment {k}: shapes x{tuple(x.shape)} W{tuple(w.shape)} do not match M={M}, N={N}")
+        s = a.seg[k]
+        s.x, s.ldx, s.w, s.ldw, s.K = ptr(x), _ld(x), ptr(w), _ld(w), x.size(1)
+        keep.append((x, w))
+    _require_no_grad(bias, scale, shift)
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.float32, device=device)
+    a.n_seg, a.M, a.N = len(segments), M, N
+    a.bias, a.scale, a.shift = ptr(bias), ptr(scale), ptr(shift)
+    a.act = ACT[act]
+    a.precision = PREC[precision or DEFAULT_PRECISION]
+    a.y, a.ldy = ptr(out), _ld(out)
+    nbytes = h.hg_linear_workspace_bytes(C.byref(a))
+    ws = _workspace(device, nbytes) if nbytes else None
+    check(h.hg_linear(C.byref(a), ptr(ws), nbytes, stream_ptr()), "hg_linear")
+    _lib.launch_count += 1
+    return out
+
+
+# ------------------------------------------------------------------------------ edge helpers
+def edge_logits(edge_attr: Tensor, csr: CSR, v: Tensor, H: int, fill: Tensor = None) -> Tensor:
+    """``a_edge[p, h] = <edge_attr[perm[p]], v[h]>`` in CSR order (added loops: ``<fill, v[h]>`` or 0)."""
+    h = lib()
+    if csr.perm is None:
+        raise ValueError("edge_logits needs a CSR built with want_perm=True")
+    edge_attr = _rows(edge_attr, "edge_attr")
+    v = _rows(v, "v")
+    D = edge_attr.size(1)
+    out = torch.empty(max(csr.cap, 1), H, dtype=torch.float32, device=v.device)
+    check(h.hg_edge_logits(ptr(edge_attr), _ld(edge_attr), D, ptr(csr.perm), csr.rowptr[-1:].data_ptr(), csr.cap,
+                           ptr(v), ptr(fill), H, ptr(out), stream_ptr()), "hg_edge_logits")
+    _lib.launch_count += 1
+    return out
+
+
+def relative_pos(pos_src: Tensor, pos_dst: Tensor, edge_index: Tensor) -> Tensor:
+    """``edge_attr = pos_dst[edge_index[1]] - pos_src[edge_index[0]]`` (mp3d_dataset.py:316-319)."""
+    h = lib()
+    pos_src, pos_dst = _f32(pos_src, "pos_src").contiguous(), _f32(pos_dst, "pos_dst").contiguous()
+    ei = edge_index.contiguous()
+    E = ei.size(1)
+    out = torch.empty(E, 3, dtype=torch.float32, device=ei.device)
+    check(h.hg_relative_pos(ptr(pos_src), ptr(pos_dst), ei.data_ptr(), ei.data_ptr() + 8 * E, E, ptr(out),
+                            stream_ptr()), "hg_relative_pos")
+    _lib.launch_count += 1
+    return out

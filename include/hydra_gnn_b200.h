@@ -1,0 +1,232 @@
+/*
+ * hydra_gnn_b200 -- C ABI of the sm_100a message-passing kernels.
+ *
+ * Drop-in boundary (inner).  The reference (MIT-SPARK/Hydra-GNN) has no FFI of its own:
+ * every arithmetic step of its forward is a call into torch_geometric (PyG) operators,
+ * which in turn run gather / scatter kernels from ATen / torch_scatter / pyg_lib.  Each
+ * entry point below replaces one such operator family; the comment above it cites the
+ * reference call site(s) (paths relative to /root/reference/src/hydra_gnn) and the PyG
+ * operator it stands in for.  INTEGRATION.md shows the ctypes binding.
+ *
+ * Conventions
+ *  - plain C: pointers and sizes only, no torch types.  All pointers are DEVICE pointers
+ *    unless the name ends in `_host`.  The caller owns every buffer (inputs, outputs,
+ *    workspace); the library never allocates, never synchronises, keeps no global state.
+ *  - every launch goes to `stream` (a cudaStream_t passed as void*), so calls are
+ *    CUDA-graph capturable and thread-safe per stream.
+ *  - return value: 0 (HG_OK) or a negative HG_E* code; hg_strerror() gives the text.
+ *  - features are fp32, row-major, with an explicit leading dimension (`ld*`, in floats);
+ *    indices inside the library are int32 (edge_index arrives as int64 and is narrowed by
+ *    hg_plan_build, which reports HG_ERANGE if a count does not fit).
+ *  - CSR: rowptr[n_dst+1], col[E'] (source ids), perm[E'] (original edge id, -1 for an
+ *    added self loop).  Rows are ordered by original edge id, added loops last: identical
+ *    to a stable sort by destination of PyG's (remove_self_loops -> add_self_loops) list.
+ */
+#ifndef HYDRA_GNN_B200_H_
+#define HYDRA_GNN_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HG_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define HG_API __attribute__((visibility("default")))
+#else
+#define HG_API
+#endif
+
+enum {
+    HG_OK = 0,
+    HG_EINVAL = -1,   /* bad argument (null pointer, negative size, unsupported shape) */
+    HG_ERANGE = -2,   /* a size does not fit int32 / an index is outside [0, n) */
+    HG_EWORKSPACE = -3, /* workspace too small */
+    HG_ECUDA = -4,    /* a CUDA runtime call failed; see hg_last_cuda_error() */
+    HG_EALIGN = -5,   /* pointer / leading dimension violates the alignment contract */
+    HG_EUNSUPPORTED = -6
+};
+
+enum { HG_REDUCE_SUM = 0, HG_REDUCE_MEAN = 1, HG_REDUCE_MAX = 2 };
+enum { HG_ACT_NONE = 0, HG_ACT_RELU = 1, HG_ACT_ELU = 2 };
+enum { HG_GROUP_SUM = 0, HG_GROUP_MEAN = 1 };
+enum { HG_PREC_FP32 = 0, HG_PREC_TF32X3 = 1 };
+
+#define HG_MAX_RELATIONS 8   /* relations fused per destination type (H-tree needs 4) */
+#define HG_MAX_SEGMENTS 8    /* K-segments of one fused projection */
+#define HG_MAX_PLAN_RELATIONS 16 /* relations per plan-build call (H-tree has 15) */
+
+HG_API const char* hg_strerror(int code);
+HG_API int hg_abi_version(void);
+/* last cudaError_t seen by this library on the calling thread (0 = none) */
+HG_API int hg_last_cuda_error(void);
+/* 0 if no usable device / kernel image for it; otherwise SM count of the current device */
+HG_API int hg_device_sm_count(void);
+/* sizeof of ABI struct #which (0 plan_rel, 1 seg_args, 2 gat_rel, 3 gat_args, 4 lin_seg, 5 linear_args) */
+HG_API int hg_sizeof(int which);
+
+/* ------------------------------------------------------------------------------------
+ * K1  Graph plan: CSR by destination for up to HG_MAX_PLAN_RELATIONS relations at once.
+ *
+ * Replaces: the implicit per-layer `index_select` + `scatter` bookkeeping of PyG
+ * MessagePassing.propagate, plus `remove_self_loops`/`add_self_loops` inside GATConv
+ * (built by models/utils.py:49-86 with add_self_loops=(source == target), :124) and
+ * `add_remaining_self_loops` inside gcn_norm (GCNConv, models/utils.py:16).  Built once
+ * per batch, reused by every layer.
+ *
+ * self_loops = 0: edges kept as they are.
+ * self_loops = 1: edges with src == dst dropped, one loop (k,k) appended for every
+ *                 k < min(n_src, n_dst) (perm = -1).  This is both GATConv's and (for unit
+ *                 edge weights) gcn_norm's edge list.
+ * Out-of-range endpoints are skipped and counted in status[0] (never dereferenced).
+ * E' = rowptr[n_dst] stays on the device; col/perm must hold E + (self_loops ? min(n_src,
+ * n_dst) : 0) entries.  Integer work: bit-exact with the stable-sort oracle.
+ * ---------------------------------------------------------------------------------- */
+typedef struct hg_plan_rel {
+    const int64_t* src;   /* [E] source ids      (edge_index[0]) */
+    const int64_t* dst;   /* [E] destination ids (edge_index[1]) */
+    int64_t n_edges;      /* E */
+    int32_t n_src;
+    int32_t n_dst;
+    int32_t self_loops;   /* 0 | 1 */
+    int32_t reserved;
+    int32_t* rowptr;      /* out [n_dst + 1] */
+    int32_t* col;         /* out [E + loops] */
+    int32_t* perm;        /* out [E + loops], may be NULL */
+    float* inv_sqrt_deg;  /* out [n_dst] deg^-1/2 (0 when deg == 0), may be NULL (gcn_norm) */
+} hg_plan_rel;
+
+HG_API size_t hg_plan_workspace_bytes(const hg_plan_rel* rels_host, int n_rel);
+HG_API int hg_plan_build(const hg_plan_rel* rels_host, int n_rel, int32_t* status /* [1], zeroed by the call */,
+                  void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * K2 / K5  Segmented reduction over CSR rows (sum / mean / max), warp-per-destination,
+ * vectorised feature loads, neighbour lists staged through shared memory.
+ *
+ *   out[r, :] = act( dst_scale[i] * reduce_{e in row i} src_scale[col[e]] * x[col[e], :]
+ *                    + self_coef * x_self[i, :] + bias[:] ),   i = row_map ? row_map[r] : r
+ *
+ * Replaces: MessagePassing.aggregate -> scatter(reduce) of SAGEConv (mean, models/utils.py:14),
+ * GCNConv (sum of D^-1/2 (A+I) D^-1/2 messages, :16; src_scale = dst_scale = deg^-1/2),
+ * GINConv (sum + (1+eps) x_i, :18-26; self_coef_ptr = eps, self_coef_add = 1),
+ * and LeafPool (mean; heterogeneous_neural_tree_network.py:18-31,181-185;
+ * homogeneous_neural_tree_network.py:100 with row_map = indices of room_mask).
+ * Empty rows reduce to 0 (PyG semantics) before the self / bias terms.
+ * ---------------------------------------------------------------------------------- */
+typedef struct hg_seg_args {
+    const float* x;  int64_t ldx;          /* [n_src, F] gathered operand */
+    const int32_t* rowptr; const int32_t* col;
+    const float* src_scale;                 /* NULL | [n_src] */
+    const float* dst_scale;                 /* NULL | [n_dst] */
+    const int32_t* row_map;                 /* NULL | [n_out] CSR row of output row r */
+    const float* x_self; int64_t ldself;    /* NULL | [n_dst, F] indexed by i */
+    const float* self_coef_ptr;             /* NULL | device scalar c; coefficient = self_coef_add + c */
+    float self_coef_add;
+    const float* bias;                      /* NULL | [F] */
+    float* out; int64_t ldout;              /* [n_out, F] */
+    int32_t n_out; int32_t F;
+    int32_t op;  /* HG_REDUCE_* */
+    int32_t act; /* HG_ACT_* */
+} hg_seg_args;
+
+HG_API int hg_seg_reduce(const hg_seg_args* args_host, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * K3 + K4  Fused GAT for ONE destination node type: for every relation r targeting it,
+ * edge score -> segment softmax -> weighted aggregation -> head concat/mean -> +bias_r;
+ * then the HeteroConv cross-relation group (sum | mean) and the model's activation, all in
+ * one pass; `out` is written exactly once.
+ *
+ *   s_e,h  = leaky_relu(a_src[col[e], h] + a_dst[i, h] (+ a_edge[e, h]), neg_slope)
+ *   w_e,h  = exp(s_e,h - max_row) / (sum_row exp(.) + 1e-16)
+ *   o_r[i] = concat_h | mean_h ( sum_e w_e,h * xs[col[e], h, :] ) + bias_r
+ *   out[i] = act( group_r o_r[i] )
+ *
+ * Replaces: GATConv.edge_update + torch_geometric.utils.softmax (4 scatter passes) +
+ * propagate + concat/mean + bias (models/utils.py:31-87,103-140), HeteroConv's
+ * `torch.stack(outs).sum(0)` / `.mean(0)` (models/utils.py:132-138;
+ * heterogeneous_neural_tree_network.py:103), and the following F.elu / F.relu
+ * (heterogeneous_network.py:108-119; homogeneous_network.py:135).
+ * xs / a_src / a_dst are columns of the fused projection output (hg_linear), hence the
+ * leading dimensions.  a_edge is in CSR order (one row per CSR entry).
+ * ---------------------------------------------------------------------------------- */
+typedef struct hg_gat_rel {
+    const float* xs;    int64_t ldxs;   /* [n_src, H*C] projected sources */
+    const float* a_src; int64_t lda_src;/* [n_src, H] */
+    const float* a_dst; int64_t lda_dst;/* [n_dst, H] */
+    const float* a_edge;                /* NULL | [E', H] contiguous, CSR order */
+    const int32_t* rowptr; const int32_t* col;
+    const float* bias;                  /* NULL | [H*C] (concat) or [C] */
+} hg_gat_rel;
+
+typedef struct hg_gat_args {
+    hg_gat_rel rel[HG_MAX_RELATIONS];
+    int32_t n_rel;
+    int32_t n_dst;
+    int32_t H; int32_t C;
+    int32_t concat;     /* 1: out width H*C; 0: head mean, out width C */
+    int32_t group;      /* HG_GROUP_* over relations */
+    int32_t act;        /* HG_ACT_* */
+    float neg_slope;
+    float* out; int64_t ldout;
+    float* alpha_saved[HG_MAX_RELATIONS]; /* NULL | [E', H] softmax weights (for backward) */
+} hg_gat_args;
+
+HG_API int hg_gat_fused(const hg_gat_args* args_host, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * K6  Fused projection:  y[M, N] = act( (sum_s x_s[M, K_s] * W_s[N, K_s]^T + bias) * scale + shift )
+ *
+ * The K dimension is a virtual concatenation of up to HG_MAX_SEGMENTS (x_s, W_s) pairs, so
+ * SAGEConv's lin_l(mean) + lin_r(x) (+ the HeteroConv sum over relations) is ONE call.  The
+ * attention logits a = (xW^T).att are produced by the same call: the caller appends the
+ * folded rows (W^T att)^T to W (see hydra_gnn_b200/nn.py), so they are just extra columns.
+ *
+ * Replaces: torch.nn.Linear inside GATConv.lin_src/lin_dst/lin_edge, SAGEConv.lin_l/lin_r,
+ * GCNConv.lin, GINConv.nn and post_mp_room/object (models/utils.py:9-28,49-86;
+ * homogeneous_network.py:119-120) -- cuBLAS SGEMM in the reference.
+ * precision: HG_PREC_FP32 = CUDA-core fp32 FMA; HG_PREC_TF32X3 = tcgen05 kind::tf32 with
+ * 3-term error compensation (fp32-class accuracy on the tensor pipe).
+ * ---------------------------------------------------------------------------------- */
+typedef struct hg_lin_seg {
+    const float* x; int64_t ldx;   /* [M, K] */
+    const float* w; int64_t ldw;   /* [N, K] */
+    int32_t K; int32_t reserved;
+} hg_lin_seg;
+
+typedef struct hg_linear_args {
+    hg_lin_seg seg[HG_MAX_SEGMENTS];
+    int32_t n_seg;
+    int32_t M; int32_t N;
+    const float* bias;   /* NULL | [N] */
+    const float* scale;  /* NULL | [N]  (eval-mode BatchNorm fold) */
+    const float* shift;  /* NULL | [N] */
+    int32_t act;         /* HG_ACT_* */
+    int32_t precision;   /* HG_PREC_* */
+    float* y; int64_t ldy;
+} hg_linear_args;
+
+HG_API size_t hg_linear_workspace_bytes(const hg_linear_args* args_host);
+HG_API int hg_linear(const hg_linear_args* args_host, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Edge-attribute helpers for GAT_edge (homogeneous_network.py:72-82;
+ * heterogeneous_network.py:68-79; mp3d_dataset.py:298-319).
+ *   hg_edge_logits: a_edge[p, h] = perm[p] >= 0 ? dot(edge_attr[perm[p], :D], v[h, :D]) : fill_h
+ *   with v = folded (lin_edge^T att_edge) [H, D]; fill_h = dot(fill[:D], v[h]) (loops).
+ *   hg_relative_pos: edge_attr[e, :] = pos_dst[dst[e], :3] - pos_src[src[e], :3]
+ * ---------------------------------------------------------------------------------- */
+HG_API int hg_edge_logits(const float* edge_attr, int64_t ld_attr, int32_t D, const int32_t* perm, const int32_t* rowptr_last,
+                   int64_t cap, const float* v /* [H, D] */, const float* fill /* NULL | [D] */, int32_t H,
+                   float* a_edge /* [cap, H] */, void* stream);
+HG_API int hg_relative_pos(const float* pos_src, const float* pos_dst, const int64_t* src, const int64_t* dst, int64_t E,
+                    float* edge_attr /* [E, 3] */, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HYDRA_GNN_B200_H_ */
