@@ -38,6 +38,19 @@ k_relative_pos(const float* __restrict__ ps, const float* __restrict__ pd, const
     }
 }
 
+// out[r, :F] = act(x[idx[r], :F])  (x[room_mask] of the homogeneous models; idx from the plan)
+__global__ void __launch_bounds__(kThreads)
+k_gather_rows(const float* __restrict__ x, int64_t ldx, const int32_t* __restrict__ idx, int64_t n_out, int F,
+              int act, float* __restrict__ out, int64_t ldout) {
+    const int64_t total = n_out * F;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += stride) {
+        const int64_t r = t / F;
+        const int f = static_cast<int>(t % F);
+        out[r * ldout + f] = apply_act(__ldg(x + static_cast<int64_t>(__ldg(idx + r)) * ldx + f), act);
+    }
+}
+
 unsigned grid_for(int64_t n) {
     const int sms = sm_count() > 0 ? sm_count() : 148;
     int64_t g = ceil_div<int64_t>(n > 0 ? n : 1, kThreads);
@@ -68,5 +81,16 @@ extern "C" int hg_relative_pos(const float* pos_src, const float* pos_dst, const
     if (!pos_src || !pos_dst || !src || !dst || !edge_attr) return HG_EINVAL;
     k_relative_pos<<<grid_for(E), kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(pos_src, pos_dst, src, dst, E,
                                                                                       edge_attr);
+    return check_launch();
+}
+
+extern "C" int hg_gather_rows(const float* x, int64_t ldx, const int32_t* idx, int64_t n_out, int32_t F, int32_t act,
+                              float* out, int64_t ldout, void* stream_) {
+    using namespace hg;
+    if (n_out < 0 || F < 0) return HG_EINVAL;
+    if (n_out == 0 || F == 0) return HG_OK;
+    if (!x || !idx || !out) return HG_EINVAL;
+    k_gather_rows<<<grid_for(n_out * F), kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(x, ldx, idx, n_out, F, act,
+                                                                                            out, ldout);
     return check_launch();
 }

@@ -281,3 +281,16 @@ def relative_pos(pos_src: Tensor, pos_dst: Tensor, edge_index: Tensor) -> Tensor
                             stream_ptr()), "hg_relative_pos")
     _lib.launch_count += 1
     return out
+
+
+def gather_rows(x: Tensor, idx: Tensor, act: str = None) -> Tensor:
+    """``act(x[idx])`` with ``idx`` int32 (the models' ``x[room_mask, :]``)."""
+    h = lib()
+    x = _rows(x, "x")
+    if idx.dtype != torch.int32:
+        raise TypeError("idx must be int32")
+    out = torch.empty(idx.numel(), x.size(1), dtype=torch.float32, device=x.device)
+    check(h.hg_gather_rows(ptr(x), _ld(x), ptr(idx), idx.numel(), x.size(1), ACT[act], ptr(out), _ld(out),
+                           stream_ptr()), "hg_gather_rows")
+    _lib.launch_count += 1
+    return out

@@ -226,6 +226,12 @@ HG_API int hg_edge_logits(const float* edge_attr, int64_t ld_attr, int32_t D, co
 HG_API int hg_relative_pos(const float* pos_src, const float* pos_dst, const int64_t* src, const int64_t* dst, int64_t E,
                     float* edge_attr /* [E, 3] */, void* stream);
 
+/* out[r, :F] = act(x[idx[r], :F]) -- the `x[room_mask, :]` / `x[object_mask, :]` row selection of
+ * homogeneous_network.py:139-145 and homogeneous_neural_tree_network.py:103-109 (idx = nonzero(mask),
+ * computed once per batch with the plan). */
+HG_API int hg_gather_rows(const float* x, int64_t ldx, const int32_t* idx, int64_t n_out, int32_t F, int32_t act,
+                          float* out, int64_t ldout, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
