@@ -1,8 +1,398 @@
-// K6 tensor-core path (tcgen05 kind::tf32, 3-term compensated) -- placeholder until the kernel lands.
+// K6 tensor-core path: y = act((sum_s x_s W_s^T + bias) * scale + shift) on tcgen05 (sm_100a).
+//
+// fp32-class accuracy on the TF32 tensor pipe by 3-term error compensation:
+//     x = x_hi + x_lo,  W = W_hi + W_lo   (hi = rna_tf32(.), lo = rna_tf32(. - hi))
+//     x W^T ~= x_hi W_hi^T + x_hi W_lo^T + x_lo W_hi^T          (dropped term ~ 2^-22)
+// accumulated in fp32 in TMEM.  The tensor core adds into the accumulator with truncation (about
+// one ulp of the accumulator per MMA), so the main term and the two 2^-11-sized correction terms
+// get SEPARATE TMEM accumulators (summed in the epilogue): the truncation chain that matters is
+// K/8 instructions long instead of 3K/8.
+//
+// CTA = one 128-row tile of x times one N tile (<= 256 columns) of W.  Warp roles:
+//   warp 0        allocates TMEM; one elected lane issues tcgen05.mma (12 per 32-wide k-block)
+//                 and tcgen05.commit (frees the smem stage / publishes the accumulator);
+//   warps 1..8    loaders: read the x tile from global with vector loads (rows of x are only
+//                 8-byte aligned when K = 306, so TMA cannot describe them), split hi/lo in
+//                 registers and store both tiles in the UMMA canonical K-major SWIZZLE_128B layout;
+//                 one lane issues a 1-D bulk copy (cp.async.bulk, UBLKCP) of the pre-swizzled
+//                 W_hi|W_lo image of the stage.  After the main loop the same warps run the
+//                 epilogue: tcgen05.ld accumulator -> bias/scale/shift/activation -> global.
+// W is re-packed (split + swizzled, 0.5 MB) into the caller's workspace by a tiny kernel in
+// the same call, so the ABI stays stateless.
 #include "hg_common.cuh"
 
 namespace hg {
-int linear_tc_supported(const hg_linear_args&) { return 0; }
-size_t linear_tc_workspace_bytes(const hg_linear_args&) { return 0; }
-int linear_tc_launch(const hg_linear_args&, void*, size_t, cudaStream_t) { return HG_EUNSUPPORTED; }
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 32;                      // fp32 elements per k-block = one 128-byte swizzle row
+constexpr int kLoaderWarps = 8;
+constexpr int kLoaderThreads = kLoaderWarps * 32;
+constexpr int kThreads = 32 + kLoaderThreads;
+constexpr int kATileBytes = BM * BK * 4;    // 16 KB
+constexpr long long kWaitCycles = 4000000000ll;  // ~2 s: a protocol bug traps instead of hanging the GPU
+
+struct TcParams {
+    hg_linear_args a;
+    const float* wp;      // packed weights: [n_tiles][n_kb][hi|lo][block_n rows x 128 B, swizzled]
+    int32_t n_tiles, block_n, n_kb, stages;
+    int32_t kb_start[HG_MAX_SEGMENTS + 1];  // first k-block of each segment
+    int32_t tmem_cols;
+    int32_t vec;          // widest vector all x segments allow (1, 2, 4)
+};
+
+// ------------------------------------------------------------------------------ PTX helpers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// Bounded wait: a protocol bug traps (sticky error on this context) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity))
+        if (clock64() - t0 > kWaitCycles) __trap();
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+__device__ __forceinline__ float tf32_rna(float v) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return __uint_as_float(r);
+}
+
+// K-major SWIZZLE_128B tile: row r (128 B = one k-block), 16-byte chunk c of the row lands in
+// chunk c ^ (r & 7); 8-row groups are 1024 B apart.  Same image a TMA SWIZZLE_128B box produces.
+__host__ __device__ __forceinline__ uint32_t swz_off(int r, int k) {
+    return static_cast<uint32_t>((r >> 3) * 1024 + (r & 7) * 128 + ((((k >> 2) ^ r) & 7) << 4) + (k & 3) * 4);
+}
+
+// UMMA shared-memory descriptor, K-major, SWIZZLE_128B: start>>4 | LBO=1 | SBO=1024>>4 | version=1 | layout=2
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
+    return static_cast<uint64_t>((saddr >> 4) & 0x3FFF) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+
+// ------------------------------------------------------------------------------ weight packing
+__global__ void __launch_bounds__(256) k_pack_w(const __grid_constant__ TcParams P, float* __restrict__ wp) {
+    const hg_linear_args& A = P.a;
+    const int64_t per_stage = static_cast<int64_t>(P.block_n) * BK;  // floats in one hi (or lo) tile
+    const int64_t total = static_cast<int64_t>(P.n_tiles) * P.n_kb * per_stage;
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total;
+         t += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int k_local = static_cast<int>(t % BK);
+        const int n_local = static_cast<int>((t / BK) % P.block_n);
+        const int kb = static_cast<int>((t / per_stage) % P.n_kb);
+        const int nt = static_cast<int>(t / (per_stage * P.n_kb));
+        int s = 0;
+        while (s + 1 < A.n_seg && kb >= P.kb_start[s + 1]) ++s;
+        const int k = (kb - P.kb_start[s]) * BK + k_local;
+        const int n = nt * P.block_n + n_local;
+        float w = 0.f;
+        if (n < A.N && k < A.seg[s].K) w = A.seg[s].w[static_cast<int64_t>(n) * A.seg[s].ldw + k];
+        const float hi = tf32_rna(w);
+        const float lo = tf32_rna(w - hi);
+        float* base = wp + (static_cast<int64_t>(nt) * P.n_kb + kb) * 2 * per_stage;
+        const uint32_t off = swz_off(n_local, k_local) / 4;
+        base[off] = hi;
+        base[per_stage + off] = lo;
+    }
+}
+
+// ------------------------------------------------------------------------------ main kernel
+template <int VEC>
+__global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant__ TcParams P) {
+    extern __shared__ uint8_t smem_raw[];
+    const hg_linear_args& A = P.a;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_tile = blockIdx.x % P.n_tiles;
+    const int64_t m0 = static_cast<int64_t>(blockIdx.x / P.n_tiles) * BM;
+    const int n0 = n_tile * P.block_n;
+    const int S = P.stages;
+    const uint32_t b_tile_bytes = static_cast<uint32_t>(P.block_n) * 128u;
+    const uint32_t stage_bytes = 2u * kATileBytes + 2u * b_tile_bytes;
+
+    // carve: [1024-aligned stages][barriers][tmem slot]
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(base + static_cast<size_t>(S) * stage_bytes);
+    uint64_t* full_a = bars;            // [S] loaders -> MMA   (count = loader warps)
+    uint64_t* full_b = bars + S;        // [S] bulk copy -> MMA (count = 1 + tx bytes)
+    uint64_t* empty = bars + 2 * S;     // [S] MMA -> loaders   (tcgen05.commit)
+    uint64_t* acc_full = bars + 3 * S;  // [1] MMA -> epilogue
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * S + 1);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < S; ++s) {
+            mbar_init(&full_a[s], kLoaderWarps);
+            mbar_init(&full_b[s], 1);
+            mbar_init(&empty[s], 1);
+        }
+        mbar_init(acc_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc(tmem_slot, static_cast<uint32_t>(P.tmem_cols));
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;                                   // main term accumulator
+    const uint32_t tmem_corr = tmem_base + static_cast<uint32_t>(P.block_n);  // correction terms accumulator
+
+    if (warp == 0) {
+        // ===================== MMA issuer =====================
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(P.block_n >> 3) << 17) |
+                               (static_cast<uint32_t>(BM >> 4) << 24);
+        for (int kb = 0; kb < P.n_kb; ++kb) {
+            const int s = kb % S;
+            const uint32_t ph = static_cast<uint32_t>(kb / S) & 1u;
+            mbar_wait(&full_a[s], ph);
+            mbar_wait(&full_b[s], ph);
+            tc_fence_after();
+            if (lane == 0) {
+                const uint32_t sa = smem_u32(base + static_cast<size_t>(s) * stage_bytes);
+                const uint64_t a_hi = make_desc(sa), a_lo = make_desc(sa + kATileBytes);
+                const uint64_t b_hi = make_desc(sa + 2 * kATileBytes), b_lo = make_desc(sa + 2 * kATileBytes + b_tile_bytes);
+#pragma unroll
+                for (int ks = 0; ks < BK / 8; ++ks) {  // UMMA_K = 8 tf32 = 32 bytes: descriptor start += 2
+                    const uint64_t adv = static_cast<uint64_t>(ks * 2);
+                    umma_tf32(tmem_base, a_hi + adv, b_hi + adv, idesc, (kb | ks) != 0 ? 1u : 0u);
+                    umma_tf32(tmem_corr, a_hi + adv, b_lo + adv, idesc, (kb | ks) != 0 ? 1u : 0u);
+                    umma_tf32(tmem_corr, a_lo + adv, b_hi + adv, idesc, 1u);
+                }
+                umma_commit(&empty[s]);                       // stage reusable once these MMAs retire
+                if (kb == P.n_kb - 1) umma_commit(acc_full);  // accumulator complete
+            }
+            __syncwarp();
+        }
+    } else {
+        // ===================== loaders / converters =====================
+        const int t = threadIdx.x - 32;
+        constexpr int kVecPerRow = BK / VEC;
+        constexpr int kRowStep = kLoaderThreads / kVecPerRow;
+        constexpr int kIters = BM / kRowStep;
+        const int cv = t % kVecPerRow, rb = t / kVecPerRow;
+        const int kcol = cv * VEC;
+
+        for (int kb = 0; kb < P.n_kb; ++kb) {
+            const int s = kb % S;
+            const uint32_t ph = static_cast<uint32_t>(kb / S) & 1u;
+            int seg = 0;
+            while (seg + 1 < A.n_seg && kb >= P.kb_start[seg + 1]) ++seg;
+            const hg_lin_seg& G = A.seg[seg];
+            const int k = (kb - P.kb_start[seg]) * BK + kcol;
+
+            float v[kIters][VEC];
+#pragma unroll
+            for (int i = 0; i < kIters; ++i) {
+                const int64_t m = m0 + rb + i * kRowStep;
+                const bool row_ok = m < A.M;
+                const float* __restrict__ src = G.x + m * G.ldx + k;
+                if (row_ok && k + VEC <= G.K) {
+                    ldg_vec<VEC>(src, v[i]);
+                } else {
+#pragma unroll
+                    for (int e = 0; e < VEC; ++e) v[i][e] = (row_ok && k + e < G.K) ? __ldg(src + e) : 0.f;
+                }
+            }
+            mbar_wait(&empty[s], ph ^ 1u);  // MMAs of the previous use of this stage have retired
+            uint8_t* stage = base + static_cast<size_t>(s) * stage_bytes;
+            if (t == 0) {
+                mbar_arrive_expect_tx(&full_b[s], 2u * b_tile_bytes);
+                const float* src = P.wp + (static_cast<int64_t>(n_tile) * P.n_kb + kb) * 2 * (b_tile_bytes / 4);
+                bulk_g2s(stage + 2 * kATileBytes, src, 2u * b_tile_bytes, &full_b[s]);
+            }
+#pragma unroll
+            for (int i = 0; i < kIters; ++i) {
+                const int r = rb + i * kRowStep;
+                float hi[VEC], lo[VEC];
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) {
+                    hi[e] = tf32_rna(v[i][e]);
+                    lo[e] = tf32_rna(v[i][e] - hi[e]);
+                }
+                const uint32_t off = swz_off(r, kcol);
+                st_vec<VEC>(reinterpret_cast<float*>(stage + off), hi);
+                st_vec<VEC>(reinterpret_cast<float*>(stage + kATileBytes + off), lo);
+            }
+            fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&full_a[s]);
+        }
+
+        // ===================== epilogue =====================
+        mbar_wait(acc_full, 0);
+        tc_fence_after();
+        const int q = warp & 3;               // TMEM lane quarter this warp may read
+        const int half = (warp - 1) >> 2;     // two warps share a quarter: even / odd 16-column chunks
+        const int64_t m = m0 + q * 32 + lane;
+        const bool vec_store = (A.ldy % 4 == 0) && ((reinterpret_cast<uintptr_t>(A.y) & 15) == 0);
+        for (int c = half; c * 16 < P.block_n; c += 2) {
+            float acc[16], corr[16];
+            const uint32_t toff = (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(c * 16);
+            tmem_ld16(tmem_base + toff, acc);
+            tmem_ld16(tmem_corr + toff, corr);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) acc[j] += corr[j];
+            const int n = n0 + c * 16;
+            if (m >= A.M || n >= A.N) continue;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const int nn = n + j;
+                if (nn < A.N) {
+                    float o = acc[j];
+                    if (A.bias) o += __ldg(A.bias + nn);
+                    if (A.scale) o *= __ldg(A.scale + nn);
+                    if (A.shift) o += __ldg(A.shift + nn);
+                    acc[j] = apply_act(o, A.act);
+                }
+            }
+            float* dst = A.y + m * A.ldy + n;
+            if (vec_store && n + 16 <= A.N) {
+#pragma unroll
+                for (int j = 0; j < 16; j += 4)
+                    *reinterpret_cast<float4*>(dst + j) = make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    if (n + j < A.N) dst[j] = acc[j];
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, static_cast<uint32_t>(P.tmem_cols));
+    }
+}
+
+constexpr size_t kSmemBudget = 200 * 1024;
+
+bool plan(const hg_linear_args& a, TcParams& P) {
+    P.a = a;
+    const int n_pad = ceil_div(a.N, 16) * 16;
+    P.n_tiles = ceil_div(n_pad, 256);
+    P.block_n = ceil_div(ceil_div(n_pad, P.n_tiles), 16) * 16;
+    int kb = 0;
+    int vec = 4;
+    for (int s = 0; s < a.n_seg; ++s) {
+        P.kb_start[s] = kb;
+        kb += ceil_div(a.seg[s].K, BK);
+        while (vec > 1 && (a.seg[s].ldx % vec || !aligned(a.seg[s].x, sizeof(float) * vec))) vec >>= 1;
+    }
+    for (int s = a.n_seg; s <= HG_MAX_SEGMENTS; ++s) P.kb_start[s] = kb;
+    P.n_kb = kb;
+    P.vec = vec;
+    const size_t stage_bytes = 2 * kATileBytes + 2 * static_cast<size_t>(P.block_n) * 128;
+    int stages = static_cast<int>(kSmemBudget / stage_bytes);
+    stages = stages > 4 ? 4 : stages;
+    stages = stages > P.n_kb ? (P.n_kb > 0 ? P.n_kb : 1) : stages;
+    P.stages = stages;
+    int cols = 32;
+    while (cols < 2 * P.block_n) cols <<= 1;  // main + correction accumulators
+    P.tmem_cols = cols;
+    return stages >= 1 && P.n_kb >= 1;
+}
+
+}  // namespace
+
+int linear_tc_supported(const hg_linear_args& a) {
+    if (a.M < 1 || a.N < 1) return 0;
+    int64_t k_total = 0;
+    for (int s = 0; s < a.n_seg; ++s) k_total += a.seg[s].K;
+    return k_total >= 1 ? 1 : 0;
+}
+
+size_t linear_tc_workspace_bytes(const hg_linear_args& a) {
+    TcParams P;
+    if (!plan(a, P)) return 0;
+    return static_cast<size_t>(P.n_tiles) * P.n_kb * 2 * P.block_n * 128 + 256;
+}
+
+int linear_tc_launch(const hg_linear_args& a, void* ws, size_t ws_bytes, cudaStream_t stream) {
+    TcParams P;
+    if (!plan(a, P)) return HG_EUNSUPPORTED;
+    const size_t need = static_cast<size_t>(P.n_tiles) * P.n_kb * 2 * P.block_n * 128;
+    if (!ws || ws_bytes < need) return HG_EWORKSPACE;
+    if (!aligned(ws, 128)) return HG_EALIGN;
+    P.wp = static_cast<const float*>(ws);
+
+    const int64_t pack_elems = static_cast<int64_t>(P.n_tiles) * P.n_kb * P.block_n * BK;
+    const unsigned pack_grid = static_cast<unsigned>(ceil_div<int64_t>(pack_elems, 256) < 1184 ? ceil_div<int64_t>(pack_elems, 256) : 1184);
+    k_pack_w<<<pack_grid, 256, 0, stream>>>(P, static_cast<float*>(ws));
+    int rc = check_launch();
+    if (rc != HG_OK) return rc;
+
+    const size_t stage_bytes = 2 * kATileBytes + 2 * static_cast<size_t>(P.block_n) * 128;
+    const size_t smem = 1024 + P.stages * stage_bytes + (3 * P.stages + 1) * sizeof(uint64_t) + 16;
+    const int64_t m_tiles = ceil_div<int64_t>(a.M, BM);
+    const int64_t grid = m_tiles * P.n_tiles;
+    if (grid >= (int64_t(1) << 31)) return HG_ERANGE;
+    auto go = [&](auto kernel) -> int {
+        HG_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        kernel<<<static_cast<unsigned>(grid), kThreads, smem, stream>>>(P);
+        return check_launch();
+    };
+    if (P.vec == 4) return go(k_linear_tc<4>);
+    if (P.vec == 2) return go(k_linear_tc<2>);
+    return go(k_linear_tc<1>);
+}
+
 }  // namespace hg

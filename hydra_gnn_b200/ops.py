@@ -15,7 +15,28 @@ from torch import Tensor
 from . import _lib
 from ._lib import ACT, GROUP, PREC, REDUCE, check, lib, ptr, stream_ptr
 
-DEFAULT_PRECISION = "fp32"
+DEFAULT_PRECISION = "auto"  # "auto": tcgen05 TF32x3 for M >= TC_MIN_ROWS, fp32 CUDA cores below
+TC_MIN_ROWS = 512
+
+# Optional per-launch timing (bench.py's roofline leg): a list that receives
+# (abi_name, meta dict, start_event, end_event) for every ABI call while it is set.
+_profile_sink = None
+
+
+def set_profile_sink(sink):
+    global _profile_sink
+    _profile_sink = sink
+
+
+def _call(name: str, meta, fn):
+    if _profile_sink is None:
+        check(fn(), name)
+        return
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start.record()
+    check(fn(), name)
+    end.record()
+    _profile_sink.append((name, meta, start, end))
 
 
 def _require_no_grad(*tensors):
@@ -132,7 +153,10 @@ def build_csr(specs: Sequence[CSRSpec]):
             raise RuntimeError("hg_plan_workspace_bytes rejected the plan (sizes out of int32 range?)")
         ws = _workspace(device, nbytes)
         st = status if lo == 0 else torch.empty(1, dtype=torch.int32, device=device)
-        check(h.hg_plan_build(rels, len(chunk), ptr(st), ptr(ws), ws.numel(), stream_ptr()), "hg_plan_build")
+        meta = dict(n_rel=len(chunk), edges=[int(s.edge_index.size(1)) for s in chunk],
+                    n_dst=[int(r.n_dst) for r in rels], caps=[c.cap for c in out[lo:]])
+        _call("hg_plan_build", meta,
+              lambda: h.hg_plan_build(rels, len(chunk), ptr(st), ptr(ws), ws.numel(), stream_ptr()))
         _lib.launch_count += 6
         if lo != 0:
             status += st
@@ -168,7 +192,8 @@ def seg_reduce(x: Tensor, csr: CSR, op: str = "sum", *, src_scale: Tensor = None
     a.out, a.ldout = ptr(out), _ld(out)
     a.n_out, a.F = n_out, F
     a.op, a.act = REDUCE[op], ACT[act]
-    check(h.hg_seg_reduce(C.byref(a), stream_ptr()), "hg_seg_reduce")
+    meta = dict(n_src=x.size(0), n_out=n_out, F=F, cap=csr.cap, scaled=src_scale is not None, self=x_self is not None)
+    _call("hg_seg_reduce", meta, lambda: h.hg_seg_reduce(C.byref(a), stream_ptr()))
     _lib.launch_count += 1
     return out
 
@@ -215,7 +240,9 @@ def gat_fused(rels: Sequence[GatRelation], n_dst: int, H: int, Cc: int, concat: 
     a.n_rel, a.n_dst, a.H, a.C = len(rels), n_dst, H, Cc
     a.concat, a.group, a.act, a.neg_slope = int(concat), GROUP[group], ACT[act], float(neg_slope)
     a.out, a.ldout = ptr(out), _ld(out)
-    check(h.hg_gat_fused(C.byref(a), stream_ptr()), "hg_gat_fused")
+    meta = dict(n_dst=n_dst, H=H, C=Cc, concat=bool(concat), width=width,
+                rels=[dict(n_src=r.xs.size(0), cap=r.csr.cap, edge=r.a_edge is not None) for r in rels])
+    _call("hg_gat_fused", meta, lambda: h.hg_gat_fused(C.byref(a), stream_ptr()))
     _lib.launch_count += 1
     return out
 
@@ -245,11 +272,15 @@ def linear(segments: Sequence, N: int, *, bias: Tensor = None, scale: Tensor = N
     a.n_seg, a.M, a.N = len(segments), M, N
     a.bias, a.scale, a.shift = ptr(bias), ptr(scale), ptr(shift)
     a.act = ACT[act]
-    a.precision = PREC[precision or DEFAULT_PRECISION]
+    precision = precision or DEFAULT_PRECISION
+    if precision == "auto":
+        precision = "tf32x3" if M >= TC_MIN_ROWS else "fp32"
+    a.precision = PREC[precision]
     a.y, a.ldy = ptr(out), _ld(out)
     nbytes = h.hg_linear_workspace_bytes(C.byref(a))
     ws = _workspace(device, nbytes) if nbytes else None
-    check(h.hg_linear(C.byref(a), ptr(ws), nbytes, stream_ptr()), "hg_linear")
+    meta = dict(M=M, N=N, K=[x.size(1) for x, _ in keep], precision=precision)
+    _call("hg_linear", meta, lambda: h.hg_linear(C.byref(a), ptr(ws), nbytes, stream_ptr()))
     _lib.launch_count += 1
     return out
 
@@ -264,8 +295,10 @@ def edge_logits(edge_attr: Tensor, csr: CSR, v: Tensor, H: int, fill: Tensor = N
     v = _rows(v, "v")
     D = edge_attr.size(1)
     out = torch.empty(max(csr.cap, 1), H, dtype=torch.float32, device=v.device)
-    check(h.hg_edge_logits(ptr(edge_attr), _ld(edge_attr), D, ptr(csr.perm), csr.rowptr[-1:].data_ptr(), csr.cap,
-                           ptr(v), ptr(fill), H, ptr(out), stream_ptr()), "hg_edge_logits")
+    last = csr.rowptr[-1:]
+    _call("hg_edge_logits", dict(cap=csr.cap, H=H, D=D),
+          lambda: h.hg_edge_logits(ptr(edge_attr), _ld(edge_attr), D, ptr(csr.perm), last.data_ptr(), csr.cap,
+                                   ptr(v), ptr(fill), H, ptr(out), stream_ptr()))
     _lib.launch_count += 1
     return out
 
@@ -277,8 +310,9 @@ def relative_pos(pos_src: Tensor, pos_dst: Tensor, edge_index: Tensor) -> Tensor
     ei = edge_index.contiguous()
     E = ei.size(1)
     out = torch.empty(E, 3, dtype=torch.float32, device=ei.device)
-    check(h.hg_relative_pos(ptr(pos_src), ptr(pos_dst), ei.data_ptr(), ei.data_ptr() + 8 * E, E, ptr(out),
-                            stream_ptr()), "hg_relative_pos")
+    _call("hg_relative_pos", dict(E=E),
+          lambda: h.hg_relative_pos(ptr(pos_src), ptr(pos_dst), ei.data_ptr(), ei.data_ptr() + 8 * E, E, ptr(out),
+                                    stream_ptr()))
     _lib.launch_count += 1
     return out
 
@@ -290,7 +324,8 @@ def gather_rows(x: Tensor, idx: Tensor, act: str = None) -> Tensor:
     if idx.dtype != torch.int32:
         raise TypeError("idx must be int32")
     out = torch.empty(idx.numel(), x.size(1), dtype=torch.float32, device=x.device)
-    check(h.hg_gather_rows(ptr(x), _ld(x), ptr(idx), idx.numel(), x.size(1), ACT[act], ptr(out), _ld(out),
-                           stream_ptr()), "hg_gather_rows")
+    _call("hg_gather_rows", dict(n=idx.numel(), F=x.size(1)),
+          lambda: h.hg_gather_rows(ptr(x), _ld(x), ptr(idx), idx.numel(), x.size(1), ACT[act], ptr(out), _ld(out),
+                                   stream_ptr()))
     _lib.launch_count += 1
     return out

@@ -1,0 +1,165 @@
+"""GPU parity of the individual C-ABI entry points (through hydra_gnn_b200.ops) against the
+oracle / exact references: K1 bit-exact, K2/K5, K6 (fp32 and tcgen05 TF32x3)."""
+import numpy as np
+import pytest
+import torch
+
+from hydra_gnn_b200 import ops
+from hydra_gnn_b200.ops import CSRSpec
+from oracle.pyg import utils as ou
+from util import assert_close
+
+pytestmark = pytest.mark.gpu
+
+
+# ------------------------------------------------------------------------------ K1 (integer, bit-exact)
+def csr_oracle(ei, n_src, n_dst, self_loops):
+    """Stable sort by destination of PyG's (remove_self_loops -> add_self_loops) edge list."""
+    ei = ei.cpu()
+    E = ei.size(1)
+    ids = torch.arange(E)
+    if self_loops:
+        keep = ei[0] != ei[1]
+        n = min(n_src, n_dst)
+        loops = torch.arange(n)
+        src = torch.cat([ei[0][keep], loops])
+        dst = torch.cat([ei[1][keep], loops])
+        ids = torch.cat([ids[keep], torch.full((n,), -1, dtype=torch.long)])
+    else:
+        src, dst = ei[0], ei[1]
+    order = torch.sort(dst, stable=True).indices
+    rowptr = torch.zeros(n_dst + 1, dtype=torch.long)
+    rowptr[1:] = torch.bincount(dst, minlength=n_dst).cumsum(0)
+    return rowptr.int(), src[order].int(), ids[order].int()
+
+
+@pytest.mark.parametrize("n_src,n_dst,E,loops", [(50, 50, 400, True), (50, 50, 400, False), (1000, 37, 5000, False),
+                                                 (37, 1000, 5000, True), (7, 7, 0, True), (0, 5, 0, False),
+                                                 (20000, 20000, 300000, True), (3, 3, 5000, True)])
+def test_plan_bit_exact(n_src, n_dst, E, loops):
+    g = torch.Generator().manual_seed(E + n_src)
+    ei = torch.stack([torch.randint(0, max(n_src, 1), (E,), generator=g),
+                      torch.randint(0, max(n_dst, 1), (E,), generator=g)]) if E else torch.zeros(2, 0, dtype=torch.long)
+    (csr,), status = ops.build_csr([CSRSpec(ei.cuda(), n_src, n_dst, loops, want_perm=True, want_norm=True)])
+    rowptr, col, perm = csr_oracle(ei, n_src, n_dst, loops)
+    n = int(rowptr[-1])
+    assert int(status.item()) == 0
+    assert torch.equal(csr.rowptr.cpu(), rowptr)
+    assert torch.equal(csr.col.cpu()[:n], col)
+    assert torch.equal(csr.perm.cpu()[:n], perm)
+    deg = (rowptr[1:] - rowptr[:-1]).float()
+    want = torch.where(deg > 0, deg.pow(-0.5), torch.zeros_like(deg))
+    assert torch.allclose(csr.inv_sqrt_deg.cpu()[:n_dst], want, rtol=1e-6, atol=0)
+
+
+def test_plan_many_relations_and_transpose():
+    g = torch.Generator().manual_seed(1)
+    specs, eis = [], []
+    for r in range(19):  # > HG_MAX_PLAN_RELATIONS: exercises chunking
+        ns, nd, E = 10 + 13 * r, 200 - 7 * r, 50 * r
+        ei = torch.stack([torch.randint(0, ns, (E,), generator=g), torch.randint(0, nd, (E,), generator=g)])
+        eis.append((ei, ns, nd))
+        specs.append(CSRSpec(ei.cuda(), ns, nd, False, want_perm=True, transpose=(r % 2 == 1)))
+    csrs, status = ops.build_csr(specs)
+    assert int(status.item()) == 0
+    for r, (csr, (ei, ns, nd)) in enumerate(zip(csrs, eis)):
+        if r % 2 == 1:
+            ei, ns, nd = ei.flip(0), nd, ns
+        rowptr, col, perm = csr_oracle(ei, ns, nd, False)
+        n = int(rowptr[-1])
+        assert torch.equal(csr.rowptr.cpu(), rowptr) and torch.equal(csr.col.cpu()[:n], col)
+        assert torch.equal(csr.perm.cpu()[:n], perm)
+
+
+def test_plan_out_of_range_edges_are_skipped_and_counted():
+    ei = torch.tensor([[0, 1, 99, 2, -1], [1, 2, 0, 77, 0]])
+    (csr,), status = ops.build_csr([CSRSpec(ei.cuda(), 3, 3, False, want_perm=True)])
+    assert int(status.item()) == 3
+    assert csr.rowptr.cpu().tolist() == [0, 0, 1, 2]
+    assert csr.col.cpu()[:2].tolist() == [0, 1]
+
+
+# ------------------------------------------------------------------------------ K2 / K5
+@pytest.mark.parametrize("F", [1, 3, 6, 26, 64, 78, 128, 306, 768, 1100])
+@pytest.mark.parametrize("op", ["sum", "mean", "max"])
+def test_seg_reduce(F, op):
+    g = torch.Generator().manual_seed(F)
+    n_src, n_dst, E = 301, 257, 2000
+    ei = torch.stack([torch.randint(0, n_src, (E,), generator=g), torch.randint(0, n_dst - 40, (E,), generator=g)])
+    x = torch.randn(n_src, F, generator=g)
+    (csr,), _ = ops.build_csr([CSRSpec(ei.cuda(), n_src, n_dst)])
+    got = ops.seg_reduce(x.cuda(), csr, op)
+    want = ou.scatter(x.double()[ei[0]], ei[1], 0, dim_size=n_dst, reduce=op)
+    assert_close(got, want, f"seg_reduce {op} F={F}", check_argmax=False)
+
+
+def test_seg_reduce_epilogue_and_row_map():
+    g = torch.Generator().manual_seed(3)
+    n, E, F = 500, 3000, 96
+    ei = torch.stack([torch.randint(0, n, (E,), generator=g), torch.randint(0, n, (E,), generator=g)])
+    x, xs = torch.randn(n, F, generator=g), torch.randn(n, F, generator=g)
+    ss, ds = torch.rand(n, generator=g), torch.rand(n, generator=g)
+    bias, eps = torch.randn(F, generator=g), torch.tensor([0.3])
+    rows = torch.randperm(n, generator=g)[:77].int()
+    (csr,), _ = ops.build_csr([CSRSpec(ei.cuda(), n, n)])
+    got = ops.seg_reduce(x.cuda(), csr, "sum", src_scale=ss.cuda(), dst_scale=ds.cuda(), row_map=rows.cuda(),
+                         x_self=xs.cuda(), self_coef=eps.cuda(), self_coef_add=1.0, bias=bias.cuda(), act="relu")
+    agg = ou.scatter((ss[ei[0]].unsqueeze(1) * x[ei[0]]).double(), ei[1], 0, dim_size=n, reduce="sum")
+    want = torch.relu(ds.unsqueeze(1).double() * agg + 1.3 * xs.double() + bias.double())[rows.long()]
+    assert_close(got, want, "seg_reduce epilogue", check_argmax=False)
+
+
+def test_seg_reduce_strided_views():
+    g = torch.Generator().manual_seed(4)
+    n, E = 300, 1500
+    ei = torch.stack([torch.randint(0, n, (E,), generator=g), torch.randint(0, n, (E,), generator=g)])
+    Y = torch.randn(n, 256, generator=g)
+    (csr,), _ = ops.build_csr([CSRSpec(ei.cuda(), n, n)])
+    Yc = Y.cuda()
+    got = ops.seg_reduce(Yc[:, :128], csr, "mean", x_self=Yc[:, 128:], self_coef_add=1.0)
+    want = ou.scatter(Y[:, :128].double()[ei[0]], ei[1], 0, dim_size=n, reduce="mean") + Y[:, 128:].double()
+    assert_close(got, want, "strided", check_argmax=False)
+
+
+# ------------------------------------------------------------------------------ K6
+SHAPES = [(1000, 396, [306]), (777, 84, [64]), (129, 16, [6]), (5000, 396, [64]), (2048, 128, [128, 128]),
+          (600, 35, [6, 6, 6]), (513, 300, [306]), (4096, 768, [768])]
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32x3"])
+@pytest.mark.parametrize("M,N,Ks", SHAPES)
+def test_linear(M, N, Ks, precision):
+    g = torch.Generator().manual_seed(M + N)
+    segs = [(torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / K ** 0.5) for K in Ks]
+    bias = torch.randn(N, generator=g)
+    got = ops.linear([(x.cuda(), w.cuda()) for x, w in segs], N, bias=bias.cuda(), precision=precision)
+    want = sum(x.double() @ w.double().t() for x, w in segs) + bias.double()
+    torch.cuda.synchronize()
+    # tf32x3: the tensor core truncates on accumulate (~1 ulp of the accumulator per K=8 MMA)
+    tol = 2e-5 if precision == "fp32" else 2e-5 + 2e-8 * sum(Ks)
+    assert_close(got, want, f"linear {precision} M={M} N={N} K={Ks}", rtol=tol, atol=tol, check_argmax=False)
+    err = (got.double().cpu() - want).abs().max().item()
+    print(f"linear {precision} M={M} N={N} K={Ks}: max abs err {err:.2e}")
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32x3"])
+def test_linear_epilogue_strided(precision):
+    g = torch.Generator().manual_seed(9)
+    M, N, K = 700, 100, 306
+    xfull = torch.randn(M, 400, generator=g)
+    x = xfull[:, 3:3 + K]  # odd offset: rows only 4-byte aligned -> scalar load path
+    w, bias = torch.randn(N, K, generator=g) / K ** 0.5, torch.randn(N, generator=g)
+    scale, shift = torch.rand(N, generator=g) + 0.5, torch.randn(N, generator=g)
+    out = torch.zeros(M, 128, device="cuda")
+    ops.linear([(xfull.cuda()[:, 3:3 + K], w.cuda())], N, bias=bias.cuda(), scale=scale.cuda(), shift=shift.cuda(),
+               act="elu", precision=precision, out=out[:, 4:4 + N])
+    want = torch.nn.functional.elu((x.double() @ w.double().t() + bias.double()) * scale.double() + shift.double())
+    assert_close(out[:, 4:4 + N], want, "linear epilogue", rtol=2e-5, atol=2e-5, check_argmax=False)
+    assert float(out[:, :4].abs().max()) == 0 and float(out[:, 4 + N:].abs().max()) == 0
+
+
+def test_gather_rows():
+    x = torch.randn(100, 37)
+    idx = torch.tensor([5, 99, 0, 5], dtype=torch.int32)
+    got = ops.gather_rows(x.cuda(), idx.cuda(), act="relu")
+    assert torch.equal(got.cpu(), torch.relu(x[idx.long()]))
