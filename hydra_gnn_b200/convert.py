@@ -1,0 +1,113 @@
+"""Heterogeneous -> homogeneous graph conversions (integer index work, bit-exact with the reference).
+
+Host-side mirror of ``heterogeneous_data_to_homogeneous`` (mp3d_dataset.py:29-69) and
+``heterogeneous_htree_to_homogeneous`` (mp3d_dataset.py:72-119), which the reference applies to
+every graph when ``network.type == homogeneous`` (scripts/train_mp3d.py:134-135;
+bin/room_classification_server:259-260).  The underlying ``HeteroData.to_homogeneous`` rule
+(SURVEY.md section 9.7): nodes concatenated in node-type order, edges concatenated in edge-type
+order with the per-type node offsets added, a ``node_type`` vector attached.
+
+These are data-format functions (they run wherever the tensors live, like the reference's);
+they are not part of the timed forward.
+"""
+from __future__ import annotations
+
+from typing import List, Tuple
+
+import torch
+
+from .data import Data, HeteroData
+
+
+def to_homogeneous(data: HeteroData, add_edge_type: bool = False) -> Data:
+    """PyG ``HeteroData.to_homogeneous(add_edge_type=...)`` for stores whose attributes agree."""
+    node_types = data.node_types
+    offsets, cum = {}, 0
+    for t in node_types:
+        offsets[t] = cum
+        cum += int(data[t].num_nodes)
+    out = Data()
+    eis, ets = [], []
+    for k, et in enumerate(data.edge_types):
+        if "edge_index" not in data[et]:
+            continue
+        ei = data[et].edge_index.long().clone()
+        ei[0] += offsets[et[0]]
+        ei[1] += offsets[et[2]]
+        eis.append(ei)
+        ets.append(torch.full((ei.size(1),), k, dtype=torch.long, device=ei.device))
+    if eis:
+        out.edge_index = torch.cat(eis, dim=1)
+    # node attributes present in EVERY node store with matching trailing shape
+    first = data[node_types[0]]
+    for key, v in first.items():
+        if not torch.is_tensor(v) or v.dim() < 1 or key in ("batch", "ptr"):
+            continue
+        vals = []
+        for t in node_types:
+            w = data[t].get(key)
+            if not torch.is_tensor(w) or w.shape[1:] != v.shape[1:]:
+                vals = None
+                break
+            vals.append(w)
+        if vals is not None:
+            out[key] = torch.cat(vals, dim=0)
+    edge_stores = [data[et] for et in data.edge_types if "edge_index" in data[et]]
+    if edge_stores and all("edge_attr" in s for s in edge_stores):
+        out.edge_attr = torch.cat([s.edge_attr for s in edge_stores], dim=0)
+    sizes = torch.tensor([int(data[t].num_nodes) for t in node_types], dtype=torch.long)
+    out.node_type = torch.arange(len(node_types)).repeat_interleave(sizes)
+    if "x" in out:
+        out.node_type = out.node_type.to(out.x.device)
+    if add_edge_type and eis:
+        out.edge_type = torch.cat(ets)
+    return out
+
+
+def heterogeneous_data_to_homogeneous(data: HeteroData) -> Tuple[Data, List[str]]:
+    """mp3d_dataset.py:29-69 (``removed_edge_type=None`` branch): zero-pad every node type's features
+    to the widest one, then ``to_homogeneous``.  Returns ``(data, node_types)``; the caller adds
+    ``room_mask = node_type == node_types.index("rooms")`` (mp3d_dataset.py:346-348)."""
+    width = max(int(data[t].num_node_features) for t in data.x_dict)
+    for t in data.x_dict:
+        x = data[t].x
+        if x.size(0) == 0:
+            data[t].x = torch.empty((0, width), dtype=x.dtype, device=x.device)
+        else:
+            data[t].x = torch.nn.functional.pad(x, (0, width - x.size(1), 0, 0), mode="constant", value=0)
+    node_types = list(data.x_dict.keys())
+    return to_homogeneous(data, add_edge_type=False), node_types
+
+
+def dsg_to_homogeneous(data: HeteroData) -> Data:
+    """``Hydra_mp3d_data.to_homogeneous`` (mp3d_dataset.py:339-348): conversion + ``room_mask``."""
+    out, node_types = heterogeneous_data_to_homogeneous(data)
+    out.room_mask = out.node_type == node_types.index("rooms")
+    return out
+
+
+def heterogeneous_htree_to_homogeneous(data: HeteroData) -> Data:
+    """mp3d_dataset.py:72-119: flat augmented H-tree with ``init_edge_index`` (source is a virtual
+    node), ``pool_edge_index`` (target is a virtual node), the remaining tree edges in
+    ``edge_index``, and ``room_mask`` / ``object_mask`` marking the virtual (classification) nodes."""
+    assert "object_virtual" in data.x_dict and "room_virtual" in data.x_dict
+    if "y" in data["room_virtual"]:
+        y = data["room_virtual"].y
+        for t in data.x_dict:
+            if "y" not in data[t]:
+                data[t].y = -torch.ones(int(data[t].num_nodes), dtype=y.dtype, device=y.device)
+    out, node_types = heterogeneous_data_to_homogeneous(data)
+    ov, rv = node_types.index("object_virtual"), node_types.index("room_virtual")
+    src_t = out.node_type[out.edge_index[0]]
+    dst_t = out.node_type[out.edge_index[1]]
+    init = (src_t == ov) | (src_t == rv)
+    pool = (dst_t == ov) | (dst_t == rv)
+    out.init_edge_index = out.edge_index[:, init]
+    out.pool_edge_index = out.edge_index[:, pool]
+    tree = ~(init | pool)
+    if "edge_attr" in out:
+        out.edge_attr = out.edge_attr[tree, :]
+    out.edge_index = out.edge_index[:, tree]
+    out.room_mask = out.node_type == rv
+    out.object_mask = out.node_type == ov
+    return out

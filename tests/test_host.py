@@ -1,0 +1,228 @@
+"""CPU tests of the host side (no GPU, no compute calls into the library): the C-ABI library
+loads and exports every symbol include/hydra_gnn_b200.h declares; containers / collate /
+hetero->homogeneous conversions are bit-exact with the reference's (committed golden, made by
+the reference's own functions); the synthetic generator is shard-invariant; weight packing
+algebra; the product fails loudly without a GPU; world_size-2 gloo run of the sharding path."""
+import os
+import re
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+import cases  # noqa: E402
+import hydra_gnn_b200 as hg  # noqa: E402
+from hydra_gnn_b200 import _lib, convert, synth  # noqa: E402
+from hydra_gnn_b200 import dist as hdist  # noqa: E402
+from hydra_gnn_b200 import nn as hnn  # noqa: E402
+from hydra_gnn_b200.data import Batch, HeteroData  # noqa: E402
+from oracle import models as om  # noqa: E402
+from oracle.pyg import data as od  # noqa: E402
+
+
+# ------------------------------------------------------------------------------ C ABI
+def test_library_exports_every_declared_symbol():
+    header = open(os.path.join(ROOT, "include", "hydra_gnn_b200.h")).read()
+    declared = set(re.findall(r"HG_API\s+[\w\s\*]+?\b(hg_\w+)\s*\(", header))
+    assert len(declared) >= 14
+    assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
+    h = _lib.load_shared_object()  # dlopen, prototypes, struct-size check
+    for name in declared:
+        assert hasattr(h, name)
+    assert h.hg_abi_version() == 1
+    assert h.hg_strerror(0) == b"ok" and b"workspace" in h.hg_strerror(-3)
+    for which, st in enumerate(_lib._STRUCTS):
+        import ctypes
+
+        assert h.hg_sizeof(which) == ctypes.sizeof(st)
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_product_fails_loudly_without_gpu():
+    net = hg.HeterogeneousNetwork(**cases.CASES["mgat"][1]).eval()
+    with pytest.raises(RuntimeError, match="CUDA"):
+        net(synth.synth_mp3d_batch(range(2)))
+
+
+def test_product_never_imports_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "hydra_gnn_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
+
+
+# ------------------------------------------------------------------------------ containers
+def _to_od(g):
+    h = od.HeteroData()
+    for nt in g.node_types:
+        for k, v in g[nt].items():
+            h[nt][k] = v
+    for et in g.edge_types:
+        for k, v in g[et].items():
+            h[et][k] = v
+    return h
+
+
+def test_batch_collate_bit_exact_with_pyg_rule():
+    graphs = [synth.synth_mp3d_batch([gid], relative_pos=True) for gid in (3, 0, 7)]
+    ours = Batch.from_data_list(graphs)
+    want = od.Batch.from_data_list([_to_od(g) for g in graphs])
+    for nt in ("objects", "rooms"):
+        assert torch.equal(ours[nt].x, want[nt].x) and torch.equal(ours[nt].batch, want[nt].batch)
+    for et in ours.edge_types:
+        assert ours[et].edge_index.dtype == torch.int64
+        assert torch.equal(ours[et].edge_index, want[et].edge_index)
+        assert torch.equal(ours[et].edge_attr, want[et].edge_attr)
+    # a batch generated in one go is the same disjoint union
+    whole = synth.synth_mp3d_batch([3, 0, 7], relative_pos=True)
+    for et in ours.edge_types:
+        assert torch.equal(ours[et].edge_index, whole[et].edge_index)
+    assert torch.equal(ours["objects"].x, whole["objects"].x)
+
+
+def test_homogeneous_batch_offsets_index_attributes():
+    trees = cases.load_htrees("htree_synth")[:3]
+    homs = [convert.heterogeneous_htree_to_homogeneous(t) for t in trees]
+    b = Batch.from_data_list(homs)
+    off = 0
+    for h in homs:
+        n = h.x.size(0)
+        for key in ("edge_index", "init_edge_index", "pool_edge_index"):
+            sel = (b[key][0] >= off) & (b[key][0] < off + n)
+            assert torch.equal(b[key][:, sel] - off, h[key])
+        off += n
+    assert b.room_mask.sum() == sum(int(h.room_mask.sum()) for h in homs)
+
+
+def test_convert_bit_exact_with_reference_functions():
+    z = np.load(os.path.join(ROOT, "tests", "golden", "convert_golden.npz"))
+    for k, t in enumerate(cases.load_htrees("htree_synth")[:3]):
+        hom = convert.heterogeneous_htree_to_homogeneous(t)
+        for key in ("edge_index", "init_edge_index", "pool_edge_index", "room_mask", "object_mask", "node_type"):
+            assert np.array_equal(hom[key].numpy(), z[f"htree{k}|{key}"]), (k, key)
+        assert np.allclose(hom.x.double().sum(0).numpy(), z[f"htree{k}|x_sum"], rtol=0, atol=0)
+        assert hom.x.size(1) == 306
+    for k, gid in enumerate([0, 3]):
+        hom, types = convert.heterogeneous_data_to_homogeneous(synth.synth_mp3d_batch([gid]))
+        assert types == ["objects", "rooms"]
+        assert np.array_equal(hom.edge_index.numpy(), z[f"dsg{k}|edge_index"])
+        assert np.array_equal(hom.node_type.numpy(), z[f"dsg{k}|node_type"])
+        assert np.array_equal(hom.x.double().sum(0).numpy(), z[f"dsg{k}|x_sum"])
+
+
+def test_fill_missing_edge_index_rule_of_the_stanford_loader():
+    """tests/test_mp3d_dataset.py:143-180 of the reference: missing rooms_to_rooms -> empty [2,0] int64;
+    missing objects_to_rooms -> rooms_to_objects.flip([0])."""
+    g = cases.stanford_hetero(cases.load_stanford()[5])
+    rr = g["rooms", "rooms_to_rooms", "rooms"].edge_index
+    assert rr.shape == (2, 0) and rr.dtype == torch.int64
+    assert torch.equal(g["objects", "objects_to_rooms", "rooms"].edge_index,
+                       g["rooms", "rooms_to_objects", "objects"].edge_index.flip([0]))
+    assert hg.schema.EDGE_TYPES == list(g.edge_types)
+
+
+def test_htree_fixture_invariants():
+    for t in cases.load_htrees("htree_synth") + cases.load_htrees("htree_stanford"):
+        n_leaf, n_rv = t["room"].x.size(0), t["room_virtual"].x.size(0)
+        pool = t["room", "r_to_rv", "room_virtual"].edge_index
+        assert pool.size(1) == n_leaf and n_rv <= n_leaf and int(pool[1].max()) < n_rv
+        assert torch.equal(pool[0].sort().values, torch.arange(n_leaf))  # every leaf pools exactly once
+        for s, r, d in hg.schema.HTREE_EDGE_TYPES:  # tree relations come in mirrored pairs
+            ei = t[s, r, d].edge_index
+            assert ei.size(1) == 0 or (int(ei[0].max()) < t[s].x.size(0) and int(ei[1].max()) < t[d].x.size(0))
+
+
+# ------------------------------------------------------------------------------ generator
+def test_synth_is_shard_invariant_and_shaped_like_mp3d():
+    whole = synth.synth_mp3d_batch(range(64))
+    lo, hi = hdist.shard_range(64, 1, 4)
+    part = synth.synth_mp3d_batch(range(lo, hi))
+    first = int((whole["objects"].batch < lo).sum())
+    n = part["objects"].x.size(0)
+    assert torch.equal(whole["objects"].x[first:first + n], part["objects"].x)
+    G = 64
+    assert 3.5 < whole["rooms"].x.size(0) / G < 6.5 and 40 < whole["objects"].x.size(0) / G < 80
+    oo = whole["objects", "objects_to_objects", "objects"].edge_index
+    assert not bool((oo[0] == oo[1]).any())
+    assert not bool((oo[1][1:] >= oo[1][:-1]).all()), "edges must arrive unsorted by destination"
+    assert whole["objects"].x.shape[1] == 306 and whole["rooms"].x.shape[1] == 6
+
+
+def test_shard_ranges_partition_the_ids():
+    for n, w in [(10, 3), (1_000_000, 8), (5, 8), (4096, 1)]:
+        spans = [hdist.shard_range(n, r, w) for r in range(w)]
+        assert spans[0][0] == 0 and spans[-1][1] == n
+        assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+        assert max(h - l for l, h in spans) - min(h - l for l, h in spans) <= 1
+
+
+# ------------------------------------------------------------------------------ packing algebra / names
+def test_attention_fold_equals_projection_then_dot():
+    g = torch.Generator().manual_seed(0)
+    H, C, K = 3, 8, 11
+    W, att, x = torch.randn(H * C, K, generator=g), torch.randn(1, H, C, generator=g), torch.randn(5, K, generator=g)
+    want = ((x @ W.t()).view(-1, H, C) * att).sum(-1)
+    got = x @ hnn.GATConv.fold(att, W, H, C).t()
+    assert torch.allclose(got, want, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("case", list(cases.CASES))
+def test_product_state_dict_interchanges_with_reference_names(case):
+    cls, kw, _ = cases.CASES[case]
+    ref_sd = cases.build_model(om, case).state_dict()
+    net = getattr(hg, cls)(**kw)
+    assert list(net.state_dict().keys()) == list(ref_sd.keys())
+    net.load_state_dict(ref_sd, strict=True)
+    for k, v in net.state_dict().items():
+        assert v.shape == ref_sd[k].shape, k
+
+
+# ------------------------------------------------------------------------------ world_size 2 (gloo)
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _gloo_worker(rank, world, port, n_graphs, out):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        lo, hi = hdist.shard_range(n_graphs, rank, world)
+        data = synth.synth_mp3d_batch(range(lo, hi), with_word2vec=False)
+        rooms = data["rooms"].x
+        # stand-in for the per-rank forward (the CUDA path needs a GPU): a fixed linear map of the room rows
+        logits = torch.cat([rooms, rooms.sum(1, keepdim=True)], dim=1)
+        gather = hdist.LogitGather(7).prepare(logits.size(0), logits.device)
+        gather(logits)
+        if rank == 0:
+            out.put((gather.counts, gather.unpad().clone()))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_world2_shard_and_gather_equals_single_process():
+    n_graphs, world = 13, 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gloo_worker, args=(r, world, port, n_graphs, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    counts, gathered = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    rooms = synth.synth_mp3d_batch(range(n_graphs), with_word2vec=False)["rooms"].x
+    want = torch.cat([rooms, rooms.sum(1, keepdim=True)], dim=1)
+    assert sum(counts) == want.size(0)
+    assert torch.equal(gathered, want)
