@@ -354,7 +354,8 @@ extern "C" int hg_gat_fused(const hg_gat_args* a, void* stream_) {
     const int F = a->H * a->C;
     for (int r = 0; r < a->n_rel; ++r) {
         const hg_gat_rel& R = a->rel[r];
-        if (!R.xs || !R.a_src || !R.a_dst || !R.rowptr || !R.col) return HG_EINVAL;
+        // xs / a_src may be NULL only for an empty source set (every row of that relation is then empty)
+        if (!R.a_dst || !R.rowptr || !R.col) return HG_EINVAL;
     }
     // Widest vector that divides C (a chunk must not straddle two heads) and fits all alignments;
     // prefer the widest one that still gives every lane of the first chunk work.

@@ -161,7 +161,8 @@ extern "C" int hg_seg_reduce(const hg_seg_args* a, void* stream_) {
     if (!a) return HG_EINVAL;
     if (a->n_out < 0 || a->F < 0) return HG_EINVAL;
     if (a->n_out == 0 || a->F == 0) return HG_OK;
-    if (!a->x || !a->rowptr || !a->out) return HG_EINVAL;
+    // x may be NULL only for an empty source set (n_src == 0): every row is then empty and x is never read
+    if (!a->rowptr || !a->out) return HG_EINVAL;
     if (a->op < HG_REDUCE_SUM || a->op > HG_REDUCE_MAX) return HG_EINVAL;
     if (a->act < HG_ACT_NONE || a->act > HG_ACT_ELU) return HG_EINVAL;
 

@@ -115,7 +115,9 @@ HG_API int hg_plan_build(const hg_plan_rel* rels_host, int n_rel, int32_t* statu
  * GINConv (sum + (1+eps) x_i, :18-26; self_coef_ptr = eps, self_coef_add = 1),
  * and LeafPool (mean; heterogeneous_neural_tree_network.py:18-31,181-185;
  * homogeneous_neural_tree_network.py:100 with row_map = indices of room_mask).
- * Empty rows reduce to 0 (PyG semantics) before the self / bias terms.
+ * Empty rows reduce to 0 (PyG semantics) before the self / bias terms.  `x` may be NULL only when the
+ * source set is empty (n_src == 0: every row is empty and x is never read); the same holds for
+ * `xs` / `a_src` of hg_gat_fused.
  * ---------------------------------------------------------------------------------- */
 typedef struct hg_seg_args {
     const float* x;  int64_t ldx;          /* [n_src, F] gathered operand */
