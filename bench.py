@@ -110,9 +110,9 @@ def algorithmic(name: str, m: dict):
             b += 4 * m["n_out"] * m["F"]
         return b, 0
     if name == "hg_gat_fused":
-        b = 4 * m["n_dst"] * m["width"]
+        b = 4 * m["n_dst"] * m["width"] * (2 if m.get("addend") else 1)
         for r in m["rels"]:
-            b += 4 * r["n_src"] * m["H"] * m["C"] + 4 * r["n_src"] * m["H"] + 4 * m["n_dst"] * m["H"]
+            b += 4 * r["n_src"] * m.get("src_width", m["H"] * m["C"]) + 4 * r["n_src"] * m["H"] + 4 * m["n_dst"] * m["H"]
             b += 4 * (m["n_dst"] + 1) + 4 * r["cap"] + (4 * r["cap"] * m["H"] if r["edge"] else 0)
         return b, 0
     if name == "hg_linear":

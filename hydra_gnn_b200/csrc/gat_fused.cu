@@ -1,19 +1,25 @@
-// K3 + K4 -- fused GAT for one destination node type.
+// K3 + K4 -- fused GAT for one destination node type (v3).
 //
-// A CTA owns a tile of kTile CONSECUTIVE destination rows (consecutive rows belong to the same
-// scene graph, so their neighbour sets overlap and the gathers of one tile hit L1/L2).  Per tile:
-//   stage   every relation's rowptr slice, neighbour ids, source logits a_src[j,h](+a_edge) and the
-//           tile's destination logits go to shared memory in bulk-parallel sweeps (all 256 threads,
-//           coalesced on col) -- this removes the rowptr -> col -> a_src dependent-load chain from
-//           the per-row critical path;
-//   row     one warp per row: per relation, lanes = edges turn the staged logits into softmax
-//           weights in place (leaky-relu, max, exp, sum + 1e-16), then lanes = feature chunks sweep
-//           the staged edges, each lane gathering its K vector chunks of xs[j] (128-bit loads when the
-//           width allows, U rows in flight) and accumulating in registers;
-//   out     head concat / head mean (through a shared-memory row) + bias_r into the cross-relation
-//           total; after the last relation: group mean, ELU/ReLU, ONE store.
+// A CTA owns a tile of consecutive destination rows (consecutive rows belong to the same scene
+// graph, so their neighbour sets overlap and the gathers of a tile hit L1/L2).  Per tile:
+//   stage    rowptr slices, destination logits, then -- threads = edges, coalesced on col -- the
+//            neighbour ids, the tile-local row of every edge and the raw logits a_src[j,h](+a_edge)
+//            of every relation go to shared memory;
+//   softmax  threads = (relation, row, head): max and 1/(sum + 1e-16) of the row; then threads =
+//            edges turn the staged logits into softmax weights in place.  No warp shuffles, no
+//            idle lanes on short rows (mean in-degree of a scene graph is ~5);
+//   gather   threads = (row, output chunk): TPR threads cooperate on a row, each owning KC vector
+//            chunks of the OUTPUT row.  For head-mean the thread walks the H head slices of xs[j]
+//            itself, so the head reduction never leaves registers; the weights of an edge are one
+//            broadcast LDS.128.  Relations are summed in the same registers;
+//   out      + summed biases (+ addend), group mean, ELU/ReLU, ONE vector store per chunk.
 // No atomics, no read-modify-write across relations, no separate softmax / stack+sum / activation
-// passes.  Rows whose tile does not fit the staging buffer (hub nodes) take a direct-from-global path.
+// passes.  Tiles whose edges do not fit the staging buffers (hub nodes) take a warp-per-row path
+// that streams from global memory.
+//
+// src_shared = 1 is the aggregate-first form: xs is [n_src, C] (ONE row shared by all heads) and the
+// output is [n_dst, H*C] with out[i, h, :] = sum_e w_eh xs[j, :]; the projection is applied afterwards
+// to the aggregated rows (used when a relation has far fewer destinations than sources).
 #include "hg_common.cuh"
 
 namespace hg {
@@ -21,64 +27,160 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / kWarp;
-constexpr int kTile = 32;  // max destination rows per CTA tile (4 per warp); fewer when n_dst is small
 constexpr int kMaxHeads = 8;
+constexpr int kMaxTile = 64;
 
 struct GatParams {
     hg_gat_args a;
     int32_t cap;        // staged edges per relation per tile (multiple of 32)
-    int32_t tile_rows;  // destination rows per tile: 8, 16 or 32
+    int32_t tile_rows;  // destination rows per tile (<= kMaxTile)
+    int32_t hs;         // padded head stride of the weight rows in shared memory: 4 or 8
+    int32_t f_begin;    // first OUTPUT column of this launch (wide rows are split over launches)
+    int32_t f_count;    // output columns of this launch
 };
 
 __device__ __forceinline__ float leaky(float v, float slope) { return v > 0.f ? v : v * slope; }
 
-template <int VEC, int K>
-__global__ void __launch_bounds__(kThreads, 3) k_gat_fused(const __grid_constant__ GatParams P) {
-    constexpr int U = (K * VEC >= 16) ? 2 : 4;
+struct Smem {
+    int32_t* rp;     // [R][kMaxTile + 1]
+    float* ad;       // [R][kMaxTile][H]
+    float* mx;       // [R][kMaxTile][H]   row max
+    float* inv;      // [R][kMaxTile][H]   1 / (row sum + 1e-16)
+    int32_t* col;    // [R][cap]
+    float* w;        // [R][cap][hs]       logits -> weights
+    uint16_t* erow;  // [R][cap]           tile-local row of the edge
+};
+
+__host__ __device__ inline size_t smem_bytes(int R, int H, int cap, int hs) {
+    size_t words = static_cast<size_t>(R) * (kMaxTile + 1) + 3 * static_cast<size_t>(R) * kMaxTile * H +
+                   static_cast<size_t>(R) * cap + static_cast<size_t>(R) * cap * hs;
+    words = (words + 3) / 4 * 4;
+    return words * 4 + static_cast<size_t>(R) * cap * 2 + 16;
+}
+
+__device__ __forceinline__ Smem carve(uint8_t* raw, int R, int H, int cap, int hs) {
+    Smem s;
+    float* p = reinterpret_cast<float*>(raw);
+    s.w = p;                      p += static_cast<size_t>(R) * cap * hs;   // first: 16-byte aligned rows
+    s.col = reinterpret_cast<int32_t*>(p);  p += static_cast<size_t>(R) * cap;
+    s.rp = reinterpret_cast<int32_t*>(p);   p += R * (kMaxTile + 1);
+    s.ad = p;                     p += R * kMaxTile * H;
+    s.mx = p;                     p += R * kMaxTile * H;
+    s.inv = p;                    p += R * kMaxTile * H;
+    s.erow = reinterpret_cast<uint16_t*>(p);
+    return s;
+}
+
+// Hub path: one warp per row, lanes = output chunks, everything streamed from global memory.
+template <int VEC>
+__device__ __noinline__ void slow_row(const GatParams& P, int64_t i, int lane) {
+    const hg_gat_args& A = P.a;
+    const int H = A.H, C = A.C, R = A.n_rel;
+    const bool head_mean = !A.concat && !A.src_shared;
+    const int nco = P.f_count / VEC;
+    const float gscale = (A.group == HG_GROUP_MEAN) ? 1.f / static_cast<float>(R) : 1.f;
+    for (int oc0 = 0; oc0 < nco; oc0 += 32) {
+        const int oc = oc0 + lane;
+        const bool live = oc < nco;
+        const int f = P.f_begin + oc * VEC;  // output column
+        float acc[VEC];
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) acc[v] = 0.f;
+        for (int r = 0; r < R; ++r) {
+            const hg_gat_rel& Rl = A.rel[r];
+            const int32_t beg = __ldg(Rl.rowptr + i), end = __ldg(Rl.rowptr + i + 1);
+            if (end <= beg) continue;
+            const int h_lo = head_mean ? 0 : (live ? f / C : 0);
+            const int h_hi = head_mean ? H : h_lo + 1;
+            for (int h = h_lo; h < h_hi; ++h) {
+                const float ad = __ldg(Rl.a_dst + i * Rl.lda_dst + h);
+                float m = -INFINITY, l = 0.f;
+                for (int32_t e = beg; e < end; ++e) {
+                    float sc = __ldg(Rl.a_src + static_cast<int64_t>(__ldg(Rl.col + e)) * Rl.lda_src + h) + ad;
+                    if (Rl.a_edge) sc += __ldg(Rl.a_edge + static_cast<int64_t>(e) * H + h);
+                    m = fmaxf(m, leaky(sc, A.neg_slope));
+                }
+                for (int32_t e = beg; e < end; ++e) {
+                    float sc = __ldg(Rl.a_src + static_cast<int64_t>(__ldg(Rl.col + e)) * Rl.lda_src + h) + ad;
+                    if (Rl.a_edge) sc += __ldg(Rl.a_edge + static_cast<int64_t>(e) * H + h);
+                    l += __expf(leaky(sc, A.neg_slope) - m);
+                }
+                const float inv = 1.f / (l + 1e-16f);
+                const int src_f = head_mean ? h * C + f : (A.src_shared ? f % C : f);
+                for (int32_t e = beg; e < end; ++e) {
+                    const int32_t j = __ldg(Rl.col + e);
+                    float sc = __ldg(Rl.a_src + static_cast<int64_t>(j) * Rl.lda_src + h) + ad;
+                    if (Rl.a_edge) sc += __ldg(Rl.a_edge + static_cast<int64_t>(e) * H + h);
+                    const float w = __expf(leaky(sc, A.neg_slope) - m) * inv;
+                    if (A.alpha_saved[r] && (head_mean ? (lane == 0 && oc0 == 0 && P.f_begin == 0) : (live && f % C == 0)))
+                        A.alpha_saved[r][static_cast<int64_t>(e) * H + h] = w;
+                    if (live) {
+                        float val[VEC];
+                        ldg_vec<VEC>(Rl.xs + static_cast<int64_t>(j) * Rl.ldxs + src_f, val);
+#pragma unroll
+                        for (int v = 0; v < VEC; ++v) acc[v] = fmaf(w, val[v], acc[v]);
+                    }
+                }
+            }
+        }
+        if (!live) continue;
+        const float hscale = head_mean ? 1.f / static_cast<float>(H) : 1.f;
+        float o[VEC];
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) o[v] = acc[v] * hscale;
+        for (int r = 0; r < R; ++r)
+            if (A.rel[r].bias) {
+#pragma unroll
+                for (int v = 0; v < VEC; ++v) o[v] += __ldg(A.rel[r].bias + f + v);
+            }
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) o[v] *= gscale;
+        if (A.addend) {
+#pragma unroll
+            for (int v = 0; v < VEC; ++v) o[v] += __ldg(A.addend + i * A.ldadd + f + v);
+        }
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) o[v] = apply_act(o[v], A.act);
+        st_vec<VEC>(A.out + i * A.ldout + f, o);
+    }
+}
+
+template <int VEC, int TPR, int KC>
+__global__ void __launch_bounds__(kThreads, (KC <= 2 ? 3 : 2)) k_gat_fused(const __grid_constant__ GatParams P) {
     extern __shared__ __align__(16) uint8_t s_raw[];
     const hg_gat_args& A = P.a;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int H = A.H, C = A.C, F = H * C, R = A.n_rel, cap = P.cap;
-    const int nc = F / VEC;
-    const int nco = (A.concat ? F : C) / VEC;  // output vector chunks
-    const bool head_mean = !(A.concat || H == 1);
-
-    // shared-memory carve-up (all 4-byte items; sizes in words)
-    float* s_stage = reinterpret_cast<float*>(s_raw);                   // [kWarps][F]   head-mean staging (16 B aligned)
-    int32_t* s_rp = reinterpret_cast<int32_t*>(s_stage + kWarps * F);   // [R][kTile + 1]
-    int32_t* s_col = s_rp + R * (kTile + 1);                            // [R][cap]
-    float* s_p = reinterpret_cast<float*>(s_col + R * cap);             // [R][H][cap]  logits -> weights
-    float* s_ad = s_p + static_cast<size_t>(R) * H * cap;               // [R][kTile][H] destination logits
-
-    int hk[K];
-    bool valid[K];
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-        const int chunk = lane + 32 * k;
-        valid[k] = chunk < nc;
-        hk[k] = valid[k] ? (chunk * VEC) / C : 0;
-    }
-    float* stage = s_stage + warp * F;
+    const int H = A.H, C = A.C, R = A.n_rel, cap = P.cap, hs = P.hs;
+    const Smem S = carve(s_raw, R, H, cap, hs);
+    const int tid = threadIdx.x;
+    const bool head_mean = !A.concat && !A.src_shared;
+    const int nco = P.f_count / VEC;          // output chunks of this launch
+    constexpr int kGroups = kThreads / TPR;   // row groups working concurrently
+    const int q = tid % TPR, grp = tid / TPR;
     const int tile_rows = P.tile_rows;
     const int64_t n_tiles = ceil_div<int64_t>(A.n_dst, tile_rows);
+    const float gscale = (A.group == HG_GROUP_MEAN) ? 1.f / static_cast<float>(R) : 1.f;
+    const float hscale = head_mean ? 1.f / static_cast<float>(H) : 1.f;
 
-    // sum of the relations' biases for this lane's output chunks (added once per row)
-    float btot[K][VEC];
+    // per-thread constants of its KC output chunks
+    int fo[KC], fsrc[KC], hk[KC];
+    float btot[KC][VEC];
 #pragma unroll
-    for (int k = 0; k < K; ++k)
+    for (int k = 0; k < KC; ++k) {
+        const int oc = q + k * TPR;
+        const bool valid = oc < nco;
+        fo[k] = valid ? P.f_begin + oc * VEC : -1;
+        hk[k] = (valid && !head_mean) ? fo[k] / C : 0;
+        fsrc[k] = valid ? (A.src_shared ? fo[k] % C : fo[k]) : 0;
 #pragma unroll
         for (int v = 0; v < VEC; ++v) btot[k][v] = 0.f;
-    for (int r = 0; r < R; ++r) {
-        if (!A.rel[r].bias) continue;
+        if (valid)
+            for (int r = 0; r < R; ++r)
+                if (A.rel[r].bias) {
+                    float bv[VEC];
+                    ldg_vec<VEC>(A.rel[r].bias + fo[k], bv);
 #pragma unroll
-        for (int k = 0; k < K; ++k) {
-            const int chunk = lane + 32 * k;
-            if (chunk >= nco) continue;
-            float bv[VEC];
-            ldg_vec<VEC>(A.rel[r].bias + chunk * VEC, bv);
-#pragma unroll
-            for (int v = 0; v < VEC; ++v) btot[k][v] += bv[v];
-        }
+                    for (int v = 0; v < VEC; ++v) btot[k][v] += bv[v];
+                }
     }
 
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -86,258 +188,199 @@ __global__ void __launch_bounds__(kThreads, 3) k_gat_fused(const __grid_constant
         const int rows = (A.n_dst - t0 < tile_rows) ? static_cast<int>(A.n_dst - t0) : tile_rows;
 
         // ---- stage 1: rowptr slices + destination logits
-        for (int idx = threadIdx.x; idx < R * (kTile + 1); idx += kThreads) {
-            const int r = idx / (kTile + 1), t = idx % (kTile + 1);
-            s_rp[idx] = __ldg(A.rel[r].rowptr + t0 + min(t, rows));
+        for (int idx = tid; idx < R * (kMaxTile + 1); idx += kThreads) {
+            const int r = idx / (kMaxTile + 1), t = idx - r * (kMaxTile + 1);
+            S.rp[idx] = __ldg(A.rel[r].rowptr + t0 + min(t, rows));
         }
-        for (int r = 0; r < R; ++r)
-            for (int idx = threadIdx.x; idx < rows * H; idx += kThreads) {
-                const int t = idx / H, h = idx - t * H;
-                s_ad[r * kTile * H + idx] = __ldg(A.rel[r].a_dst + (t0 + t) * A.rel[r].lda_dst + h);
-            }
+        for (int idx = tid; idx < R * rows * H; idx += kThreads) {
+            const int r = idx / (rows * H), rem = idx - r * rows * H;
+            const int t = rem / H, h = rem - t * H;
+            S.ad[(r * kMaxTile + t) * H + h] = __ldg(A.rel[r].a_dst + (t0 + t) * A.rel[r].lda_dst + h);
+        }
         __syncthreads();
+        bool fits = true;
+        for (int r = 0; r < R; ++r) fits = fits && (S.rp[r * (kMaxTile + 1) + rows] - S.rp[r * (kMaxTile + 1)] <= cap);
+        if (!fits) {  // hub tile (uniform branch): warp per row straight from global memory
+            for (int t = tid >> 5; t < rows; t += kWarps) slow_row<VEC>(P, t0 + t, tid & 31);
+            __syncthreads();
+            continue;
+        }
 
-        // ---- stage 2: neighbour ids + source logits of every relation that fits
+        // ---- stage 2: neighbour ids, edge -> row map, raw logits (threads = edges)
         for (int r = 0; r < R; ++r) {
             const hg_gat_rel& Rl = A.rel[r];
-            const int32_t e0 = s_rp[r * (kTile + 1)], e1 = s_rp[r * (kTile + 1) + rows];
-            if (e1 - e0 > cap) continue;
-            for (int32_t e = e0 + threadIdx.x; e < e1; e += kThreads) {
-                const int32_t j = __ldg(Rl.col + e);
-                s_col[r * cap + (e - e0)] = j;
+            const int32_t* rp = S.rp + r * (kMaxTile + 1);
+            const int32_t e0 = rp[0], ne = rp[rows] - e0;
+            for (int e = tid; e < ne; e += kThreads) {
+                const int32_t j = __ldg(Rl.col + e0 + e);
+                S.col[r * cap + e] = j;
+                int lo = 0, hi = rows;  // row t with rp[t] <= e0 + e < rp[t + 1]
+                while (hi - lo > 1) {
+                    const int mid = (lo + hi) >> 1;
+                    if (rp[mid] <= e0 + e) lo = mid; else hi = mid;
+                }
+                S.erow[r * cap + e] = static_cast<uint16_t>(lo);
+                float* wrow = S.w + (static_cast<size_t>(r) * cap + e) * hs;
                 for (int h = 0; h < H; ++h) {
                     float s = __ldg(Rl.a_src + static_cast<int64_t>(j) * Rl.lda_src + h);
-                    if (Rl.a_edge) s += __ldg(Rl.a_edge + static_cast<int64_t>(e) * H + h);
-                    s_p[(r * H + h) * cap + (e - e0)] = s;
+                    if (Rl.a_edge) s += __ldg(Rl.a_edge + static_cast<int64_t>(e0 + e) * H + h);
+                    wrow[h] = s;
+                }
+                for (int h = H; h < hs; ++h) wrow[h] = 0.f;
+            }
+        }
+        __syncthreads();
+
+        // ---- softmax statistics: threads = (relation, row, head)
+        for (int idx = tid; idx < R * rows * H; idx += kThreads) {
+            const int r = idx / (rows * H), rem = idx - r * rows * H;
+            const int t = rem / H, h = rem - t * H;
+            const int32_t* rp = S.rp + r * (kMaxTile + 1);
+            const int beg = rp[t] - rp[0], end = rp[t + 1] - rp[0];
+            const float ad = S.ad[(r * kMaxTile + t) * H + h];
+            const float* w = S.w + static_cast<size_t>(r) * cap * hs + h;
+            float m = -INFINITY;
+            for (int e = beg; e < end; ++e) m = fmaxf(m, leaky(w[e * hs] + ad, A.neg_slope));
+            float l = 0.f;
+            for (int e = beg; e < end; ++e) l += __expf(leaky(w[e * hs] + ad, A.neg_slope) - m);
+            S.mx[(r * kMaxTile + t) * H + h] = m;
+            S.inv[(r * kMaxTile + t) * H + h] = 1.f / (l + 1e-16f);
+        }
+        __syncthreads();
+        // ---- logits -> weights in place: threads = edges
+        for (int r = 0; r < R; ++r) {
+            const int32_t e0 = S.rp[r * (kMaxTile + 1)], ne = S.rp[r * (kMaxTile + 1) + rows] - e0;
+            float* alpha = (P.f_begin == 0) ? A.alpha_saved[r] : nullptr;
+            for (int e = tid; e < ne; e += kThreads) {
+                const int t = S.erow[r * cap + e];
+                float* wrow = S.w + (static_cast<size_t>(r) * cap + e) * hs;
+                const int base = (r * kMaxTile + t) * H;
+                for (int h = 0; h < H; ++h) {
+                    const float w = __expf(leaky(wrow[h] + S.ad[base + h], A.neg_slope) - S.mx[base + h]) * S.inv[base + h];
+                    wrow[h] = w;
+                    if (alpha) alpha[static_cast<int64_t>(e0 + e) * H + h] = w;
                 }
             }
         }
         __syncthreads();
 
-        // ---- rows: one warp per row
-        for (int t = warp; t < rows; t += kWarps) {
+        // ---- gather-accumulate: threads = (row, output chunk)
+        for (int t = grp; t < rows; t += kGroups) {
             const int64_t i = t0 + t;
-            float acc[K][VEC];  // sum over relations, still in [H*C] layout (head mean is linear)
+            float acc[KC][VEC];
 #pragma unroll
-            for (int k = 0; k < K; ++k)
+            for (int k = 0; k < KC; ++k)
 #pragma unroll
                 for (int v = 0; v < VEC; ++v) acc[k][v] = 0.f;
-
             for (int r = 0; r < R; ++r) {
                 const hg_gat_rel& Rl = A.rel[r];
-                const int32_t e0 = s_rp[r * (kTile + 1)], e1 = s_rp[r * (kTile + 1) + rows];
-                const int32_t beg = s_rp[r * (kTile + 1) + t], end = s_rp[r * (kTile + 1) + t + 1];
-                const int n = end - beg;
-                if (n <= 0) continue;
-                if ((e1 - e0) <= cap) {
-                    const int lo = beg - e0;
-                    const int32_t* colp = s_col + r * cap + lo;
-                    float* wbase = s_p + static_cast<size_t>(r) * H * cap + lo;
-                    // logits -> softmax weights, in place (lanes = edges)
-                    if (n == 1) {  // softmax over one edge: exp(0) / (1 + 1e-16) == 1
-                        if (lane < H) {
-                            wbase[lane * cap] = 1.f;
-                            if (A.alpha_saved[r]) A.alpha_saved[r][static_cast<int64_t>(beg) * H + lane] = 1.f;
-                        }
-                    } else if (n <= 32) {  // whole row in registers: one pass per head
-                        for (int h = 0; h < H; ++h) {
-                            float* p = wbase + h * cap;
-                            const float ad = s_ad[(r * kTile + t) * H + h];
-                            const float sc = lane < n ? leaky(p[lane] + ad, A.neg_slope) : -INFINITY;
-                            const float m = warp_max(sc);
-                            const float ex = lane < n ? __expf(sc - m) : 0.f;
-                            const float w = __fdividef(ex, warp_sum(ex) + 1e-16f);
-                            if (lane < n) {
-                                p[lane] = w;
-                                if (A.alpha_saved[r]) A.alpha_saved[r][static_cast<int64_t>(beg + lane) * H + h] = w;
-                            }
-                        }
-                    } else {
-                        for (int h = 0; h < H; ++h) {
-                            float* p = wbase + h * cap;
-                            const float ad = s_ad[(r * kTile + t) * H + h];
-                            float m = -INFINITY;
-                            for (int e = lane; e < n; e += 32) {
-                                const float sc = leaky(p[e] + ad, A.neg_slope);
-                                p[e] = sc;
-                                m = fmaxf(m, sc);
-                            }
-                            m = warp_max(m);
-                            float l = 0.f;
-                            for (int e = lane; e < n; e += 32) {
-                                const float ex = __expf(p[e] - m);
-                                p[e] = ex;
-                                l += ex;
-                            }
-                            l = warp_sum(l) + 1e-16f;
-                            for (int e = lane; e < n; e += 32) {
-                                const float w = __fdividef(p[e], l);
-                                p[e] = w;
-                                if (A.alpha_saved[r]) A.alpha_saved[r][static_cast<int64_t>(beg + e) * H + h] = w;
-                            }
-                        }
-                    }
-                    __syncwarp();
-                    // gather-accumulate (lanes = feature chunks)
-                    for (int e = 0; e < n; e += U) {
-                        float val[U][K][VEC];
-                        float w[U][K];
+                const int32_t* rp = S.rp + r * (kMaxTile + 1);
+                const int beg = rp[t] - rp[0], end = rp[t + 1] - rp[0];
+                const int32_t* colp = S.col + r * cap;
+                const float* wp = S.w + static_cast<size_t>(r) * cap * hs;
+                if (head_mean) {
+                    for (int e = beg; e < end; ++e) {
+                        const float* __restrict__ row = Rl.xs + static_cast<int64_t>(colp[e]) * Rl.ldxs;
+                        for (int hb = 0; hb < H; hb += 4) {  // the weights of 4 heads are one broadcast LDS.128
+                            const float4 w4 = *reinterpret_cast<const float4*>(wp + e * hs + hb);
+                            const float wv[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
-                        for (int u = 0; u < U; ++u) {
-                            const bool live = e + u < n;
-                            const int32_t j = live ? colp[e + u] : 0;
-                            const float* __restrict__ row = Rl.xs + static_cast<int64_t>(j) * Rl.ldxs;
+                            for (int hh = 0; hh < 4; ++hh) {
+                                if (hb + hh < H) {
 #pragma unroll
-                            for (int k = 0; k < K; ++k) {
-                                if (live && valid[k]) {
-                                    ldg_vec<VEC>(row + (lane + 32 * k) * VEC, val[u][k]);
-                                    w[u][k] = wbase[hk[k] * cap + e + u];
-                                } else {
-                                    w[u][k] = 0.f;
+                                    for (int k = 0; k < KC; ++k)
+                                        if (fo[k] >= 0) {
+                                            float val[VEC];
+                                            ldg_vec<VEC>(row + (hb + hh) * C + fsrc[k], val);
 #pragma unroll
-                                    for (int v = 0; v < VEC; ++v) val[u][k][v] = 0.f;
+                                            for (int v = 0; v < VEC; ++v) acc[k][v] = fmaf(wv[hh], val[v], acc[k][v]);
+                                        }
                                 }
                             }
                         }
-#pragma unroll
-                        for (int u = 0; u < U; ++u)
-#pragma unroll
-                            for (int k = 0; k < K; ++k)
-#pragma unroll
-                                for (int v = 0; v < VEC; ++v) acc[k][v] = fmaf(w[u][k], val[u][k][v], acc[k][v]);
                     }
-                    __syncwarp();
                 } else {
-                    // hub path: the tile's edges do not fit the staging buffer -> stream from global
-                    for (int h = 0; h < H; ++h) {
-                        const float ad = s_ad[(r * kTile + t) * H + h];
-                        float m = -INFINITY, l = 0.f;
-                        for (int32_t e = beg + lane; e < end; e += 32) {
-                            float sc = __ldg(Rl.a_src + static_cast<int64_t>(__ldg(Rl.col + e)) * Rl.lda_src + h) + ad;
-                            if (Rl.a_edge) sc += __ldg(Rl.a_edge + static_cast<int64_t>(e) * H + h);
-                            m = fmaxf(m, leaky(sc, A.neg_slope));
-                        }
-                        m = warp_max(m);
-                        for (int32_t e = beg + lane; e < end; e += 32) {
-                            float sc = __ldg(Rl.a_src + static_cast<int64_t>(__ldg(Rl.col + e)) * Rl.lda_src + h) + ad;
-                            if (Rl.a_edge) sc += __ldg(Rl.a_edge + static_cast<int64_t>(e) * H + h);
-                            l += __expf(leaky(sc, A.neg_slope) - m);
-                        }
-                        l = warp_sum(l) + 1e-16f;
-                        for (int32_t e = beg; e < end; ++e) {  // warp-uniform sweep, one edge at a time
-                            const int32_t j = __ldg(Rl.col + e);
-                            float sc = __ldg(Rl.a_src + static_cast<int64_t>(j) * Rl.lda_src + h) + ad;
-                            if (Rl.a_edge) sc += __ldg(Rl.a_edge + static_cast<int64_t>(e) * H + h);
-                            const float w = __fdividef(__expf(leaky(sc, A.neg_slope) - m), l);
-                            if (A.alpha_saved[r] && lane == 0) A.alpha_saved[r][static_cast<int64_t>(e) * H + h] = w;
-                            const float* __restrict__ row = Rl.xs + static_cast<int64_t>(j) * Rl.ldxs;
+                    for (int e = beg; e < end; ++e) {
+                        const float* __restrict__ row = Rl.xs + static_cast<int64_t>(colp[e]) * Rl.ldxs;
+                        const float* we = wp + e * hs;
 #pragma unroll
-                            for (int k = 0; k < K; ++k) {
-                                if (valid[k] && hk[k] == h) {
-                                    float val[VEC];
-                                    ldg_vec<VEC>(row + (lane + 32 * k) * VEC, val);
+                        for (int k = 0; k < KC; ++k)
+                            if (fo[k] >= 0) {
+                                float val[VEC];
+                                ldg_vec<VEC>(row + fsrc[k], val);
+                                const float w = we[hk[k]];
 #pragma unroll
-                                    for (int v = 0; v < VEC; ++v) acc[k][v] = fmaf(w, val[v], acc[k][v]);
-                                }
+                                for (int v = 0; v < VEC; ++v) acc[k][v] = fmaf(w, val[v], acc[k][v]);
                             }
-                        }
                     }
                 }
             }
-
-            // ---- row epilogue: head concat | head mean, + summed biases, group mean, activation, ONE store
-            const float gscale = (A.group == HG_GROUP_MEAN) ? 1.f / static_cast<float>(R) : 1.f;
-            if (head_mean) {
+            // ---- epilogue: head mean scale, summed biases, group mean, addend, activation, ONE store
 #pragma unroll
-                for (int k = 0; k < K; ++k)
-                    if (valid[k]) st_vec<VEC>(stage + (lane + 32 * k) * VEC, acc[k]);
-                __syncwarp();
-                const float inv_h = 1.f / static_cast<float>(H);
-#pragma unroll
-                for (int k = 0; k < K; ++k) {
-                    const int chunk = lane + 32 * k;
-                    if (chunk >= nco) continue;
-                    float sum[VEC];
-#pragma unroll
-                    for (int v = 0; v < VEC; ++v) sum[v] = 0.f;
-                    for (int h = 0; h < H; ++h) {
-                        float hv[VEC];
-#pragma unroll
-                        for (int v = 0; v < VEC; ++v) hv[v] = stage[h * C + chunk * VEC + v];
-#pragma unroll
-                        for (int v = 0; v < VEC; ++v) sum[v] += hv[v];
-                    }
-#pragma unroll
-                    for (int v = 0; v < VEC; ++v) acc[k][v] = sum[v] * inv_h;
-                }
-                __syncwarp();
-            }
-#pragma unroll
-            for (int k = 0; k < K; ++k) {
-                const int chunk = lane + 32 * k;
-                if (chunk >= nco) continue;
+            for (int k = 0; k < KC; ++k) {
+                if (fo[k] < 0) continue;
                 float o[VEC];
 #pragma unroll
+                for (int v = 0; v < VEC; ++v) o[v] = (acc[k][v] * hscale + btot[k][v]) * gscale;
+                if (A.addend) {
+                    float av[VEC];
+                    ldg_vec<VEC>(A.addend + i * A.ldadd + fo[k], av);
+#pragma unroll
+                    for (int v = 0; v < VEC; ++v) o[v] += av[v];
+                }
+#pragma unroll
                 for (int v = 0; v < VEC; ++v) {
-                    float y = (acc[k][v] + btot[k][v]) * gscale;
+                    float y = o[v];
                     if (A.act == HG_ACT_RELU) y = fmaxf(y, 0.f);
                     else if (A.act == HG_ACT_ELU) y = y > 0.f ? y : __expf(y) - 1.f;  // F.elu: exp(x) - 1
                     o[v] = y;
                 }
-                st_vec<VEC>(A.out + i * A.ldout + chunk * VEC, o);
+                st_vec<VEC>(A.out + i * A.ldout + fo[k], o);
             }
         }
         __syncthreads();  // staging buffers are reused by the next tile
     }
 }
 
-size_t smem_words(const hg_gat_args& A, int cap) {
-    const size_t R = A.n_rel, H = A.H;
-    return R * (kTile + 1) + R * cap + R * H * cap + R * kTile * H + static_cast<size_t>(kWarps) * H * A.C;
-}
-
-template <int VEC, int K>
+template <int VEC, int TPR, int KC>
 int launch(GatParams& P, cudaStream_t stream) {
     const hg_gat_args& A = P.a;
-    // staging capacity: as much as ~40 KB of shared memory holds, 64..1024 edges per relation per tile
-    const size_t budget_words = 40 * 1024 / 4;
-    const size_t fixed = smem_words(A, 0);
-    int cap = fixed < budget_words ? static_cast<int>((budget_words - fixed) / (A.n_rel * (1 + A.H))) : 0;
+    constexpr int kGroups = kThreads / TPR;
+    P.tile_rows = kGroups > 32 ? kMaxTile : 32;
+    P.hs = A.H <= 4 ? 4 : 8;
+    // staging capacity: what ~44 KB of shared memory holds, 128..2048 edges per relation per tile
+    const size_t fixed = smem_bytes(A.n_rel, A.H, 0, P.hs);
+    const size_t per_edge = static_cast<size_t>(A.n_rel) * (4 + 4 * P.hs + 2);
+    int cap = fixed < 44 * 1024 ? static_cast<int>((44 * 1024 - fixed) / per_edge) : 0;
     cap = cap / 32 * 32;
-    cap = cap < 64 ? 64 : (cap > 1024 ? 1024 : cap);
+    cap = cap < 128 ? 128 : (cap > 2048 ? 2048 : cap);
     P.cap = cap;
-    const size_t smem = smem_words(A, cap) * 4;
+    const size_t smem = smem_bytes(A.n_rel, A.H, cap, P.hs);
     if (smem > 200 * 1024) return HG_EUNSUPPORTED;
     if (smem > 48 * 1024) {
-        HG_CUDA_TRY(cudaFuncSetAttribute(k_gat_fused<VEC, K>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        HG_CUDA_TRY(cudaFuncSetAttribute(k_gat_fused<VEC, TPR, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem)));
     }
     const int sms = sm_count() > 0 ? sm_count() : 148;
-    // small destination sets (rooms) get smaller tiles so that every SM still has several CTAs
-    int tile_rows = kTile;
-    while (tile_rows > 8 && ceil_div<int64_t>(A.n_dst, tile_rows) < static_cast<int64_t>(sms) * 12) tile_rows >>= 1;
-    P.tile_rows = tile_rows;
-    const int64_t need = ceil_div<int64_t>(A.n_dst, tile_rows);
-    const int64_t cap_grid = static_cast<int64_t>(sms) * 8 * 16;
+    const int64_t need = ceil_div<int64_t>(A.n_dst, P.tile_rows);
+    const int64_t cap_grid = static_cast<int64_t>(sms) * 4 * 8;  // 8 waves of 148 SMs x 4 resident CTAs
     const unsigned grid = static_cast<unsigned>(need < cap_grid ? need : cap_grid);
-    k_gat_fused<VEC, K><<<grid, kThreads, smem, stream>>>(P);
+    k_gat_fused<VEC, TPR, KC><<<grid, kThreads, smem, stream>>>(P);
     return check_launch();
 }
 
 template <int VEC>
-int dispatch(GatParams& P, int nc, cudaStream_t stream) {
-    const int k = ceil_div(nc, 32);
-    switch (k) {
-        case 1: return launch<VEC, 1>(P, stream);
-        case 2: return launch<VEC, 2>(P, stream);
-        case 3: return launch<VEC, 3>(P, stream);
-        case 4: return launch<VEC, 4>(P, stream);
-        case 5: return launch<VEC, 5>(P, stream);
-        case 6: return launch<VEC, 6>(P, stream);
-        case 7:
-        case 8: return launch<VEC, 8>(P, stream);
-        default: return HG_EUNSUPPORTED;
-    }
+int dispatch(GatParams& P, cudaStream_t stream) {
+    const int nco = P.f_count / VEC;
+    if (nco <= 4) return launch<VEC, 4, 1>(P, stream);
+    if (nco <= 8) return launch<VEC, 8, 1>(P, stream);
+    if (nco <= 16) return launch<VEC, 16, 1>(P, stream);
+    if (nco <= 32) return launch<VEC, 32, 1>(P, stream);
+    if (nco <= 64) return launch<VEC, 32, 2>(P, stream);
+    if (nco <= 96) return launch<VEC, 32, 3>(P, stream);
+    if (nco <= 128) return launch<VEC, 32, 4>(P, stream);
+    if (nco <= 192) return launch<VEC, 32, 6>(P, stream);
+    return launch<VEC, 32, 8>(P, stream);
 }
 
 }  // namespace
@@ -349,19 +392,22 @@ extern "C" int hg_gat_fused(const hg_gat_args* a, void* stream_) {
     if (!a) return HG_EINVAL;
     if (a->n_rel < 1 || a->n_rel > HG_MAX_RELATIONS || a->n_dst < 0) return HG_EINVAL;
     if (a->H < 1 || a->H > kMaxHeads || a->C < 1) return HG_EINVAL;
+    if (a->act < HG_ACT_NONE || a->act > HG_ACT_ELU) return HG_EINVAL;
+    if (a->src_shared && !a->concat) return HG_EINVAL;  // aggregate-first output is always [n_dst, H*C]
     if (a->n_dst == 0) return HG_OK;
     if (!a->out) return HG_EINVAL;
-    const int F = a->H * a->C;
     for (int r = 0; r < a->n_rel; ++r) {
         const hg_gat_rel& R = a->rel[r];
         // xs / a_src may be NULL only for an empty source set (every row of that relation is then empty)
         if (!R.a_dst || !R.rowptr || !R.col) return HG_EINVAL;
     }
-    // Widest vector that divides C (a chunk must not straddle two heads) and fits all alignments;
-    // prefer the widest one that still gives every lane of the first chunk work.
+    const bool head_mean = !a->concat && !a->src_shared;
+    const int width = head_mean ? a->C : a->H * a->C;
+    // Widest vector that divides C (a chunk must not straddle two heads) and fits all alignments.
     auto ok = [&](int vec) {
         const size_t bytes = sizeof(float) * vec;
         if (a->C % vec || a->ldout % vec || !aligned(a->out, bytes)) return false;
+        if (a->addend && (a->ldadd % vec || !aligned(a->addend, bytes))) return false;
         for (int r = 0; r < a->n_rel; ++r) {
             const hg_gat_rel& R = a->rel[r];
             if (R.ldxs % vec || !aligned(R.xs, bytes)) return false;
@@ -369,15 +415,15 @@ extern "C" int hg_gat_fused(const hg_gat_args* a, void* stream_) {
         }
         return true;
     };
-    int vec = 1;
-    if (ok(4) && F / 4 >= 32) vec = 4;
-    else if (ok(2) && F / 2 >= 32) vec = 2;
-    else if (F >= 32) vec = 1;
-    else vec = ok(4) ? 4 : (ok(2) ? 2 : 1);
-    GatParams P;
-    P.a = *a;
-    P.cap = 0;
-    P.tile_rows = kTile;
-    const int nc = F / vec;
-    return vec == 4 ? dispatch<4>(P, nc, stream) : (vec == 2 ? dispatch<2>(P, nc, stream) : dispatch<1>(P, nc, stream));
+    const int vec = ok(4) ? 4 : (ok(2) ? 2 : 1);
+    const int block = 32 * 8 * vec;  // widest output block one launch covers
+    for (int f0 = 0; f0 < width; f0 += block) {
+        GatParams P;
+        P.a = *a;
+        P.f_begin = f0;
+        P.f_count = (width - f0 < block) ? width - f0 : block;
+        const int rc = vec == 4 ? dispatch<4>(P, stream) : (vec == 2 ? dispatch<2>(P, stream) : dispatch<1>(P, stream));
+        if (rc != HG_OK) return rc;
+    }
+    return HG_OK;
 }

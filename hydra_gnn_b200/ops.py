@@ -211,8 +211,16 @@ class GatRelation:
 
 
 def gat_fused(rels: Sequence[GatRelation], n_dst: int, H: int, Cc: int, concat: bool, *, group: str = "sum",
-              act: str = None, neg_slope: float = 0.2, out: Tensor = None) -> Tensor:
+              act: str = None, neg_slope: float = 0.2, out: Tensor = None, addend: Tensor = None,
+              src_shared: bool = False) -> Tensor:
+    """Fused GAT aggregation of every relation targeting one node type (``hg_gat_fused``).
+
+    ``src_shared=True`` is the aggregate-first form: ``xs`` is ``[n_src, C]`` (one row shared by all
+    heads) and the result is ``[n_dst, H*C]`` with ``out[i, h] = sum_e w_eh xs[col[e]]``.
+    ``addend`` ``[n_dst, width]`` is added after the relation group, before the activation."""
     h = lib()
+    if src_shared:
+        concat = True
     if not 1 <= len(rels) <= _lib.HG_MAX_RELATIONS:
         raise ValueError("1..8 relations per destination type")
     device = rels[0].xs.device
@@ -226,7 +234,7 @@ def gat_fused(rels: Sequence[GatRelation], n_dst: int, H: int, Cc: int, concat: 
             _f32(t, nm)
             if t.dim() != 2 or (t.size(1) > 1 and t.stride(1) != 1):
                 raise ValueError(f"{nm}: expected 2-D with unit feature stride")
-        if r.xs.size(1) != H * Cc or r.a_src.size(1) != H or r.a_dst.size(1) != H:
+        if r.xs.size(1) != (Cc if src_shared else H * Cc) or r.a_src.size(1) != H or r.a_dst.size(1) != H:
             raise ValueError("GAT operand widths do not match H, C")
         if r.csr.n_dst != n_dst:
             raise ValueError("relation CSR has a different destination count")
@@ -240,7 +248,15 @@ def gat_fused(rels: Sequence[GatRelation], n_dst: int, H: int, Cc: int, concat: 
     a.n_rel, a.n_dst, a.H, a.C = len(rels), n_dst, H, Cc
     a.concat, a.group, a.act, a.neg_slope = int(concat), GROUP[group], ACT[act], float(neg_slope)
     a.out, a.ldout = ptr(out), _ld(out)
-    meta = dict(n_dst=n_dst, H=H, C=Cc, concat=bool(concat), width=width,
+    if addend is not None:
+        _require_no_grad(addend)
+        addend = _rows(addend, "addend")
+        if addend.shape != (n_dst, width):
+            raise ValueError("addend shape mismatch")
+        a.addend, a.ldadd = ptr(addend), _ld(addend)
+    a.src_shared = int(src_shared)
+    meta = dict(n_dst=n_dst, H=H, C=Cc, concat=bool(concat), width=width, src_width=Cc if src_shared else H * Cc,
+                addend=addend is not None,
                 rels=[dict(n_src=r.xs.size(0), cap=r.csr.cap, edge=r.a_edge is not None) for r in rels])
     _call("hg_gat_fused", meta, lambda: h.hg_gat_fused(C.byref(a), stream_ptr()))
     _lib.launch_count += 1

@@ -146,7 +146,7 @@ HG_API int hg_seg_reduce(const hg_seg_args* args_host, void* stream);
  *   s_e,h  = leaky_relu(a_src[col[e], h] + a_dst[i, h] (+ a_edge[e, h]), neg_slope)
  *   w_e,h  = exp(s_e,h - max_row) / (sum_row exp(.) + 1e-16)
  *   o_r[i] = concat_h | mean_h ( sum_e w_e,h * xs[col[e], h, :] ) + bias_r
- *   out[i] = act( group_r o_r[i] )
+ *   out[i] = act( group_r o_r[i] + addend[i] )
  *
  * Replaces: GATConv.edge_update + torch_geometric.utils.softmax (4 scatter passes) +
  * propagate + concat/mean + bias (models/utils.py:31-87,103-140), HeteroConv's
@@ -176,6 +176,11 @@ typedef struct hg_gat_args {
     float neg_slope;
     float* out; int64_t ldout;
     float* alpha_saved[HG_MAX_RELATIONS]; /* NULL | [E', H] softmax weights (for backward) */
+    const float* addend; int64_t ldadd;   /* NULL | [n_dst, out width]: added after the group, before act
+                                             (output of aggregate-first relations of the same dst type) */
+    int32_t src_shared; /* 1: aggregate-first form -- xs is [n_src, C], ONE row shared by all heads;
+                           out[i, h, :] = sum_e w_eh xs[col[e], :], width H*C (requires concat = 1) */
+    int32_t reserved;
 } hg_gat_args;
 
 HG_API int hg_gat_fused(const hg_gat_args* args_host, void* stream);

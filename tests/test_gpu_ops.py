@@ -163,3 +163,76 @@ def test_gather_rows():
     idx = torch.tensor([5, 99, 0, 5], dtype=torch.int32)
     got = ops.gather_rows(x.cuda(), idx.cuda(), act="relu")
     assert torch.equal(got.cpu(), torch.relu(x[idx.long()]))
+
+
+# ------------------------------------------------------------------------------ K3 + K4
+def gat_reference(xs, a_src, a_dst, ei, n_dst, H, C, concat, src_shared=False, slope=0.2):
+    """fp64 gather -> leaky_relu -> segment softmax (+1e-16) -> weighted scatter (PyG GATConv, section 9.2)."""
+    j, i = ei[0], ei[1]
+    s = torch.nn.functional.leaky_relu(a_src.double()[j] + a_dst.double()[i], slope)  # [E, H]
+    w = ou.softmax(s, i, None, n_dst)
+    src = xs.double()[j]
+    msg = w.unsqueeze(-1) * (src.unsqueeze(1) if src_shared else src.view(-1, H, C))
+    out = ou.scatter(msg, i, 0, dim_size=n_dst, reduce="sum")
+    return (out.reshape(n_dst, H * C) if (concat or src_shared) else out.mean(1)), w
+
+
+GAT_SHAPES = [(3, 64, False), (3, 26, False), (6, 64, True), (1, 6, False), (1, 306, False), (5, 35, True),
+              (8, 16, True), (2, 640, True), (3, 7, False)]
+
+
+@pytest.mark.parametrize("H,C,concat", GAT_SHAPES)
+def test_gat_fused_two_relations(H, C, concat):
+    g = torch.Generator().manual_seed(H * 1000 + C)
+    n_dst, n_a, n_b = 333, 333, 57
+    rels, want, biases = [], 0, []
+    for n_src, E in ((n_a, 1700), (n_b, 400)):
+        ei = torch.stack([torch.randint(0, n_src, (E,), generator=g), torch.randint(0, n_dst - 20, (E,), generator=g)])
+        xs = torch.randn(n_src, H * C + 8, generator=g)  # strided view: leading dimension != width
+        a_s, a_d = torch.randn(n_src, H, generator=g), torch.randn(n_dst, H, generator=g)
+        bias = torch.randn(H * C if concat else C, generator=g)
+        (csr,), _ = ops.build_csr([CSRSpec(ei.cuda(), n_src, n_dst, want_perm=True)])
+        alpha = torch.zeros(E, H, device="cuda")
+        rels.append(ops.GatRelation(xs.cuda()[:, :H * C], a_s.cuda(), a_d.cuda(), csr, bias.cuda(), None, alpha))
+        o, w = gat_reference(xs[:, :H * C], a_s, a_d, ei, n_dst, H, C, concat)
+        want = want + o + bias.double()
+        biases.append((csr, w, alpha))
+    addend = torch.randn(n_dst, H * C if concat else C, generator=g)
+    got = ops.gat_fused(rels, n_dst, H, C, concat, act="elu", addend=addend.cuda())
+    assert_close(got, torch.nn.functional.elu(want + addend.double()), f"gat H={H} C={C}", check_argmax=False)
+    for csr, w, alpha in biases:  # softmax weights saved in CSR order
+        perm = csr.perm.cpu().long()
+        assert_close(alpha.cpu(), w[perm].float(), "alpha", check_argmax=False)
+
+
+def test_gat_fused_group_mean_and_aggregate_first():
+    g = torch.Generator().manual_seed(11)
+    n_src, n_dst, E, H, C = 400, 90, 1500, 3, 64
+    ei = torch.stack([torch.randint(0, n_src, (E,), generator=g), torch.randint(0, n_dst, (E,), generator=g)])
+    x = torch.randn(n_src, C, generator=g)
+    a_s, a_d = torch.randn(n_src, H, generator=g), torch.randn(n_dst, H, generator=g)
+    (csr,), _ = ops.build_csr([CSRSpec(ei.cuda(), n_src, n_dst)])
+    rel = ops.GatRelation(x.cuda(), a_s.cuda(), a_d.cuda(), csr)
+    got = ops.gat_fused([rel], n_dst, H, C, True, src_shared=True)
+    want, _ = gat_reference(x, a_s, a_d, ei, n_dst, H, C, True, src_shared=True)
+    assert_close(got, want, "aggregate-first", check_argmax=False)
+    xs = torch.randn(n_src, H * C, generator=g)
+    rel2 = ops.GatRelation(xs.cuda(), a_s.cuda(), a_d.cuda(), csr, torch.ones(C).cuda())
+    got = ops.gat_fused([rel2, rel2], n_dst, H, C, False, group="mean", act="relu")
+    want, _ = gat_reference(xs, a_s, a_d, ei, n_dst, H, C, False)
+    assert_close(got, torch.relu(want + 1.0), "group mean", check_argmax=False)
+
+
+def test_gat_fused_hub_rows_take_the_streaming_path():
+    g = torch.Generator().manual_seed(12)
+    n_src, n_dst, H, C = 5000, 70, 3, 64
+    hub = torch.stack([torch.randint(0, n_src, (6000,), generator=g), torch.full((6000,), 3)])  # one row of degree 6000
+    rest = torch.stack([torch.randint(0, n_src, (500,), generator=g), torch.randint(0, n_dst, (500,), generator=g)])
+    ei = torch.cat([hub, rest], dim=1)
+    xs = torch.randn(n_src, H * C, generator=g)
+    a_s, a_d = torch.randn(n_src, H, generator=g), torch.randn(n_dst, H, generator=g)
+    (csr,), _ = ops.build_csr([CSRSpec(ei.cuda(), n_src, n_dst)])
+    for concat in (False, True):
+        got = ops.gat_fused([ops.GatRelation(xs.cuda(), a_s.cuda(), a_d.cuda(), csr)], n_dst, H, C, concat)
+        want, _ = gat_reference(xs, a_s, a_d, ei, n_dst, H, C, concat)
+        assert_close(got, want, f"hub concat={concat}", check_argmax=False)
