@@ -21,7 +21,8 @@ GROUP = {"sum": 0, "mean": 1}
 PREC = {"fp32": 0, "tf32x3": 1}
 
 _SO_NAME = "libhydra_gnn_b200.so"
-SO_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), _SO_NAME)
+# HYDRA_GNN_B200_SO: alternative build of the same library (A/B runs of kernel variants)
+SO_PATH = os.environ.get("HYDRA_GNN_B200_SO") or os.path.join(os.path.dirname(os.path.abspath(__file__)), _SO_NAME)
 
 vp, i32, i64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
 

@@ -1,13 +1,15 @@
-// K3 + K4 -- fused GAT for one destination node type (v3).
+// K3 + K4 -- fused GAT for one destination node type (v5).
 //
-// A CTA owns a tile of consecutive destination rows (consecutive rows belong to the same scene
-// graph, so their neighbour sets overlap and the gathers of a tile hit L1/L2).  Per tile:
-//   stage    rowptr slices, destination logits, then -- threads = edges, coalesced on col -- the
+// A CTA (128 threads, up to 6 resident per SM) owns a tile of 16-32 consecutive destination rows
+// (consecutive rows belong to the same scene graph, so their neighbour sets overlap and the gathers
+// of a tile hit L1/L2).  Per tile:
+//   stage    rowptr slices and destination logits; then -- threads = edges, coalesced on col -- the
 //            neighbour ids, the tile-local row of every edge and the raw logits a_src[j,h](+a_edge)
 //            of every relation go to shared memory;
 //   softmax  threads = (relation, row, head): max and 1/(sum + 1e-16) of the row; then threads =
-//            edges turn the staged logits into softmax weights in place.  No warp shuffles, no
-//            idle lanes on short rows (mean in-degree of a scene graph is ~5);
+//            edges turn the staged logits into softmax weights in place.  No shuffles, no idle lanes
+//            on short rows (mean in-degree of a scene graph is ~5), no runtime integer divisions
+//            (all index maps are shifts and masks over padded layouts);
 //   gather   threads = (row, output chunk): TPR threads cooperate on a row, each owning KC vector
 //            chunks of the OUTPUT row.  For head-mean the thread walks the H head slices of xs[j]
 //            itself, so the head reduction never leaves registers; the weights of an edge are one
@@ -25,16 +27,16 @@
 namespace hg {
 namespace {
 
-constexpr int kThreads = 256;
+constexpr int kThreads = 128;
 constexpr int kWarps = kThreads / kWarp;
 constexpr int kMaxHeads = 8;
-constexpr int kMaxTile = 64;
+constexpr int kMaxTile = 32;  // rows per tile: 16 (32 when a row needs only 4 threads)
 
 struct GatParams {
     hg_gat_args a;
     int32_t cap;        // staged edges per relation per tile (multiple of 32)
-    int32_t tile_rows;  // destination rows per tile (<= kMaxTile)
-    int32_t hs;         // padded head stride of the weight rows in shared memory: 4 or 8
+    int32_t tile_rows;  // 16 or 32
+    int32_t hs;         // padded head stride in shared memory: 4 or 8
     int32_t f_begin;    // first OUTPUT column of this launch (wide rows are split over launches)
     int32_t f_count;    // output columns of this launch
 };
@@ -42,32 +44,34 @@ struct GatParams {
 __device__ __forceinline__ float leaky(float v, float slope) { return v > 0.f ? v : v * slope; }
 
 struct Smem {
-    int32_t* rp;     // [R][kMaxTile + 1]
-    float* ad;       // [R][kMaxTile][H]
-    float* mx;       // [R][kMaxTile][H]   row max
-    float* inv;      // [R][kMaxTile][H]   1 / (row sum + 1e-16)
+    float* w;        // [R][cap][hs]        logits -> weights (16-byte aligned rows)
+    float* ad;       // [R][kMaxTile][hs]   destination logits
+    float* mx;       // [R][kMaxTile][hs]   row max
+    float* inv;      // [R][kMaxTile][hs]   1 / (row sum + 1e-16)
+    float* bias;     // [f_count]           summed biases of this launch's output columns
     int32_t* col;    // [R][cap]
-    float* w;        // [R][cap][hs]       logits -> weights
-    uint16_t* erow;  // [R][cap]           tile-local row of the edge
+    int32_t* rp;     // [R][kMaxTile + 1]
+    uint8_t* erow;   // [R][cap]            tile-local row of the edge
 };
 
-__host__ __device__ inline size_t smem_bytes(int R, int H, int cap, int hs) {
-    size_t words = static_cast<size_t>(R) * (kMaxTile + 1) + 3 * static_cast<size_t>(R) * kMaxTile * H +
-                   static_cast<size_t>(R) * cap + static_cast<size_t>(R) * cap * hs;
-    words = (words + 3) / 4 * 4;
-    return words * 4 + static_cast<size_t>(R) * cap * 2 + 16;
+__host__ __device__ inline size_t smem_bytes(int R, int cap, int hs, int f_count) {
+    size_t words = static_cast<size_t>(R) * cap * hs + 3 * static_cast<size_t>(R) * kMaxTile * hs +
+                   static_cast<size_t>((f_count + 3) / 4 * 4) + static_cast<size_t>(R) * cap +
+                   static_cast<size_t>(R) * (kMaxTile + 1);
+    return words * 4 + static_cast<size_t>(R) * cap + 16;
 }
 
-__device__ __forceinline__ Smem carve(uint8_t* raw, int R, int H, int cap, int hs) {
+__device__ __forceinline__ Smem carve(uint8_t* raw, int R, int cap, int hs, int f_count) {
     Smem s;
     float* p = reinterpret_cast<float*>(raw);
-    s.w = p;                      p += static_cast<size_t>(R) * cap * hs;   // first: 16-byte aligned rows
+    s.w = p;      p += static_cast<size_t>(R) * cap * hs;
+    s.ad = p;     p += R * kMaxTile * hs;
+    s.mx = p;     p += R * kMaxTile * hs;
+    s.inv = p;    p += R * kMaxTile * hs;
+    s.bias = p;   p += (f_count + 3) / 4 * 4;
     s.col = reinterpret_cast<int32_t*>(p);  p += static_cast<size_t>(R) * cap;
     s.rp = reinterpret_cast<int32_t*>(p);   p += R * (kMaxTile + 1);
-    s.ad = p;                     p += R * kMaxTile * H;
-    s.mx = p;                     p += R * kMaxTile * H;
-    s.inv = p;                    p += R * kMaxTile * H;
-    s.erow = reinterpret_cast<uint16_t*>(p);
+    s.erow = reinterpret_cast<uint8_t*>(p);
     return s;
 }
 
@@ -144,26 +148,32 @@ __device__ __noinline__ void slow_row(const GatParams& P, int64_t i, int lane) {
         st_vec<VEC>(A.out + i * A.ldout + f, o);
     }
 }
-
 template <int VEC, int TPR, int KC>
-__global__ void __launch_bounds__(kThreads, (KC <= 2 ? 3 : 2)) k_gat_fused(const __grid_constant__ GatParams P) {
+__global__ void __launch_bounds__(kThreads, (KC <= 2 ? 6 : 4)) k_gat_fused(const __grid_constant__ GatParams P) {
     extern __shared__ __align__(16) uint8_t s_raw[];
     const hg_gat_args& A = P.a;
     const int H = A.H, C = A.C, R = A.n_rel, cap = P.cap, hs = P.hs;
-    const Smem S = carve(s_raw, R, H, cap, hs);
+    const int hsh = hs == 4 ? 2 : 3;          // log2(hs)
+    const Smem S = carve(s_raw, R, cap, hs, P.f_count);
     const int tid = threadIdx.x;
     const bool head_mean = !A.concat && !A.src_shared;
     const int nco = P.f_count / VEC;          // output chunks of this launch
-    constexpr int kGroups = kThreads / TPR;   // row groups working concurrently
+    constexpr int kGroups = kThreads / TPR;   // rows gathered concurrently
     const int q = tid % TPR, grp = tid / TPR;
     const int tile_rows = P.tile_rows;
     const int64_t n_tiles = ceil_div<int64_t>(A.n_dst, tile_rows);
     const float gscale = (A.group == HG_GROUP_MEAN) ? 1.f / static_cast<float>(R) : 1.f;
     const float hscale = head_mean ? 1.f / static_cast<float>(H) : 1.f;
 
+    for (int f = tid; f < P.f_count; f += kThreads) {
+        float b = 0.f;
+        for (int r = 0; r < R; ++r)
+            if (A.rel[r].bias) b += __ldg(A.rel[r].bias + P.f_begin + f);
+        S.bias[f] = b;
+    }
+
     // per-thread constants of its KC output chunks
     int fo[KC], fsrc[KC], hk[KC];
-    float btot[KC][VEC];
 #pragma unroll
     for (int k = 0; k < KC; ++k) {
         const int oc = q + k * TPR;
@@ -171,38 +181,27 @@ __global__ void __launch_bounds__(kThreads, (KC <= 2 ? 3 : 2)) k_gat_fused(const
         fo[k] = valid ? P.f_begin + oc * VEC : -1;
         hk[k] = (valid && !head_mean) ? fo[k] / C : 0;
         fsrc[k] = valid ? (A.src_shared ? fo[k] % C : fo[k]) : 0;
-#pragma unroll
-        for (int v = 0; v < VEC; ++v) btot[k][v] = 0.f;
-        if (valid)
-            for (int r = 0; r < R; ++r)
-                if (A.rel[r].bias) {
-                    float bv[VEC];
-                    ldg_vec<VEC>(A.rel[r].bias + fo[k], bv);
-#pragma unroll
-                    for (int v = 0; v < VEC; ++v) btot[k][v] += bv[v];
-                }
     }
 
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const int64_t t0 = tile * tile_rows;
         const int rows = (A.n_dst - t0 < tile_rows) ? static_cast<int>(A.n_dst - t0) : tile_rows;
+        __syncthreads();  // previous tile fully consumed (also orders the bias fill before its first use)
 
-        // ---- stage 1: rowptr slices + destination logits
+        // ---- stage 1: rowptr slices + destination logits (padded [R][32][hs] layout: shifts only)
         for (int idx = tid; idx < R * (kMaxTile + 1); idx += kThreads) {
             const int r = idx / (kMaxTile + 1), t = idx - r * (kMaxTile + 1);
             S.rp[idx] = __ldg(A.rel[r].rowptr + t0 + min(t, rows));
         }
-        for (int idx = tid; idx < R * rows * H; idx += kThreads) {
-            const int r = idx / (rows * H), rem = idx - r * rows * H;
-            const int t = rem / H, h = rem - t * H;
-            S.ad[(r * kMaxTile + t) * H + h] = __ldg(A.rel[r].a_dst + (t0 + t) * A.rel[r].lda_dst + h);
+        for (int idx = tid; idx < (R * kMaxTile) << hsh; idx += kThreads) {
+            const int h = idx & (hs - 1), t = (idx >> hsh) & (kMaxTile - 1), r = idx >> (hsh + 5);
+            if (t < rows && h < H) S.ad[idx] = __ldg(A.rel[r].a_dst + (t0 + t) * A.rel[r].lda_dst + h);
         }
         __syncthreads();
         bool fits = true;
         for (int r = 0; r < R; ++r) fits = fits && (S.rp[r * (kMaxTile + 1) + rows] - S.rp[r * (kMaxTile + 1)] <= cap);
         if (!fits) {  // hub tile (uniform branch): warp per row straight from global memory
             for (int t = tid >> 5; t < rows; t += kWarps) slow_row<VEC>(P, t0 + t, tid & 31);
-            __syncthreads();
             continue;
         }
 
@@ -211,6 +210,9 @@ __global__ void __launch_bounds__(kThreads, (KC <= 2 ? 3 : 2)) k_gat_fused(const
             const hg_gat_rel& Rl = A.rel[r];
             const int32_t* rp = S.rp + r * (kMaxTile + 1);
             const int32_t e0 = rp[0], ne = rp[rows] - e0;
+            const float* __restrict__ a_src = Rl.a_src;
+            const float* __restrict__ a_edge = Rl.a_edge;
+            const int64_t lda = Rl.lda_src;
             for (int e = tid; e < ne; e += kThreads) {
                 const int32_t j = __ldg(Rl.col + e0 + e);
                 S.col[r * cap + e] = j;
@@ -219,32 +221,38 @@ __global__ void __launch_bounds__(kThreads, (KC <= 2 ? 3 : 2)) k_gat_fused(const
                     const int mid = (lo + hi) >> 1;
                     if (rp[mid] <= e0 + e) lo = mid; else hi = mid;
                 }
-                S.erow[r * cap + e] = static_cast<uint16_t>(lo);
-                float* wrow = S.w + (static_cast<size_t>(r) * cap + e) * hs;
-                for (int h = 0; h < H; ++h) {
-                    float s = __ldg(Rl.a_src + static_cast<int64_t>(j) * Rl.lda_src + h);
-                    if (Rl.a_edge) s += __ldg(Rl.a_edge + static_cast<int64_t>(e0 + e) * H + h);
-                    wrow[h] = s;
+                S.erow[r * cap + e] = static_cast<uint8_t>(lo);
+                float* wrow = S.w + ((static_cast<size_t>(r) * cap + e) << hsh);
+                const float* src = a_src + static_cast<int64_t>(j) * lda;
+#pragma unroll
+                for (int h = 0; h < kMaxHeads; ++h) {
+                    if (h < hs) {
+                        float s = 0.f;
+                        if (h < H) {
+                            s = __ldg(src + h);
+                            if (a_edge) s += __ldg(a_edge + static_cast<int64_t>(e0 + e) * H + h);
+                        }
+                        wrow[h] = s;
+                    }
                 }
-                for (int h = H; h < hs; ++h) wrow[h] = 0.f;
             }
         }
         __syncthreads();
 
-        // ---- softmax statistics: threads = (relation, row, head)
-        for (int idx = tid; idx < R * rows * H; idx += kThreads) {
-            const int r = idx / (rows * H), rem = idx - r * rows * H;
-            const int t = rem / H, h = rem - t * H;
+        // ---- softmax statistics: threads = (relation, row, head) over the padded layout
+        for (int idx = tid; idx < (R * kMaxTile) << hsh; idx += kThreads) {
+            const int h = idx & (hs - 1), t = (idx >> hsh) & (kMaxTile - 1), r = idx >> (hsh + 5);
+            if (t >= rows || h >= H) continue;
             const int32_t* rp = S.rp + r * (kMaxTile + 1);
             const int beg = rp[t] - rp[0], end = rp[t + 1] - rp[0];
-            const float ad = S.ad[(r * kMaxTile + t) * H + h];
-            const float* w = S.w + static_cast<size_t>(r) * cap * hs + h;
+            const float ad = S.ad[idx];
+            const float* w = S.w + ((static_cast<size_t>(r) * cap) << hsh) + h;
             float m = -INFINITY;
-            for (int e = beg; e < end; ++e) m = fmaxf(m, leaky(w[e * hs] + ad, A.neg_slope));
+            for (int e = beg; e < end; ++e) m = fmaxf(m, leaky(w[e << hsh] + ad, A.neg_slope));
             float l = 0.f;
-            for (int e = beg; e < end; ++e) l += __expf(leaky(w[e * hs] + ad, A.neg_slope) - m);
-            S.mx[(r * kMaxTile + t) * H + h] = m;
-            S.inv[(r * kMaxTile + t) * H + h] = 1.f / (l + 1e-16f);
+            for (int e = beg; e < end; ++e) l += __expf(leaky(w[e << hsh] + ad, A.neg_slope) - m);
+            S.mx[idx] = m;
+            S.inv[idx] = 1.f / (l + 1e-16f);
         }
         __syncthreads();
         // ---- logits -> weights in place: threads = edges
@@ -253,12 +261,15 @@ __global__ void __launch_bounds__(kThreads, (KC <= 2 ? 3 : 2)) k_gat_fused(const
             float* alpha = (P.f_begin == 0) ? A.alpha_saved[r] : nullptr;
             for (int e = tid; e < ne; e += kThreads) {
                 const int t = S.erow[r * cap + e];
-                float* wrow = S.w + (static_cast<size_t>(r) * cap + e) * hs;
-                const int base = (r * kMaxTile + t) * H;
-                for (int h = 0; h < H; ++h) {
-                    const float w = __expf(leaky(wrow[h] + S.ad[base + h], A.neg_slope) - S.mx[base + h]) * S.inv[base + h];
-                    wrow[h] = w;
-                    if (alpha) alpha[static_cast<int64_t>(e0 + e) * H + h] = w;
+                float* wrow = S.w + ((static_cast<size_t>(r) * cap + e) << hsh);
+                const int base = (r * kMaxTile + t) << hsh;
+#pragma unroll
+                for (int h = 0; h < kMaxHeads; ++h) {
+                    if (h < H) {
+                        const float w = __expf(leaky(wrow[h] + S.ad[base + h], A.neg_slope) - S.mx[base + h]) * S.inv[base + h];
+                        wrow[h] = w;
+                        if (alpha) alpha[static_cast<int64_t>(e0 + e) * H + h] = w;
+                    }
                 }
             }
         }
@@ -273,41 +284,51 @@ __global__ void __launch_bounds__(kThreads, (KC <= 2 ? 3 : 2)) k_gat_fused(const
 #pragma unroll
                 for (int v = 0; v < VEC; ++v) acc[k][v] = 0.f;
             for (int r = 0; r < R; ++r) {
-                const hg_gat_rel& Rl = A.rel[r];
+                const float* __restrict__ xsb = A.rel[r].xs + fsrc[0];
+                const int64_t ld = A.rel[r].ldxs;
                 const int32_t* rp = S.rp + r * (kMaxTile + 1);
                 const int beg = rp[t] - rp[0], end = rp[t + 1] - rp[0];
                 const int32_t* colp = S.col + r * cap;
-                const float* wp = S.w + static_cast<size_t>(r) * cap * hs;
+                const float* wp = S.w + ((static_cast<size_t>(r) * cap) << hsh);
                 if (head_mean) {
-                    for (int e = beg; e < end; ++e) {
-                        const float* __restrict__ row = Rl.xs + static_cast<int64_t>(colp[e]) * Rl.ldxs;
-                        for (int hb = 0; hb < H; hb += 4) {  // the weights of 4 heads are one broadcast LDS.128
-                            const float4 w4 = *reinterpret_cast<const float4*>(wp + e * hs + hb);
-                            const float wv[4] = {w4.x, w4.y, w4.z, w4.w};
+                    for (int hb = 0; hb < H; hb += 4) {  // heads in blocks of 4: their weights are one LDS.128
+                        const float* __restrict__ xsh = xsb + hb * C;
+                        const int hn = H - hb;  // live heads of this block (>= 1)
+#pragma unroll(KC <= 2 ? 2 : 1)
+                        for (int e = beg; e < end; ++e) {
+                            const float* __restrict__ rowh = xsh + static_cast<int64_t>(colp[e]) * ld;
+                            const float4 wa = *reinterpret_cast<const float4*>(wp + (e << hsh) + hb);
+                            const float wv[4] = {wa.x, wa.y, wa.z, wa.w};
+                            float val[4][KC][VEC];
 #pragma unroll
-                            for (int hh = 0; hh < 4; ++hh) {
-                                if (hb + hh < H) {
+                            for (int hh = 0; hh < 4; ++hh)  // all loads of the edge first: independent, in flight together
 #pragma unroll
-                                    for (int k = 0; k < KC; ++k)
-                                        if (fo[k] >= 0) {
-                                            float val[VEC];
-                                            ldg_vec<VEC>(row + (hb + hh) * C + fsrc[k], val);
+                                for (int k = 0; k < KC; ++k) {
+                                    if (hh < hn && fo[k] >= 0) {
+                                        ldg_vec<VEC>(rowh + hh * C + (fsrc[k] - fsrc[0]), val[hh][k]);
+                                    } else {
 #pragma unroll
-                                            for (int v = 0; v < VEC; ++v) acc[k][v] = fmaf(wv[hh], val[v], acc[k][v]);
-                                        }
+                                        for (int v = 0; v < VEC; ++v) val[hh][k][v] = 0.f;
+                                    }
                                 }
-                            }
+#pragma unroll
+                            for (int hh = 0; hh < 4; ++hh)
+#pragma unroll
+                                for (int k = 0; k < KC; ++k)
+#pragma unroll
+                                    for (int v = 0; v < VEC; ++v) acc[k][v] = fmaf(wv[hh], val[hh][k][v], acc[k][v]);
                         }
                     }
                 } else {
+#pragma unroll 2
                     for (int e = beg; e < end; ++e) {
-                        const float* __restrict__ row = Rl.xs + static_cast<int64_t>(colp[e]) * Rl.ldxs;
-                        const float* we = wp + e * hs;
+                        const float* __restrict__ row = xsb + static_cast<int64_t>(colp[e]) * ld;
+                        const float* we = wp + (e << hsh);
 #pragma unroll
                         for (int k = 0; k < KC; ++k)
                             if (fo[k] >= 0) {
                                 float val[VEC];
-                                ldg_vec<VEC>(row + fsrc[k], val);
+                                ldg_vec<VEC>(row + (fsrc[k] - fsrc[0]), val);
                                 const float w = we[hk[k]];
 #pragma unroll
                                 for (int v = 0; v < VEC; ++v) acc[k][v] = fmaf(w, val[v], acc[k][v]);
@@ -315,13 +336,13 @@ __global__ void __launch_bounds__(kThreads, (KC <= 2 ? 3 : 2)) k_gat_fused(const
                     }
                 }
             }
-            // ---- epilogue: head mean scale, summed biases, group mean, addend, activation, ONE store
+            // ---- epilogue: head-mean scale, summed biases, group mean, addend, activation, ONE store
 #pragma unroll
             for (int k = 0; k < KC; ++k) {
                 if (fo[k] < 0) continue;
                 float o[VEC];
 #pragma unroll
-                for (int v = 0; v < VEC; ++v) o[v] = (acc[k][v] * hscale + btot[k][v]) * gscale;
+                for (int v = 0; v < VEC; ++v) o[v] = (acc[k][v] * hscale + S.bias[fo[k] - P.f_begin + v]) * gscale;
                 if (A.addend) {
                     float av[VEC];
                     ldg_vec<VEC>(A.addend + i * A.ldadd + fo[k], av);
@@ -338,7 +359,6 @@ __global__ void __launch_bounds__(kThreads, (KC <= 2 ? 3 : 2)) k_gat_fused(const
                 st_vec<VEC>(A.out + i * A.ldout + fo[k], o);
             }
         }
-        __syncthreads();  // staging buffers are reused by the next tile
     }
 }
 
@@ -346,16 +366,16 @@ template <int VEC, int TPR, int KC>
 int launch(GatParams& P, cudaStream_t stream) {
     const hg_gat_args& A = P.a;
     constexpr int kGroups = kThreads / TPR;
-    P.tile_rows = kGroups > 32 ? kMaxTile : 32;
+    P.tile_rows = kGroups > 16 ? kMaxTile : 16;
     P.hs = A.H <= 4 ? 4 : 8;
-    // staging capacity: what ~44 KB of shared memory holds, 128..2048 edges per relation per tile
-    const size_t fixed = smem_bytes(A.n_rel, A.H, 0, P.hs);
-    const size_t per_edge = static_cast<size_t>(A.n_rel) * (4 + 4 * P.hs + 2);
-    int cap = fixed < 44 * 1024 ? static_cast<int>((44 * 1024 - fixed) / per_edge) : 0;
+    // staging capacity: what ~24 KB of shared memory holds, 128..2048 edges per relation per tile
+    const size_t fixed = smem_bytes(A.n_rel, 0, P.hs, P.f_count);
+    const size_t per_edge = static_cast<size_t>(A.n_rel) * (4 + 4 * P.hs + 1);
+    int cap = fixed < 24 * 1024 ? static_cast<int>((24 * 1024 - fixed) / per_edge) : 0;
     cap = cap / 32 * 32;
     cap = cap < 128 ? 128 : (cap > 2048 ? 2048 : cap);
     P.cap = cap;
-    const size_t smem = smem_bytes(A.n_rel, A.H, cap, P.hs);
+    const size_t smem = smem_bytes(A.n_rel, cap, P.hs, P.f_count);
     if (smem > 200 * 1024) return HG_EUNSUPPORTED;
     if (smem > 48 * 1024) {
         HG_CUDA_TRY(cudaFuncSetAttribute(k_gat_fused<VEC, TPR, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -363,7 +383,7 @@ int launch(GatParams& P, cudaStream_t stream) {
     }
     const int sms = sm_count() > 0 ? sm_count() : 148;
     const int64_t need = ceil_div<int64_t>(A.n_dst, P.tile_rows);
-    const int64_t cap_grid = static_cast<int64_t>(sms) * 4 * 8;  // 8 waves of 148 SMs x 4 resident CTAs
+    const int64_t cap_grid = static_cast<int64_t>(sms) * 6 * 8;  // 8 waves of 148 SMs x 6 resident CTAs
     const unsigned grid = static_cast<unsigned>(need < cap_grid ? need : cap_grid);
     k_gat_fused<VEC, TPR, KC><<<grid, kThreads, smem, stream>>>(P);
     return check_launch();
