@@ -57,7 +57,8 @@ class LinSeg(C.Structure):
 
 class LinearArgs(C.Structure):
     _fields_ = [("seg", LinSeg * HG_MAX_SEGMENTS), ("n_seg", i32), ("M", i32), ("N", i32), ("bias", vp),
-                ("scale", vp), ("shift", vp), ("act", i32), ("precision", i32), ("y", vp), ("ldy", i64)]
+                ("scale", vp), ("shift", vp), ("act", i32), ("precision", i32), ("y", vp), ("ldy", i64),
+                ("w_prepacked", i32), ("reserved", i32)]
 
 
 _STRUCTS = [PlanRel, SegArgs, GatRel, GatArgs, LinSeg, LinearArgs]
@@ -74,6 +75,7 @@ SYMBOLS = {
     "hg_seg_reduce": (C.c_int, [C.POINTER(SegArgs), vp]),
     "hg_gat_fused": (C.c_int, [C.POINTER(GatArgs), vp]),
     "hg_linear_workspace_bytes": (C.c_size_t, [C.POINTER(LinearArgs)]),
+    "hg_linear_pack_weights": (C.c_int, [C.POINTER(LinearArgs), vp, C.c_size_t, vp]),
     "hg_linear": (C.c_int, [C.POINTER(LinearArgs), vp, C.c_size_t, vp]),
     "hg_edge_logits": (C.c_int, [vp, i64, i32, vp, vp, i64, vp, vp, i32, vp, vp]),
     "hg_relative_pos": (C.c_int, [vp, vp, vp, vp, i64, vp, vp]),

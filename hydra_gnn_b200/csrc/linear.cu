@@ -9,7 +9,8 @@
 namespace hg {
 
 int linear_tc_supported(const hg_linear_args& a);
-size_t linear_tc_workspace_bytes(const hg_linear_args& a);
+size_t linear_tc_packed_bytes(const hg_linear_args& a);
+int linear_tc_pack(const hg_linear_args& a, void* dst, size_t dst_bytes, cudaStream_t stream);
 int linear_tc_launch(const hg_linear_args& a, void* ws, size_t ws_bytes, cudaStream_t stream);
 
 namespace {
@@ -110,8 +111,20 @@ int validate(const hg_linear_args* a) {
 
 extern "C" size_t hg_linear_workspace_bytes(const hg_linear_args* a) {
     if (!a || hg::validate(a) != HG_OK) return 0;
-    if (a->precision == HG_PREC_TF32X3 && hg::linear_tc_supported(*a)) return hg::linear_tc_workspace_bytes(*a);
+    if (a->precision == HG_PREC_TF32X3 && hg::linear_tc_supported(*a)) return hg::linear_tc_packed_bytes(*a);
     return 0;
+}
+
+extern "C" int hg_linear_pack_weights(const hg_linear_args* a, void* dst, size_t dst_bytes, void* stream_) {
+    using namespace hg;
+    if (!a || a->n_seg < 1 || a->n_seg > HG_MAX_SEGMENTS || a->N < 1) return HG_EINVAL;
+    for (int s = 0; s < a->n_seg; ++s)
+        if (a->seg[s].K < 0 || (a->seg[s].K > 0 && !a->seg[s].w)) return HG_EINVAL;
+    if (a->precision != HG_PREC_TF32X3) return HG_OK;  // the fp32 path reads W as it is
+    hg_linear_args b = *a;
+    if (b.M < 1) b.M = 1;
+    if (!linear_tc_supported(b)) return HG_EUNSUPPORTED;
+    return linear_tc_pack(b, dst, dst_bytes, static_cast<cudaStream_t>(stream_));
 }
 
 extern "C" int hg_linear(const hg_linear_args* a, void* workspace, size_t workspace_bytes, void* stream_) {

@@ -3,22 +3,21 @@
 // fp32-class accuracy on the TF32 tensor pipe by 3-term error compensation:
 //     x = x_hi + x_lo,  W = W_hi + W_lo   (hi = rna_tf32(.), lo = rna_tf32(. - hi))
 //     x W^T ~= x_hi W_hi^T + x_hi W_lo^T + x_lo W_hi^T          (dropped term ~ 2^-22)
-// accumulated in fp32 in TMEM.  The tensor core adds into the accumulator with truncation (about
-// one ulp of the accumulator per MMA), so the main term and the two 2^-11-sized correction terms
-// get SEPARATE TMEM accumulators (summed in the epilogue): the truncation chain that matters is
-// K/8 instructions long instead of 3K/8.
+// accumulated in fp32 in TMEM.
 //
-// CTA = one 128-row tile of x times one N tile (<= 256 columns) of W.  Warp roles:
-//   warp 0        allocates TMEM; one elected lane issues tcgen05.mma (12 per 32-wide k-block)
-//                 and tcgen05.commit (frees the smem stage / publishes the accumulator);
-//   warps 1..8    loaders: read the x tile from global with vector loads (rows of x are only
-//                 8-byte aligned when K = 306, so TMA cannot describe them), split hi/lo in
-//                 registers and store both tiles in the UMMA canonical K-major SWIZZLE_128B layout;
-//                 one lane issues a 1-D bulk copy (cp.async.bulk, UBLKCP) of the pre-swizzled
-//                 W_hi|W_lo image of the stage.  After the main loop the same warps run the
-//                 epilogue: tcgen05.ld accumulator -> bias/scale/shift/activation -> global.
-// W is re-packed (split + swizzled, 0.5 MB) into the caller's workspace by a tiny kernel in
-// the same call, so the ABI stays stateless.
+// Persistent, warp-specialised kernel: one CTA per SM walks the (m-tile, n-tile) list; three
+// pipelines run concurrently and never meet at a CTA barrier:
+//   warps 2..9    A loaders: x rows are only 8-byte aligned when K = 306, so TMA cannot describe
+//                 them; the loaders read the 128 x 32 k-block with vector loads THREE k-blocks ahead
+//                 (a register ring, ~48 KB in flight per SM), split hi/lo in registers and store
+//                 both tiles in the UMMA canonical K-major SWIZZLE_128B layout;
+//   warp 1        W producer: one lane issues a 1-D bulk copy (cp.async.bulk, UBLKCP) of the
+//                 pre-swizzled W_hi|W_lo image of the k-block (packed once per weight version);
+//   warp 0        allocates TMEM; one elected lane issues tcgen05.mma (12 per 32-wide k-block) into
+//                 one of TWO accumulator buffers and tcgen05.commit (frees the smem stage / publishes
+//                 the accumulator);
+//   warps 10..13  epilogue: tcgen05.ld accumulator -> bias/scale/shift/activation -> global, while
+//                 the MMA warp already fills the other accumulator buffer with the next tile.
 #include "hg_common.cuh"
 
 namespace hg {
@@ -28,8 +27,10 @@ constexpr int BM = 128;
 constexpr int BK = 32;                      // fp32 elements per k-block = one 128-byte swizzle row
 constexpr int kLoaderWarps = 8;
 constexpr int kLoaderThreads = kLoaderWarps * 32;
-constexpr int kThreads = 32 + kLoaderThreads;
+constexpr int kEpiWarps = 4;
+constexpr int kThreads = 64 + kLoaderThreads + kEpiWarps * 32;  // 448
 constexpr int kATileBytes = BM * BK * 4;    // 16 KB
+constexpr int kPrefetch = 3;                // k-blocks of A in flight per loader thread
 constexpr long long kWaitCycles = 4000000000ll;  // ~2 s: a protocol bug traps instead of hanging the GPU
 
 struct TcParams {
@@ -39,6 +40,7 @@ struct TcParams {
     int32_t kb_start[HG_MAX_SEGMENTS + 1];  // first k-block of each segment
     int32_t tmem_cols;
     int32_t vec;          // widest vector all x segments allow (1, 2, 4)
+    int64_t m_tiles;
 };
 
 // ------------------------------------------------------------------------------ PTX helpers
@@ -157,26 +159,106 @@ __global__ void __launch_bounds__(256) k_pack_w(const __grid_constant__ TcParams
 }
 
 // ------------------------------------------------------------------------------ main kernel
+// Position of global k-block g (the loaders, the W producer and the MMA warp all walk the same
+// sequence: tiles of this CTA in order, k-blocks of a tile in order).
+struct KbPos {
+    int64_t m0;
+    int n_tile, kb;
+};
+__device__ __forceinline__ KbPos kb_pos(const TcParams& P, int g) {
+    const int it = g / P.n_kb;
+    const int64_t tile = static_cast<int64_t>(blockIdx.x) + static_cast<int64_t>(it) * gridDim.x;
+    KbPos p;
+    p.kb = g - it * P.n_kb;
+    p.n_tile = static_cast<int>(tile % P.n_tiles);
+    p.m0 = (tile / P.n_tiles) * BM;
+    return p;
+}
+
+template <int VEC>
+struct Loader {
+    static constexpr int kVecPerRow = BK / VEC;
+    static constexpr int kRowStep = kLoaderThreads / kVecPerRow;
+    static constexpr int kIters = BM / kRowStep;
+
+    // global -> registers (one k-block slice of this thread: kIters vectors)
+    static __device__ __forceinline__ void load(const TcParams& P, int g, int t, float (&v)[kIters][VEC]) {
+        const hg_linear_args& A = P.a;
+        const KbPos p = kb_pos(P, g);
+        int seg = 0;
+        while (seg + 1 < A.n_seg && p.kb >= P.kb_start[seg + 1]) ++seg;
+        const hg_lin_seg& G = A.seg[seg];
+        const int cv = t % kVecPerRow, rb = t / kVecPerRow;
+        const int k = (p.kb - P.kb_start[seg]) * BK + cv * VEC;
+#pragma unroll
+        for (int i = 0; i < kIters; ++i) {
+            const int64_t m = p.m0 + rb + i * kRowStep;
+            const bool row_ok = m < A.M;
+            const float* __restrict__ src = G.x + m * G.ldx + k;
+            if (row_ok && k + VEC <= G.K) {
+                ldg_vec<VEC>(src, v[i]);
+            } else {
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) v[i][e] = (row_ok && k + e < G.K) ? __ldg(src + e) : 0.f;
+            }
+        }
+    }
+
+    // registers -> hi/lo swizzled smem tiles of the stage
+    static __device__ __forceinline__ void store(uint8_t* stage, int t, const float (&v)[kIters][VEC]) {
+        const int cv = t % kVecPerRow, rb = t / kVecPerRow;
+#pragma unroll
+        for (int i = 0; i < kIters; ++i) {
+            const int r = rb + i * kRowStep;
+            float hi[VEC], lo[VEC];
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) {
+                hi[e] = tf32_rna(v[i][e]);
+                lo[e] = tf32_rna(v[i][e] - hi[e]);
+            }
+            const uint32_t off = swz_off(r, cv * VEC);
+            st_vec<VEC>(reinterpret_cast<float*>(stage + off), hi);
+            st_vec<VEC>(reinterpret_cast<float*>(stage + kATileBytes + off), lo);
+        }
+    }
+};
+
 template <int VEC>
 __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant__ TcParams P) {
     extern __shared__ uint8_t smem_raw[];
     const hg_linear_args& A = P.a;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n_tile = blockIdx.x % P.n_tiles;
-    const int64_t m0 = static_cast<int64_t>(blockIdx.x / P.n_tiles) * BM;
-    const int n0 = n_tile * P.block_n;
     const int S = P.stages;
     const uint32_t b_tile_bytes = static_cast<uint32_t>(P.block_n) * 128u;
     const uint32_t stage_bytes = 2u * kATileBytes + 2u * b_tile_bytes;
 
+    // tiles of this CTA: blockIdx.x, blockIdx.x + gridDim.x, ...
+    const int64_t total_tiles = P.m_tiles * P.n_tiles;
+    const int my_tiles = static_cast<int>((total_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x);
+    const int G = my_tiles * P.n_kb;  // k-blocks this CTA streams
+
     // carve: [1024-aligned stages][barriers][tmem slot]
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint64_t* bars = reinterpret_cast<uint64_t*>(base + static_cast<size_t>(S) * stage_bytes);
-    uint64_t* full_a = bars;            // [S] loaders -> MMA   (count = loader warps)
-    uint64_t* full_b = bars + S;        // [S] bulk copy -> MMA (count = 1 + tx bytes)
-    uint64_t* empty = bars + 2 * S;     // [S] MMA -> loaders   (tcgen05.commit)
-    uint64_t* acc_full = bars + 3 * S;  // [1] MMA -> epilogue
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * S + 1);
+    uint64_t* full_a = bars;             // [S] loaders -> MMA   (count = loader warps)
+    uint64_t* full_b = bars + S;         // [S] bulk copy -> MMA (count = 1 + tx bytes)
+    uint64_t* empty = bars + 2 * S;      // [S] MMA -> loaders / W producer (tcgen05.commit)
+    uint64_t* acc_full = bars + 3 * S;   // [2] MMA -> epilogue
+    uint64_t* acc_empty = acc_full + 2;  // [2] epilogue -> MMA (count = epilogue warps)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+    // per-column epilogue affine  y = act(acc * sc[n] + sh[n])  (bias / scale / shift folded once per CTA)
+    float* s_sc = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tmem_slot + 4) + 15) & ~uintptr_t(15));
+    float* s_sh = s_sc + P.n_tiles * P.block_n;
+    for (int n = threadIdx.x; n < P.n_tiles * P.block_n; n += kThreads) {
+        float sc = 1.f, sh = 0.f;
+        if (n < A.N) {
+            if (A.bias) sh = __ldg(A.bias + n);
+            if (A.scale) { sc = __ldg(A.scale + n); sh *= sc; }
+            if (A.shift) sh += __ldg(A.shift + n);
+        }
+        s_sc[n] = sc;
+        s_sh[n] = sh;
+    }
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < S; ++s) {
@@ -184,134 +266,144 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
             mbar_init(&full_b[s], 1);
             mbar_init(&empty[s], 1);
         }
-        mbar_init(acc_full, 1);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&acc_full[b], 1);
+            mbar_init(&acc_empty[b], kEpiWarps);
+        }
         fence_barrier_init();
     }
     if (warp == 0) tmem_alloc(tmem_slot, static_cast<uint32_t>(P.tmem_cols));
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;                                   // main term accumulator
-    const uint32_t tmem_corr = tmem_base + static_cast<uint32_t>(P.block_n);  // correction terms accumulator
+    const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
         // ===================== MMA issuer =====================
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(P.block_n >> 3) << 17) |
                                (static_cast<uint32_t>(BM >> 4) << 24);
-        for (int kb = 0; kb < P.n_kb; ++kb) {
-            const int s = kb % S;
-            const uint32_t ph = static_cast<uint32_t>(kb / S) & 1u;
-            mbar_wait(&full_a[s], ph);
-            mbar_wait(&full_b[s], ph);
+        int g = 0;
+        for (int it = 0; it < my_tiles; ++it) {
+            const int ab = it & 1;
+            mbar_wait(&acc_empty[ab], ((static_cast<uint32_t>(it) >> 1) & 1u) ^ 1u);  // epilogue drained this buffer
             tc_fence_after();
-            if (lane == 0) {
-                const uint32_t sa = smem_u32(base + static_cast<size_t>(s) * stage_bytes);
-                const uint64_t a_hi = make_desc(sa), a_lo = make_desc(sa + kATileBytes);
-                const uint64_t b_hi = make_desc(sa + 2 * kATileBytes), b_lo = make_desc(sa + 2 * kATileBytes + b_tile_bytes);
+            const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(ab * P.block_n);
+            for (int kb = 0; kb < P.n_kb; ++kb, ++g) {
+                const int s = g % S;
+                const uint32_t ph = static_cast<uint32_t>(g / S) & 1u;
+                mbar_wait(&full_a[s], ph);
+                mbar_wait(&full_b[s], ph);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint32_t sa = smem_u32(base + static_cast<size_t>(s) * stage_bytes);
+                    const uint64_t a_hi = make_desc(sa), a_lo = make_desc(sa + kATileBytes);
+                    const uint64_t b_hi = make_desc(sa + 2 * kATileBytes), b_lo = make_desc(sa + 2 * kATileBytes + b_tile_bytes);
 #pragma unroll
-                for (int ks = 0; ks < BK / 8; ++ks) {  // UMMA_K = 8 tf32 = 32 bytes: descriptor start += 2
-                    const uint64_t adv = static_cast<uint64_t>(ks * 2);
-                    umma_tf32(tmem_base, a_hi + adv, b_hi + adv, idesc, (kb | ks) != 0 ? 1u : 0u);
-                    umma_tf32(tmem_corr, a_hi + adv, b_lo + adv, idesc, (kb | ks) != 0 ? 1u : 0u);
-                    umma_tf32(tmem_corr, a_lo + adv, b_hi + adv, idesc, 1u);
+                    for (int ks = 0; ks < BK / 8; ++ks) {  // UMMA_K = 8 tf32 = 32 bytes: descriptor start += 2
+                        const uint64_t adv = static_cast<uint64_t>(ks * 2);
+                        // small terms first, the main term last (one accumulator holds all three)
+                        umma_tf32(d_tmem, a_hi + adv, b_lo + adv, idesc, (kb | ks) != 0 ? 1u : 0u);
+                        umma_tf32(d_tmem, a_lo + adv, b_hi + adv, idesc, 1u);
+                        umma_tf32(d_tmem, a_hi + adv, b_hi + adv, idesc, 1u);
+                    }
+                    umma_commit(&empty[s]);                            // stage reusable once these MMAs retire
+                    if (kb == P.n_kb - 1) umma_commit(&acc_full[ab]);  // accumulator complete
                 }
-                umma_commit(&empty[s]);                       // stage reusable once these MMAs retire
-                if (kb == P.n_kb - 1) umma_commit(acc_full);  // accumulator complete
+                __syncwarp();
             }
-            __syncwarp();
         }
-    } else {
-        // ===================== loaders / converters =====================
-        const int t = threadIdx.x - 32;
-        constexpr int kVecPerRow = BK / VEC;
-        constexpr int kRowStep = kLoaderThreads / kVecPerRow;
-        constexpr int kIters = BM / kRowStep;
-        const int cv = t % kVecPerRow, rb = t / kVecPerRow;
-        const int kcol = cv * VEC;
-
-        for (int kb = 0; kb < P.n_kb; ++kb) {
-            const int s = kb % S;
-            const uint32_t ph = static_cast<uint32_t>(kb / S) & 1u;
-            int seg = 0;
-            while (seg + 1 < A.n_seg && kb >= P.kb_start[seg + 1]) ++seg;
-            const hg_lin_seg& G = A.seg[seg];
-            const int k = (kb - P.kb_start[seg]) * BK + kcol;
-
-            float v[kIters][VEC];
-#pragma unroll
-            for (int i = 0; i < kIters; ++i) {
-                const int64_t m = m0 + rb + i * kRowStep;
-                const bool row_ok = m < A.M;
-                const float* __restrict__ src = G.x + m * G.ldx + k;
-                if (row_ok && k + VEC <= G.K) {
-                    ldg_vec<VEC>(src, v[i]);
-                } else {
-#pragma unroll
-                    for (int e = 0; e < VEC; ++e) v[i][e] = (row_ok && k + e < G.K) ? __ldg(src + e) : 0.f;
-                }
-            }
-            mbar_wait(&empty[s], ph ^ 1u);  // MMAs of the previous use of this stage have retired
-            uint8_t* stage = base + static_cast<size_t>(s) * stage_bytes;
-            if (t == 0) {
+    } else if (warp == 1) {
+        // ===================== W producer =====================
+        if (lane == 0) {
+            for (int g = 0; g < G; ++g) {
+                const int s = g % S;
+                const uint32_t ph = static_cast<uint32_t>(g / S) & 1u;
+                const KbPos p = kb_pos(P, g);
+                mbar_wait(&empty[s], ph ^ 1u);
+                uint8_t* stage = base + static_cast<size_t>(s) * stage_bytes;
                 mbar_arrive_expect_tx(&full_b[s], 2u * b_tile_bytes);
-                const float* src = P.wp + (static_cast<int64_t>(n_tile) * P.n_kb + kb) * 2 * (b_tile_bytes / 4);
+                const float* src = P.wp + (static_cast<int64_t>(p.n_tile) * P.n_kb + p.kb) * 2 * (b_tile_bytes / 4);
                 bulk_g2s(stage + 2 * kATileBytes, src, 2u * b_tile_bytes, &full_b[s]);
             }
-#pragma unroll
-            for (int i = 0; i < kIters; ++i) {
-                const int r = rb + i * kRowStep;
-                float hi[VEC], lo[VEC];
-#pragma unroll
-                for (int e = 0; e < VEC; ++e) {
-                    hi[e] = tf32_rna(v[i][e]);
-                    lo[e] = tf32_rna(v[i][e] - hi[e]);
-                }
-                const uint32_t off = swz_off(r, kcol);
-                st_vec<VEC>(reinterpret_cast<float*>(stage + off), hi);
-                st_vec<VEC>(reinterpret_cast<float*>(stage + kATileBytes + off), lo);
-            }
+        }
+    } else if (warp < 2 + kLoaderWarps) {
+        // ===================== A loaders / converters =====================
+        using L = Loader<VEC>;
+        const int t = threadIdx.x - 64;
+        float v0[L::kIters][VEC], v1[L::kIters][VEC], v2[L::kIters][VEC];
+        auto finish = [&](int g, const float (&v)[L::kIters][VEC]) {
+            const int s = g % S;
+            const uint32_t ph = static_cast<uint32_t>(g / S) & 1u;
+            mbar_wait(&empty[s], ph ^ 1u);  // MMAs of the previous use of this stage have retired
+            L::store(base + static_cast<size_t>(s) * stage_bytes, t, v);
             fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
             __syncwarp();
             if (lane == 0) mbar_arrive(&full_a[s]);
+        };
+        if (0 < G) L::load(P, 0, t, v0);
+        if (1 < G) L::load(P, 1, t, v1);
+        if (2 < G) L::load(P, 2, t, v2);
+        for (int g = 0; g < G; g += kPrefetch) {
+            finish(g, v0);
+            if (g + 3 < G) L::load(P, g + 3, t, v0);
+            if (g + 1 < G) {
+                finish(g + 1, v1);
+                if (g + 4 < G) L::load(P, g + 4, t, v1);
+            }
+            if (g + 2 < G) {
+                finish(g + 2, v2);
+                if (g + 5 < G) L::load(P, g + 5, t, v2);
+            }
         }
-
+    } else {
         // ===================== epilogue =====================
-        mbar_wait(acc_full, 0);
-        tc_fence_after();
-        const int q = warp & 3;               // TMEM lane quarter this warp may read
-        const int half = (warp - 1) >> 2;     // two warps share a quarter: even / odd 16-column chunks
-        const int64_t m = m0 + q * 32 + lane;
+        const int q = warp & 3;  // TMEM lane quarter this warp may read
         const bool vec_store = (A.ldy % 4 == 0) && ((reinterpret_cast<uintptr_t>(A.y) & 15) == 0);
-        for (int c = half; c * 16 < P.block_n; c += 2) {
-            float acc[16], corr[16];
-            const uint32_t toff = (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(c * 16);
-            tmem_ld16(tmem_base + toff, acc);
-            tmem_ld16(tmem_corr + toff, corr);
+        for (int it = 0; it < my_tiles; ++it) {
+            const int ab = it & 1;
+            const int64_t tile = static_cast<int64_t>(blockIdx.x) + static_cast<int64_t>(it) * gridDim.x;
+            const int n0 = static_cast<int>(tile % P.n_tiles) * P.block_n;
+            const int64_t m = (tile / P.n_tiles) * BM + q * 32 + lane;
+            mbar_wait(&acc_full[ab], (static_cast<uint32_t>(it) >> 1) & 1u);
+            tc_fence_after();
+            const uint32_t t_acc = tmem_base + static_cast<uint32_t>(ab * P.block_n) + (static_cast<uint32_t>(q * 32) << 16);
+            const int act = A.act;
+            for (int c = 0; c * 16 < P.block_n; ++c) {
+                float acc[16];
+                tmem_ld16(t_acc + static_cast<uint32_t>(c * 16), acc);
+                const int n = n0 + c * 16;
+                if (m >= A.M || n >= A.N) continue;
+                const float4* sc4 = reinterpret_cast<const float4*>(s_sc + n);
+                const float4* sh4 = reinterpret_cast<const float4*>(s_sh + n);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) acc[j] += corr[j];
-            const int n = n0 + c * 16;
-            if (m >= A.M || n >= A.N) continue;
+                for (int j4 = 0; j4 < 4; ++j4) {
+                    const float4 sc = sc4[j4], sh = sh4[j4];  // broadcast LDS.128
+                    acc[4 * j4 + 0] = fmaf(acc[4 * j4 + 0], sc.x, sh.x);
+                    acc[4 * j4 + 1] = fmaf(acc[4 * j4 + 1], sc.y, sh.y);
+                    acc[4 * j4 + 2] = fmaf(acc[4 * j4 + 2], sc.z, sh.z);
+                    acc[4 * j4 + 3] = fmaf(acc[4 * j4 + 3], sc.w, sh.w);
+                }
+                if (act == HG_ACT_RELU) {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const int nn = n + j;
-                if (nn < A.N) {
-                    float o = acc[j];
-                    if (A.bias) o += __ldg(A.bias + nn);
-                    if (A.scale) o *= __ldg(A.scale + nn);
-                    if (A.shift) o += __ldg(A.shift + nn);
-                    acc[j] = apply_act(o, A.act);
+                    for (int j = 0; j < 16; ++j) acc[j] = fmaxf(acc[j], 0.f);
+                } else if (act == HG_ACT_ELU) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) acc[j] = acc[j] > 0.f ? acc[j] : expm1f(acc[j]);
+                }
+                float* dst = A.y + m * A.ldy + n;
+                if (vec_store && n + 16 <= A.N) {
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4)
+                        *reinterpret_cast<float4*>(dst + j) = make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        if (n + j < A.N) dst[j] = acc[j];
                 }
             }
-            float* dst = A.y + m * A.ldy + n;
-            if (vec_store && n + 16 <= A.N) {
-#pragma unroll
-                for (int j = 0; j < 16; j += 4)
-                    *reinterpret_cast<float4*>(dst + j) = make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
-            } else {
-#pragma unroll
-                for (int j = 0; j < 16; ++j)
-                    if (n + j < A.N) dst[j] = acc[j];
-            }
+            tc_fence_before();  // all tcgen05.ld of this buffer done (tmem_ld16 waits) -> hand it back
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[ab]);
         }
     }
 
@@ -340,15 +432,27 @@ bool plan(const hg_linear_args& a, TcParams& P) {
     for (int s = a.n_seg; s <= HG_MAX_SEGMENTS; ++s) P.kb_start[s] = kb;
     P.n_kb = kb;
     P.vec = vec;
+    P.m_tiles = ceil_div<int64_t>(a.M, BM);
     const size_t stage_bytes = 2 * kATileBytes + 2 * static_cast<size_t>(P.block_n) * 128;
-    int stages = static_cast<int>(kSmemBudget / stage_bytes);
+    const size_t affine_bytes = 2 * static_cast<size_t>(P.n_tiles) * P.block_n * sizeof(float);
+    if (affine_bytes > 32 * 1024) return false;  // N <= 4096
+    int stages = static_cast<int>((kSmemBudget - affine_bytes) / stage_bytes);
     stages = stages > 4 ? 4 : stages;
-    stages = stages > P.n_kb ? (P.n_kb > 0 ? P.n_kb : 1) : stages;
     P.stages = stages;
     int cols = 32;
-    while (cols < 2 * P.block_n) cols <<= 1;  // main + correction accumulators
+    while (cols < 2 * P.block_n) cols <<= 1;  // two accumulator buffers
     P.tmem_cols = cols;
-    return stages >= 1 && P.n_kb >= 1;
+    return stages >= 1 && P.n_kb >= 1 && cols <= 512;
+}
+
+size_t packed_bytes(const TcParams& P) { return static_cast<size_t>(P.n_tiles) * P.n_kb * 2 * P.block_n * 128; }
+
+int pack_launch(const TcParams& P, float* dst, cudaStream_t stream) {
+    const int64_t pack_elems = static_cast<int64_t>(P.n_tiles) * P.n_kb * P.block_n * BK;
+    const int64_t want = ceil_div<int64_t>(pack_elems, 256);
+    const unsigned pack_grid = static_cast<unsigned>(want < 1184 ? want : 1184);
+    k_pack_w<<<pack_grid, 256, 0, stream>>>(P, dst);
+    return check_launch();
 }
 
 }  // namespace
@@ -360,34 +464,40 @@ int linear_tc_supported(const hg_linear_args& a) {
     return k_total >= 1 ? 1 : 0;
 }
 
-size_t linear_tc_workspace_bytes(const hg_linear_args& a) {
+size_t linear_tc_packed_bytes(const hg_linear_args& a) {
     TcParams P;
     if (!plan(a, P)) return 0;
-    return static_cast<size_t>(P.n_tiles) * P.n_kb * 2 * P.block_n * 128 + 256;
+    return packed_bytes(P);
+}
+
+// Split + swizzle the weights of `a` into `dst` (reusable for every call with the same weights / N / K layout).
+int linear_tc_pack(const hg_linear_args& a, void* dst, size_t dst_bytes, cudaStream_t stream) {
+    TcParams P;
+    if (!plan(a, P)) return HG_EUNSUPPORTED;
+    if (!dst || dst_bytes < packed_bytes(P)) return HG_EWORKSPACE;
+    if (!aligned(dst, 128)) return HG_EALIGN;
+    return pack_launch(P, static_cast<float*>(dst), stream);
 }
 
 int linear_tc_launch(const hg_linear_args& a, void* ws, size_t ws_bytes, cudaStream_t stream) {
     TcParams P;
     if (!plan(a, P)) return HG_EUNSUPPORTED;
-    const size_t need = static_cast<size_t>(P.n_tiles) * P.n_kb * 2 * P.block_n * 128;
-    if (!ws || ws_bytes < need) return HG_EWORKSPACE;
+    if (!ws || ws_bytes < packed_bytes(P)) return HG_EWORKSPACE;
     if (!aligned(ws, 128)) return HG_EALIGN;
     P.wp = static_cast<const float*>(ws);
-
-    const int64_t pack_elems = static_cast<int64_t>(P.n_tiles) * P.n_kb * P.block_n * BK;
-    const unsigned pack_grid = static_cast<unsigned>(ceil_div<int64_t>(pack_elems, 256) < 1184 ? ceil_div<int64_t>(pack_elems, 256) : 1184);
-    k_pack_w<<<pack_grid, 256, 0, stream>>>(P, static_cast<float*>(ws));
-    int rc = check_launch();
-    if (rc != HG_OK) return rc;
-
+    if (!a.w_prepacked) {
+        const int rc = pack_launch(P, static_cast<float*>(ws), stream);
+        if (rc != HG_OK) return rc;
+    }
     const size_t stage_bytes = 2 * kATileBytes + 2 * static_cast<size_t>(P.block_n) * 128;
-    const size_t smem = 1024 + P.stages * stage_bytes + (3 * P.stages + 1) * sizeof(uint64_t) + 16;
-    const int64_t m_tiles = ceil_div<int64_t>(a.M, BM);
-    const int64_t grid = m_tiles * P.n_tiles;
-    if (grid >= (int64_t(1) << 31)) return HG_ERANGE;
+    const size_t smem = 1024 + P.stages * stage_bytes + (3 * P.stages + 4) * sizeof(uint64_t) + 48 +
+                        2 * static_cast<size_t>(P.n_tiles) * P.block_n * sizeof(float);
+    const int64_t total = P.m_tiles * P.n_tiles;
+    const int sms = sm_count() > 0 ? sm_count() : 148;
+    const unsigned grid = static_cast<unsigned>(total < sms ? total : sms);  // persistent: one CTA per SM
     auto go = [&](auto kernel) -> int {
         HG_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-        kernel<<<static_cast<unsigned>(grid), kThreads, smem, stream>>>(P);
+        kernel<<<grid, kThreads, smem, stream>>>(P);
         return check_launch();
     };
     if (P.vec == 4) return go(k_linear_tc<4>);

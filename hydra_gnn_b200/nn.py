@@ -55,7 +55,7 @@ class Linear(nn.Module):
             nn.init.uniform_(self.bias, -bound, bound)
 
     def forward(self, x: Tensor, act: str = None) -> Tensor:
-        return ops.linear([(x, self.weight)], self.out_channels, bias=self.bias, act=act)
+        return ops.linear([(x, self.weight)], self.out_channels, bias=self.bias, act=act, pack_cache=_wcache(self, "w"))
 
 
 # =============================================================================== graph plan
@@ -112,6 +112,11 @@ class PlanCache:
             plan.csr[(r.key, r.self_loops)] = c
         self._sig, self._plan = (sig, plan) if self.enabled else (None, None)
         return plan
+
+
+def _wcache(owner, site: str) -> dict:
+    """Per-(module, call site) cache of the packed weight image read by the tensor-core projection."""
+    return owner.__dict__.setdefault("_wpack", {}).setdefault(site, {})
 
 
 def _param_signature(params: Sequence[Optional[Tensor]]):
@@ -206,6 +211,7 @@ class _GatPack:
         self.as_off: Dict[EdgeType, int] = {}
         self.ad_off: Dict[EdgeType, int] = {}
         self.v_edge: Dict[EdgeType, Tensor] = {}
+        self.wcache: Dict[str, dict] = {}
         types: List[str] = []
         for s, _, d in rels:
             for t in (s, d):
@@ -273,7 +279,7 @@ def run_gat_layer(convs: Dict[EdgeType, GATConv], rels: Sequence[EdgeType], x: D
     if only_dst is not None:
         rels = [et for et in rels if et[2] in only_dst]
     pack = _gat_pack(owner, convs, rels, x)
-    Y = {T: ops.linear([(x[T], W)], W.size(0)) for T, W in pack.W.items()}
+    Y = {T: ops.linear([(x[T], W)], W.size(0), pack_cache=pack.wcache.setdefault(T, {})) for T, W in pack.W.items()}
     out: Dict[str, Tensor] = {}
     for T in dict.fromkeys(et[2] for et in rels):
         grp: List[GatRelation] = []
@@ -328,7 +334,8 @@ def run_sage(conv: SAGEConv, x_src: Tensor, x_dst: Tensor, csr: CSR, act: str = 
     d_in, d_out = conv.in_channels[0], conv.out_channels
     if d_in <= d_out or x_src is not x_dst:
         mean = ops.seg_reduce(x_src, csr, "mean")
-        return ops.linear([(mean, conv.lin_l.weight), (x_dst, conv.lin_r.weight)], d_out, bias=conv.lin_l.bias, act=act)
+        return ops.linear([(mean, conv.lin_l.weight), (x_dst, conv.lin_r.weight)], d_out, bias=conv.lin_l.bias, act=act,
+                          pack_cache=_wcache(conv, "lr"))
     W = torch.cat([conv.lin_l.weight, conv.lin_r.weight], dim=0)
     Y = ops.linear([(x_src, W)], 2 * d_out)
     return ops.seg_reduce(Y[:, :d_out], csr, "mean", x_self=Y[:, d_out:], self_coef_add=1.0, bias=conv.lin_l.bias,
@@ -359,7 +366,7 @@ def run_hetero_sage(convs: Dict[EdgeType, SAGEConv], rels: Sequence[EdgeType], x
         w_root, bias, w_l = cache[T][1]
         segs = [(ops.seg_reduce(x[et[0]], csr[et], "mean"), w) for et, w in zip(mine, w_l)]
         segs.append((x[T], w_root))
-        out[T] = ops.linear(segs, convs[mine[0]].out_channels, bias=bias, act=act)
+        out[T] = ops.linear(segs, convs[mine[0]].out_channels, bias=bias, act=act, pack_cache=_wcache(owner, "sage_" + T))
     return out
 
 
@@ -387,7 +394,7 @@ class GCNConv(nn.Module):
 
 
 def run_gcn(conv: GCNConv, x: Tensor, csr: CSR, act: str = None) -> Tensor:
-    y = ops.linear([(x, conv.lin.weight)], conv.out_channels)
+    y = ops.linear([(x, conv.lin.weight)], conv.out_channels, pack_cache=_wcache(conv, "lin"))
     return ops.seg_reduce(y, csr, "sum", src_scale=csr.inv_sqrt_deg, dst_scale=csr.inv_sqrt_deg, bias=conv.bias, act=act)
 
 
@@ -420,7 +427,7 @@ def run_gin(conv: GINConv, x: Tensor, csr: CSR, act: str = None, bn: "BatchNorm"
             if last and bn is not None:
                 scale, shift = bn.affine()
             h = ops.linear([(h, m.weight)], m.out_features, bias=m.bias, scale=scale, shift=shift,
-                           act="relu" if fuse_relu else (act if last else None))
+                           act="relu" if fuse_relu else (act if last else None), pack_cache=_wcache(conv, f"nn{k}"))
         elif isinstance(m, nn.ReLU):
             continue  # fused into the preceding projection
         else:

@@ -265,8 +265,12 @@ def gat_fused(rels: Sequence[GatRelation], n_dst: int, H: int, Cc: int, concat: 
 
 # ------------------------------------------------------------------------------ K6
 def linear(segments: Sequence, N: int, *, bias: Tensor = None, scale: Tensor = None, shift: Tensor = None,
-           act: str = None, precision: str = None, out: Tensor = None) -> Tensor:
-    """``y = act((sum_s x_s @ W_s^T + bias) * scale + shift)``; ``segments`` = [(x_s, W_s), ...]."""
+           act: str = None, precision: str = None, out: Tensor = None, pack_cache: dict = None) -> Tensor:
+    """``y = act((sum_s x_s @ W_s^T + bias) * scale + shift)``; ``segments`` = [(x_s, W_s), ...].
+
+    ``pack_cache``: a dict owned by whoever owns the weights (a layer module).  The tensor-core path
+    reads a split + swizzled image of W; with a cache the image is built once per weight version
+    (``hg_linear_pack_weights``) and every later call is a single kernel launch."""
     h = lib()
     if not 1 <= len(segments) <= _lib.HG_MAX_SEGMENTS:
         raise ValueError("1..8 K-segments")
@@ -293,11 +297,28 @@ def linear(segments: Sequence, N: int, *, bias: Tensor = None, scale: Tensor = N
         precision = "tf32x3" if M >= TC_MIN_ROWS else "fp32"
     a.precision = PREC[precision]
     a.y, a.ldy = ptr(out), _ld(out)
-    nbytes = h.hg_linear_workspace_bytes(C.byref(a))
-    ws = _workspace(device, nbytes) if nbytes else None
     meta = dict(M=M, N=N, K=[x.size(1) for x, _ in keep], precision=precision)
+    if M == 0 or N == 0:
+        return out
+    nbytes = h.hg_linear_workspace_bytes(C.byref(a))
+    ws = None
+    if nbytes and pack_cache is not None:
+        key = (N, tuple((w.data_ptr(), w._version, w.size(1), _ld(w)) for _, w in keep))
+        ws = pack_cache.get(key)
+        if ws is None:
+            pack_cache.clear()  # one live image per owner: older weight versions are dead
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+            _call("hg_linear_pack_weights", dict(bytes=nbytes),
+                  lambda: h.hg_linear_pack_weights(C.byref(a), ptr(ws), nbytes, stream_ptr()))
+            _lib.launch_count += 1
+            pack_cache[key] = ws
+        a.w_prepacked = 1
+        launches = 1
+    else:
+        ws = _workspace(device, nbytes) if nbytes else None
+        launches = 2 if nbytes else 1
     _call("hg_linear", meta, lambda: h.hg_linear(C.byref(a), ptr(ws), nbytes, stream_ptr()))
-    _lib.launch_count += 1
+    _lib.launch_count += launches
     return out
 
 

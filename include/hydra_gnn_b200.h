@@ -215,9 +215,16 @@ typedef struct hg_linear_args {
     int32_t act;         /* HG_ACT_* */
     int32_t precision;   /* HG_PREC_* */
     float* y; int64_t ldy;
+    int32_t w_prepacked; /* 1: `workspace` already holds the image written by hg_linear_pack_weights for these
+                            weights (same N, K segmentation); the call then launches ONE kernel */
+    int32_t reserved;
 } hg_linear_args;
 
+/* Bytes of the split + swizzled weight image the tensor-core path reads (0 for HG_PREC_FP32): the size of
+ * `workspace` for hg_linear and of `dst` for hg_linear_pack_weights.  Depends on N and the K segments only. */
 HG_API size_t hg_linear_workspace_bytes(const hg_linear_args* args_host);
+/* Weights are constant across the batches of an inference run: pack them once (x / y / M are ignored). */
+HG_API int hg_linear_pack_weights(const hg_linear_args* args_host, void* dst, size_t dst_bytes, void* stream);
 HG_API int hg_linear(const hg_linear_args* args_host, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------
