@@ -28,6 +28,8 @@ import torch  # noqa: E402
 METRIC = "scene_graphs_per_s_forward"
 UNIT = "graphs/s"
 GRAPHS_PER_GPU = 4096
+WORKLOAD = ("configs[1]: synthetic MP3D-shaped room/object HeteroData (306-d object features), heterogeneous GAT "
+            "(M-GAT) forward, 4096 graphs per GPU per step, graph plan (K1) rebuilt every step")
 M_GAT = dict(input_dim_dict={"objects": 306, "rooms": 6}, output_dim=26, conv_block="GAT", GAT_hidden_dims=[64, 64],
              GAT_heads=[3, 3, 3], GAT_concats=[False, False, False], dropout=0.4)
 
@@ -163,10 +165,12 @@ def roofline_from(sink, steps, peaks):
 
 
 # ------------------------------------------------------------------------------ CPU arm (oracle port)
-def cpu_forward_rate(n_graphs: int, iters: int, warmup: int = 1):
+def cpu_forward_rate(n_graphs: int, min_seconds: float, max_iters: int, warmup: int = 1):
     """The reference's CPU path for this workload: PyG is not installable here, so this is the
     oracle port (plain-torch restatement of PyG's gather/scatter operators hosting the
-    reference's model control flow), all host threads.  Returns (graphs/s, threads, seconds)."""
+    reference's model control flow), all host threads.  Runs whole forwards over the SAME
+    n_graphs batch until ``min_seconds`` of work (at most ``max_iters``).
+    Returns (graphs/s, threads, seconds, iterations)."""
     from hydra_gnn_b200 import synth
     from oracle import models as om  # the one place bench.py executes oracle/: the CPU baseline
 
@@ -176,70 +180,90 @@ def cpu_forward_rate(n_graphs: int, iters: int, warmup: int = 1):
     with torch.no_grad():
         for _ in range(warmup):
             ref(data)
-        t0 = time.perf_counter()
-        for _ in range(iters):
+        iters, t0 = 0, time.perf_counter()
+        while iters < max_iters and (iters == 0 or time.perf_counter() - t0 < min_seconds):
             ref(data)
+            iters += 1
         dt = time.perf_counter() - t0
-    return n_graphs * iters / dt, torch.get_num_threads(), dt
+    return n_graphs * iters / dt, torch.get_num_threads(), dt, iters
 
 
 def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU path (oracle port) on the host cores, same config;
+    each step = one forward over the full 4096-graph batch (about 1 s of CPU work)."""
     if rank != 0:
         return
-    sample = 512
-    rates = []
-    for _ in range(args.warmup):
-        cpu_forward_rate(sample, 1, warmup=0)
-    t0 = time.perf_counter()
-    rate, threads, _ = cpu_forward_rate(sample, args.steps, warmup=0)
-    dt = time.perf_counter() - t0
+    from hydra_gnn_b200 import synth
+    from oracle import models as om
+
+    torch.set_num_threads(os.cpu_count() or 1)
+    G = args.graphs
+    ref = synth.random_state_dict_(om.HeterogeneousNetwork(**M_GAT), seed=0).eval()
+    data = synth.synth_mp3d_batch(range(G))
+    with torch.no_grad():
+        for _ in range(args.warmup):
+            ref(data)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            ref(data)
+        dt = time.perf_counter() - t0
+    rate, threads = G * args.steps / dt, torch.get_num_threads()
     line = {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * sample / rate, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "configs[1]: synthetic MP3D-shaped hetero GAT (M-GAT) forward", "graphs_per_step": sample},
+        "config": {"workload": WORKLOAD, "graphs_per_gpu": G},
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": f"{sample} graphs per step x {args.steps} steps of the same synthetic workload "
-                                   "(oracle port of the PyG CPU path; PyG itself is not installable on this image)"},
+                         "sample": f"{args.steps} forwards over the full {G}-graph batch ({dt:.1f} s; oracle port of the "
+                                   "PyG CPU path, all host threads; PyG itself is not installable on this image)"},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
 
 
-# ------------------------------------------------------------------------------ GPU arm
+def _traffic_table():
+    """ncu-measured DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum), committed
+    under profiles/ by the round's ncu --set full capture; None when no capture matches."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f)
+    return {}
+
+
 def run_ours(args, rank, world, local_rank):
     import hydra_gnn_b200 as hg
     from hydra_gnn_b200 import _lib, ops, synth
+    from hydra_gnn_b200.dist import LogitGather, shard_range
     import torch.distributed as dist
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     G = args.graphs
-    ids = range(rank * G, (rank + 1) * G)  # shard by contiguous graph-id range; no data-path exchange
+    lo, hi = shard_range(G * world, rank, world)  # shard by contiguous graph-id range; no data-path exchange
+    ids = range(lo, hi)
     host = synth.synth_mp3d_batch(ids, pin=True)
-    ref_sd = None
     net = hg.HeterogeneousNetwork(**M_GAT)
     synth.random_state_dict_(net, seed=0)
     net = net.eval().to(dev)
     net.plan_cache.enabled = False  # K1 (graph plan) is rebuilt every step: it is part of the path
 
-    resident = synth.synth_mp3d_batch(ids, device=dev)
-    n_rooms = resident["rooms"].x.size(0)
-    h2d = host.nbytes()
-    max_rooms = None
-    if world > 1:
-        cnt = torch.tensor([n_rooms], device=dev, dtype=torch.int64)
-        dist.all_reduce(cnt, op=dist.ReduceOp.MAX)
-        max_rooms = int(cnt.item())
-        gather_buf = torch.empty(world * max_rooms, 26, device=dev)
-        pad = torch.zeros(max_rooms, 26, device=dev)
+    def device_copy():
+        d = hg.data.HeteroData()
+        for t in host.node_types:
+            d[t].x = host[t].x.to(dev)
+        for t in host.edge_types:
+            d[t].edge_index = host[t].edge_index.to(dev)
+        return d
+
+    n_rooms = host["rooms"].x.size(0)
+    gather = LogitGather(26).prepare(n_rooms, dev) if world > 1 else None
 
     def step(data):
         logits = net(data)
-        if world > 1:  # the only collective on the path: gather of the room logits (config 4)
-            pad[:n_rooms].copy_(logits)
-            dist.all_gather_into_tensor(gather_buf, pad)
+        if gather is not None:  # the only collective on the path: gather of the room logits (config 4)
+            gather(logits)
         return logits
 
     def fence():
@@ -247,44 +271,91 @@ def run_ours(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    # ---- static buffers + captured steps (CUDA graphs: the forward is 20-odd short kernels)
+    bufs = [device_copy(), device_copy()]
+    outs = [None, None]
+    for b in bufs:  # eager warm-up: packs weights, sizes workspaces
+        step(b)
+    fence()
+    graphs = [None, None]
+    use_graph = not args.no_graph
+    if use_graph:
+        cap_stream = torch.cuda.Stream(dev)
+        with torch.cuda.stream(cap_stream):
+            for k in range(2):
+                step(bufs[k])
+            cap_stream.synchronize()
+            for k in range(2):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=cap_stream):
+                    outs[k] = step(bufs[k])
+                graphs[k] = g
+        fence()
+
+    def run(k):
+        if use_graph:
+            graphs[k].replay()
+            return outs[k]
+        return step(bufs[k])
+
     # ---- device-resident arm (value): inputs already in HBM
     for _ in range(args.warmup):
-        step(resident)
+        run(0)
     fence()
-    sink = []
-    ops.set_profile_sink(sink)
-    launches0 = _lib.launch_count
     with ClockSampler(local_rank) as clocks:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(args.steps):
-            step(resident)
+            run(0)
         e1.record()
         fence()
-    ops.set_profile_sink(None)
-    launches = _lib.launch_count - launches0
     ms = e0.elapsed_time(e1)
 
-    # ---- end-to-end arm (e2e): pinned host buffers -> H2D -> forward -> D2H of the logits
-    out_host = torch.empty(n_rooms, 26, pin_memory=True)
+    # ---- roofline leg: the same K steps launched eagerly with a CUDA-event pair around every launch
+    sink = []
+    ops.set_profile_sink(sink)
+    launches0 = _lib.launch_count
+    for _ in range(args.steps):
+        step(bufs[0])
+    fence()
+    ops.set_profile_sink(None)
+    launches = _lib.launch_count - launches0
 
-    def e2e_step():
-        d = hg.data.HeteroData()
-        for t in host.node_types:
-            d[t].x = host[t].x.to(dev, non_blocking=True)
-        for t in host.edge_types:
-            d[t].edge_index = host[t].edge_index.to(dev, non_blocking=True)
-        out_host.copy_(step(d), non_blocking=True)
+    # ---- end-to-end arm (e2e): pinned host buffers -> H2D -> forward -> D2H of the logits, double-buffered:
+    # the copy engine fills buffer k+1 while the SMs run the step on buffer k.
+    out_host = [torch.empty(n_rooms, 26, pin_memory=True) for _ in range(2)]
+    copy_stream, main = torch.cuda.Stream(dev), torch.cuda.current_stream(dev)
+    loaded = [torch.cuda.Event() for _ in range(2)]
+    freed = [torch.cuda.Event() for _ in range(2)]
+
+    def upload(k):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(freed[k])  # the step that read buffer k has finished
+            for t in host.node_types:
+                bufs[k][t].x.copy_(host[t].x, non_blocking=True)
+            for t in host.edge_types:
+                bufs[k][t].edge_index.copy_(host[t].edge_index, non_blocking=True)
+            loaded[k].record(copy_stream)
+
+    def e2e_loop(n):
+        for k in range(2):
+            freed[k].record(main)
+        upload(0)
+        for i in range(n):
+            k = i & 1
+            if i + 1 < n:
+                upload(k ^ 1)
+            main.wait_event(loaded[k])
+            out_host[k].copy_(run(k), non_blocking=True)
+            freed[k].record(main)
 
     h2d = sum(host[t].x.numel() * 4 for t in host.node_types) + sum(host[t].edge_index.numel() * 8 for t in host.edge_types)
-    d2h = out_host.numel() * 4
-    for _ in range(args.warmup):
-        e2e_step()
+    d2h = out_host[0].numel() * 4
+    e2e_loop(max(args.warmup, 2))
     fence()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
-    for _ in range(args.steps):
-        e2e_step()
+    e2e_loop(args.steps)
     f1.record()
     fence()
     ms_e2e = f0.elapsed_time(f1)
@@ -297,29 +368,33 @@ def run_ours(args, rank, world, local_rank):
         return
     peaks = _peaks()
     roof, table = roofline_from(sink, args.steps, peaks)
+    traffic = _traffic_table()
+    roof["traffic"] = traffic.get(roof["kernel"])
+    roof["timing"] = "eager pass of the same K steps, one CUDA-event pair per launch (the value arm replays CUDA graphs)"
     total_graphs = G * world
     line = {
         "metric": METRIC, "value": total_graphs * args.steps / (ms / 1e3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "configs[1]: synthetic MP3D-shaped hetero GAT (M-GAT) forward, plan (K1) rebuilt every step",
-                   "graphs_per_gpu": G, "objects": int(resident["objects"].x.size(0)), "rooms": int(n_rooms),
-                   "edges": {et[1]: int(resident[et].edge_index.size(1)) for et in resident.edge_types},
-                   "l2": "inputs larger than L2 (object features 297 MB + 390 MB projections per layer vs 126 MB L2)",
-                   "projection_precision": ops.DEFAULT_PRECISION,
+        "config": {"workload": WORKLOAD,
+                   "graphs_per_gpu": G, "objects": int(host["objects"].x.size(0)), "rooms": int(n_rooms),
+                   "edges": {et[1]: int(host[et].edge_index.size(1)) for et in host.edge_types},
+                   "l2": "inputs larger than L2 (object features 297 MB + ~190 MB of projections per layer vs 126 MB L2)",
+                   "projection_precision": ops.DEFAULT_PRECISION, "cuda_graph": use_graph,
                    "collective": "all_gather_into_tensor(room logits)" if world > 1 else "none"},
         "e2e": {"value": total_graphs * args.steps / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
+                "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps,
+                "pipeline": "double-buffered: H2D of step k+1 overlaps the forward of step k"},
         "gpu_launches": launches,
         "clocks": clocks.summary(),
         "roofline": roof,
         "kernels": table,
     }
     if world == 1 and not args.no_cpu:
-        rate, threads, secs = cpu_forward_rate(args.cpu_graphs, args.cpu_iters)
+        rate, threads, secs, iters = cpu_forward_rate(G, args.cpu_seconds, 40)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
-                                "sample": f"{args.cpu_graphs} graphs x {args.cpu_iters} forwards of the same workload "
-                                          f"({secs:.1f} s; oracle port of the PyG CPU path, all host threads)"}
+                                "sample": f"{iters} forwards over the same {G}-graph batch ({secs:.1f} s; oracle port of "
+                                          "the PyG CPU path, all host threads)"}
     print(json.dumps(line), flush=True)
 
 
@@ -332,8 +407,8 @@ def main():
     ap.add_argument("--graphs", type=int, default=GRAPHS_PER_GPU, help="graphs per GPU per step")
     ap.add_argument("--precision", default=None, choices=[None, "fp32", "tf32x3"])
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--cpu-graphs", type=int, default=1024)
-    ap.add_argument("--cpu-iters", type=int, default=3)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU-baseline sample: seconds of CPU work")
+    ap.add_argument("--no-graph", action="store_true", help="launch every step eagerly instead of replaying a CUDA graph")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

@@ -199,19 +199,40 @@ def _pad4(n: int) -> int:
     return (n + 3) // 4 * 4
 
 
-class _GatPack:
-    """Packed projection weights of one GAT layer: per node type one ``[cols, in]`` matrix whose
-    rows are, in order: the ``lin_src`` blocks of every relation leaving the type (each padded
-    to a multiple of 4 rows), the folded ``att_src`` rows of those relations, the folded
-    ``att_dst`` rows of every relation entering the type."""
+AGG_FIRST_RATIO = 4  # a relation aggregates first when it has >= 4x fewer destinations than sources
 
-    def __init__(self, convs: Dict[EdgeType, GATConv], rels: Sequence[EdgeType], in_dims: Dict[str, int]):
+
+def _gat_modes(convs, rels: Sequence[EdgeType], x: Dict[str, Tensor], group: str) -> Tuple[bool, ...]:
+    """Per relation: True = aggregate-first (``out_h = W_h (sum_e w_eh x_j)``: gather the raw source
+    rows with the H weight sets, project the few aggregated rows afterwards), False = project-first.
+    Same value up to fp32 re-association.  Chosen by shapes only (host-known, no sync): far fewer
+    destinations than sources AND raw rows no wider than the projected ones (else the gather of the
+    raw rows costs more than the projection it saves -- the 306-d input layer stays project-first)."""
+    if group != "sum":
+        return tuple(False for _ in rels)
+    return tuple(x[et[2]].size(0) * AGG_FIRST_RATIO <= x[et[0]].size(0)
+                 and x[et[0]].size(1) <= convs[et].heads * convs[et].out_channels for et in rels)
+
+
+class _GatPack:
+    """Packed projection weights of one GAT layer.  Per node type one ``[cols, in]`` matrix whose rows
+    are, in order: the ``lin_src`` blocks of every PROJECT-FIRST relation leaving the type (each padded
+    to a multiple of 4 rows), the folded ``att_src`` rows of every relation leaving it, the folded
+    ``att_dst`` rows of every relation entering it.  Per aggregate-first relation the re-arranged
+    ``lin_src`` applied after the aggregation (``[C, H*K]`` with the head mean folded in, or the
+    block-diagonal ``[H*C, H*K]`` for concat)."""
+
+    def __init__(self, convs: Dict[EdgeType, GATConv], rels: Sequence[EdgeType], in_dims: Dict[str, int],
+                 modes: Sequence[bool]):
         self.W: Dict[str, Tensor] = {}
         self.xs_off: Dict[EdgeType, int] = {}
         self.as_off: Dict[EdgeType, int] = {}
         self.ad_off: Dict[EdgeType, int] = {}
         self.v_edge: Dict[EdgeType, Tensor] = {}
+        self.w_post: Dict[EdgeType, Tensor] = {}
+        self.post_bias: Dict[str, Optional[Tensor]] = {}
         self.wcache: Dict[str, dict] = {}
+        self.agg_first = dict(zip(rels, modes))
         types: List[str] = []
         for s, _, d in rels:
             for t in (s, d):
@@ -220,7 +241,7 @@ class _GatPack:
         for T in types:
             blocks, col = [], 0
             for et in rels:
-                if et[0] != T:
+                if et[0] != T or self.agg_first[et]:
                     continue
                 c = convs[et]
                 W = c.lin_src.weight
@@ -252,21 +273,35 @@ class _GatPack:
             c = convs[et]
             if c.lin_edge is not None:
                 self.v_edge[et] = GATConv.fold(c.att_edge, c.lin_edge.weight, c.heads, c.out_channels).contiguous()
+            if self.agg_first[et]:
+                H, C = c.heads, c.out_channels
+                W3 = c.lin_src.weight.reshape(H, C, -1)  # [H, C, K]
+                K = W3.size(2)
+                if c.concat:
+                    Wp = W3.new_zeros(H * C, H * K)
+                    for h in range(H):
+                        Wp[h * C:(h + 1) * C, h * K:(h + 1) * K] = W3[h]
+                else:
+                    Wp = (W3.permute(1, 0, 2).reshape(C, H * K) / H)
+                self.w_post[et] = Wp.contiguous()
+        for T in dict.fromkeys(et[2] for et in rels):
+            bs = [convs[et].bias for et in rels if et[2] == T and self.agg_first[et] and convs[et].bias is not None]
+            self.post_bias[T] = torch.stack(bs).sum(0).contiguous() if bs else None
 
 
 def _gat_pack(owner: nn.Module, convs: Dict[EdgeType, GATConv], rels: Sequence[EdgeType],
-              x: Dict[str, Tensor]) -> _GatPack:
+              x: Dict[str, Tensor], modes: Sequence[bool]) -> _GatPack:
     params: List[Optional[Tensor]] = []
     for et in rels:
         c = convs[et]
-        params += [c.lin_src.weight, c.lin_dst.weight, c.att_src, c.att_dst, c.att_edge,
+        params += [c.lin_src.weight, c.lin_dst.weight, c.att_src, c.att_dst, c.att_edge, c.bias,
                    c.lin_edge.weight if c.lin_edge is not None else None]
-    sig = (tuple(rels), _param_signature(params))
+    sig = (tuple(rels), tuple(modes), _param_signature(params))
     cached = getattr(owner, "_pack", None)
     if cached is not None and cached[0] == sig:
         return cached[1]
     with torch.no_grad():
-        pack = _GatPack(convs, rels, {t: v.size(1) for t, v in x.items()})
+        pack = _GatPack(convs, rels, {t: v.size(1) for t, v in x.items()}, modes)
     owner._pack = (sig, pack)
     return pack
 
@@ -275,14 +310,19 @@ def run_gat_layer(convs: Dict[EdgeType, GATConv], rels: Sequence[EdgeType], x: D
                   csr: Dict[EdgeType, CSR], *, act: str = None, group: str = "sum",
                   edge_attr: Dict[EdgeType, Tensor] = None, owner: nn.Module = None,
                   only_dst: Sequence[str] = None) -> Dict[str, Tensor]:
-    """One GAT layer over ``rels`` (HeteroConv semantics; a homogeneous layer is the 1-relation case)."""
+    """One GAT layer over ``rels`` (HeteroConv semantics; a homogeneous layer is the 1-relation case).
+
+    Per node type ONE projection (sources of the project-first relations + all attention logits);
+    per destination type: the aggregate-first relations (gather raw rows -> small projection),
+    then ONE fused aggregation of the project-first relations that adds that partial result,
+    the biases and the activation in its epilogue."""
     if only_dst is not None:
         rels = [et for et in rels if et[2] in only_dst]
-    pack = _gat_pack(owner, convs, rels, x)
+    pack = _gat_pack(owner, convs, rels, x, _gat_modes(convs, rels, x, group))
     Y = {T: ops.linear([(x[T], W)], W.size(0), pack_cache=pack.wcache.setdefault(T, {})) for T, W in pack.W.items()}
     out: Dict[str, Tensor] = {}
     for T in dict.fromkeys(et[2] for et in rels):
-        grp: List[GatRelation] = []
+        first, late = [], []  # project-first relations / (aggregated rows, post weight) of aggregate-first ones
         H = C = concat = slope = None
         for et in rels:
             if et[2] != T:
@@ -295,12 +335,29 @@ def run_gat_layer(convs: Dict[EdgeType, GATConv], rels: Sequence[EdgeType], x: D
             if c.training and c.dropout > 0:
                 raise NotImplementedError("attention dropout (training mode) is not implemented; call model.eval()")
             ys, yd = Y[et[0]], Y[T]
-            xo, ao, do = pack.xs_off[et], pack.as_off[et], pack.ad_off[et]
+            ao, do = pack.as_off[et], pack.ad_off[et]
             a_edge = None
             if c.lin_edge is not None and edge_attr is not None and edge_attr.get(et) is not None:
                 a_edge = ops.edge_logits(edge_attr[et], csr[et], pack.v_edge[et], H, fill=c.fill_vector(ys.device))
-            grp.append(GatRelation(ys[:, xo: xo + H * C], ys[:, ao: ao + H], yd[:, do: do + H], csr[et], c.bias, a_edge))
-        out[T] = ops.gat_fused(grp, x[T].size(0), H, C, concat, group=group, act=act, neg_slope=slope)
+            if pack.agg_first[et]:
+                xsrc = x[et[0]]
+                rel = GatRelation(xsrc, ys[:, ao: ao + H], yd[:, do: do + H], csr[et], None, a_edge)
+                agg = ops.gat_fused([rel], x[T].size(0), H, xsrc.size(1), True, neg_slope=slope, src_shared=True)
+                late.append((agg, pack.w_post[et]))
+            else:
+                xo = pack.xs_off[et]
+                first.append(GatRelation(ys[:, xo: xo + H * C], ys[:, ao: ao + H], yd[:, do: do + H], csr[et], c.bias,
+                                         a_edge))
+        width = H * C if concat else C
+        partial = None
+        if late:
+            partial = ops.linear(late, width, bias=pack.post_bias[T], act=None if first else act,
+                                 pack_cache=pack.wcache.setdefault("post_" + T, {}))
+        if first:
+            out[T] = ops.gat_fused(first, x[T].size(0), H, C, concat, group=group, act=act, neg_slope=slope,
+                                   addend=partial)
+        else:
+            out[T] = partial
     return out
 
 
