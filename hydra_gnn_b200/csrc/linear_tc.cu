@@ -1,7 +1,7 @@
 // K6 tensor-core path: y = act((sum_s x_s W_s^T + bias) * scale + shift) on tcgen05 (sm_100a).
 //
 // fp32-class accuracy on the TF32 tensor pipe by 3-term error compensation:
-//     x = x_hi + x_lo,  W = W_hi + W_lo   (hi = rna_tf32(.), lo = rna_tf32(. - hi))
+//     x = x_hi + x_lo,  W = W_hi + W_lo   (W: hi = rna_tf32(.), lo = rna_tf32(. - hi); x: hi = trunc_tf32, lo = x - hi)
 //     x W^T ~= x_hi W_hi^T + x_hi W_lo^T + x_lo W_hi^T          (dropped term ~ 2^-22)
 // accumulated in fp32 in TMEM.
 //
@@ -78,6 +78,22 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// multicast variant: the bytes land at the same smem offset, and complete_tx on the same barrier offset, in every CTA of `mask`
+__device__ __forceinline__ void bulk_g2s_mc(void* dst, const void* src, uint32_t bytes, uint64_t* bar, uint16_t mask) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;"
+        ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "h"(mask)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -101,6 +117,12 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint
 }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+// arrives on the barrier at the same smem offset in every CTA of `mask`
+__device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"(mask)
                  : "memory");
 }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
@@ -165,65 +187,76 @@ struct KbPos {
     int64_t m0;
     int n_tile, kb;
 };
-__device__ __forceinline__ KbPos kb_pos(const TcParams& P, int g) {
+// Work unit u = (group of CS consecutive m-tiles) x n-tile; cluster c takes u = c, c + n_clusters, ...;
+// CTA rank r of the cluster computes m-tile CS * group + r (possibly past the end: all-zero rows, no stores),
+// so the CTAs of a cluster walk the SAME (n-tile, k-block) sequence and can share every W k-block.
+template <int CS>
+__device__ __forceinline__ int64_t unit_of(int it) {
+    return static_cast<int64_t>(blockIdx.x / CS) + static_cast<int64_t>(it) * (gridDim.x / CS);
+}
+template <int CS>
+__device__ __forceinline__ KbPos kb_pos(const TcParams& P, int g, uint32_t rank) {
     const int it = g / P.n_kb;
-    const int64_t tile = static_cast<int64_t>(blockIdx.x) + static_cast<int64_t>(it) * gridDim.x;
+    const int64_t u = unit_of<CS>(it);
     KbPos p;
     p.kb = g - it * P.n_kb;
-    p.n_tile = static_cast<int>(tile % P.n_tiles);
-    p.m0 = (tile / P.n_tiles) * BM;
+    p.n_tile = static_cast<int>(u % P.n_tiles);
+    p.m0 = ((u / P.n_tiles) * CS + rank) * BM;
     return p;
 }
 
-template <int VEC>
+template <int VEC, int CS>
 struct Loader {
     static constexpr int kVecPerRow = BK / VEC;
     static constexpr int kRowStep = kLoaderThreads / kVecPerRow;
     static constexpr int kIters = BM / kRowStep;
 
     // global -> registers (one k-block slice of this thread: kIters vectors)
-    static __device__ __forceinline__ void load(const TcParams& P, int g, int t, float (&v)[kIters][VEC]) {
+    static __device__ __forceinline__ void load(const TcParams& P, int g, int t, uint32_t rank, float (&v)[kIters][VEC]) {
         const hg_linear_args& A = P.a;
-        const KbPos p = kb_pos(P, g);
+        const KbPos p = kb_pos<CS>(P, g, rank);
         int seg = 0;
         while (seg + 1 < A.n_seg && p.kb >= P.kb_start[seg + 1]) ++seg;
         const hg_lin_seg& G = A.seg[seg];
         const int cv = t % kVecPerRow, rb = t / kVecPerRow;
-        const int k = (p.kb - P.kb_start[seg]) * BK + cv * VEC;
+        const int k0 = (p.kb - P.kb_start[seg]) * BK;
+        const int k = k0 + cv * VEC;
+        const int64_t step = static_cast<int64_t>(kRowStep) * G.ldx;
+        const float* __restrict__ src = G.x + (p.m0 + rb) * G.ldx + k;
+        if (p.m0 + BM <= A.M && k0 + BK <= G.K) {  // interior k-block (CTA-uniform): no per-element checks
 #pragma unroll
-        for (int i = 0; i < kIters; ++i) {
-            const int64_t m = p.m0 + rb + i * kRowStep;
-            const bool row_ok = m < A.M;
-            const float* __restrict__ src = G.x + m * G.ldx + k;
-            if (row_ok && k + VEC <= G.K) {
-                ldg_vec<VEC>(src, v[i]);
-            } else {
+            for (int i = 0; i < kIters; ++i) ldg_vec<VEC>(src + i * step, v[i]);
+        } else {
 #pragma unroll
-                for (int e = 0; e < VEC; ++e) v[i][e] = (row_ok && k + e < G.K) ? __ldg(src + e) : 0.f;
+            for (int i = 0; i < kIters; ++i) {
+                const bool row_ok = p.m0 + rb + i * kRowStep < A.M;
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) v[i][e] = (row_ok && k + e < G.K) ? __ldg(src + i * step + e) : 0.f;
             }
         }
     }
 
-    // registers -> hi/lo swizzled smem tiles of the stage
+    // registers -> hi/lo swizzled smem tiles of the stage.  hi = x with the 13 low mantissa bits cleared
+    // (exactly what the tf32 datapath reads), lo = x - hi (exact; the datapath reads its top 11 bits).
     static __device__ __forceinline__ void store(uint8_t* stage, int t, const float (&v)[kIters][VEC]) {
+        static_assert(kRowStep % 8 == 0, "rows of one thread must share their swizzle phase");
         const int cv = t % kVecPerRow, rb = t / kVecPerRow;
+        uint8_t* dst = stage + swz_off(rb, cv * VEC);  // row rb + i * kRowStep: same phase, (kRowStep / 8) KB further
 #pragma unroll
         for (int i = 0; i < kIters; ++i) {
-            const int r = rb + i * kRowStep;
             float hi[VEC], lo[VEC];
 #pragma unroll
             for (int e = 0; e < VEC; ++e) {
-                hi[e] = tf32_rna(v[i][e]);
-                lo[e] = tf32_rna(v[i][e] - hi[e]);
+                hi[e] = __uint_as_float(__float_as_uint(v[i][e]) & 0xFFFFE000u);
+                lo[e] = v[i][e] - hi[e];
             }
-            const uint32_t off = swz_off(r, cv * VEC);
-            st_vec<VEC>(reinterpret_cast<float*>(stage + off), hi);
-            st_vec<VEC>(reinterpret_cast<float*>(stage + kATileBytes + off), lo);
+            st_vec<VEC>(reinterpret_cast<float*>(dst + i * (kRowStep / 8) * 1024), hi);
+            st_vec<VEC>(reinterpret_cast<float*>(dst + kATileBytes + i * (kRowStep / 8) * 1024), lo);
         }
     }
 };
 
-template <int VEC>
+template <int VEC, int CS>
 __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant__ TcParams P) {
     extern __shared__ uint8_t smem_raw[];
     const hg_linear_args& A = P.a;
@@ -233,9 +266,12 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
     const uint32_t stage_bytes = 2u * kATileBytes + 2u * b_tile_bytes;
 
     // tiles of this CTA: blockIdx.x, blockIdx.x + gridDim.x, ...
-    const int64_t total_tiles = P.m_tiles * P.n_tiles;
-    const int my_tiles = static_cast<int>((total_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x);
-    const int G = my_tiles * P.n_kb;  // k-blocks this CTA streams
+    const uint32_t rank = CS > 1 ? cluster_ctarank() : 0u;
+    constexpr uint16_t kAllMask = static_cast<uint16_t>((1u << CS) - 1u);
+    const int64_t total_units = ceil_div<int64_t>(P.m_tiles, CS) * P.n_tiles;
+    const int64_t n_clusters = gridDim.x / CS, cluster_id = blockIdx.x / CS;
+    const int my_tiles = static_cast<int>((total_units - cluster_id + n_clusters - 1) / n_clusters);
+    const int G = my_tiles * P.n_kb;  // k-blocks this CTA streams (identical for every CTA of the cluster)
 
     // carve: [1024-aligned stages][barriers][tmem slot]
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -264,7 +300,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
         for (int s = 0; s < S; ++s) {
             mbar_init(&full_a[s], kLoaderWarps);
             mbar_init(&full_b[s], 1);
-            mbar_init(&empty[s], 1);
+            mbar_init(&empty[s], CS);  // one tcgen05.commit from every CTA that reads the shared W stage
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(&acc_full[b], 1);
@@ -275,6 +311,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
     if (warp == 0) tmem_alloc(tmem_slot, static_cast<uint32_t>(P.tmem_cols));
     tc_fence_before();
     __syncthreads();
+    if (CS > 1) cluster_sync_all();  // peers' barriers are initialised before anything remote arrives on them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -306,7 +343,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
                         umma_tf32(d_tmem, a_lo + adv, b_hi + adv, idesc, 1u);
                         umma_tf32(d_tmem, a_hi + adv, b_hi + adv, idesc, 1u);
                     }
-                    umma_commit(&empty[s]);                            // stage reusable once these MMAs retire
+                    if (CS > 1) umma_commit_mc(&empty[s], kAllMask);   // the W stage is shared: tell every CTA
+                    else umma_commit(&empty[s]);                       // stage reusable once these MMAs retire
                     if (kb == P.n_kb - 1) umma_commit(&acc_full[ab]);  // accumulator complete
                 }
                 __syncwarp();
@@ -318,17 +356,23 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
             for (int g = 0; g < G; ++g) {
                 const int s = g % S;
                 const uint32_t ph = static_cast<uint32_t>(g / S) & 1u;
-                const KbPos p = kb_pos(P, g);
-                mbar_wait(&empty[s], ph ^ 1u);
+                const KbPos p = kb_pos<CS>(P, g, rank);
+                mbar_wait(&empty[s], ph ^ 1u);  // every CTA of the cluster has retired its MMAs on this stage
                 uint8_t* stage = base + static_cast<size_t>(s) * stage_bytes;
                 mbar_arrive_expect_tx(&full_b[s], 2u * b_tile_bytes);
                 const float* src = P.wp + (static_cast<int64_t>(p.n_tile) * P.n_kb + p.kb) * 2 * (b_tile_bytes / 4);
-                bulk_g2s(stage + 2 * kATileBytes, src, 2u * b_tile_bytes, &full_b[s]);
+                if (CS > 1) {  // this CTA fetches 1/CS of the W_hi|W_lo image and multicasts it to the whole cluster
+                    const uint32_t part = 2u * b_tile_bytes / CS;
+                    bulk_g2s_mc(stage + 2 * kATileBytes + rank * part, reinterpret_cast<const uint8_t*>(src) + rank * part,
+                                part, &full_b[s], kAllMask);
+                } else {
+                    bulk_g2s(stage + 2 * kATileBytes, src, 2u * b_tile_bytes, &full_b[s]);
+                }
             }
         }
     } else if (warp < 2 + kLoaderWarps) {
         // ===================== A loaders / converters =====================
-        using L = Loader<VEC>;
+        using L = Loader<VEC, CS>;
         const int t = threadIdx.x - 64;
         float v0[L::kIters][VEC], v1[L::kIters][VEC], v2[L::kIters][VEC];
         auto finish = [&](int g, const float (&v)[L::kIters][VEC]) {
@@ -340,19 +384,19 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
             __syncwarp();
             if (lane == 0) mbar_arrive(&full_a[s]);
         };
-        if (0 < G) L::load(P, 0, t, v0);
-        if (1 < G) L::load(P, 1, t, v1);
-        if (2 < G) L::load(P, 2, t, v2);
+        if (0 < G) L::load(P, 0, t, rank, v0);
+        if (1 < G) L::load(P, 1, t, rank, v1);
+        if (2 < G) L::load(P, 2, t, rank, v2);
         for (int g = 0; g < G; g += kPrefetch) {
             finish(g, v0);
-            if (g + 3 < G) L::load(P, g + 3, t, v0);
+            if (g + 3 < G) L::load(P, g + 3, t, rank, v0);
             if (g + 1 < G) {
                 finish(g + 1, v1);
-                if (g + 4 < G) L::load(P, g + 4, t, v1);
+                if (g + 4 < G) L::load(P, g + 4, t, rank, v1);
             }
             if (g + 2 < G) {
                 finish(g + 2, v2);
-                if (g + 5 < G) L::load(P, g + 5, t, v2);
+                if (g + 5 < G) L::load(P, g + 5, t, rank, v2);
             }
         }
     } else {
@@ -361,9 +405,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
         const bool vec_store = (A.ldy % 4 == 0) && ((reinterpret_cast<uintptr_t>(A.y) & 15) == 0);
         for (int it = 0; it < my_tiles; ++it) {
             const int ab = it & 1;
-            const int64_t tile = static_cast<int64_t>(blockIdx.x) + static_cast<int64_t>(it) * gridDim.x;
-            const int n0 = static_cast<int>(tile % P.n_tiles) * P.block_n;
-            const int64_t m = (tile / P.n_tiles) * BM + q * 32 + lane;
+            const int64_t u = unit_of<CS>(it);
+            const int n0 = static_cast<int>(u % P.n_tiles) * P.block_n;
+            const int64_t m = ((u / P.n_tiles) * CS + rank) * BM + q * 32 + lane;
             mbar_wait(&acc_full[ab], (static_cast<uint32_t>(it) >> 1) & 1u);
             tc_fence_after();
             const uint32_t t_acc = tmem_base + static_cast<uint32_t>(ab * P.block_n) + (static_cast<uint32_t>(q * 32) << 16);
@@ -409,6 +453,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
 
     tc_fence_before();
     __syncthreads();
+    if (CS > 1) cluster_sync_all();  // no CTA leaves while a peer may still multicast into its smem / barriers
     if (warp == 0) {
         tc_fence_after();
         tmem_dealloc(tmem_base, static_cast<uint32_t>(P.tmem_cols));
@@ -492,17 +537,38 @@ int linear_tc_launch(const hg_linear_args& a, void* ws, size_t ws_bytes, cudaStr
     const size_t stage_bytes = 2 * kATileBytes + 2 * static_cast<size_t>(P.block_n) * 128;
     const size_t smem = 1024 + P.stages * stage_bytes + (3 * P.stages + 4) * sizeof(uint64_t) + 48 +
                         2 * static_cast<size_t>(P.n_tiles) * P.block_n * sizeof(float);
-    const int64_t total = P.m_tiles * P.n_tiles;
     const int sms = sm_count() > 0 ? sm_count() : 148;
-    const unsigned grid = static_cast<unsigned>(total < sms ? total : sms);  // persistent: one CTA per SM
-    auto go = [&](auto kernel) -> int {
+    // Big problems run as clusters of 2 CTAs that share every W k-block (each fetches half, multicast to both):
+    // W re-streaming from L2 is what bounds the 306-wide projection.  Small ones keep independent CTAs.
+    const bool pair = P.m_tiles >= 2 * static_cast<int64_t>(sms) && (2 * P.block_n * 128 / 2) % 16 == 0;
+    auto go = [&](auto kernel, int cs) -> int {
         HG_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-        kernel<<<grid, kThreads, smem, stream>>>(P);
+        const int64_t units = ceil_div<int64_t>(P.m_tiles, cs) * P.n_tiles;
+        int64_t ctas = units * cs < sms ? units * cs : sms;  // persistent: one CTA per SM
+        ctas = ctas / cs * cs;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(static_cast<unsigned>(ctas));
+        cfg.blockDim = dim3(kThreads);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = cs;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        HG_CUDA_TRY(cudaLaunchKernelEx(&cfg, kernel, P));
         return check_launch();
     };
-    if (P.vec == 4) return go(k_linear_tc<4>);
-    if (P.vec == 2) return go(k_linear_tc<2>);
-    return go(k_linear_tc<1>);
+    if (pair) {
+        if (P.vec == 4) return go(k_linear_tc<4, 2>, 2);
+        if (P.vec == 2) return go(k_linear_tc<2, 2>, 2);
+        return go(k_linear_tc<1, 2>, 2);
+    }
+    if (P.vec == 4) return go(k_linear_tc<4, 1>, 1);
+    if (P.vec == 2) return go(k_linear_tc<2, 1>, 1);
+    return go(k_linear_tc<1, 1>, 1);
 }
 
 }  // namespace hg

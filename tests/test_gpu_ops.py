@@ -123,7 +123,8 @@ def test_seg_reduce_strided_views():
 
 # ------------------------------------------------------------------------------ K6
 SHAPES = [(1000, 396, [306]), (777, 84, [64]), (129, 16, [6]), (5000, 396, [64]), (2048, 128, [128, 128]),
-          (600, 35, [6, 6, 6]), (513, 300, [306]), (4096, 768, [768])]
+          (600, 35, [6, 6, 6]), (513, 300, [306]), (4096, 768, [768]),
+          (40001, 204, [306]), (38000, 396, [64])]  # the last two: >= 2 m-tiles per SM -> 2-CTA clusters sharing W
 
 
 @pytest.mark.parametrize("precision", ["fp32", "tf32x3"])
