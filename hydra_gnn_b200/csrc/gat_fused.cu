@@ -1,19 +1,20 @@
-// K3 + K4 -- fused GAT for one destination node type (v5).
+// K3 + K4 -- fused GAT for one destination node type (v6).
 //
-// A CTA (128 threads, up to 6 resident per SM) owns a tile of 16-32 consecutive destination rows
+// A CTA (128 threads, 6-8 resident per SM) owns a tile of 16-32 consecutive destination rows
 // (consecutive rows belong to the same scene graph, so their neighbour sets overlap and the gathers
-// of a tile hit L1/L2).  Per tile:
-//   stage    rowptr slices and destination logits; then -- threads = edges, coalesced on col -- the
-//            neighbour ids, the tile-local row of every edge and the raw logits a_src[j,h](+a_edge)
-//            of every relation go to shared memory;
-//   softmax  threads = (relation, row, head): max and 1/(sum + 1e-16) of the row; then threads =
-//            edges turn the staged logits into softmax weights in place.  No shuffles, no idle lanes
-//            on short rows (mean in-degree of a scene graph is ~5), no runtime integer divisions
-//            (all index maps are shifts and masks over padded layouts);
-//   gather   threads = (row, output chunk): TPR threads cooperate on a row, each owning KC vector
-//            chunks of the OUTPUT row.  For head-mean the thread walks the H head slices of xs[j]
-//            itself, so the head reduction never leaves registers; the weights of an edge are one
-//            broadcast LDS.128.  Relations are summed in the same registers;
+// of a tile hit L1/L2).  Per tile, three barriers:
+//   stage    rowptr slices and destination logits; and -- threads = edges, coalesced on col -- the
+//            neighbour ids and the raw logits a_src[j,h](+a_edge) of every relation go to shared memory;
+//   softmax  threads = (relation, row, head): leaky-relu + max, exp + sum, normalise -- three passes over
+//            the row's staged logits, in place.  No shuffles, no idle lanes on short rows (mean in-degree
+//            of a scene graph is ~5), no runtime integer divisions (index maps are shifts and masks over
+//            padded layouts), no edge -> row map;
+//   gather   threads = (row, chunk): TPR threads cooperate on a row, each owning KC vector chunks.
+//            Head-mean (MODE 1, H compile-time): the thread walks the H head slices of xs[j] itself, so the
+//            head reduction never leaves registers.  Aggregate-first (MODE 2): the thread owns a chunk of
+//            the SOURCE row and accumulates the H weighted copies, so xs[j] is read once, not H times.
+//            The weights of an edge are one broadcast LDS.128; addresses are one IMAD.WIDE per load.
+//            Relations are summed in the same registers;
 //   out      + summed biases (+ addend), group mean, ELU/ReLU, ONE vector store per chunk.
 // No atomics, no read-modify-write across relations, no separate softmax / stack+sum / activation
 // passes.  Tiles whose edges do not fit the staging buffers (hub nodes) take a warp-per-row path
@@ -37,8 +38,9 @@ struct GatParams {
     int32_t cap;        // staged edges per relation per tile (multiple of 32)
     int32_t tile_rows;  // 16 or 32
     int32_t hs;         // padded head stride in shared memory: 4 or 8
-    int32_t f_begin;    // first OUTPUT column of this launch (wide rows are split over launches)
-    int32_t f_count;    // output columns of this launch
+    int32_t f_begin;    // first column of this launch (wide rows are split over launches);
+    int32_t f_count;    // columns of this launch.  OUTPUT columns, except MODE 2: columns of the source row
+    int32_t n_bias;     // staged bias values: f_count (MODE 2: H * f_count, head-major)
 };
 
 __device__ __forceinline__ float leaky(float v, float slope) { return v > 0.f ? v : v * slope; }
@@ -46,47 +48,41 @@ __device__ __forceinline__ float leaky(float v, float slope) { return v > 0.f ? 
 struct Smem {
     float* w;        // [R][cap][hs]        logits -> weights (16-byte aligned rows)
     float* ad;       // [R][kMaxTile][hs]   destination logits
-    float* mx;       // [R][kMaxTile][hs]   row max
-    float* inv;      // [R][kMaxTile][hs]   1 / (row sum + 1e-16)
-    float* bias;     // [f_count]           summed biases of this launch's output columns
+    float* bias;     // [n_bias]            summed biases of this launch's output columns
     int32_t* col;    // [R][cap]
     int32_t* rp;     // [R][kMaxTile + 1]
-    uint8_t* erow;   // [R][cap]            tile-local row of the edge
 };
 
-__host__ __device__ inline size_t smem_bytes(int R, int cap, int hs, int f_count) {
-    size_t words = static_cast<size_t>(R) * cap * hs + 3 * static_cast<size_t>(R) * kMaxTile * hs +
-                   static_cast<size_t>((f_count + 3) / 4 * 4) + static_cast<size_t>(R) * cap +
+__host__ __device__ inline size_t smem_bytes(int R, int cap, int hs, int n_bias) {
+    size_t words = static_cast<size_t>(R) * cap * hs + static_cast<size_t>(R) * kMaxTile * hs +
+                   static_cast<size_t>((n_bias + 3) / 4 * 4) + static_cast<size_t>(R) * cap +
                    static_cast<size_t>(R) * (kMaxTile + 1);
-    return words * 4 + static_cast<size_t>(R) * cap + 16;
+    return words * 4 + 16;
 }
 
-__device__ __forceinline__ Smem carve(uint8_t* raw, int R, int cap, int hs, int f_count) {
+__device__ __forceinline__ Smem carve(uint8_t* raw, int R, int cap, int hs, int n_bias) {
     Smem s;
     float* p = reinterpret_cast<float*>(raw);
     s.w = p;      p += static_cast<size_t>(R) * cap * hs;
     s.ad = p;     p += R * kMaxTile * hs;
-    s.mx = p;     p += R * kMaxTile * hs;
-    s.inv = p;    p += R * kMaxTile * hs;
-    s.bias = p;   p += (f_count + 3) / 4 * 4;
+    s.bias = p;   p += (n_bias + 3) / 4 * 4;
     s.col = reinterpret_cast<int32_t*>(p);  p += static_cast<size_t>(R) * cap;
-    s.rp = reinterpret_cast<int32_t*>(p);   p += R * (kMaxTile + 1);
-    s.erow = reinterpret_cast<uint8_t*>(p);
+    s.rp = reinterpret_cast<int32_t*>(p);
     return s;
 }
 
 // Hub path: one warp per row, lanes = output chunks, everything streamed from global memory.
 template <int VEC>
-__device__ __noinline__ void slow_row(const GatParams& P, int64_t i, int lane) {
+__device__ __noinline__ void slow_row(const GatParams& P, int64_t i, int lane, int f_begin, int f_count) {
     const hg_gat_args& A = P.a;
     const int H = A.H, C = A.C, R = A.n_rel;
     const bool head_mean = !A.concat && !A.src_shared;
-    const int nco = P.f_count / VEC;
+    const int nco = f_count / VEC;
     const float gscale = (A.group == HG_GROUP_MEAN) ? 1.f / static_cast<float>(R) : 1.f;
     for (int oc0 = 0; oc0 < nco; oc0 += 32) {
         const int oc = oc0 + lane;
         const bool live = oc < nco;
-        const int f = P.f_begin + oc * VEC;  // output column
+        const int f = f_begin + oc * VEC;  // output column
         float acc[VEC];
 #pragma unroll
         for (int v = 0; v < VEC; ++v) acc[v] = 0.f;
@@ -116,7 +112,7 @@ __device__ __noinline__ void slow_row(const GatParams& P, int64_t i, int lane) {
                     float sc = __ldg(Rl.a_src + static_cast<int64_t>(j) * Rl.lda_src + h) + ad;
                     if (Rl.a_edge) sc += __ldg(Rl.a_edge + static_cast<int64_t>(e) * H + h);
                     const float w = __expf(leaky(sc, A.neg_slope) - m) * inv;
-                    if (A.alpha_saved[r] && (head_mean ? (lane == 0 && oc0 == 0 && P.f_begin == 0) : (live && f % C == 0)))
+                    if (A.alpha_saved[r] && (head_mean ? (lane == 0 && oc0 == 0 && f_begin == 0) : (live && f % C == 0)))
                         A.alpha_saved[r][static_cast<int64_t>(e) * H + h] = w;
                     if (live) {
                         float val[VEC];
@@ -148,16 +144,23 @@ __device__ __noinline__ void slow_row(const GatParams& P, int64_t i, int lane) {
         st_vec<VEC>(A.out + i * A.ldout + f, o);
     }
 }
-template <int VEC, int TPR, int KC>
-__global__ void __launch_bounds__(kThreads, (KC <= 2 ? 6 : 4)) k_gat_fused(const __grid_constant__ GatParams P) {
+
+
+// MODE 0: generic (concat / src_shared / head-mean with any H <= 8; thread chunks are OUTPUT chunks).
+// MODE 1: head-mean, H == HT (<= 4).   MODE 2: aggregate-first (src_shared), H == HT: chunks of the SOURCE row.
+template <int VEC, int TPR, int KC, int MODE, int HT>
+__global__ void __launch_bounds__(kThreads, (KC * (MODE == 2 ? HT : 1) <= 4 ? 6 : 4))
+k_gat_fused(const __grid_constant__ GatParams P) {
     extern __shared__ __align__(16) uint8_t s_raw[];
     const hg_gat_args& A = P.a;
-    const int H = A.H, C = A.C, R = A.n_rel, cap = P.cap, hs = P.hs;
-    const int hsh = hs == 4 ? 2 : 3;          // log2(hs)
-    const Smem S = carve(s_raw, R, cap, hs, P.f_count);
+    const int H = MODE ? HT : A.H;
+    const int C = A.C, R = A.n_rel, cap = P.cap;
+    const int hs = MODE ? 4 : P.hs;
+    const int hsh = MODE ? 2 : (P.hs == 4 ? 2 : 3);  // log2(hs)
+    const Smem S = carve(s_raw, R, cap, hs, P.n_bias);
     const int tid = threadIdx.x;
-    const bool head_mean = !A.concat && !A.src_shared;
-    const int nco = P.f_count / VEC;          // output chunks of this launch
+    const bool head_mean = MODE == 1 || (MODE == 0 && !A.concat && !A.src_shared);
+    const int nco = P.f_count / VEC;          // chunks of this launch
     constexpr int kGroups = kThreads / TPR;   // rows gathered concurrently
     const int q = tid % TPR, grp = tid / TPR;
     const int tile_rows = P.tile_rows;
@@ -165,22 +168,25 @@ __global__ void __launch_bounds__(kThreads, (KC <= 2 ? 6 : 4)) k_gat_fused(const
     const float gscale = (A.group == HG_GROUP_MEAN) ? 1.f / static_cast<float>(R) : 1.f;
     const float hscale = head_mean ? 1.f / static_cast<float>(H) : 1.f;
 
-    for (int f = tid; f < P.f_count; f += kThreads) {
+    for (int f = tid; f < P.n_bias; f += kThreads) {
+        // MODE 2 stages [H][f_count] (head-major); the others [f_count]
+        const int col = (MODE == 2) ? (f / P.f_count) * C + P.f_begin + f % P.f_count : P.f_begin + f;
         float b = 0.f;
         for (int r = 0; r < R; ++r)
-            if (A.rel[r].bias) b += __ldg(A.rel[r].bias + P.f_begin + f);
+            if (A.rel[r].bias) b += __ldg(A.rel[r].bias + col);
         S.bias[f] = b;
     }
 
-    // per-thread constants of its KC output chunks
-    int fo[KC], fsrc[KC], hk[KC];
+    // per-thread constants: chunk k of this thread starts at column f0 + k * TPR * VEC of the launch
+    const int f0 = P.f_begin + q * VEC;
+    bool live[KC];
+    int hk[KC], fsrc[KC];  // MODE 0: head of the chunk (concat / src_shared) and its column in the source row
 #pragma unroll
     for (int k = 0; k < KC; ++k) {
-        const int oc = q + k * TPR;
-        const bool valid = oc < nco;
-        fo[k] = valid ? P.f_begin + oc * VEC : -1;
-        hk[k] = (valid && !head_mean) ? fo[k] / C : 0;
-        fsrc[k] = valid ? (A.src_shared ? fo[k] % C : fo[k]) : 0;
+        live[k] = q + k * TPR < nco;
+        const int fo = f0 + k * TPR * VEC;
+        hk[k] = (MODE == 0 && live[k] && !head_mean) ? fo / C : 0;
+        fsrc[k] = (MODE == 0 && A.src_shared && live[k]) ? fo % C : fo;
     }
 
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -188,7 +194,7 @@ __global__ void __launch_bounds__(kThreads, (KC <= 2 ? 6 : 4)) k_gat_fused(const
         const int rows = (A.n_dst - t0 < tile_rows) ? static_cast<int>(A.n_dst - t0) : tile_rows;
         __syncthreads();  // previous tile fully consumed (also orders the bias fill before its first use)
 
-        // ---- stage 1: rowptr slices + destination logits (padded [R][32][hs] layout: shifts only)
+        // ---- stage: rowptr slices + destination logits (padded [R][32][hs] layout: shifts only) ...
         for (int idx = tid; idx < R * (kMaxTile + 1); idx += kThreads) {
             const int r = idx / (kMaxTile + 1), t = idx - r * (kMaxTile + 1);
             S.rp[idx] = __ldg(A.rel[r].rowptr + t0 + min(t, rows));
@@ -197,31 +203,31 @@ __global__ void __launch_bounds__(kThreads, (KC <= 2 ? 6 : 4)) k_gat_fused(const
             const int h = idx & (hs - 1), t = (idx >> hsh) & (kMaxTile - 1), r = idx >> (hsh + 5);
             if (t < rows && h < H) S.ad[idx] = __ldg(A.rel[r].a_dst + (t0 + t) * A.rel[r].lda_dst + h);
         }
-        __syncthreads();
+        // ... the tile's edge range per relation straight from global memory (uniform loads), so the
+        // edge staging does not have to wait for the rowptr slices behind a barrier
         bool fits = true;
-        for (int r = 0; r < R; ++r) fits = fits && (S.rp[r * (kMaxTile + 1) + rows] - S.rp[r * (kMaxTile + 1)] <= cap);
+        for (int r = 0; r < R; ++r)
+            fits = fits && (__ldg(A.rel[r].rowptr + t0 + rows) - __ldg(A.rel[r].rowptr + t0) <= cap);
         if (!fits) {  // hub tile (uniform branch): warp per row straight from global memory
-            for (int t = tid >> 5; t < rows; t += kWarps) slow_row<VEC>(P, t0 + t, tid & 31);
+            for (int t = tid >> 5; t < rows; t += kWarps) {
+                if (MODE == 2) {
+                    for (int h = 0; h < H; ++h) slow_row<VEC>(P, t0 + t, tid & 31, h * C + P.f_begin, P.f_count);
+                } else {
+                    slow_row<VEC>(P, t0 + t, tid & 31, P.f_begin, P.f_count);
+                }
+            }
             continue;
         }
-
-        // ---- stage 2: neighbour ids, edge -> row map, raw logits (threads = edges)
+        // ---- ... neighbour ids and raw logits (threads = edges)
         for (int r = 0; r < R; ++r) {
             const hg_gat_rel& Rl = A.rel[r];
-            const int32_t* rp = S.rp + r * (kMaxTile + 1);
-            const int32_t e0 = rp[0], ne = rp[rows] - e0;
+            const int32_t e0 = __ldg(Rl.rowptr + t0), ne = __ldg(Rl.rowptr + t0 + rows) - e0;
             const float* __restrict__ a_src = Rl.a_src;
             const float* __restrict__ a_edge = Rl.a_edge;
-            const int64_t lda = Rl.lda_src;
+            const int lda = static_cast<int>(Rl.lda_src);
             for (int e = tid; e < ne; e += kThreads) {
                 const int32_t j = __ldg(Rl.col + e0 + e);
                 S.col[r * cap + e] = j;
-                int lo = 0, hi = rows;  // row t with rp[t] <= e0 + e < rp[t + 1]
-                while (hi - lo > 1) {
-                    const int mid = (lo + hi) >> 1;
-                    if (rp[mid] <= e0 + e) lo = mid; else hi = mid;
-                }
-                S.erow[r * cap + e] = static_cast<uint8_t>(lo);
                 float* wrow = S.w + ((static_cast<size_t>(r) * cap + e) << hsh);
                 const float* src = a_src + static_cast<int64_t>(j) * lda;
 #pragma unroll
@@ -239,58 +245,107 @@ __global__ void __launch_bounds__(kThreads, (KC <= 2 ? 6 : 4)) k_gat_fused(const
         }
         __syncthreads();
 
-        // ---- softmax statistics: threads = (relation, row, head) over the padded layout
+        // ---- softmax in place: threads = (relation, row, head) over the padded layout
         for (int idx = tid; idx < (R * kMaxTile) << hsh; idx += kThreads) {
             const int h = idx & (hs - 1), t = (idx >> hsh) & (kMaxTile - 1), r = idx >> (hsh + 5);
             if (t >= rows || h >= H) continue;
             const int32_t* rp = S.rp + r * (kMaxTile + 1);
-            const int beg = rp[t] - rp[0], end = rp[t + 1] - rp[0];
+            const int e0 = rp[0], beg = rp[t] - e0, end = rp[t + 1] - e0;
             const float ad = S.ad[idx];
-            const float* w = S.w + ((static_cast<size_t>(r) * cap) << hsh) + h;
+            float* w = S.w + ((static_cast<size_t>(r) * cap) << hsh) + h;
             float m = -INFINITY;
-            for (int e = beg; e < end; ++e) m = fmaxf(m, leaky(w[e << hsh] + ad, A.neg_slope));
+            for (int e = beg; e < end; ++e) {
+                const float v = leaky(w[e << hsh] + ad, A.neg_slope);
+                w[e << hsh] = v;
+                m = fmaxf(m, v);
+            }
             float l = 0.f;
-            for (int e = beg; e < end; ++e) l += __expf(leaky(w[e << hsh] + ad, A.neg_slope) - m);
-            S.mx[idx] = m;
-            S.inv[idx] = 1.f / (l + 1e-16f);
-        }
-        __syncthreads();
-        // ---- logits -> weights in place: threads = edges
-        for (int r = 0; r < R; ++r) {
-            const int32_t e0 = S.rp[r * (kMaxTile + 1)], ne = S.rp[r * (kMaxTile + 1) + rows] - e0;
+            for (int e = beg; e < end; ++e) {
+                const float p = __expf(w[e << hsh] - m);
+                w[e << hsh] = p;
+                l += p;
+            }
+            const float inv = 1.f / (l + 1e-16f);
             float* alpha = (P.f_begin == 0) ? A.alpha_saved[r] : nullptr;
-            for (int e = tid; e < ne; e += kThreads) {
-                const int t = S.erow[r * cap + e];
-                float* wrow = S.w + ((static_cast<size_t>(r) * cap + e) << hsh);
-                const int base = (r * kMaxTile + t) << hsh;
-#pragma unroll
-                for (int h = 0; h < kMaxHeads; ++h) {
-                    if (h < H) {
-                        const float w = __expf(leaky(wrow[h] + S.ad[base + h], A.neg_slope) - S.mx[base + h]) * S.inv[base + h];
-                        wrow[h] = w;
-                        if (alpha) alpha[static_cast<int64_t>(e0 + e) * H + h] = w;
-                    }
-                }
+            for (int e = beg; e < end; ++e) {
+                const float a = w[e << hsh] * inv;
+                w[e << hsh] = a;
+                if (alpha) alpha[static_cast<int64_t>(e0 + e) * H + h] = a;
             }
         }
         __syncthreads();
 
-        // ---- gather-accumulate: threads = (row, output chunk)
+        // ---- gather-accumulate: threads = (row, chunk)
+        if (KC == 1 && !live[0]) continue;  // no barrier below this point
         for (int t = grp; t < rows; t += kGroups) {
             const int64_t i = t0 + t;
-            float acc[KC][VEC];
+            constexpr int NH = (MODE == 2) ? HT : 1;  // accumulators per chunk
+            float acc[NH][KC][VEC];
 #pragma unroll
-            for (int k = 0; k < KC; ++k)
+            for (int h = 0; h < NH; ++h)
 #pragma unroll
-                for (int v = 0; v < VEC; ++v) acc[k][v] = 0.f;
+                for (int k = 0; k < KC; ++k)
+#pragma unroll
+                    for (int v = 0; v < VEC; ++v) acc[h][k][v] = 0.f;
             for (int r = 0; r < R; ++r) {
                 const float* __restrict__ xsb = A.rel[r].xs + fsrc[0];
-                const int64_t ld = A.rel[r].ldxs;
+                const int ld = static_cast<int>(A.rel[r].ldxs);
                 const int32_t* rp = S.rp + r * (kMaxTile + 1);
                 const int beg = rp[t] - rp[0], end = rp[t + 1] - rp[0];
                 const int32_t* colp = S.col + r * cap;
                 const float* wp = S.w + ((static_cast<size_t>(r) * cap) << hsh);
-                if (head_mean) {
+                if constexpr (MODE == 1) {
+                    const float* __restrict__ xh[HT];  // one base per head: an address is then ONE IMAD.WIDE
+#pragma unroll
+                    for (int hh = 0; hh < HT; ++hh) xh[hh] = xsb + hh * C;
+#pragma unroll 2
+                    for (int e = beg; e < end; ++e) {
+                        const int j = colp[e];
+                        const float4 wa = *reinterpret_cast<const float4*>(wp + (e << 2));
+                        const float wv[4] = {wa.x, wa.y, wa.z, wa.w};
+                        float val[HT][KC][VEC];
+#pragma unroll
+                        for (int hh = 0; hh < HT; ++hh)  // all loads of the edge first: independent, in flight together
+#pragma unroll
+                            for (int k = 0; k < KC; ++k) {
+                                if (KC == 1 || live[k]) {
+                                    ldg_vec<VEC>(xh[hh] + static_cast<int64_t>(j) * ld + k * TPR * VEC, val[hh][k]);
+                                } else {
+#pragma unroll
+                                    for (int v = 0; v < VEC; ++v) val[hh][k][v] = 0.f;
+                                }
+                            }
+#pragma unroll
+                        for (int hh = 0; hh < HT; ++hh)
+#pragma unroll
+                            for (int k = 0; k < KC; ++k)
+#pragma unroll
+                                for (int v = 0; v < VEC; ++v) acc[0][k][v] = fmaf(wv[hh], val[hh][k][v], acc[0][k][v]);
+                    }
+                } else if constexpr (MODE == 2) {
+#pragma unroll(KC <= 2 ? 4 : 2)
+                    for (int e = beg; e < end; ++e) {
+                        const int j = colp[e];
+                        const float4 wa = *reinterpret_cast<const float4*>(wp + (e << 2));
+                        const float wv[4] = {wa.x, wa.y, wa.z, wa.w};
+                        float val[KC][VEC];
+#pragma unroll
+                        for (int k = 0; k < KC; ++k) {
+                            if (KC == 1 || live[k]) {
+                                ldg_vec<VEC>(xsb + static_cast<int64_t>(j) * ld + k * TPR * VEC, val[k]);
+                            } else {
+#pragma unroll
+                                for (int v = 0; v < VEC; ++v) val[k][v] = 0.f;
+                            }
+                        }
+#pragma unroll
+                        for (int hh = 0; hh < HT; ++hh)
+#pragma unroll
+                            for (int k = 0; k < KC; ++k)
+#pragma unroll
+                                for (int v = 0; v < VEC; ++v) acc[hh][k][v] = fmaf(wv[hh], val[k][v], acc[hh][k][v]);
+                    }
+                } else if (head_mean) {
                     for (int hb = 0; hb < H; hb += 4) {  // heads in blocks of 4: their weights are one LDS.128
                         const float* __restrict__ xsh = xsb + hb * C;
                         const int hn = H - hb;  // live heads of this block (>= 1)
@@ -301,10 +356,10 @@ __global__ void __launch_bounds__(kThreads, (KC <= 2 ? 6 : 4)) k_gat_fused(const
                             const float wv[4] = {wa.x, wa.y, wa.z, wa.w};
                             float val[4][KC][VEC];
 #pragma unroll
-                            for (int hh = 0; hh < 4; ++hh)  // all loads of the edge first: independent, in flight together
+                            for (int hh = 0; hh < 4; ++hh)
 #pragma unroll
                                 for (int k = 0; k < KC; ++k) {
-                                    if (hh < hn && fo[k] >= 0) {
+                                    if (hh < hn && live[k]) {
                                         ldg_vec<VEC>(rowh + hh * C + (fsrc[k] - fsrc[0]), val[hh][k]);
                                     } else {
 #pragma unroll
@@ -316,7 +371,7 @@ __global__ void __launch_bounds__(kThreads, (KC <= 2 ? 6 : 4)) k_gat_fused(const
 #pragma unroll
                                 for (int k = 0; k < KC; ++k)
 #pragma unroll
-                                    for (int v = 0; v < VEC; ++v) acc[k][v] = fmaf(wv[hh], val[hh][k][v], acc[k][v]);
+                                    for (int v = 0; v < VEC; ++v) acc[0][k][v] = fmaf(wv[hh], val[hh][k][v], acc[0][k][v]);
                         }
                     }
                 } else {
@@ -326,81 +381,115 @@ __global__ void __launch_bounds__(kThreads, (KC <= 2 ? 6 : 4)) k_gat_fused(const
                         const float* we = wp + (e << hsh);
 #pragma unroll
                         for (int k = 0; k < KC; ++k)
-                            if (fo[k] >= 0) {
+                            if (live[k]) {
                                 float val[VEC];
                                 ldg_vec<VEC>(row + (fsrc[k] - fsrc[0]), val);
                                 const float w = we[hk[k]];
 #pragma unroll
-                                for (int v = 0; v < VEC; ++v) acc[k][v] = fmaf(w, val[v], acc[k][v]);
+                                for (int v = 0; v < VEC; ++v) acc[0][k][v] = fmaf(w, val[v], acc[0][k][v]);
                             }
                     }
                 }
             }
-            // ---- epilogue: head-mean scale, summed biases, group mean, addend, activation, ONE store
+            // ---- epilogue: head-mean scale, summed biases, group mean, addend, activation, ONE store per chunk
+            const float* __restrict__ addp = A.addend ? A.addend + i * A.ldadd : nullptr;
+            float* __restrict__ outp = A.out + i * A.ldout;
+            const int act = A.act;
 #pragma unroll
-            for (int k = 0; k < KC; ++k) {
-                if (fo[k] < 0) continue;
-                float o[VEC];
+            for (int h = 0; h < NH; ++h)
 #pragma unroll
-                for (int v = 0; v < VEC; ++v) o[v] = (acc[k][v] * hscale + S.bias[fo[k] - P.f_begin + v]) * gscale;
-                if (A.addend) {
-                    float av[VEC];
-                    ldg_vec<VEC>(A.addend + i * A.ldadd + fo[k], av);
+                for (int k = 0; k < KC; ++k) {
+                    if (KC > 1 && !live[k]) continue;
+                    const int lc = (q + k * TPR) * VEC;  // column within the launch
+                    const int oc = (MODE == 2 ? h * C : 0) + P.f_begin + lc;
+                    const float* bp = S.bias + (MODE == 2 ? h * P.f_count : 0) + lc;
+                    float o[VEC];
 #pragma unroll
-                    for (int v = 0; v < VEC; ++v) o[v] += av[v];
+                    for (int v = 0; v < VEC; ++v) o[v] = (acc[h][k][v] * hscale + bp[v]) * gscale;
+                    if (addp) {
+                        float av[VEC];
+                        ldg_vec<VEC>(addp + oc, av);
+#pragma unroll
+                        for (int v = 0; v < VEC; ++v) o[v] += av[v];
+                    }
+                    if (act == HG_ACT_RELU) {
+#pragma unroll
+                        for (int v = 0; v < VEC; ++v) o[v] = fmaxf(o[v], 0.f);
+                    } else if (act == HG_ACT_ELU) {
+#pragma unroll
+                        for (int v = 0; v < VEC; ++v) o[v] = o[v] > 0.f ? o[v] : __expf(o[v]) - 1.f;  // F.elu: exp(x) - 1
+                    }
+                    st_vec<VEC>(outp + oc, o);
                 }
-#pragma unroll
-                for (int v = 0; v < VEC; ++v) {
-                    float y = o[v];
-                    if (A.act == HG_ACT_RELU) y = fmaxf(y, 0.f);
-                    else if (A.act == HG_ACT_ELU) y = y > 0.f ? y : __expf(y) - 1.f;  // F.elu: exp(x) - 1
-                    o[v] = y;
-                }
-                st_vec<VEC>(A.out + i * A.ldout + fo[k], o);
-            }
         }
     }
 }
 
-template <int VEC, int TPR, int KC>
+template <int VEC, int TPR, int KC, int MODE, int HT>
 int launch(GatParams& P, cudaStream_t stream) {
     const hg_gat_args& A = P.a;
     constexpr int kGroups = kThreads / TPR;
     P.tile_rows = kGroups > 16 ? kMaxTile : 16;
     P.hs = A.H <= 4 ? 4 : 8;
+    P.n_bias = MODE == 2 ? A.H * P.f_count : P.f_count;
     // staging capacity: what ~24 KB of shared memory holds, 128..2048 edges per relation per tile
-    const size_t fixed = smem_bytes(A.n_rel, 0, P.hs, P.f_count);
-    const size_t per_edge = static_cast<size_t>(A.n_rel) * (4 + 4 * P.hs + 1);
+    const size_t fixed = smem_bytes(A.n_rel, 0, P.hs, P.n_bias);
+    const size_t per_edge = static_cast<size_t>(A.n_rel) * (4 + 4 * P.hs);
     int cap = fixed < 24 * 1024 ? static_cast<int>((24 * 1024 - fixed) / per_edge) : 0;
     cap = cap / 32 * 32;
     cap = cap < 128 ? 128 : (cap > 2048 ? 2048 : cap);
     P.cap = cap;
-    const size_t smem = smem_bytes(A.n_rel, cap, P.hs, P.f_count);
+    const size_t smem = smem_bytes(A.n_rel, cap, P.hs, P.n_bias);
     if (smem > 200 * 1024) return HG_EUNSUPPORTED;
+    auto kernel = k_gat_fused<VEC, TPR, KC, MODE, HT>;
     if (smem > 48 * 1024) {
-        HG_CUDA_TRY(cudaFuncSetAttribute(k_gat_fused<VEC, TPR, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         static_cast<int>(smem)));
+        HG_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     }
     const int sms = sm_count() > 0 ? sm_count() : 148;
     const int64_t need = ceil_div<int64_t>(A.n_dst, P.tile_rows);
     const int64_t cap_grid = static_cast<int64_t>(sms) * 6 * 8;  // 8 waves of 148 SMs x 6 resident CTAs
     const unsigned grid = static_cast<unsigned>(need < cap_grid ? need : cap_grid);
-    k_gat_fused<VEC, TPR, KC><<<grid, kThreads, smem, stream>>>(P);
+    kernel<<<grid, kThreads, smem, stream>>>(P);
     return check_launch();
 }
 
 template <int VEC>
 int dispatch(GatParams& P, cudaStream_t stream) {
     const int nco = P.f_count / VEC;
-    if (nco <= 4) return launch<VEC, 4, 1>(P, stream);
-    if (nco <= 8) return launch<VEC, 8, 1>(P, stream);
-    if (nco <= 16) return launch<VEC, 16, 1>(P, stream);
-    if (nco <= 32) return launch<VEC, 32, 1>(P, stream);
-    if (nco <= 64) return launch<VEC, 32, 2>(P, stream);
-    if (nco <= 96) return launch<VEC, 32, 3>(P, stream);
-    if (nco <= 128) return launch<VEC, 32, 4>(P, stream);
-    if (nco <= 192) return launch<VEC, 32, 6>(P, stream);
-    return launch<VEC, 32, 8>(P, stream);
+    if (nco <= 4) return launch<VEC, 4, 1, 0, 0>(P, stream);
+    if (nco <= 8) return launch<VEC, 8, 1, 0, 0>(P, stream);
+    if (nco <= 16) return launch<VEC, 16, 1, 0, 0>(P, stream);
+    if (nco <= 32) return launch<VEC, 32, 1, 0, 0>(P, stream);
+    if (nco <= 64) return launch<VEC, 32, 2, 0, 0>(P, stream);
+    if (nco <= 96) return launch<VEC, 32, 3, 0, 0>(P, stream);
+    if (nco <= 128) return launch<VEC, 32, 4, 0, 0>(P, stream);
+    if (nco <= 192) return launch<VEC, 32, 6, 0, 0>(P, stream);
+    return launch<VEC, 32, 8, 0, 0>(P, stream);
+}
+
+// Specialised forms (float4 chunks, H <= 4 compile-time): MODE 1 covers C <= 128, MODE 2 C <= 256.
+template <int MODE, int HT>
+int dispatch_special(GatParams& P, cudaStream_t stream) {
+    const int nco = P.f_count / 4;
+    if (nco <= 4) return launch<4, 4, 1, MODE, HT>(P, stream);
+    if (nco <= 8) return launch<4, 8, 1, MODE, HT>(P, stream);
+    if (nco <= 16) return launch<4, 16, 1, MODE, HT>(P, stream);
+    if (nco <= 32) return launch<4, 32, 1, MODE, HT>(P, stream);
+    if constexpr (MODE == 2) {
+        if (nco <= 64) return launch<4, 32, 2, MODE, HT>(P, stream);
+    }
+    return HG_EUNSUPPORTED;
+}
+
+template <int MODE>
+int dispatch_heads(GatParams& P, cudaStream_t stream) {
+    switch (P.a.H) {
+        case 1: return dispatch_special<MODE, 1>(P, stream);
+        case 2: return dispatch_special<MODE, 2>(P, stream);
+        case 3: return dispatch_special<MODE, 3>(P, stream);
+        case 4: return dispatch_special<MODE, 4>(P, stream);
+        default: return HG_EUNSUPPORTED;
+    }
 }
 
 }  // namespace
@@ -436,6 +525,13 @@ extern "C" int hg_gat_fused(const hg_gat_args* a, void* stream_) {
         return true;
     };
     const int vec = ok(4) ? 4 : (ok(2) ? 2 : 1);
+    if (vec == 4 && a->H <= 4 && ((head_mean && a->C <= 128) || (a->src_shared && a->C <= 256))) {
+        GatParams P;
+        P.a = *a;
+        P.f_begin = 0;
+        P.f_count = a->C;
+        return head_mean ? dispatch_heads<1>(P, stream) : dispatch_heads<2>(P, stream);
+    }
     const int block = 32 * 8 * vec;  // widest output block one launch covers
     for (int f0 = 0; f0 < width; f0 += block) {
         GatParams P;
