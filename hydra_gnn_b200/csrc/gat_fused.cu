@@ -1,6 +1,6 @@
 // K3 + K4 -- fused GAT for one destination node type (v6).
 //
-// A CTA (128 threads, 6-8 resident per SM) owns a tile of 16-32 consecutive destination rows
+// A CTA (128 threads, 6-8 resident per SM) owns a tile of 32 consecutive destination rows
 // (consecutive rows belong to the same scene graph, so their neighbour sets overlap and the gathers
 // of a tile hit L1/L2).  Per tile, three barriers:
 //   stage    rowptr slices and destination logits; and -- threads = edges, coalesced on col -- the
@@ -31,12 +31,12 @@ namespace {
 constexpr int kThreads = 128;
 constexpr int kWarps = kThreads / kWarp;
 constexpr int kMaxHeads = 8;
-constexpr int kMaxTile = 32;  // rows per tile: 16 (32 when a row needs only 4 threads)
+constexpr int kMaxTile = 32;  // rows per tile
 
 struct GatParams {
     hg_gat_args a;
     int32_t cap;        // staged edges per relation per tile (multiple of 32)
-    int32_t tile_rows;  // 16 or 32
+    int32_t tile_rows;  // kMaxTile
     int32_t hs;         // padded head stride in shared memory: 4 or 8
     int32_t f_begin;    // first column of this launch (wide rows are split over launches);
     int32_t f_count;    // columns of this launch.  OUTPUT columns, except MODE 2: columns of the source row
@@ -148,8 +148,9 @@ __device__ __noinline__ void slow_row(const GatParams& P, int64_t i, int lane, i
 
 // MODE 0: generic (concat / src_shared / head-mean with any H <= 8; thread chunks are OUTPUT chunks).
 // MODE 1: head-mean, H == HT (<= 4).   MODE 2: aggregate-first (src_shared), H == HT: chunks of the SOURCE row.
-template <int VEC, int TPR, int KC, int MODE, int HT>
-__global__ void __launch_bounds__(kThreads, (KC * (MODE == 2 ? HT : 1) <= 4 ? 6 : 4))
+// OCC: resident CTAs per SM the kernel is compiled for (register cap); 8 pays on grids of many waves.
+template <int VEC, int TPR, int KC, int MODE, int HT, int OCC>
+__global__ void __launch_bounds__(kThreads, OCC)
 k_gat_fused(const __grid_constant__ GatParams P) {
     extern __shared__ __align__(16) uint8_t s_raw[];
     const hg_gat_args& A = P.a;
@@ -290,17 +291,18 @@ k_gat_fused(const __grid_constant__ GatParams P) {
             for (int r = 0; r < R; ++r) {
                 const float* __restrict__ xsb = A.rel[r].xs + fsrc[0];
                 const int ld = static_cast<int>(A.rel[r].ldxs);
+                const uint32_t ldb = static_cast<uint32_t>(ld) * 4u;  // row pitch in bytes (< 4 GB, checked by the host)
                 const int32_t* rp = S.rp + r * (kMaxTile + 1);
                 const int beg = rp[t] - rp[0], end = rp[t + 1] - rp[0];
                 const int32_t* colp = S.col + r * cap;
                 const float* wp = S.w + ((static_cast<size_t>(r) * cap) << hsh);
                 if constexpr (MODE == 1) {
-                    const float* __restrict__ xh[HT];  // one base per head: an address is then ONE IMAD.WIDE
+                    const char* xh[HT];  // one byte base per head: an address is then ONE IMAD.WIDE.U32
 #pragma unroll
-                    for (int hh = 0; hh < HT; ++hh) xh[hh] = xsb + hh * C;
-#pragma unroll 2
+                    for (int hh = 0; hh < HT; ++hh) xh[hh] = reinterpret_cast<const char*>(xsb + hh * C);
+#pragma unroll(OCC >= 8 ? 1 : 2)
                     for (int e = beg; e < end; ++e) {
-                        const int j = colp[e];
+                        const uint32_t j = static_cast<uint32_t>(colp[e]);
                         const float4 wa = *reinterpret_cast<const float4*>(wp + (e << 2));
                         const float wv[4] = {wa.x, wa.y, wa.z, wa.w};
                         float val[HT][KC][VEC];
@@ -309,7 +311,7 @@ k_gat_fused(const __grid_constant__ GatParams P) {
 #pragma unroll
                             for (int k = 0; k < KC; ++k) {
                                 if (KC == 1 || live[k]) {
-                                    ldg_vec<VEC>(xh[hh] + static_cast<int64_t>(j) * ld + k * TPR * VEC, val[hh][k]);
+                                    ldg_vec<VEC>(reinterpret_cast<const float*>(xh[hh] + static_cast<uint64_t>(j) * ldb) + k * TPR * VEC, val[hh][k]);
                                 } else {
 #pragma unroll
                                     for (int v = 0; v < VEC; ++v) val[hh][k][v] = 0.f;
@@ -325,14 +327,14 @@ k_gat_fused(const __grid_constant__ GatParams P) {
                 } else if constexpr (MODE == 2) {
 #pragma unroll(KC <= 2 ? 4 : 2)
                     for (int e = beg; e < end; ++e) {
-                        const int j = colp[e];
+                        const uint32_t j = static_cast<uint32_t>(colp[e]);
                         const float4 wa = *reinterpret_cast<const float4*>(wp + (e << 2));
                         const float wv[4] = {wa.x, wa.y, wa.z, wa.w};
                         float val[KC][VEC];
 #pragma unroll
                         for (int k = 0; k < KC; ++k) {
                             if (KC == 1 || live[k]) {
-                                ldg_vec<VEC>(xsb + static_cast<int64_t>(j) * ld + k * TPR * VEC, val[k]);
+                                ldg_vec<VEC>(reinterpret_cast<const float*>(reinterpret_cast<const char*>(xsb) + static_cast<uint64_t>(j) * ldb) + k * TPR * VEC, val[k]);
                             } else {
 #pragma unroll
                                 for (int v = 0; v < VEC; ++v) val[k][v] = 0.f;
@@ -428,8 +430,7 @@ k_gat_fused(const __grid_constant__ GatParams P) {
 template <int VEC, int TPR, int KC, int MODE, int HT>
 int launch(GatParams& P, cudaStream_t stream) {
     const hg_gat_args& A = P.a;
-    constexpr int kGroups = kThreads / TPR;
-    P.tile_rows = kGroups > 16 ? kMaxTile : 16;
+    P.tile_rows = kMaxTile;
     P.hs = A.H <= 4 ? 4 : 8;
     P.n_bias = MODE == 2 ? A.H * P.f_count : P.f_count;
     // staging capacity: what ~24 KB of shared memory holds, 128..2048 edges per relation per tile
@@ -441,16 +442,23 @@ int launch(GatParams& P, cudaStream_t stream) {
     P.cap = cap;
     const size_t smem = smem_bytes(A.n_rel, cap, P.hs, P.n_bias);
     if (smem > 200 * 1024) return HG_EUNSUPPORTED;
-    auto kernel = k_gat_fused<VEC, TPR, KC, MODE, HT>;
-    if (smem > 48 * 1024) {
-        HG_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    }
     const int sms = sm_count() > 0 ? sm_count() : 148;
     const int64_t need = ceil_div<int64_t>(A.n_dst, P.tile_rows);
     const int64_t cap_grid = static_cast<int64_t>(sms) * 6 * 8;  // 8 waves of 148 SMs x 6 resident CTAs
     const unsigned grid = static_cast<unsigned>(need < cap_grid ? need : cap_grid);
-    kernel<<<grid, kThreads, smem, stream>>>(P);
-    return check_launch();
+    auto go = [&](auto kernel) -> int {
+        if (smem > 48 * 1024) {
+            HG_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        }
+        kernel<<<grid, kThreads, smem, stream>>>(P);
+        return check_launch();
+    };
+    constexpr int kOcc = KC * (MODE == 2 ? HT : 1) <= 4 ? 6 : 4;
+    if constexpr (MODE == 1) {
+        // latency-bound on long grids: more resident warps beat more loads in flight per warp
+        if (need >= static_cast<int64_t>(sms) * 6 * 4) return go(k_gat_fused<VEC, TPR, KC, MODE, HT, 8>);
+    }
+    return go(k_gat_fused<VEC, TPR, KC, MODE, HT, kOcc>);
 }
 
 template <int VEC>
@@ -509,6 +517,7 @@ extern "C" int hg_gat_fused(const hg_gat_args* a, void* stream_) {
         const hg_gat_rel& R = a->rel[r];
         // xs / a_src may be NULL only for an empty source set (every row of that relation is then empty)
         if (!R.a_dst || !R.rowptr || !R.col) return HG_EINVAL;
+        if (R.ldxs < 0 || R.ldxs > (INT32_MAX >> 2) || R.lda_src < 0 || R.lda_src > INT32_MAX) return HG_EINVAL;
     }
     const bool head_mean = !a->concat && !a->src_shared;
     const int width = head_mean ? a->C : a->H * a->C;
