@@ -49,34 +49,52 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok;
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(ok)
-        : "r"(smem_u32(bar)), "r"(parity)
+        : "r"(bar), "r"(parity)
         : "memory");
     return ok != 0;
 }
 // Bounded wait: a protocol bug traps (sticky error on this context) instead of hanging the GPU.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     const long long t0 = clock64();
     while (!mbar_try_wait(bar, parity))
         if (clock64() - t0 > kWaitCycles) __trap();
 }
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) { mbar_wait(smem_u32(bar), parity); }
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_mc(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint16_t mask) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;"
+        ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "h"(mask)
+        : "memory");
 }
 // multicast variant: the bytes land at the same smem offset, and complete_tx on the same barrier offset, in every CTA of `mask`
 __device__ __forceinline__ void bulk_g2s_mc(void* dst, const void* src, uint32_t bytes, uint64_t* bar, uint16_t mask) {
@@ -107,22 +125,25 @@ __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
 __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
 }
-__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
+// Descriptors travel as their low words (start address | LBO); the high word (SBO | version | swizzle) is one constant.
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint32_t a_desc_lo, uint32_t b_desc_lo, uint32_t desc_hi,
+                                          uint32_t idesc, uint32_t acc) {
     asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_desc_lo), "r"(b_desc_lo), "r"(desc_hi), "r"(idesc), "r"(acc)
         : "memory");
 }
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-                 : "memory");
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 // arrives on the barrier at the same smem offset in every CTA of `mask`
-__device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t mask) {
+__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                 ::"r"(smem_u32(bar)), "h"(mask)
+                 ::"r"(bar), "h"(mask)
                  : "memory");
 }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
@@ -149,9 +170,26 @@ __host__ __device__ __forceinline__ uint32_t swz_off(int r, int k) {
     return static_cast<uint32_t>((r >> 3) * 1024 + (r & 7) * 128 + ((((k >> 2) ^ r) & 7) << 4) + (k & 3) * 4);
 }
 
-// UMMA shared-memory descriptor, K-major, SWIZZLE_128B: start>>4 | LBO=1 | SBO=1024>>4 | version=1 | layout=2
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
-    return static_cast<uint64_t>((saddr >> 4) & 0x3FFF) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+// UMMA shared-memory descriptor, K-major, SWIZZLE_128B: start>>4 | LBO=1 | SBO=1024>>4 | version=1 | layout=2.
+// Low word: start address (16-byte units; adding n advances 16 n bytes) | LBO.  High word: constant.
+__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr) { return ((saddr >> 4) & 0x3FFFu) | (1u << 16); }
+constexpr uint32_t kDescHi = 64u | (1u << 14) | (2u << 29);
+
+// explicit shared-space vector accesses on 32-bit shared addresses (never generic ST/LD)
+template <int VEC>
+__device__ __forceinline__ void sts_vec(uint32_t addr, const float (&v)[VEC]) {
+    if constexpr (VEC == 4) {
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]) : "memory");
+    } else if constexpr (VEC == 2) {
+        asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(v[0]), "f"(v[1]) : "memory");
+    } else {
+        asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v[0]) : "memory");
+    }
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
 }
 
 // ------------------------------------------------------------------------------ weight packing
@@ -181,29 +219,58 @@ __global__ void __launch_bounds__(256) k_pack_w(const __grid_constant__ TcParams
 }
 
 // ------------------------------------------------------------------------------ main kernel
-// Position of global k-block g (the loaders, the W producer and the MMA warp all walk the same
-// sequence: tiles of this CTA in order, k-blocks of a tile in order).
-struct KbPos {
-    int64_t m0;
-    int n_tile, kb;
-};
 // Work unit u = (group of CS consecutive m-tiles) x n-tile; cluster c takes u = c, c + n_clusters, ...;
 // CTA rank r of the cluster computes m-tile CS * group + r (possibly past the end: all-zero rows, no stores),
 // so the CTAs of a cluster walk the SAME (n-tile, k-block) sequence and can share every W k-block.
+// The loaders, the W producer and the MMA warp all walk that sequence (tiles of this CTA in order, k-blocks
+// of a tile in order) with incremental cursors: no division in any per-k-block path.
+struct Ring {  // pipeline stage + phase parity of the next k-block
+    int s = 0;
+    uint32_t ph = 0;
+    __device__ __forceinline__ void next(int S) {
+        if (++s == S) {
+            s = 0;
+            ph ^= 1u;
+        }
+    }
+};
+
 template <int CS>
-__device__ __forceinline__ int64_t unit_of(int it) {
-    return static_cast<int64_t>(blockIdx.x / CS) + static_cast<int64_t>(it) * (gridDim.x / CS);
-}
+struct TilePos {
+    int n_tile;
+    int64_t m0;
+    __device__ __forceinline__ TilePos(const TcParams& P, int it, uint32_t rank) {
+        const uint32_t u = blockIdx.x / CS + static_cast<uint32_t>(it) * (gridDim.x / CS);  // < 2^31 (plan())
+        const uint32_t grp = u / static_cast<uint32_t>(P.n_tiles);
+        n_tile = static_cast<int>(u - grp * P.n_tiles);
+        m0 = (static_cast<int64_t>(grp) * CS + rank) * BM;
+    }
+};
+
 template <int CS>
-__device__ __forceinline__ KbPos kb_pos(const TcParams& P, int g, uint32_t rank) {
-    const int it = g / P.n_kb;
-    const int64_t u = unit_of<CS>(it);
-    KbPos p;
-    p.kb = g - it * P.n_kb;
-    p.n_tile = static_cast<int>(u % P.n_tiles);
-    p.m0 = ((u / P.n_tiles) * CS + rank) * BM;
-    return p;
-}
+struct KbCursor {  // k-block g of this CTA: tile `it`, k-block kb = segment seg at column k0
+    int it = 0, kb = 0, seg = 0, k0 = 0;
+    int n_tile;
+    int64_t m0;
+    __device__ __forceinline__ KbCursor(const TcParams& P, uint32_t rank) {
+        const TilePos<CS> t(P, 0, rank);
+        n_tile = t.n_tile;
+        m0 = t.m0;
+    }
+    __device__ __forceinline__ void advance(const TcParams& P, uint32_t rank) {
+        ++kb;
+        k0 += BK;
+        if (kb == P.n_kb) {
+            kb = 0; seg = 0; k0 = 0;
+            const TilePos<CS> t(P, ++it, rank);
+            n_tile = t.n_tile;
+            m0 = t.m0;
+        } else if (kb == P.kb_start[seg + 1]) {
+            ++seg;
+            k0 = 0;
+        }
+    }
+};
 
 template <int VEC, int CS>
 struct Loader {
@@ -212,36 +279,33 @@ struct Loader {
     static constexpr int kIters = BM / kRowStep;
 
     // global -> registers (one k-block slice of this thread: kIters vectors)
-    static __device__ __forceinline__ void load(const TcParams& P, int g, int t, uint32_t rank, float (&v)[kIters][VEC]) {
+    static __device__ __forceinline__ void load(const TcParams& P, const KbCursor<CS>& c, int t, float (&v)[kIters][VEC]) {
         const hg_linear_args& A = P.a;
-        const KbPos p = kb_pos<CS>(P, g, rank);
-        int seg = 0;
-        while (seg + 1 < A.n_seg && p.kb >= P.kb_start[seg + 1]) ++seg;
-        const hg_lin_seg& G = A.seg[seg];
+        const hg_lin_seg& G = A.seg[c.seg];
         const int cv = t % kVecPerRow, rb = t / kVecPerRow;
-        const int k0 = (p.kb - P.kb_start[seg]) * BK;
-        const int k = k0 + cv * VEC;
+        const int k = c.k0 + cv * VEC;
         const int64_t step = static_cast<int64_t>(kRowStep) * G.ldx;
-        const float* __restrict__ src = G.x + (p.m0 + rb) * G.ldx + k;
-        if (p.m0 + BM <= A.M && k0 + BK <= G.K) {  // interior k-block (CTA-uniform): no per-element checks
+        const float* __restrict__ src = G.x + (c.m0 + rb) * G.ldx + k;
+        if (c.m0 + BM <= A.M && c.k0 + BK <= G.K) {  // interior k-block (CTA-uniform): no per-element checks
 #pragma unroll
             for (int i = 0; i < kIters; ++i) ldg_vec<VEC>(src + i * step, v[i]);
         } else {
 #pragma unroll
             for (int i = 0; i < kIters; ++i) {
-                const bool row_ok = p.m0 + rb + i * kRowStep < A.M;
+                const bool row_ok = c.m0 + rb + i * kRowStep < A.M;
 #pragma unroll
                 for (int e = 0; e < VEC; ++e) v[i][e] = (row_ok && k + e < G.K) ? __ldg(src + i * step + e) : 0.f;
             }
         }
     }
 
-    // registers -> hi/lo swizzled smem tiles of the stage.  hi = x with the 13 low mantissa bits cleared
-    // (exactly what the tf32 datapath reads), lo = x - hi (exact; the datapath reads its top 11 bits).
-    static __device__ __forceinline__ void store(uint8_t* stage, int t, const float (&v)[kIters][VEC]) {
+    // registers -> hi/lo swizzled smem tiles of the stage (shared address `stage`).  hi = x with the 13 low
+    // mantissa bits cleared (exactly what the tf32 datapath reads), lo = x - hi (exact; the datapath reads
+    // its top 11 bits).
+    static __device__ __forceinline__ void store(uint32_t stage, int t, const float (&v)[kIters][VEC]) {
         static_assert(kRowStep % 8 == 0, "rows of one thread must share their swizzle phase");
         const int cv = t % kVecPerRow, rb = t / kVecPerRow;
-        uint8_t* dst = stage + swz_off(rb, cv * VEC);  // row rb + i * kRowStep: same phase, (kRowStep / 8) KB further
+        const uint32_t dst = stage + swz_off(rb, cv * VEC);  // row rb + i * kRowStep: same phase, (kRowStep / 8) KB further
 #pragma unroll
         for (int i = 0; i < kIters; ++i) {
             float hi[VEC], lo[VEC];
@@ -250,8 +314,8 @@ struct Loader {
                 hi[e] = __uint_as_float(__float_as_uint(v[i][e]) & 0xFFFFE000u);
                 lo[e] = v[i][e] - hi[e];
             }
-            st_vec<VEC>(reinterpret_cast<float*>(dst + i * (kRowStep / 8) * 1024), hi);
-            st_vec<VEC>(reinterpret_cast<float*>(dst + kATileBytes + i * (kRowStep / 8) * 1024), lo);
+            sts_vec<VEC>(dst + i * (kRowStep / 8) * 1024, hi);
+            sts_vec<VEC>(dst + kATileBytes + i * (kRowStep / 8) * 1024, lo);
         }
     }
 };
@@ -273,18 +337,19 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
     const int my_tiles = static_cast<int>((total_units - cluster_id + n_clusters - 1) / n_clusters);
     const int G = my_tiles * P.n_kb;  // k-blocks this CTA streams (identical for every CTA of the cluster)
 
-    // carve: [1024-aligned stages][barriers][tmem slot]
-    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* bars = reinterpret_cast<uint64_t*>(base + static_cast<size_t>(S) * stage_bytes);
-    uint64_t* full_a = bars;             // [S] loaders -> MMA   (count = loader warps)
-    uint64_t* full_b = bars + S;         // [S] bulk copy -> MMA (count = 1 + tx bytes)
-    uint64_t* empty = bars + 2 * S;      // [S] MMA -> loaders / W producer (tcgen05.commit)
-    uint64_t* acc_full = bars + 3 * S;   // [2] MMA -> epilogue
-    uint64_t* acc_empty = acc_full + 2;  // [2] epilogue -> MMA (count = epilogue warps)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+    // carve (all as 32-bit shared addresses): [1024-aligned stages][barriers][tmem slot][epilogue affine]
+    const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bars = sbase + static_cast<uint32_t>(S) * stage_bytes;
+    const uint32_t full_a = bars;                  // [S] loaders -> MMA   (count = loader warps)
+    const uint32_t full_b = bars + 8u * S;         // [S] bulk copy -> MMA (count = 1 + tx bytes)
+    const uint32_t empty = bars + 16u * S;         // [S] MMA -> loaders / W producer (tcgen05.commit)
+    const uint32_t acc_full = bars + 24u * S;      // [2] MMA -> epilogue
+    const uint32_t acc_empty = acc_full + 16u;     // [2] epilogue -> MMA (count = epilogue warps)
+    const uint32_t tmem_slot = acc_empty + 16u;
     // per-column epilogue affine  y = act(acc * sc[n] + sh[n])  (bias / scale / shift folded once per CTA)
-    float* s_sc = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tmem_slot + 4) + 15) & ~uintptr_t(15));
-    float* s_sh = s_sc + P.n_tiles * P.block_n;
+    const uint32_t s_sc = (tmem_slot + 16u + 15u) & ~15u;
+    const uint32_t s_sh = s_sc + 4u * static_cast<uint32_t>(P.n_tiles * P.block_n);
+    uint8_t* const gen = smem_raw + (sbase - smem_u32(smem_raw));  // generic view of sbase
     for (int n = threadIdx.x; n < P.n_tiles * P.block_n; n += kThreads) {
         float sc = 1.f, sh = 0.f;
         if (n < A.N) {
@@ -292,81 +357,82 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
             if (A.scale) { sc = __ldg(A.scale + n); sh *= sc; }
             if (A.shift) sh += __ldg(A.shift + n);
         }
-        s_sc[n] = sc;
-        s_sh[n] = sh;
+        reinterpret_cast<float*>(gen + (s_sc - sbase))[n] = sc;
+        reinterpret_cast<float*>(gen + (s_sh - sbase))[n] = sh;
     }
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < S; ++s) {
-            mbar_init(&full_a[s], kLoaderWarps);
-            mbar_init(&full_b[s], 1);
-            mbar_init(&empty[s], CS);  // one tcgen05.commit from every CTA that reads the shared W stage
+            mbar_init(reinterpret_cast<uint64_t*>(gen + (full_a - sbase)) + s, kLoaderWarps);
+            mbar_init(reinterpret_cast<uint64_t*>(gen + (full_b - sbase)) + s, 1);
+            mbar_init(reinterpret_cast<uint64_t*>(gen + (empty - sbase)) + s, CS);  // one tcgen05.commit per CTA sharing the W stage
         }
         for (int b = 0; b < 2; ++b) {
-            mbar_init(&acc_full[b], 1);
-            mbar_init(&acc_empty[b], kEpiWarps);
+            mbar_init(reinterpret_cast<uint64_t*>(gen + (acc_full - sbase)) + b, 1);
+            mbar_init(reinterpret_cast<uint64_t*>(gen + (acc_empty - sbase)) + b, kEpiWarps);
         }
         fence_barrier_init();
     }
-    if (warp == 0) tmem_alloc(tmem_slot, static_cast<uint32_t>(P.tmem_cols));
+    if (warp == 0) tmem_alloc(reinterpret_cast<uint32_t*>(gen + (tmem_slot - sbase)), static_cast<uint32_t>(P.tmem_cols));
     tc_fence_before();
     __syncthreads();
     if (CS > 1) cluster_sync_all();  // peers' barriers are initialised before anything remote arrives on them
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(gen + (tmem_slot - sbase));
 
     if (warp == 0) {
         // ===================== MMA issuer =====================
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(P.block_n >> 3) << 17) |
                                (static_cast<uint32_t>(BM >> 4) << 24);
-        int g = 0;
+        const uint32_t a_lo_off = kATileBytes >> 4, b_hi_off = (2 * kATileBytes) >> 4;
+        const uint32_t b_lo_off = b_hi_off + (b_tile_bytes >> 4);
+        Ring r;
         for (int it = 0; it < my_tiles; ++it) {
-            const int ab = it & 1;
-            mbar_wait(&acc_empty[ab], ((static_cast<uint32_t>(it) >> 1) & 1u) ^ 1u);  // epilogue drained this buffer
+            const uint32_t ab = static_cast<uint32_t>(it) & 1u;
+            mbar_wait(acc_empty + 8u * ab, ((static_cast<uint32_t>(it) >> 1) & 1u) ^ 1u);  // epilogue drained this buffer
             tc_fence_after();
-            const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(ab * P.block_n);
-            for (int kb = 0; kb < P.n_kb; ++kb, ++g) {
-                const int s = g % S;
-                const uint32_t ph = static_cast<uint32_t>(g / S) & 1u;
-                mbar_wait(&full_a[s], ph);
-                mbar_wait(&full_b[s], ph);
+            const uint32_t d_tmem = tmem_base + ab * static_cast<uint32_t>(P.block_n);
+            for (int kb = 0; kb < P.n_kb; ++kb) {
+                mbar_wait(full_a + 8u * r.s, r.ph);
+                mbar_wait(full_b + 8u * r.s, r.ph);
                 tc_fence_after();
+                const uint32_t a_hi = desc_lo(sbase + static_cast<uint32_t>(r.s) * stage_bytes);  // descriptor low words
                 if (lane == 0) {
-                    const uint32_t sa = smem_u32(base + static_cast<size_t>(s) * stage_bytes);
-                    const uint64_t a_hi = make_desc(sa), a_lo = make_desc(sa + kATileBytes);
-                    const uint64_t b_hi = make_desc(sa + 2 * kATileBytes), b_lo = make_desc(sa + 2 * kATileBytes + b_tile_bytes);
 #pragma unroll
-                    for (int ks = 0; ks < BK / 8; ++ks) {  // UMMA_K = 8 tf32 = 32 bytes: descriptor start += 2
-                        const uint64_t adv = static_cast<uint64_t>(ks * 2);
+                    for (uint32_t ks = 0; ks < BK / 8; ++ks) {  // UMMA_K = 8 tf32 = 32 bytes: start address += 2
+                        const uint32_t a = a_hi + 2u * ks;
                         // small terms first, the main term last (one accumulator holds all three)
-                        umma_tf32(d_tmem, a_hi + adv, b_lo + adv, idesc, (kb | ks) != 0 ? 1u : 0u);
-                        umma_tf32(d_tmem, a_lo + adv, b_hi + adv, idesc, 1u);
-                        umma_tf32(d_tmem, a_hi + adv, b_hi + adv, idesc, 1u);
+                        umma_tf32(d_tmem, a, a + b_lo_off, kDescHi, idesc, ks != 0 ? 1u : static_cast<uint32_t>(kb != 0));
+                        umma_tf32(d_tmem, a + a_lo_off, a + b_hi_off, kDescHi, idesc, 1u);
+                        umma_tf32(d_tmem, a, a + b_hi_off, kDescHi, idesc, 1u);
                     }
-                    if (CS > 1) umma_commit_mc(&empty[s], kAllMask);   // the W stage is shared: tell every CTA
-                    else umma_commit(&empty[s]);                       // stage reusable once these MMAs retire
-                    if (kb == P.n_kb - 1) umma_commit(&acc_full[ab]);  // accumulator complete
+                    if (CS > 1) umma_commit_mc(empty + 8u * r.s, kAllMask);   // the W stage is shared: tell every CTA
+                    else umma_commit(empty + 8u * r.s);                       // stage reusable once these MMAs retire
+                    if (kb == P.n_kb - 1) umma_commit(acc_full + 8u * ab);    // accumulator complete
                 }
                 __syncwarp();
+                r.next(S);
             }
         }
     } else if (warp == 1) {
         // ===================== W producer =====================
         if (lane == 0) {
-            for (int g = 0; g < G; ++g) {
-                const int s = g % S;
-                const uint32_t ph = static_cast<uint32_t>(g / S) & 1u;
-                const KbPos p = kb_pos<CS>(P, g, rank);
-                mbar_wait(&empty[s], ph ^ 1u);  // every CTA of the cluster has retired its MMAs on this stage
-                uint8_t* stage = base + static_cast<size_t>(s) * stage_bytes;
-                mbar_arrive_expect_tx(&full_b[s], 2u * b_tile_bytes);
-                const float* src = P.wp + (static_cast<int64_t>(p.n_tile) * P.n_kb + p.kb) * 2 * (b_tile_bytes / 4);
-                if (CS > 1) {  // this CTA fetches 1/CS of the W_hi|W_lo image and multicasts it to the whole cluster
-                    const uint32_t part = 2u * b_tile_bytes / CS;
-                    bulk_g2s_mc(stage + 2 * kATileBytes + rank * part, reinterpret_cast<const uint8_t*>(src) + rank * part,
-                                part, &full_b[s], kAllMask);
-                } else {
-                    bulk_g2s(stage + 2 * kATileBytes, src, 2u * b_tile_bytes, &full_b[s]);
+            Ring r;
+            const uint32_t w_bytes = 2u * b_tile_bytes;  // W_hi | W_lo image of one (n-tile, k-block)
+            for (int it = 0; it < my_tiles; ++it) {
+                const TilePos<CS> tp(P, it, rank);
+                const uint8_t* src = reinterpret_cast<const uint8_t*>(P.wp) + static_cast<size_t>(tp.n_tile) * P.n_kb * w_bytes;
+                for (int kb = 0; kb < P.n_kb; ++kb, src += w_bytes) {
+                    mbar_wait(empty + 8u * r.s, r.ph ^ 1u);  // every CTA of the cluster has retired its MMAs on this stage
+                    const uint32_t dst = sbase + static_cast<uint32_t>(r.s) * stage_bytes + 2u * kATileBytes;
+                    mbar_arrive_expect_tx(full_b + 8u * r.s, w_bytes);
+                    if (CS > 1) {  // this CTA fetches 1/CS of the image and multicasts it to the whole cluster
+                        const uint32_t part = w_bytes / CS;
+                        bulk_g2s_mc(dst + rank * part, src + rank * part, part, full_b + 8u * r.s, kAllMask);
+                    } else {
+                        bulk_g2s(dst, src, w_bytes, full_b + 8u * r.s);
+                    }
+                    r.next(S);
                 }
             }
         }
@@ -375,53 +441,60 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
         using L = Loader<VEC, CS>;
         const int t = threadIdx.x - 64;
         float v0[L::kIters][VEC], v1[L::kIters][VEC], v2[L::kIters][VEC];
-        auto finish = [&](int g, const float (&v)[L::kIters][VEC]) {
-            const int s = g % S;
-            const uint32_t ph = static_cast<uint32_t>(g / S) & 1u;
-            mbar_wait(&empty[s], ph ^ 1u);  // MMAs of the previous use of this stage have retired
-            L::store(base + static_cast<size_t>(s) * stage_bytes, t, v);
+        Ring r;
+        KbCursor<CS> cur(P, rank);
+        int fetched = 0;
+        auto fetch = [&](float (&v)[L::kIters][VEC]) {  // next k-block of the sequence -> registers
+            if (fetched < G) {
+                L::load(P, cur, t, v);
+                cur.advance(P, rank);
+            }
+            ++fetched;
+        };
+        auto finish = [&](const float (&v)[L::kIters][VEC]) {  // registers -> stage r.s, publish
+            mbar_wait(empty + 8u * r.s, r.ph ^ 1u);  // MMAs of the previous use of this stage have retired
+            L::store(sbase + static_cast<uint32_t>(r.s) * stage_bytes, t, v);
             fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
             __syncwarp();
-            if (lane == 0) mbar_arrive(&full_a[s]);
+            if (lane == 0) mbar_arrive(full_a + 8u * r.s);
+            r.next(S);
         };
-        if (0 < G) L::load(P, 0, t, rank, v0);
-        if (1 < G) L::load(P, 1, t, rank, v1);
-        if (2 < G) L::load(P, 2, t, rank, v2);
+        fetch(v0);
+        fetch(v1);
+        fetch(v2);
         for (int g = 0; g < G; g += kPrefetch) {
-            finish(g, v0);
-            if (g + 3 < G) L::load(P, g + 3, t, rank, v0);
+            finish(v0);
+            fetch(v0);
             if (g + 1 < G) {
-                finish(g + 1, v1);
-                if (g + 4 < G) L::load(P, g + 4, t, rank, v1);
+                finish(v1);
+                fetch(v1);
             }
             if (g + 2 < G) {
-                finish(g + 2, v2);
-                if (g + 5 < G) L::load(P, g + 5, t, rank, v2);
+                finish(v2);
+                fetch(v2);
             }
         }
     } else {
         // ===================== epilogue =====================
         const int q = warp & 3;  // TMEM lane quarter this warp may read
         const bool vec_store = (A.ldy % 4 == 0) && ((reinterpret_cast<uintptr_t>(A.y) & 15) == 0);
+        const int act = A.act;
         for (int it = 0; it < my_tiles; ++it) {
-            const int ab = it & 1;
-            const int64_t u = unit_of<CS>(it);
-            const int n0 = static_cast<int>(u % P.n_tiles) * P.block_n;
-            const int64_t m = ((u / P.n_tiles) * CS + rank) * BM + q * 32 + lane;
-            mbar_wait(&acc_full[ab], (static_cast<uint32_t>(it) >> 1) & 1u);
+            const uint32_t ab = static_cast<uint32_t>(it) & 1u;
+            const TilePos<CS> tp(P, it, rank);
+            const int n0 = tp.n_tile * P.block_n;
+            const int64_t m = tp.m0 + q * 32 + lane;
+            mbar_wait(acc_full + 8u * ab, (static_cast<uint32_t>(it) >> 1) & 1u);
             tc_fence_after();
-            const uint32_t t_acc = tmem_base + static_cast<uint32_t>(ab * P.block_n) + (static_cast<uint32_t>(q * 32) << 16);
-            const int act = A.act;
+            const uint32_t t_acc = tmem_base + ab * static_cast<uint32_t>(P.block_n) + (static_cast<uint32_t>(q * 32) << 16);
             for (int c = 0; c * 16 < P.block_n; ++c) {
                 float acc[16];
                 tmem_ld16(t_acc + static_cast<uint32_t>(c * 16), acc);
                 const int n = n0 + c * 16;
                 if (m >= A.M || n >= A.N) continue;
-                const float4* sc4 = reinterpret_cast<const float4*>(s_sc + n);
-                const float4* sh4 = reinterpret_cast<const float4*>(s_sh + n);
 #pragma unroll
                 for (int j4 = 0; j4 < 4; ++j4) {
-                    const float4 sc = sc4[j4], sh = sh4[j4];  // broadcast LDS.128
+                    const float4 sc = lds128(s_sc + 4u * (n + 4 * j4)), sh = lds128(s_sh + 4u * (n + 4 * j4));  // broadcast
                     acc[4 * j4 + 0] = fmaf(acc[4 * j4 + 0], sc.x, sh.x);
                     acc[4 * j4 + 1] = fmaf(acc[4 * j4 + 1], sc.y, sh.y);
                     acc[4 * j4 + 2] = fmaf(acc[4 * j4 + 2], sc.z, sh.z);
@@ -447,7 +520,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
             }
             tc_fence_before();  // all tcgen05.ld of this buffer done (tmem_ld16 waits) -> hand it back
             __syncwarp();
-            if (lane == 0) mbar_arrive(&acc_empty[ab]);
+            if (lane == 0) mbar_arrive(acc_empty + 8u * ab);
         }
     }
 
@@ -487,6 +560,7 @@ bool plan(const hg_linear_args& a, TcParams& P) {
     int cols = 32;
     while (cols < 2 * P.block_n) cols <<= 1;  // two accumulator buffers
     P.tmem_cols = cols;
+    if (ceil_div<int64_t>(P.m_tiles, 1) * P.n_tiles >= (int64_t{1} << 31)) return false;  // 32-bit work-unit ids
     return stages >= 1 && P.n_kb >= 1 && cols <= 512;
 }
 
