@@ -23,6 +23,10 @@
 namespace hg {
 namespace {
 
+#ifndef HG_TC_EXP
+#define HG_TC_EXP 0  // timing experiments only (wrong results): 1 no y stores, 2 no x loads, 4 no W copies, 8 no MMA
+#endif
+
 constexpr int BM = 128;
 constexpr int BK = 32;                      // fp32 elements per k-block = one 128-byte swizzle row
 constexpr int kLoaderWarps = 8;
@@ -158,6 +162,24 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+        "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void sts128(uint32_t addr, float a, float b, float c, float d) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 __device__ __forceinline__ float tf32_rna(float v) {
     uint32_t r;
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
@@ -286,6 +308,9 @@ struct Loader {
         const int k = c.k0 + cv * VEC;
         const int64_t step = static_cast<int64_t>(kRowStep) * G.ldx;
         const float* __restrict__ src = G.x + (c.m0 + rb) * G.ldx + k;
+#if HG_TC_EXP & 2
+        if (true) { for (int i = 0; i < kIters; ++i) for (int e = 0; e < VEC; ++e) v[i][e] = 1.f + t; return; }
+#endif
         if (c.m0 + BM <= A.M && c.k0 + BK <= G.K) {  // interior k-block (CTA-uniform): no per-element checks
 #pragma unroll
             for (int i = 0; i < kIters; ++i) ldg_vec<VEC>(src + i * step, v[i]);
@@ -349,6 +374,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
     // per-column epilogue affine  y = act(acc * sc[n] + sh[n])  (bias / scale / shift folded once per CTA)
     const uint32_t s_sc = (tmem_slot + 16u + 15u) & ~15u;
     const uint32_t s_sh = s_sc + 4u * static_cast<uint32_t>(P.n_tiles * P.block_n);
+    const uint32_t s_xp = s_sh + 4u * static_cast<uint32_t>(P.n_tiles * P.block_n);  // [epilogue warps][4 KB] transpose buffers
     uint8_t* const gen = smem_raw + (sbase - smem_u32(smem_raw));  // generic view of sbase
     for (int n = threadIdx.x; n < P.n_tiles * P.block_n; n += kThreads) {
         float sc = 1.f, sh = 0.f;
@@ -399,7 +425,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
                 const uint32_t a_hi = desc_lo(sbase + static_cast<uint32_t>(r.s) * stage_bytes);  // descriptor low words
                 if (lane == 0) {
 #pragma unroll
-                    for (uint32_t ks = 0; ks < BK / 8; ++ks) {  // UMMA_K = 8 tf32 = 32 bytes: start address += 2
+                    for (uint32_t ks = 0; ks < ((HG_TC_EXP & 8) ? 0 : BK / 8); ++ks) {  // UMMA_K = 8 tf32 = 32 bytes: start address += 2
                         const uint32_t a = a_hi + 2u * ks;
                         // small terms first, the main term last (one accumulator holds all three)
                         umma_tf32(d_tmem, a, a + b_lo_off, kDescHi, idesc, ks != 0 ? 1u : static_cast<uint32_t>(kb != 0));
@@ -425,6 +451,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
                 for (int kb = 0; kb < P.n_kb; ++kb, src += w_bytes) {
                     mbar_wait(empty + 8u * r.s, r.ph ^ 1u);  // every CTA of the cluster has retired its MMAs on this stage
                     const uint32_t dst = sbase + static_cast<uint32_t>(r.s) * stage_bytes + 2u * kATileBytes;
+#if HG_TC_EXP & 4
+                    mbar_arrive(full_b + 8u * r.s); r.next(S); continue;
+#endif
                     mbar_arrive_expect_tx(full_b + 8u * r.s, w_bytes);
                     if (CS > 1) {  // this CTA fetches 1/CS of the image and multicasts it to the whole cluster
                         const uint32_t part = w_bytes / CS;
@@ -476,49 +505,90 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
         }
     } else {
         // ===================== epilogue =====================
+        // tcgen05.ld gives lane r the columns of ROW r; a global store wants a warp on consecutive columns.
+        // Each warp transposes 32 x 32 chunks through a private 4 KB XOR-swizzled buffer: 8 STS.128 + 8 LDS.128
+        // per lane, both conflict-free, then every STG.128 of the warp writes four full 128-byte lines.
         const int q = warp & 3;  // TMEM lane quarter this warp may read
-        const bool vec_store = (A.ldy % 4 == 0) && ((reinterpret_cast<uintptr_t>(A.y) & 15) == 0);
+        const bool vec_store = (A.ldy % 4 == 0) && (A.N % 4 == 0) && ((reinterpret_cast<uintptr_t>(A.y) & 15) == 0);
         const int act = A.act;
-        for (int it = 0; it < my_tiles; ++it) {
-            const uint32_t ab = static_cast<uint32_t>(it) & 1u;
-            const TilePos<CS> tp(P, it, rank);
-            const int n0 = tp.n_tile * P.block_n;
-            const int64_t m = tp.m0 + q * 32 + lane;
-            mbar_wait(acc_full + 8u * ab, (static_cast<uint32_t>(it) >> 1) & 1u);
-            tc_fence_after();
-            const uint32_t t_acc = tmem_base + ab * static_cast<uint32_t>(P.block_n) + (static_cast<uint32_t>(q * 32) << 16);
-            for (int c = 0; c * 16 < P.block_n; ++c) {
-                float acc[16];
-                tmem_ld16(t_acc + static_cast<uint32_t>(c * 16), acc);
-                const int n = n0 + c * 16;
-                if (m >= A.M || n >= A.N) continue;
+        const uint32_t xbuf = s_xp + static_cast<uint32_t>(warp - (2 + kLoaderWarps)) * 4096u;
+        const uint32_t xrow = xbuf + static_cast<uint32_t>(lane) * 128u;
+        auto affine_act = [&](float (&acc)[32], int n, int cw) {
 #pragma unroll
-                for (int j4 = 0; j4 < 4; ++j4) {
+            for (int j4 = 0; j4 < 8; ++j4) {
+                if (4 * j4 < cw) {
                     const float4 sc = lds128(s_sc + 4u * (n + 4 * j4)), sh = lds128(s_sh + 4u * (n + 4 * j4));  // broadcast
                     acc[4 * j4 + 0] = fmaf(acc[4 * j4 + 0], sc.x, sh.x);
                     acc[4 * j4 + 1] = fmaf(acc[4 * j4 + 1], sc.y, sh.y);
                     acc[4 * j4 + 2] = fmaf(acc[4 * j4 + 2], sc.z, sh.z);
                     acc[4 * j4 + 3] = fmaf(acc[4 * j4 + 3], sc.w, sh.w);
                 }
-                if (act == HG_ACT_RELU) {
+            }
+            if (act == HG_ACT_RELU) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) acc[j] = fmaxf(acc[j], 0.f);
-                } else if (act == HG_ACT_ELU) {
+                for (int j = 0; j < 32; ++j) acc[j] = fmaxf(acc[j], 0.f);
+            } else if (act == HG_ACT_ELU) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) acc[j] = acc[j] > 0.f ? acc[j] : expm1f(acc[j]);
-                }
-                float* dst = A.y + m * A.ldy + n;
-                if (vec_store && n + 16 <= A.N) {
-#pragma unroll
-                    for (int j = 0; j < 16; j += 4)
-                        *reinterpret_cast<float4*>(dst + j) = make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
+                for (int j = 0; j < 32; ++j) acc[j] = acc[j] > 0.f ? acc[j] : expm1f(acc[j]);
+            }
+        };
+        for (int it = 0; it < my_tiles; ++it) {
+            const uint32_t ab = static_cast<uint32_t>(it) & 1u;
+            const TilePos<CS> tp(P, it, rank);
+            const int n0 = tp.n_tile * P.block_n;
+            const int64_t mq = tp.m0 + q * 32;  // first row of this warp's quarter
+            mbar_wait(acc_full + 8u * ab, (static_cast<uint32_t>(it) >> 1) & 1u);
+            tc_fence_after();
+            const uint32_t t_acc = tmem_base + ab * static_cast<uint32_t>(P.block_n) + (static_cast<uint32_t>(q * 32) << 16);
+            for (int c0 = 0; c0 < P.block_n; c0 += 32) {
+                const int cw = P.block_n - c0 < 32 ? 16 : 32;  // block_n is a multiple of 16
+                const int n = n0 + c0;
+                float acc[32];
+                if (cw == 32) {
+                    tmem_ld32(t_acc + static_cast<uint32_t>(c0), acc);
                 } else {
+                    float lo16[16];
+                    tmem_ld16(t_acc + static_cast<uint32_t>(c0), lo16);
 #pragma unroll
-                    for (int j = 0; j < 16; ++j)
-                        if (n + j < A.N) dst[j] = acc[j];
+                    for (int j = 0; j < 16; ++j) acc[j] = lo16[j], acc[16 + j] = 0.f;
+                }
+                if (n >= A.N) continue;  // warp-uniform
+                affine_act(acc, n, cw);
+#if HG_TC_EXP & 1
+                if (acc[0] != 123.456f) continue;
+#endif
+                if (vec_store) {
+                    __syncwarp();  // the previous chunk has been read back by every lane
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        if (4 * j < cw)
+                            sts128(xrow + (static_cast<uint32_t>(j ^ (lane & 7)) << 4), acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
+                    __syncwarp();
+                    if (cw == 32) {  // lane -> (row 4 i + lane / 8, 16-byte chunk lane % 8)
+                        const int ch = lane & 7, col = n + 4 * ch;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int row = 4 * i + (lane >> 3);
+                            const float4 v = lds128(xbuf + static_cast<uint32_t>(row) * 128u + (static_cast<uint32_t>(ch ^ (row & 7)) << 4));
+                            if (mq + row < A.M && col < A.N) *reinterpret_cast<float4*>(A.y + (mq + row) * A.ldy + col) = v;
+                        }
+                    } else {  // 16 columns: lane -> (row 8 i + lane / 4, chunk lane % 4)
+                        const int ch = lane & 3, col = n + 4 * ch;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int row = 8 * i + (lane >> 2);
+                            const float4 v = lds128(xbuf + static_cast<uint32_t>(row) * 128u + (static_cast<uint32_t>(ch ^ (row & 7)) << 4));
+                            if (mq + row < A.M && col < A.N) *reinterpret_cast<float4*>(A.y + (mq + row) * A.ldy + col) = v;
+                        }
+                    }
+                } else if (mq + lane < A.M) {
+                    float* dst = A.y + (mq + lane) * A.ldy + n;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < cw && n + j < A.N) dst[j] = acc[j];
                 }
             }
-            tc_fence_before();  // all tcgen05.ld of this buffer done (tmem_ld16 waits) -> hand it back
+            tc_fence_before();  // all tcgen05.ld of this buffer done (tmem_ld waits) -> hand it back
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_empty + 8u * ab);
         }
@@ -533,6 +603,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
     }
 }
 
+#ifndef HG_TC_CS
+#define HG_TC_CS 2  // CTAs per cluster sharing each W k-block on large problems
+#endif
 constexpr size_t kSmemBudget = 200 * 1024;
 
 bool plan(const hg_linear_args& a, TcParams& P) {
@@ -554,7 +627,7 @@ bool plan(const hg_linear_args& a, TcParams& P) {
     const size_t stage_bytes = 2 * kATileBytes + 2 * static_cast<size_t>(P.block_n) * 128;
     const size_t affine_bytes = 2 * static_cast<size_t>(P.n_tiles) * P.block_n * sizeof(float);
     if (affine_bytes > 32 * 1024) return false;  // N <= 4096
-    int stages = static_cast<int>((kSmemBudget - affine_bytes) / stage_bytes);
+    int stages = static_cast<int>((kSmemBudget - affine_bytes - kEpiWarps * 4096) / stage_bytes);
     stages = stages > 4 ? 4 : stages;
     P.stages = stages;
     int cols = 32;
@@ -610,11 +683,11 @@ int linear_tc_launch(const hg_linear_args& a, void* ws, size_t ws_bytes, cudaStr
     }
     const size_t stage_bytes = 2 * kATileBytes + 2 * static_cast<size_t>(P.block_n) * 128;
     const size_t smem = 1024 + P.stages * stage_bytes + (3 * P.stages + 4) * sizeof(uint64_t) + 48 +
-                        2 * static_cast<size_t>(P.n_tiles) * P.block_n * sizeof(float);
+                        2 * static_cast<size_t>(P.n_tiles) * P.block_n * sizeof(float) + kEpiWarps * 4096;
     const int sms = sm_count() > 0 ? sm_count() : 148;
     // Big problems run as clusters of 2 CTAs that share every W k-block (each fetches half, multicast to both):
     // W re-streaming from L2 is what bounds the 306-wide projection.  Small ones keep independent CTAs.
-    const bool pair = P.m_tiles >= 2 * static_cast<int64_t>(sms) && (2 * P.block_n * 128 / 2) % 16 == 0;
+    const bool pair = P.m_tiles >= 2 * static_cast<int64_t>(sms) && (2 * P.block_n * 128 / HG_TC_CS) % 16 == 0;
     auto go = [&](auto kernel, int cs) -> int {
         HG_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
         const int64_t units = ceil_div<int64_t>(P.m_tiles, cs) * P.n_tiles;
@@ -630,15 +703,16 @@ int linear_tc_launch(const hg_linear_args& a, void* ws, size_t ws_bytes, cudaStr
         attr[0].val.clusterDim.x = cs;
         attr[0].val.clusterDim.y = 1;
         attr[0].val.clusterDim.z = 1;
+        if (cs > 8) HG_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         cfg.attrs = attr;
         cfg.numAttrs = 1;
         HG_CUDA_TRY(cudaLaunchKernelEx(&cfg, kernel, P));
         return check_launch();
     };
     if (pair) {
-        if (P.vec == 4) return go(k_linear_tc<4, 2>, 2);
-        if (P.vec == 2) return go(k_linear_tc<2, 2>, 2);
-        return go(k_linear_tc<1, 2>, 2);
+        if (P.vec == 4) return go(k_linear_tc<4, HG_TC_CS>, HG_TC_CS);
+        if (P.vec == 2) return go(k_linear_tc<2, HG_TC_CS>, HG_TC_CS);
+        return go(k_linear_tc<1, HG_TC_CS>, HG_TC_CS);
     }
     if (P.vec == 4) return go(k_linear_tc<4, 1>, 1);
     if (P.vec == 2) return go(k_linear_tc<2, 1>, 1);
