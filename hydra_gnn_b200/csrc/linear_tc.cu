@@ -31,7 +31,10 @@ constexpr int BM = 128;
 constexpr int BK = 32;                      // fp32 elements per k-block = one 128-byte swizzle row
 constexpr int kLoaderWarps = 8;
 constexpr int kLoaderThreads = kLoaderWarps * 32;
-constexpr int kEpiWarps = 4;
+#ifndef HG_TC_EPI
+#define HG_TC_EPI 4
+#endif
+constexpr int kEpiWarps = HG_TC_EPI;       // 4 or 8: warps sharing a TMEM lane quarter alternate over the 32-column chunks
 constexpr int kThreads = 64 + kLoaderThreads + kEpiWarps * 32;  // 448
 constexpr int kATileBytes = BM * BK * 4;    // 16 KB
 constexpr int kPrefetch = 3;                // k-blocks of A in flight per loader thread
@@ -540,7 +543,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
             mbar_wait(acc_full + 8u * ab, (static_cast<uint32_t>(it) >> 1) & 1u);
             tc_fence_after();
             const uint32_t t_acc = tmem_base + ab * static_cast<uint32_t>(P.block_n) + (static_cast<uint32_t>(q * 32) << 16);
-            for (int c0 = 0; c0 < P.block_n; c0 += 32) {
+            for (int c0 = 32 * ((warp - (2 + kLoaderWarps)) >> 2); c0 < P.block_n; c0 += 32 * (kEpiWarps / 4)) {
                 const int cw = P.block_n - c0 < 32 ? 16 : 32;  // block_n is a multiple of 16
                 const int n = n0 + c0;
                 float acc[32];
