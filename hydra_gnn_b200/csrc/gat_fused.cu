@@ -28,6 +28,10 @@
 namespace hg {
 namespace {
 
+#ifndef HG_GAT_SMEM_KB
+#define HG_GAT_SMEM_KB 24
+#endif
+constexpr size_t kStageBudget = HG_GAT_SMEM_KB * 1024;  // shared memory per CTA for staging (the rest of the SM's 256 KB is L1)
 constexpr int kThreads = 128;
 constexpr int kWarps = kThreads / kWarp;
 constexpr int kMaxHeads = 8;
@@ -433,10 +437,10 @@ int launch(GatParams& P, cudaStream_t stream) {
     P.tile_rows = kMaxTile;
     P.hs = A.H <= 4 ? 4 : 8;
     P.n_bias = MODE == 2 ? A.H * P.f_count : P.f_count;
-    // staging capacity: what ~24 KB of shared memory holds, 128..2048 edges per relation per tile
+    // staging capacity: what the shared-memory budget holds, 128..2048 edges per relation per tile
     const size_t fixed = smem_bytes(A.n_rel, 0, P.hs, P.n_bias);
     const size_t per_edge = static_cast<size_t>(A.n_rel) * (4 + 4 * P.hs);
-    int cap = fixed < 24 * 1024 ? static_cast<int>((24 * 1024 - fixed) / per_edge) : 0;
+    int cap = fixed < kStageBudget ? static_cast<int>((kStageBudget - fixed) / per_edge) : 0;
     cap = cap / 32 * 32;
     cap = cap < 128 ? 128 : (cap > 2048 ? 2048 : cap);
     P.cap = cap;

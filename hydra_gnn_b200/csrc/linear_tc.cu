@@ -11,7 +11,7 @@
 //                 them; the loaders read the 128 x 32 k-block with vector loads THREE k-blocks ahead
 //                 (a register ring, ~48 KB in flight per SM), split hi/lo in registers and store
 //                 both tiles in the UMMA canonical K-major SWIZZLE_128B layout;
-//   warp 1        W producer: one lane issues a 1-D bulk copy (cp.async.bulk, UBLKCP) of the
+//   warp 1        W producer: one lane issues 1-D bulk copies (cp.async.bulk, UBLKCP) of the
 //                 pre-swizzled W_hi|W_lo image of the k-block (packed once per weight version);
 //   warp 0        allocates TMEM; one elected lane issues tcgen05.mma (12 per 32-wide k-block) into
 //                 one of TWO accumulator buffers and tcgen05.commit (frees the smem stage / publishes
@@ -47,6 +47,7 @@ struct TcParams {
     int32_t kb_start[HG_MAX_SEGMENTS + 1];  // first k-block of each segment
     int32_t tmem_cols;
     int32_t vec;          // widest vector all x segments allow (1, 2, 4)
+    int32_t cs;           // 1, or 2 = CTA-pair mode (cta_group::2)
     int64_t m_tiles;
 };
 
@@ -58,12 +59,6 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
 }
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
@@ -86,29 +81,34 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity))
         if (clock64() - t0 > kWaitCycles) __trap();
 }
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) { mbar_wait(smem_u32(bar), parity); }
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
+// cluster-scope acquire: the arrivals come from the peer CTA (pair mode)
+__device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+    if (mbar_try_wait_cluster(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait_cluster(bar, parity))
+        if (clock64() - t0 > kWaitCycles) __trap();
+}
+// arrive on the barrier at the same shared offset in CTA `cta` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t cta) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(bar), "r"(cta));
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(r) : "memory");
 }
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
                  : "memory");
-}
-__device__ __forceinline__ void bulk_g2s_mc(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint16_t mask) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;"
-        ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "h"(mask)
-        : "memory");
-}
-// multicast variant: the bytes land at the same smem offset, and complete_tx on the same barrier offset, in every CTA of `mask`
-__device__ __forceinline__ void bulk_g2s_mc(void* dst, const void* src, uint32_t bytes, uint64_t* bar, uint16_t mask) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;"
-        ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "h"(mask)
-        : "memory");
 }
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
@@ -124,34 +124,59 @@ __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarr
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+template <int CG>
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {  // one warp of EACH CTA of the group
+    if constexpr (CG == 2) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
 }
+template <int CG>
 __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+    if constexpr (CG == 2) {
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+    } else {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+    }
 }
 // Descriptors travel as their low words (start address | LBO); the high word (SBO | version | swizzle) is one constant.
+template <int CG>
 __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint32_t a_desc_lo, uint32_t b_desc_lo, uint32_t desc_hi,
                                           uint32_t idesc, uint32_t acc) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
-        "setp.ne.b32 p, %5, 0;\n\t"
-        "mov.b64 da, {%1, %3};\n\t"
-        "mov.b64 db, {%2, %3};\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, p;\n\t}"
-        ::"r"(d_tmem), "r"(a_desc_lo), "r"(b_desc_lo), "r"(desc_hi), "r"(idesc), "r"(acc)
-        : "memory");
+    if constexpr (CG == 2) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+            "setp.ne.b32 p, %5, 0;\n\t"
+            "mov.b64 da, {%1, %3};\n\t"
+            "mov.b64 db, {%2, %3};\n\t"
+            "tcgen05.mma.cta_group::2.kind::tf32 [%0], da, db, %4, p;\n\t}"
+            ::"r"(d_tmem), "r"(a_desc_lo), "r"(b_desc_lo), "r"(desc_hi), "r"(idesc), "r"(acc)
+            : "memory");
+    } else {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+            "setp.ne.b32 p, %5, 0;\n\t"
+            "mov.b64 da, {%1, %3};\n\t"
+            "mov.b64 db, {%2, %3};\n\t"
+            "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, p;\n\t}"
+            ::"r"(d_tmem), "r"(a_desc_lo), "r"(b_desc_lo), "r"(desc_hi), "r"(idesc), "r"(acc)
+            : "memory");
+    }
 }
+// tcgen05.commit: the barrier is arrived on when every MMA issued so far by this thread has retired.
+// Pair mode: the arrive is multicast to the same barrier offset in both CTAs of the pair.
+template <int CG>
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-// arrives on the barrier at the same smem offset in every CTA of `mask`
-__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                 ::"r"(bar), "h"(mask)
-                 : "memory");
+    if constexpr (CG == 2) {
+        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                     ::"r"(bar), "h"(static_cast<uint16_t>(3))
+                     : "memory");
+    } else {
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+    }
 }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
     uint32_t r[16];
@@ -178,6 +203,26 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+// Split issue / wait so the next chunk's TMEM read overlaps the processing of the current one.  The wait
+// names the registers as in/out operands: nothing that reads them can be scheduled above it.
+__device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[32]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]), "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+                 :
+                 : "memory");
 }
 __device__ __forceinline__ void sts128(uint32_t addr, float a, float b, float c, float d) {
     asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
@@ -245,8 +290,11 @@ __global__ void __launch_bounds__(256) k_pack_w(const __grid_constant__ TcParams
 
 // ------------------------------------------------------------------------------ main kernel
 // Work unit u = (group of CS consecutive m-tiles) x n-tile; cluster c takes u = c, c + n_clusters, ...;
-// CTA rank r of the cluster computes m-tile CS * group + r (possibly past the end: all-zero rows, no stores),
-// so the CTAs of a cluster walk the SAME (n-tile, k-block) sequence and can share every W k-block.
+// CTA rank r of the cluster computes m-tile CS * group + r (possibly past the end: all-zero rows, no stores).
+// CS = 2 is the CTA-pair mode (tcgen05 cta_group::2): one MMA of M = 256 spans both SMs, each CTA stages its
+// own 128 rows of A and HALF of the W rows of the n-tile, and the tensor cores read the other half from the
+// peer's shared memory -- W fill and W operand traffic per SM halve (shared-memory bandwidth is the bound of
+// the 3-term TF32 scheme).  Rank 0 issues every MMA; rank 1's warp 0 relays "my stage is filled".
 // The loaders, the W producer and the MMA warp all walk that sequence (tiles of this CTA in order, k-blocks
 // of a tile in order) with incremental cursors: no division in any per-k-block path.
 struct Ring {  // pipeline stage + phase parity of the next k-block
@@ -354,12 +402,11 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
     const hg_linear_args& A = P.a;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int S = P.stages;
-    const uint32_t b_tile_bytes = static_cast<uint32_t>(P.block_n) * 128u;
+    const uint32_t b_tile_bytes = static_cast<uint32_t>(P.block_n / CS) * 128u;  // W rows staged by THIS CTA
     const uint32_t stage_bytes = 2u * kATileBytes + 2u * b_tile_bytes;
 
     // tiles of this CTA: blockIdx.x, blockIdx.x + gridDim.x, ...
     const uint32_t rank = CS > 1 ? cluster_ctarank() : 0u;
-    constexpr uint16_t kAllMask = static_cast<uint16_t>((1u << CS) - 1u);
     const int64_t total_units = ceil_div<int64_t>(P.m_tiles, CS) * P.n_tiles;
     const int64_t n_clusters = gridDim.x / CS, cluster_id = blockIdx.x / CS;
     const int my_tiles = static_cast<int>((total_units - cluster_id + n_clusters - 1) / n_clusters);
@@ -372,8 +419,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
     const uint32_t full_b = bars + 8u * S;         // [S] bulk copy -> MMA (count = 1 + tx bytes)
     const uint32_t empty = bars + 16u * S;         // [S] MMA -> loaders / W producer (tcgen05.commit)
     const uint32_t acc_full = bars + 24u * S;      // [2] MMA -> epilogue
-    const uint32_t acc_empty = acc_full + 16u;     // [2] epilogue -> MMA (count = epilogue warps)
-    const uint32_t tmem_slot = acc_empty + 16u;
+    const uint32_t acc_empty = acc_full + 16u;     // [2] epilogue -> MMA (count = epilogue warps of the whole pair)
+    const uint32_t peer_full = acc_empty + 16u;    // [S] pair mode, rank 0 only: rank 1's stage is filled (count = 1)
+    const uint32_t tmem_slot = peer_full + 8u * S;
     // per-column epilogue affine  y = act(acc * sc[n] + sh[n])  (bias / scale / shift folded once per CTA)
     const uint32_t s_sc = (tmem_slot + 16u + 15u) & ~15u;
     const uint32_t s_sh = s_sc + 4u * static_cast<uint32_t>(P.n_tiles * P.block_n);
@@ -394,36 +442,39 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
         for (int s = 0; s < S; ++s) {
             mbar_init(reinterpret_cast<uint64_t*>(gen + (full_a - sbase)) + s, kLoaderWarps);
             mbar_init(reinterpret_cast<uint64_t*>(gen + (full_b - sbase)) + s, 1);
-            mbar_init(reinterpret_cast<uint64_t*>(gen + (empty - sbase)) + s, CS);  // one tcgen05.commit per CTA sharing the W stage
+            mbar_init(reinterpret_cast<uint64_t*>(gen + (empty - sbase)) + s, 1);
+            mbar_init(reinterpret_cast<uint64_t*>(gen + (peer_full - sbase)) + s, 1);
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(reinterpret_cast<uint64_t*>(gen + (acc_full - sbase)) + b, 1);
-            mbar_init(reinterpret_cast<uint64_t*>(gen + (acc_empty - sbase)) + b, kEpiWarps);
+            mbar_init(reinterpret_cast<uint64_t*>(gen + (acc_empty - sbase)) + b, kEpiWarps * CS);
         }
         fence_barrier_init();
     }
-    if (warp == 0) tmem_alloc(reinterpret_cast<uint32_t*>(gen + (tmem_slot - sbase)), static_cast<uint32_t>(P.tmem_cols));
+    if (warp == 0) tmem_alloc<CS>(tmem_slot, static_cast<uint32_t>(P.tmem_cols));
     tc_fence_before();
     __syncthreads();
     if (CS > 1) cluster_sync_all();  // peers' barriers are initialised before anything remote arrives on them
     tc_fence_after();
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(gen + (tmem_slot - sbase));
 
-    if (warp == 0) {
-        // ===================== MMA issuer =====================
+    if (warp == 0 && rank == 0) {
+        // ===================== MMA issuer (pair mode: for both CTAs) =====================
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(P.block_n >> 3) << 17) |
-                               (static_cast<uint32_t>(BM >> 4) << 24);
+                               (static_cast<uint32_t>((BM * CS) >> 4) << 24);
         const uint32_t a_lo_off = kATileBytes >> 4, b_hi_off = (2 * kATileBytes) >> 4;
         const uint32_t b_lo_off = b_hi_off + (b_tile_bytes >> 4);
         Ring r;
         for (int it = 0; it < my_tiles; ++it) {
             const uint32_t ab = static_cast<uint32_t>(it) & 1u;
-            mbar_wait(acc_empty + 8u * ab, ((static_cast<uint32_t>(it) >> 1) & 1u) ^ 1u);  // epilogue drained this buffer
+            if (CS > 1) mbar_wait_cluster(acc_empty + 8u * ab, ((static_cast<uint32_t>(it) >> 1) & 1u) ^ 1u);
+            else mbar_wait(acc_empty + 8u * ab, ((static_cast<uint32_t>(it) >> 1) & 1u) ^ 1u);  // epilogue(s) drained this buffer
             tc_fence_after();
             const uint32_t d_tmem = tmem_base + ab * static_cast<uint32_t>(P.block_n);
             for (int kb = 0; kb < P.n_kb; ++kb) {
                 mbar_wait(full_a + 8u * r.s, r.ph);
                 mbar_wait(full_b + 8u * r.s, r.ph);
+                if (CS > 1) mbar_wait_cluster(peer_full + 8u * r.s, r.ph);  // the peer's A rows and W half are in place
                 tc_fence_after();
                 const uint32_t a_hi = desc_lo(sbase + static_cast<uint32_t>(r.s) * stage_bytes);  // descriptor low words
                 if (lane == 0) {
@@ -431,36 +482,48 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
                     for (uint32_t ks = 0; ks < ((HG_TC_EXP & 8) ? 0 : BK / 8); ++ks) {  // UMMA_K = 8 tf32 = 32 bytes: start address += 2
                         const uint32_t a = a_hi + 2u * ks;
                         // small terms first, the main term last (one accumulator holds all three)
-                        umma_tf32(d_tmem, a, a + b_lo_off, kDescHi, idesc, ks != 0 ? 1u : static_cast<uint32_t>(kb != 0));
-                        umma_tf32(d_tmem, a + a_lo_off, a + b_hi_off, kDescHi, idesc, 1u);
-                        umma_tf32(d_tmem, a, a + b_hi_off, kDescHi, idesc, 1u);
+                        umma_tf32<CS>(d_tmem, a, a + b_lo_off, kDescHi, idesc, ks != 0 ? 1u : static_cast<uint32_t>(kb != 0));
+                        umma_tf32<CS>(d_tmem, a + a_lo_off, a + b_hi_off, kDescHi, idesc, 1u);
+                        umma_tf32<CS>(d_tmem, a, a + b_hi_off, kDescHi, idesc, 1u);
                     }
-                    if (CS > 1) umma_commit_mc(empty + 8u * r.s, kAllMask);   // the W stage is shared: tell every CTA
-                    else umma_commit(empty + 8u * r.s);                       // stage reusable once these MMAs retire
-                    if (kb == P.n_kb - 1) umma_commit(acc_full + 8u * ab);    // accumulator complete
+                    umma_commit<CS>(empty + 8u * r.s);                           // stage reusable once these MMAs retire
+                    if (kb == P.n_kb - 1) umma_commit<CS>(acc_full + 8u * ab);  // accumulator complete
                 }
                 __syncwarp();
                 r.next(S);
             }
         }
+    } else if (warp == 0) {
+        // ===================== pair mode, rank 1: relay "stage filled" to the issuer =====================
+        Ring r;
+        for (int g = 0; g < G; ++g) {
+            mbar_wait(full_a + 8u * r.s, r.ph);
+            mbar_wait(full_b + 8u * r.s, r.ph);
+            if (lane == 0) mbar_arrive_remote(peer_full + 8u * r.s, 0u);
+            __syncwarp();
+            r.next(S);
+        }
     } else if (warp == 1) {
         // ===================== W producer =====================
         if (lane == 0) {
             Ring r;
-            const uint32_t w_bytes = 2u * b_tile_bytes;  // W_hi | W_lo image of one (n-tile, k-block)
+            // packed image of one (n-tile, k-block): [W_hi: block_n rows x 128 B][W_lo: same]; this CTA stages
+            // rows [rank * block_n / CS, (rank + 1) * block_n / CS) of both
+            const uint32_t img_bytes = 2u * CS * b_tile_bytes, w_bytes = 2u * b_tile_bytes;
             for (int it = 0; it < my_tiles; ++it) {
                 const TilePos<CS> tp(P, it, rank);
-                const uint8_t* src = reinterpret_cast<const uint8_t*>(P.wp) + static_cast<size_t>(tp.n_tile) * P.n_kb * w_bytes;
-                for (int kb = 0; kb < P.n_kb; ++kb, src += w_bytes) {
-                    mbar_wait(empty + 8u * r.s, r.ph ^ 1u);  // every CTA of the cluster has retired its MMAs on this stage
+                const uint8_t* src = reinterpret_cast<const uint8_t*>(P.wp) + static_cast<size_t>(tp.n_tile) * P.n_kb * img_bytes +
+                                     rank * b_tile_bytes;
+                for (int kb = 0; kb < P.n_kb; ++kb, src += img_bytes) {
+                            mbar_wait(empty + 8u * r.s, r.ph ^ 1u);  // the MMAs that read this stage have retired
                     const uint32_t dst = sbase + static_cast<uint32_t>(r.s) * stage_bytes + 2u * kATileBytes;
 #if HG_TC_EXP & 4
                     mbar_arrive(full_b + 8u * r.s); r.next(S); continue;
 #endif
                     mbar_arrive_expect_tx(full_b + 8u * r.s, w_bytes);
-                    if (CS > 1) {  // this CTA fetches 1/CS of the image and multicasts it to the whole cluster
-                        const uint32_t part = w_bytes / CS;
-                        bulk_g2s_mc(dst + rank * part, src + rank * part, part, full_b + 8u * r.s, kAllMask);
+                    if (CS > 1) {
+                        bulk_g2s(dst, src, b_tile_bytes, full_b + 8u * r.s);
+                        bulk_g2s(dst + b_tile_bytes, src + CS * b_tile_bytes, b_tile_bytes, full_b + 8u * r.s);
                     } else {
                         bulk_g2s(dst, src, w_bytes, full_b + 8u * r.s);
                     }
@@ -516,10 +579,11 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
         const int act = A.act;
         const uint32_t xbuf = s_xp + static_cast<uint32_t>(warp - (2 + kLoaderWarps)) * 4096u;
         const uint32_t xrow = xbuf + static_cast<uint32_t>(lane) * 128u;
+        const bool has_affine = A.bias || A.scale || A.shift;  // GAT projections have none: skip the pass
         auto affine_act = [&](float (&acc)[32], int n, int cw) {
 #pragma unroll
             for (int j4 = 0; j4 < 8; ++j4) {
-                if (4 * j4 < cw) {
+                if (has_affine && 4 * j4 < cw) {
                     const float4 sc = lds128(s_sc + 4u * (n + 4 * j4)), sh = lds128(s_sh + 4u * (n + 4 * j4));  // broadcast
                     acc[4 * j4 + 0] = fmaf(acc[4 * j4 + 0], sc.x, sh.x);
                     acc[4 * j4 + 1] = fmaf(acc[4 * j4 + 1], sc.y, sh.y);
@@ -593,7 +657,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
             }
             tc_fence_before();  // all tcgen05.ld of this buffer done (tmem_ld waits) -> hand it back
             __syncwarp();
-            if (lane == 0) mbar_arrive(acc_empty + 8u * ab);
+            if (lane == 0) {
+                if (CS > 1 && rank != 0) mbar_arrive_remote(acc_empty + 8u * ab, 0u);
+                else mbar_arrive(acc_empty + 8u * ab);
+            }
         }
     }
 
@@ -602,12 +669,12 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
     if (CS > 1) cluster_sync_all();  // no CTA leaves while a peer may still multicast into its smem / barriers
     if (warp == 0) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, static_cast<uint32_t>(P.tmem_cols));
+        tmem_dealloc<CS>(tmem_base, static_cast<uint32_t>(P.tmem_cols));
     }
 }
 
-#ifndef HG_TC_CS
-#define HG_TC_CS 2  // CTAs per cluster sharing each W k-block on large problems
+#ifndef HG_TC_PAIR
+#define HG_TC_PAIR 1
 #endif
 constexpr size_t kSmemBudget = 200 * 1024;
 
@@ -627,7 +694,11 @@ bool plan(const hg_linear_args& a, TcParams& P) {
     P.n_kb = kb;
     P.vec = vec;
     P.m_tiles = ceil_div<int64_t>(a.M, BM);
-    const size_t stage_bytes = 2 * kATileBytes + 2 * static_cast<size_t>(P.block_n) * 128;
+    // CTA-pair mode (cta_group::2) when every SM gets at least two m-tiles: halves the W traffic per SM
+    const int sms = sm_count() > 0 ? sm_count() : 148;
+    // and the k-loop is long enough to amortise the cross-CTA hand-offs (measured: K = 64 is faster unpaired)
+    P.cs = (HG_TC_PAIR && P.m_tiles >= 2 * static_cast<int64_t>(sms) && P.n_kb >= 4) ? 2 : 1;
+    const size_t stage_bytes = 2 * kATileBytes + 2 * static_cast<size_t>(P.block_n / P.cs) * 128;
     const size_t affine_bytes = 2 * static_cast<size_t>(P.n_tiles) * P.block_n * sizeof(float);
     if (affine_bytes > 32 * 1024) return false;  // N <= 4096
     int stages = static_cast<int>((kSmemBudget - affine_bytes - kEpiWarps * 4096) / stage_bytes);
@@ -684,13 +755,10 @@ int linear_tc_launch(const hg_linear_args& a, void* ws, size_t ws_bytes, cudaStr
         const int rc = pack_launch(P, static_cast<float*>(ws), stream);
         if (rc != HG_OK) return rc;
     }
-    const size_t stage_bytes = 2 * kATileBytes + 2 * static_cast<size_t>(P.block_n) * 128;
-    const size_t smem = 1024 + P.stages * stage_bytes + (3 * P.stages + 4) * sizeof(uint64_t) + 48 +
+    const size_t stage_bytes = 2 * kATileBytes + 2 * static_cast<size_t>(P.block_n / P.cs) * 128;
+    const size_t smem = 1024 + P.stages * stage_bytes + (4 * P.stages + 4) * sizeof(uint64_t) + 48 +
                         2 * static_cast<size_t>(P.n_tiles) * P.block_n * sizeof(float) + kEpiWarps * 4096;
     const int sms = sm_count() > 0 ? sm_count() : 148;
-    // Big problems run as clusters of 2 CTAs that share every W k-block (each fetches half, multicast to both):
-    // W re-streaming from L2 is what bounds the 306-wide projection.  Small ones keep independent CTAs.
-    const bool pair = P.m_tiles >= 2 * static_cast<int64_t>(sms) && (2 * P.block_n * 128 / HG_TC_CS) % 16 == 0;
     auto go = [&](auto kernel, int cs) -> int {
         HG_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
         const int64_t units = ceil_div<int64_t>(P.m_tiles, cs) * P.n_tiles;
@@ -706,16 +774,15 @@ int linear_tc_launch(const hg_linear_args& a, void* ws, size_t ws_bytes, cudaStr
         attr[0].val.clusterDim.x = cs;
         attr[0].val.clusterDim.y = 1;
         attr[0].val.clusterDim.z = 1;
-        if (cs > 8) HG_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         cfg.attrs = attr;
         cfg.numAttrs = 1;
         HG_CUDA_TRY(cudaLaunchKernelEx(&cfg, kernel, P));
         return check_launch();
     };
-    if (pair) {
-        if (P.vec == 4) return go(k_linear_tc<4, HG_TC_CS>, HG_TC_CS);
-        if (P.vec == 2) return go(k_linear_tc<2, HG_TC_CS>, HG_TC_CS);
-        return go(k_linear_tc<1, HG_TC_CS>, HG_TC_CS);
+    if (P.cs == 2) {
+        if (P.vec == 4) return go(k_linear_tc<4, 2>, 2);
+        if (P.vec == 2) return go(k_linear_tc<2, 2>, 2);
+        return go(k_linear_tc<1, 2>, 2);
     }
     if (P.vec == 4) return go(k_linear_tc<4, 1>, 1);
     if (P.vec == 2) return go(k_linear_tc<2, 1>, 1);
