@@ -631,21 +631,39 @@ __global__ void __launch_bounds__(kThreads, 1) k_linear_tc(const __grid_constant
                         if (4 * j < cw)
                             sts128(xrow + (static_cast<uint32_t>(j ^ (lane & 7)) << 4), acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
                     __syncwarp();
+                    // read back transposed: all LDS first, then the stores back to back
                     if (cw == 32) {  // lane -> (row 4 i + lane / 8, 16-byte chunk lane % 8)
-                        const int ch = lane & 7, col = n + 4 * ch;
+                        const int ch = lane & 7, r0 = lane >> 3;
+                        float4 v[8];
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
-                            const int row = 4 * i + (lane >> 3);
-                            const float4 v = lds128(xbuf + static_cast<uint32_t>(row) * 128u + (static_cast<uint32_t>(ch ^ (row & 7)) << 4));
-                            if (mq + row < A.M && col < A.N) *reinterpret_cast<float4*>(A.y + (mq + row) * A.ldy + col) = v;
+                            const int row = 4 * i + r0;
+                            v[i] = lds128(xbuf + static_cast<uint32_t>(row) * 128u + (static_cast<uint32_t>(ch ^ (row & 7)) << 4));
+                        }
+                        float* dst = A.y + (mq + r0) * A.ldy + n + 4 * ch;
+                        const int64_t step = 4 * A.ldy;
+                        if (mq + 32 <= A.M && n + 32 <= A.N) {  // interior chunk (warp-uniform)
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) *reinterpret_cast<float4*>(dst + i * step) = v[i];
+                        } else if (n + 4 * ch < A.N) {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i)
+                                if (mq + r0 + 4 * i < A.M) *reinterpret_cast<float4*>(dst + i * step) = v[i];
                         }
                     } else {  // 16 columns: lane -> (row 8 i + lane / 4, chunk lane % 4)
-                        const int ch = lane & 3, col = n + 4 * ch;
+                        const int ch = lane & 3, r0 = lane >> 2;
+                        float4 v[4];
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
-                            const int row = 8 * i + (lane >> 2);
-                            const float4 v = lds128(xbuf + static_cast<uint32_t>(row) * 128u + (static_cast<uint32_t>(ch ^ (row & 7)) << 4));
-                            if (mq + row < A.M && col < A.N) *reinterpret_cast<float4*>(A.y + (mq + row) * A.ldy + col) = v;
+                            const int row = 8 * i + r0;
+                            v[i] = lds128(xbuf + static_cast<uint32_t>(row) * 128u + (static_cast<uint32_t>(ch ^ (row & 7)) << 4));
+                        }
+                        float* dst = A.y + (mq + r0) * A.ldy + n + 4 * ch;
+                        const int64_t step = 8 * A.ldy;
+                        if (n + 4 * ch < A.N) {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i)
+                                if (mq + r0 + 8 * i < A.M) *reinterpret_cast<float4*>(dst + i * step) = v[i];
                         }
                     }
                 } else if (mq + lane < A.M) {
