@@ -111,7 +111,10 @@ class _Base(nn.Module):
         raise NotImplementedError("fp64 mode (base_training_job.py:50-51) is not supported by the sm_100a kernels")
 
     def forward(self, data):
-        if self.training:
-            return self._forward(data)
-        with torch.no_grad():
-            return self._forward(data)
+        try:
+            if self.training:
+                return self._forward(data)
+            with torch.no_grad():
+                return self._forward(data)
+        finally:
+            self._plans.join()  # a side-stream plan that no kernel consumed

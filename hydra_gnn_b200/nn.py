@@ -95,11 +95,18 @@ class PlanCache:
 
     def __init__(self):
         self.enabled = True
+        self.overlap = True  # build on a side stream; joined by the first kernel that reads a CSR
         self._sig = None
         self._plan: Optional[GraphPlan] = None
 
     def clear(self):
         self._sig, self._plan = None, None
+
+    def join(self):
+        """Joins a side-stream plan nobody consumed (keeps stream capture well formed)."""
+        j = self.__dict__.pop("_pending", None)
+        if j is not None:
+            j.wait()
 
     def get(self, requests: Sequence[PlanRequest]) -> GraphPlan:
         sig = tuple(r.signature() for r in requests)
@@ -107,7 +114,8 @@ class PlanCache:
             return self._plan
         plan = GraphPlan()
         specs = [CSRSpec(r.edge_index, r.n_src, r.n_dst, r.self_loops, r.want_perm, r.want_norm) for r in requests]
-        csrs, plan.status = ops.build_csr(specs)
+        csrs, plan.status = ops.build_csr(specs, overlap=self.overlap)
+        self._pending = csrs[0].join if csrs else None
         for r, c in zip(requests, csrs):
             plan.csr[(r.key, r.self_loops)] = c
         self._sig, self._plan = (sig, plan) if self.enabled else (None, None)

@@ -7,7 +7,7 @@ from __future__ import annotations
 
 import ctypes as C
 from dataclasses import dataclass
-from typing import List, Optional, Sequence
+from typing import Dict, List, Optional, Sequence
 
 import torch
 from torch import Tensor
@@ -83,6 +83,34 @@ def _workspace(device, nbytes: int) -> Tensor:
 
 
 # ------------------------------------------------------------------------------ K1 plan
+class _Join:
+    """A plan built on the side stream: the first consumer of any of its CSRs makes the consuming
+    stream wait for it (so K1 overlaps whatever was launched in between -- the first projection)."""
+    __slots__ = ("side", "tensors", "done")
+
+    def __init__(self, side, tensors):
+        self.side, self.tensors, self.done = side, tensors, False
+
+    def wait(self):
+        if self.done:
+            return
+        cur = torch.cuda.current_stream(self.tensors[0].device)
+        cur.wait_stream(self.side)
+        for t in self.tensors:  # allocated while `side` was current, consumed on `cur`
+            t.record_stream(cur)
+        self.done = True
+
+
+_side_streams: Dict[int, "torch.cuda.Stream"] = {}
+
+
+def _side_stream(device) -> "torch.cuda.Stream":
+    s = _side_streams.get(device.index)
+    if s is None:
+        s = _side_streams[device.index] = torch.cuda.Stream(device)
+    return s
+
+
 @dataclass
 class CSR:
     """Destination-sorted adjacency of one relation (device int32)."""
@@ -94,6 +122,13 @@ class CSR:
     n_dst: int
     cap: int  # allocated entries; the live count is rowptr[-1] (kept on the device)
     self_loops: bool
+    join: Optional[_Join] = None
+
+    def ready(self) -> "CSR":
+        """Call before handing the arrays to a kernel on the current stream."""
+        if self.join is not None:
+            self.join.wait()
+        return self
 
 
 @dataclass
@@ -107,18 +142,34 @@ class CSRSpec:
     transpose: bool = False  # build the CSR of the reversed relation (rows = sources)
 
 
-def build_csr(specs: Sequence[CSRSpec]):
+def build_csr(specs: Sequence[CSRSpec], overlap: bool = False):
     """All relations of a batch in one ``hg_plan_build`` call (six launches in total).
+
+    ``overlap=True`` launches the plan on a side stream forked from the current one; the current
+    stream joins it at the first ``CSR.ready()`` (every op below calls it), so independent work
+    launched in between runs concurrently with K1.
 
     Returns (list of CSR, status) -- ``status`` is a device int32[1] counting edges whose
     endpoints were outside [0, n) (skipped, never dereferenced); read it with
     ``int(status)`` only when a sync is acceptable.
     """
+    if len(specs) == 0:
+        return [], None
+    device = specs[0].edge_index.device
+    if not specs[0].edge_index.is_cuda:
+        raise RuntimeError("edge_index must be a CUDA tensor; hydra_gnn_b200 has no CPU path")
+    if overlap:
+        cur, side = torch.cuda.current_stream(device), _side_stream(device)
+        side.wait_stream(cur)  # the edge lists are ready on the current stream
+        with torch.cuda.stream(side):
+            out, status = build_csr(specs)
+        tensors = [t for c in out for t in (c.rowptr, c.col, c.perm, c.inv_sqrt_deg) if t is not None] + [status]
+        join = _Join(side, tensors)
+        for c in out:
+            c.join = join
+        return out, status
     h = lib()
     out: List[CSR] = []
-    if len(specs) == 0:
-        return out, None
-    device = specs[0].edge_index.device
     status = torch.empty(1, dtype=torch.int32, device=device)
     for lo in range(0, len(specs), _lib.HG_MAX_PLAN_RELATIONS):
         chunk = specs[lo: lo + _lib.HG_MAX_PLAN_RELATIONS]
@@ -171,6 +222,7 @@ def seg_reduce(x: Tensor, csr: CSR, op: str = "sum", *, src_scale: Tensor = None
     h = lib()
     x = _rows(x, "x")
     F = x.size(1)
+    csr.ready()
     n_out = csr.n_dst if row_map is None else row_map.numel()
     if out is None:
         out = torch.empty(n_out, F, dtype=torch.float32, device=x.device)
@@ -236,6 +288,7 @@ def gat_fused(rels: Sequence[GatRelation], n_dst: int, H: int, Cc: int, concat: 
                 raise ValueError(f"{nm}: expected 2-D with unit feature stride")
         if r.xs.size(1) != (Cc if src_shared else H * Cc) or r.a_src.size(1) != H or r.a_dst.size(1) != H:
             raise ValueError("GAT operand widths do not match H, C")
+        r.csr.ready()
         if r.csr.n_dst != n_dst:
             raise ValueError("relation CSR has a different destination count")
         g = a.rel[k]
@@ -326,6 +379,7 @@ def linear(segments: Sequence, N: int, *, bias: Tensor = None, scale: Tensor = N
 def edge_logits(edge_attr: Tensor, csr: CSR, v: Tensor, H: int, fill: Tensor = None) -> Tensor:
     """``a_edge[p, h] = <edge_attr[perm[p]], v[h]>`` in CSR order (added loops: ``<fill, v[h]>`` or 0)."""
     h = lib()
+    csr.ready()
     if csr.perm is None:
         raise ValueError("edge_logits needs a CSR built with want_perm=True")
     edge_attr = _rows(edge_attr, "edge_attr")
