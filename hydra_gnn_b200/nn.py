@@ -327,9 +327,10 @@ def run_gat_layer(convs: Dict[EdgeType, GATConv], rels: Sequence[EdgeType], x: D
     if only_dst is not None:
         rels = [et for et in rels if et[2] in only_dst]
     pack = _gat_pack(owner, convs, rels, x, _gat_modes(convs, rels, x, group))
+    device = next(iter(x.values())).device
     Y = {T: ops.linear([(x[T], W)], W.size(0), pack_cache=pack.wcache.setdefault(T, {})) for T, W in pack.W.items()}
-    out: Dict[str, Tensor] = {}
-    for T in dict.fromkeys(et[2] for et in rels):
+
+    def branch(T):  # everything that produces destination type T: independent of the other types
         first, late = [], []  # project-first relations / (aggregated rows, post weight) of aggregate-first ones
         H = C = concat = slope = None
         for et in rels:
@@ -362,11 +363,16 @@ def run_gat_layer(convs: Dict[EdgeType, GATConv], rels: Sequence[EdgeType], x: D
             partial = ops.linear(late, width, bias=pack.post_bias[T], act=None if first else act,
                                  pack_cache=pack.wcache.setdefault("post_" + T, {}))
         if first:
-            out[T] = ops.gat_fused(first, x[T].size(0), H, C, concat, group=group, act=act, neg_slope=slope,
-                                   addend=partial)
-        else:
-            out[T] = partial
-    return out
+            return ops.gat_fused(first, x[T].size(0), H, C, concat, group=group, act=act, neg_slope=slope,
+                                 addend=partial)
+        return partial
+
+    dsts = list(dict.fromkeys(et[2] for et in rels))
+    # the branch with the most source rows is the long one: it stays on the current stream
+    dsts.sort(key=lambda T: -sum(x[et[0]].size(0) for et in rels if et[2] == T))
+    res = ops.parallel([lambda T=T: branch(T) for T in dsts], device)
+    got = dict(zip(dsts, res))
+    return {T: got[T] for T in dict.fromkeys(et[2] for et in rels)}
 
 
 # =============================================================================== SAGE / GCN / GIN

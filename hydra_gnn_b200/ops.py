@@ -92,23 +92,61 @@ class _Join:
         self.side, self.tensors, self.done = side, tensors, False
 
     def wait(self):
-        if self.done:
-            return
         cur = torch.cuda.current_stream(self.tensors[0].device)
+        if self.done is False:
+            self.done = set()
+        if cur.cuda_stream in self.done:  # every consuming stream joins once
+            return
         cur.wait_stream(self.side)
         for t in self.tensors:  # allocated while `side` was current, consumed on `cur`
             t.record_stream(cur)
-        self.done = True
+        self.done.add(cur.cuda_stream)
 
 
-_side_streams: Dict[int, "torch.cuda.Stream"] = {}
+_side_streams: Dict[tuple, "torch.cuda.Stream"] = {}
+PARALLEL_BRANCHES = True  # independent per-destination-type chains of a hetero layer on concurrent streams
 
 
-def _side_stream(device) -> "torch.cuda.Stream":
-    s = _side_streams.get(device.index)
+def _side_stream(device, k: int = 0) -> "torch.cuda.Stream":
+    """Side stream k of the device (0: the plan; 1..: branches).  High priority: their kernels are the
+    short ones that fill the gaps of the long kernel on the main stream."""
+    s = _side_streams.get((device.index, k))
     if s is None:
-        s = _side_streams[device.index] = torch.cuda.Stream(device)
+        s = _side_streams[(device.index, k)] = torch.cuda.Stream(device, priority=-1)
     return s
+
+
+def _tensors_of(obj):
+    if isinstance(obj, Tensor):
+        return [obj]
+    if isinstance(obj, (list, tuple)):
+        return [t for o in obj for t in _tensors_of(o)]
+    if isinstance(obj, dict):
+        return [t for o in obj.values() for t in _tensors_of(o)]
+    return []
+
+
+def parallel(fns, device):
+    """Runs the zero-argument callables as concurrent branches: the first on the current stream, the
+    others on side streams forked from it and joined back (also valid under CUDA-graph capture).
+    Each branch may only read tensors that exist before the call and returns the tensors it produced."""
+    if len(fns) <= 1 or not PARALLEL_BRANCHES:
+        return [f() for f in fns]
+    cur = torch.cuda.current_stream(device)
+    results = [None] * len(fns)
+    sides = []
+    for k in range(1, len(fns)):
+        s = _side_stream(device, k)
+        s.wait_stream(cur)
+        with torch.cuda.stream(s):
+            results[k] = fns[k]()
+        sides.append(s)
+    results[0] = fns[0]()
+    for k, s in enumerate(sides, 1):
+        cur.wait_stream(s)
+        for t in _tensors_of(results[k]):  # allocated on the side stream, consumed on the current one
+            t.record_stream(cur)
+    return results
 
 
 @dataclass
