@@ -32,6 +32,9 @@ namespace {
 #define HG_GAT_SMEM_KB 24
 #endif
 constexpr size_t kStageBudget = HG_GAT_SMEM_KB * 1024;  // shared memory per CTA for staging (the rest of the SM's 256 KB is L1)
+#ifndef HG_GAT_MIN_TILE
+#define HG_GAT_MIN_TILE 32  // smaller tiles on short grids measured slower (8, 16)
+#endif
 constexpr int kThreads = 128;
 constexpr int kWarps = kThreads / kWarp;
 constexpr int kMaxHeads = 8;
@@ -434,7 +437,10 @@ k_gat_fused(const __grid_constant__ GatParams P) {
 template <int VEC, int TPR, int KC, int MODE, int HT>
 int launch(GatParams& P, cudaStream_t stream) {
     const hg_gat_args& A = P.a;
+    // short grids (the rooms side of a scene-graph batch) take smaller tiles: more CTAs in flight per SM
+    const int sms0 = sm_count() > 0 ? sm_count() : 148;
     P.tile_rows = kMaxTile;
+    while (P.tile_rows > HG_GAT_MIN_TILE && ceil_div<int64_t>(A.n_dst, P.tile_rows) < static_cast<int64_t>(sms0) * 6) P.tile_rows >>= 1;
     P.hs = A.H <= 4 ? 4 : 8;
     P.n_bias = MODE == 2 ? A.H * P.f_count : P.f_count;
     // staging capacity: what the shared-memory budget holds, 128..2048 edges per relation per tile
