@@ -80,6 +80,8 @@ SYMBOLS = {
     "hg_edge_logits": (C.c_int, [vp, i64, i32, vp, vp, i64, vp, vp, i32, vp, vp]),
     "hg_relative_pos": (C.c_int, [vp, vp, vp, vp, i64, vp, vp]),
     "hg_gather_rows": (C.c_int, [vp, i64, vp, i64, i32, i32, vp, i64, vp]),
+    "hg_collate_offsets": (C.c_int, [vp, i64, vp, vp, vp, i32, vp]),
+    "hg_batch_vector": (C.c_int, [vp, i64, vp, i32, vp]),
 }
 
 _lock = threading.Lock()

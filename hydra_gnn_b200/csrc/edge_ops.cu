@@ -58,6 +58,35 @@ unsigned grid_for(int64_t n) {
     return static_cast<unsigned>(g < cap ? g : cap);
 }
 
+// graph of element e: largest g with ptr[g] <= e (ptr ascending, ptr[0] = 0, empty graphs allowed)
+__device__ __forceinline__ int32_t graph_of(const int64_t* __restrict__ ptr, int32_t n_graphs, int64_t e) {
+    int32_t lo = 0, hi = n_graphs;  // invariant: ptr[lo] <= e < ptr[hi]
+    while (hi - lo > 1) {
+        const int32_t mid = (lo + hi) >> 1;
+        if (__ldg(ptr + mid) <= e) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(kThreads) k_collate_offsets(int64_t* __restrict__ index, int64_t E,
+                                                              const int64_t* __restrict__ edge_ptr,
+                                                              const int64_t* __restrict__ src_ptr,
+                                                              const int64_t* __restrict__ dst_ptr, int32_t n_graphs) {
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; e < E; e += stride) {
+        const int32_t g = graph_of(edge_ptr, n_graphs, e);
+        index[e] += __ldg(src_ptr + g);
+        index[E + e] += __ldg(dst_ptr + g);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_batch_vector(int64_t* __restrict__ batch, int64_t N,
+                                                           const int64_t* __restrict__ ptr, int32_t n_graphs) {
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t n = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; n < N; n += stride)
+        batch[n] = graph_of(ptr, n_graphs, n);
+}
+
 }  // namespace
 }  // namespace hg
 
@@ -92,5 +121,25 @@ extern "C" int hg_gather_rows(const float* x, int64_t ldx, const int32_t* idx, i
     if (!x || !idx || !out) return HG_EINVAL;
     k_gather_rows<<<grid_for(n_out * F), kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(x, ldx, idx, n_out, F, act,
                                                                                             out, ldout);
+    return check_launch();
+}
+
+extern "C" int hg_collate_offsets(int64_t* index, int64_t n_edges, const int64_t* edge_ptr, const int64_t* src_ptr,
+                                  const int64_t* dst_ptr, int32_t n_graphs, void* stream_) {
+    using namespace hg;
+    if (n_edges < 0 || n_graphs < 0) return HG_EINVAL;
+    if (n_edges == 0) return HG_OK;
+    if (!index || !edge_ptr || !src_ptr || !dst_ptr || n_graphs < 1) return HG_EINVAL;
+    k_collate_offsets<<<grid_for(n_edges), kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(index, n_edges, edge_ptr,
+                                                                                              src_ptr, dst_ptr, n_graphs);
+    return check_launch();
+}
+
+extern "C" int hg_batch_vector(int64_t* batch, int64_t n_nodes, const int64_t* ptr, int32_t n_graphs, void* stream_) {
+    using namespace hg;
+    if (n_nodes < 0 || n_graphs < 0) return HG_EINVAL;
+    if (n_nodes == 0) return HG_OK;
+    if (!batch || !ptr || n_graphs < 1) return HG_EINVAL;
+    k_batch_vector<<<grid_for(n_nodes), kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(batch, n_nodes, ptr, n_graphs);
     return check_launch();
 }

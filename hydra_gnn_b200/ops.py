@@ -458,3 +458,34 @@ def gather_rows(x: Tensor, idx: Tensor, act: str = None) -> Tensor:
                                    stream_ptr()))
     _lib.launch_count += 1
     return out
+
+
+# ------------------------------------------------------------------------------ collate (integer, bit-exact)
+def collate_offsets_(index: Tensor, edge_ptr: Tensor, src_ptr: Tensor, dst_ptr: Tensor) -> Tensor:
+    """In place: ``index[0, e] += src_ptr[g(e)]``, ``index[1, e] += dst_ptr[g(e)]`` where ``g(e)`` is the
+    graph whose column range ``edge_ptr[g]:edge_ptr[g+1]`` holds ``e`` (all device int64)."""
+    h = lib()
+    if index.dtype != torch.int64 or index.dim() != 2 or index.size(0) != 2 or not index.is_contiguous():
+        raise TypeError("index must be a contiguous int64 [2, E] tensor")
+    for t in (edge_ptr, src_ptr, dst_ptr):
+        if t.dtype != torch.int64 or not t.is_cuda or t.numel() != edge_ptr.numel():
+            raise TypeError("ptr arrays must be CUDA int64 of the same length (n_graphs + 1)")
+    if not index.is_cuda:
+        raise RuntimeError("index must be a CUDA tensor; hydra_gnn_b200 has no CPU path")
+    _call("hg_collate_offsets", dict(E=index.size(1)),
+          lambda: h.hg_collate_offsets(ptr(index), index.size(1), ptr(edge_ptr), ptr(src_ptr), ptr(dst_ptr),
+                                       edge_ptr.numel() - 1, stream_ptr()))
+    _lib.launch_count += 1
+    return index
+
+
+def batch_vector(ptr_: Tensor, n_nodes: int) -> Tensor:
+    """``batch[n] = g`` for ``ptr[g] <= n < ptr[g+1]`` (device int64), PyG's ``batch`` vector."""
+    h = lib()
+    if ptr_.dtype != torch.int64 or not ptr_.is_cuda:
+        raise TypeError("ptr must be a CUDA int64 tensor")
+    out = torch.empty(n_nodes, dtype=torch.int64, device=ptr_.device)
+    _call("hg_batch_vector", dict(N=n_nodes),
+          lambda: h.hg_batch_vector(ptr(out), n_nodes, ptr(ptr_), ptr_.numel() - 1, stream_ptr()))
+    _lib.launch_count += 1
+    return out

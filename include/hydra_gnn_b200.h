@@ -246,6 +246,17 @@ HG_API int hg_relative_pos(const float* pos_src, const float* pos_dst, const int
 HG_API int hg_gather_rows(const float* x, int64_t ldx, const int32_t* idx, int64_t n_out, int32_t F, int32_t act,
                           float* out, int64_t ldout, void* stream);
 
+/* Collate (integer, bit-exact): the index half of PyG `Batch.from_data_list` (torch_geometric is what
+ * base_training_job.py:164-178's DataLoader calls; restated in hydra_gnn_b200/data.py).  `index` is the
+ * plain concatenation [2, E] of the per-graph edge lists (graph-local node ids); entries of graph g
+ * (columns edge_ptr[g] .. edge_ptr[g+1]) get src_ptr[g] added to row 0 and dst_ptr[g] to row 1, in place.
+ * All pointers are device int64; `*_ptr` have n_graphs + 1 entries (exclusive prefix sums of the counts). */
+HG_API int hg_collate_offsets(int64_t* index, int64_t n_edges, const int64_t* edge_ptr, const int64_t* src_ptr,
+                              const int64_t* dst_ptr, int32_t n_graphs, void* stream);
+
+/* batch[n] = g for ptr[g] <= n < ptr[g+1]: the `batch` vector of a collated node type (device int64). */
+HG_API int hg_batch_vector(int64_t* batch, int64_t n_nodes, const int64_t* ptr, int32_t n_graphs, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 import torch
 
-from hydra_gnn_b200 import ops
+from hydra_gnn_b200 import ops, synth
 from hydra_gnn_b200.ops import CSRSpec
 from oracle.pyg import utils as ou
 from util import assert_close
@@ -237,3 +237,55 @@ def test_gat_fused_hub_rows_take_the_streaming_path():
         got = ops.gat_fused([ops.GatRelation(xs.cuda(), a_s.cuda(), a_d.cuda(), csr)], n_dst, H, C, concat)
         want, _ = gat_reference(xs, a_s, a_d, ei, n_dst, H, C, concat)
         assert_close(got, want, f"hub concat={concat}", check_argmax=False)
+
+
+# ------------------------------------------------------------------------------ GPU collate (bit-exact)
+def _graph_list(n, hetero=True):
+    from hydra_gnn_b200 import convert
+    out = []
+    for i in range(n):
+        g = synth.synth_mp3d_batch([i], relative_pos=True)
+        out.append(g if hetero else convert.dsg_to_homogeneous(g))
+    return out
+
+
+@pytest.mark.parametrize("hetero", [True, False])
+def test_gpu_collate_is_bit_identical_to_cpu_collate(hetero):
+    from hydra_gnn_b200.data import Batch
+    graphs = _graph_list(37, hetero)
+    want = Batch.from_data_list(graphs)
+    got = Batch.from_data_list(graphs, device="cuda")
+    torch.cuda.synchronize()
+    stores_w = list(want._stores()) if hetero else [want]
+    stores_g = list(got._stores()) if hetero else [got]
+    assert len(stores_w) == len(stores_g)
+    n = 0
+    for sw, sg in zip(stores_w, stores_g):
+        assert set(sw.keys()) == set(sg.keys())
+        for k, v in sw.items():
+            if torch.is_tensor(v):
+                assert sg[k].is_cuda and sg[k].dtype == v.dtype and torch.equal(sg[k].cpu(), v), k
+                n += 1
+            else:
+                assert sg[k] == v, k
+    assert n >= 8
+
+
+def test_collate_offsets_with_empty_graphs():
+    # graphs 1 and 3 have no edges; graph 2 has no nodes of the source type
+    edge_counts, src_counts, dst_counts = [3, 0, 2, 0, 4], [2, 5, 0, 1, 3], [4, 1, 2, 2, 1]
+    def prefix(c):
+        p = torch.zeros(len(c) + 1, dtype=torch.long)
+        p[1:] = torch.tensor(c).cumsum(0)
+        return p
+    ep, sp, dp = prefix(edge_counts), prefix(src_counts), prefix(dst_counts)
+    g = torch.Generator().manual_seed(3)
+    idx = torch.randint(0, 5, (2, int(ep[-1])), generator=g)
+    want = idx.clone()
+    for k in range(len(edge_counts)):
+        want[0, ep[k]:ep[k + 1]] += sp[k]
+        want[1, ep[k]:ep[k + 1]] += dp[k]
+    got = ops.collate_offsets_(idx.cuda(), ep.cuda(), sp.cuda(), dp.cuda())
+    assert torch.equal(got.cpu(), want)
+    bv = ops.batch_vector(sp.cuda(), int(sp[-1]))
+    assert torch.equal(bv.cpu(), torch.repeat_interleave(torch.arange(len(src_counts)), torch.tensor(src_counts)))
