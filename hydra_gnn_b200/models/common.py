@@ -79,6 +79,26 @@ def cross_entropy_loss(pred, label, mask=None):
     return total / count
 
 
+def remap_checkpoint_keys(state_dict, own_keys):
+    """PyG >= 2.4 parameter spelling -> the PyG 2.3 spelling this package keeps (pure renaming)."""
+    own = set(own_keys)
+    out = {}
+    for k, v in state_dict.items():
+        if "<" in k and "___" in k:  # ModuleDict key of HeteroConv: '<a___b___c>' -> 'a__b__c'
+            head, rest = k.split("<", 1)
+            name, tail = rest.split(">", 1)
+            k = head + "__".join(name.split("___")) + tail
+        if k not in own and k.endswith(".lin.weight"):  # GATConv(in_channels=int): lin -> lin_src (= lin_dst)
+            base = k[: -len("lin.weight")]
+            if base + "lin_src.weight" in own:
+                out[base + "lin_src.weight"] = v
+                if base + "lin_dst.weight" in own:
+                    out[base + "lin_dst.weight"] = v
+                continue
+        out[k] = v
+    return out
+
+
 class _Base(nn.Module):
     """Shared pieces: activation choice (ELU for GAT*, ReLU otherwise -- section 9.8), dropout,
     loss, the per-batch plan cache, and the inference-mode guard."""
@@ -88,6 +108,13 @@ class _Base(nn.Module):
 
     def _init_runtime(self):
         self._plans = hnn.PlanCache()
+
+    def load_state_dict(self, state_dict, strict: bool = True, **kwargs):
+        """Accepts checkpoints written by the reference under PyG 2.3 (this module's own spelling) and
+        under PyG >= 2.4: hetero keys ``convs.<src___rel___dst>.`` and a GATConv
+        with one shared projection stored as ``lin.weight`` instead of ``lin_src`` / ``lin_dst``."""
+        return super().load_state_dict(remap_checkpoint_keys(state_dict, self.state_dict().keys()), strict=strict,
+                                       **kwargs)
 
     @property
     def plan_cache(self) -> hnn.PlanCache:

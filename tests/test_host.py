@@ -226,3 +226,31 @@ def test_gloo_world2_shard_and_gather_equals_single_process():
     want = torch.cat([rooms, rooms.sum(1, keepdim=True)], dim=1)
     assert sum(counts) == want.size(0)
     assert torch.equal(gathered, want)
+
+
+def test_checkpoint_keys_of_newer_pyg_are_accepted():
+    """accept the PyG >= 2.4 spelling on load (hetero '<a___b___c>' keys, shared GAT 'lin')."""
+    net = hg.HeterogeneousNetwork(**cases.CASES["mgat"][1])
+    sd = net.state_dict()
+    new = {}
+    for k, v in sd.items():
+        parts = k.split(".")
+        if len(parts) > 3 and parts[2] == "convs" and "__" in parts[3]:
+            parts[3] = "<" + "___".join(parts[3].split("__")) + ">"
+        new[".".join(parts)] = v.clone() + 1.0
+    other = hg.HeterogeneousNetwork(**cases.CASES["mgat"][1])
+    other.load_state_dict(new, strict=True)
+    for k, v in other.state_dict().items():
+        assert torch.equal(v, sd[k] + 1.0), k
+    # homogeneous GAT: one shared projection stored as lin.weight
+    hom = hg.HomogeneousNetwork(**cases.CASES["hom_gat"][1])
+    sd = hom.state_dict()
+    new = {}
+    for k, v in sd.items():
+        if k.endswith("lin_dst.weight"):
+            continue
+        new[k.replace("lin_src.weight", "lin.weight")] = v.clone() * 2.0
+    other = hg.HomogeneousNetwork(**cases.CASES["hom_gat"][1])
+    other.load_state_dict(new, strict=True)
+    for k, v in other.state_dict().items():
+        assert torch.equal(v, sd[k] * 2.0), k
