@@ -491,6 +491,12 @@ int dispatch_special(GatParams& P, cudaStream_t stream) {
     const int nco = P.f_count / 4;
     if (nco <= 4) return launch<4, 4, 1, MODE, HT>(P, stream);
     if (nco <= 8) return launch<4, 8, 1, MODE, HT>(P, stream);
+    if constexpr (MODE == 1) {
+        // long grids (the 8-CTA/SM build): two chunks per thread amortise the per-edge address/weight work
+        const int sms = sm_count() > 0 ? sm_count() : 148;
+        const bool long_grid = ceil_div<int64_t>(P.a.n_dst, kMaxTile) >= static_cast<int64_t>(sms) * 6 * 4;
+        if (long_grid && nco <= 16 && nco > 8) return launch<4, 8, 2, MODE, HT>(P, stream);
+    }
     if (nco <= 16) return launch<4, 16, 1, MODE, HT>(P, stream);
     if (nco <= 32) return launch<4, 32, 1, MODE, HT>(P, stream);
     if constexpr (MODE == 2) {
