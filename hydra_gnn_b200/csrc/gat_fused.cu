@@ -32,6 +32,9 @@ namespace {
 #define HG_GAT_SMEM_KB 24
 #endif
 constexpr size_t kStageBudget = HG_GAT_SMEM_KB * 1024;  // shared memory per CTA for staging (the rest of the SM's 256 KB is L1)
+#ifndef HG_GAT_OCC_LONG
+#define HG_GAT_OCC_LONG 8
+#endif
 #ifndef HG_GAT_MIN_TILE
 #define HG_GAT_MIN_TILE 32  // smaller tiles on short grids measured slower (8, 16)
 #endif
@@ -307,7 +310,7 @@ k_gat_fused(const __grid_constant__ GatParams P) {
                     const char* xh[HT];  // one byte base per head: an address is then ONE IMAD.WIDE.U32
 #pragma unroll
                     for (int hh = 0; hh < HT; ++hh) xh[hh] = reinterpret_cast<const char*>(xsb + hh * C);
-#pragma unroll(OCC >= 8 ? 1 : 2)
+#pragma unroll(OCC >= 7 ? 1 : 2)
                     for (int e = beg; e < end; ++e) {
                         const uint32_t j = static_cast<uint32_t>(colp[e]);
                         const float4 wa = *reinterpret_cast<const float4*>(wp + (e << 2));
@@ -466,7 +469,7 @@ int launch(GatParams& P, cudaStream_t stream) {
     constexpr int kOcc = KC * (MODE == 2 ? HT : 1) <= 4 ? 6 : 4;
     if constexpr (MODE == 1) {
         // latency-bound on long grids: more resident warps beat more loads in flight per warp
-        if (need >= static_cast<int64_t>(sms) * 6 * 4) return go(k_gat_fused<VEC, TPR, KC, MODE, HT, 8>);
+        if (need >= static_cast<int64_t>(sms) * 6 * 4) return go(k_gat_fused<VEC, TPR, KC, MODE, HT, HG_GAT_OCC_LONG>);
     }
     return go(k_gat_fused<VEC, TPR, KC, MODE, HT, kOcc>);
 }
