@@ -1,0 +1,206 @@
+"""CPU tests of the native H-tree builder (libhydra_htree.so, include/hydra_htree.h) -- SURVEY.md 8(f3).
+
+The checker is the REFERENCE's own networkx pipeline (neural_tree/construct.py:241-371 on
+generate_junction_tree_hierarchies.py), run in the build container by tests/golden/make_golden.py:
+  * SHA-256 of the 482 Stanford3DSG H-trees (SURVEY.md 8c golden hash, tests/golden/meta.json),
+  * per-graph SHA-256 of the H-trees of eight synthetic MP3D-shaped graphs,
+  * the tensors nx_htree_to_torch gives for those graphs (tests/golden/htree_*.npz).
+Integer work: every comparison is exact.  The container-order model (pyorder.hpp) is checked against the
+CPython this test runs on."""
+import ctypes
+import hashlib
+import json
+import os
+import random
+import re
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+import cases  # noqa: E402
+from hydra_gnn_b200 import convert, htree, synth  # noqa: E402
+from hydra_gnn_b200.data import Batch  # noqa: E402
+
+META = json.load(open(os.path.join(ROOT, "tests", "golden", "meta.json")))
+
+
+def _hom_inputs(g):
+    """(is_room, edge_index) of a room-object HeteroData in to_homogeneous() order (construct.py:46)."""
+    off, cum = {}, 0
+    for nt in g.node_types:
+        off[nt] = cum
+        cum += g[nt].x.size(0)
+    is_room = np.zeros(cum, np.uint8)
+    is_room[off["rooms"]:off["rooms"] + g["rooms"].x.size(0)] = 1
+    eis = []
+    for et in g.edge_types:
+        ei = g[et].edge_index.clone().long()
+        ei[0] += off[et[0]]
+        ei[1] += off[et[2]]
+        eis.append(ei)
+    return is_room, torch.cat(eis, 1).numpy()
+
+
+# ------------------------------------------------------------------------------ C ABI
+def test_htree_library_exports_every_declared_symbol():
+    header = open(os.path.join(ROOT, "include", "hydra_htree.h")).read()
+    declared = set(re.findall(r"HG_HTREE_API\s+[\w\s\*]+?\b(hg_\w+)\s*\(", header))
+    assert declared == set(htree._SYMBOLS), declared ^ set(htree._SYMBOLS)
+    lib = htree.load_shared_object()
+    for name in declared:
+        assert hasattr(lib, name)
+    raw = ctypes.CDLL(htree.library_path())
+    exported = {n for n in declared if hasattr(raw, n)}
+    assert exported == declared
+
+
+def test_htree_bad_inputs_raise():
+    with pytest.raises(RuntimeError):  # edge endpoint outside the graph
+        htree.build_raw([(np.array([0, 1], np.uint8), np.array([[0], [5]], np.int64))])
+    with pytest.raises(RuntimeError):  # component without a room: the reference asserts (construct.py:256-262)
+        htree.build_raw([(np.array([0, 0], np.uint8), np.array([[0], [1]], np.int64))])
+    raw = htree.build_raw([])
+    assert raw["node_ptr"].tolist() == [0] and raw["edge_ptr"].tolist() == [0]
+
+
+# ------------------------------------------------------------------------------ golden hashes of the reference
+def test_stanford_htrees_match_reference_sha256():
+    """All 482 graphs of data/Stanford3DSG.pkl; inputs in the order make_golden.stanford_nx_signature feeds
+    networkx (objects 0..n-2, room n-1; edge_index columns, then object-room edges)."""
+    graphs = []
+    for g in cases.load_stanford():
+        n = g["x"].shape[0]
+        is_room = np.zeros(n, np.uint8)
+        is_room[n - 1] = 1
+        src, dst = [], []
+        for i, j in g["edge_index"].T.tolist():
+            a = n - 1 if i == 0 else i - 1
+            b = n - 1 if j == 0 else j - 1
+            if a != b:
+                src.append(a), dst.append(b)
+        src += list(range(n - 1))
+        dst += [n - 1] * (n - 1)
+        graphs.append((is_room, np.array([src, dst], np.int64).reshape(2, -1)))
+    assert len(graphs) == META["stanford_graphs"] == 482
+    raw = htree.build_raw(graphs)
+    sha = hashlib.sha256()
+    for k in range(len(graphs)):
+        sha.update(htree.signature(raw, k).encode())
+    assert sha.hexdigest() == META["stanford_htree_sha256"]
+    # thread count does not change the result
+    raw1 = htree.build_raw(graphs, n_threads=1)
+    for key in raw:
+        assert np.array_equal(raw[key], raw1[key]), key
+
+
+def test_synth_htrees_match_reference_sha256():
+    ids = [int(k) for k in META["htree_synth_sha256"]]
+    assert sorted(ids) == sorted(cases.HTREE_SYNTH_IDS)
+    raw = htree.build_raw([_hom_inputs(synth.synth_mp3d_batch([i])) for i in ids])
+    for k, gid in enumerate(ids):
+        got = hashlib.sha256(htree.signature(raw, k).encode()).hexdigest()
+        assert got == META["htree_synth_sha256"][str(gid)], gid
+
+
+# ------------------------------------------------------------------------------ tensors (nx_htree_to_torch)
+def _assert_same_tree(got, want, what):
+    for nt in cases.HTREE_ALL_NODE_TYPES:
+        assert torch.equal(got[nt].x, want[nt].x), (what, nt, "x")
+        assert torch.equal(got[nt].clique_has.int(), want[nt].clique_has.int()), (what, nt, "clique_has")
+        assert torch.equal(got[nt].label.int(), want[nt].label.int()), (what, nt, "label")
+    for et in cases.HTREE_ALL_EDGE_TYPES:
+        assert got[et].edge_index.dtype == torch.int64
+        assert torch.equal(got[et].edge_index, want[et].edge_index), (what, et)
+
+
+def test_generate_htree_equals_reference_fixtures_synth():
+    want = cases.load_htrees("htree_synth")
+    for gid, w in zip(cases.HTREE_SYNTH_IDS, want):
+        _assert_same_tree(htree.generate_htree(synth.synth_mp3d_batch([gid])), w, gid)
+
+
+def test_generate_htree_equals_reference_fixtures_stanford():
+    st = cases.load_stanford()
+    want = cases.load_htrees("htree_stanford")
+    for gid, w in zip(cases.HTREE_STANFORD_IDS, want):
+        g = cases.stanford_hetero(st[gid])
+        g["objects"].label, g["rooms"].label = g["objects"].y.int(), g["rooms"].y.int()
+        _assert_same_tree(htree.generate_htree(g), w, gid)
+
+
+def test_batched_build_equals_collate_of_single_builds():
+    """generate_htree_batch on a collated batch == Batch.from_data_list of the per-graph trees (the DataLoader
+    path of the reference, base_training_job.py:164-178), and the homogeneous conversion of both agrees."""
+    ids = list(range(12))
+    whole = htree.generate_htree_batch(synth.synth_mp3d_batch(ids))
+    parts = Batch.from_data_list([htree.generate_htree(synth.synth_mp3d_batch([i])) for i in ids])
+    for nt in cases.HTREE_ALL_NODE_TYPES:
+        assert torch.equal(whole[nt].x, parts[nt].x), nt
+        assert torch.equal(whole[nt].batch, parts[nt].batch), nt
+        assert torch.equal(whole[nt].ptr, parts[nt].ptr), nt
+    for et in cases.HTREE_ALL_EDGE_TYPES:
+        assert torch.equal(whole[et].edge_index, parts[et].edge_index), et
+    a = convert.heterogeneous_htree_to_homogeneous(whole)
+    b = convert.heterogeneous_htree_to_homogeneous(parts)
+    for key in ("edge_index", "init_edge_index", "pool_edge_index", "room_mask", "object_mask"):
+        assert torch.equal(a[key], b[key]), key
+
+
+def test_htree_structure_invariants_on_a_larger_batch():
+    """Size-independent properties at a size the reference takes minutes for (256 graphs): the leaves of every H-tree cover every source node at least once, virtual nodes are one per source node in source order."""
+    ids = list(range(1000, 1256))
+    src = synth.synth_mp3d_batch(ids)
+    t, raw = htree.generate_htree_batch(src, return_raw=True)
+    n_obj, n_room = src["objects"].x.size(0), src["rooms"].x.size(0)
+    assert t["object_virtual"].x.size(0) == n_obj and t["room_virtual"].x.size(0) == n_room
+    assert t["object"].x.size(0) >= n_obj and t["room"].x.size(0) >= n_room
+    # tree relations come as both directions of every undirected clique/leaf edge (to_directed, construct.py:323);
+    # the reference's hierarchy is not always acyclic at the room-room level, so no forest check here
+    for g in range(len(ids)):
+        e0, e1 = int(raw["edge_ptr"][g]), int(raw["edge_ptr"][g + 1])
+        sel = raw["edge_type"][e0:e1] < len(htree.HTREE_EDGE_TYPES)
+        fwd = set(zip(raw["edge_src"][e0:e1][sel].tolist(), raw["edge_dst"][e0:e1][sel].tolist()))
+        assert fwd == {(b, a) for a, b in fwd}, g
+    # pooling edges: every leaf points at the virtual copy of the source node it stands for
+    for leaf, rel, virt in htree.HTREE_POOL_EDGE_TYPES:
+        ei = t[leaf, rel, virt].edge_index
+        assert torch.equal(ei[0].sort()[0], torch.arange(t[leaf].x.size(0)))
+        assert torch.equal(t[leaf].x[ei[0]], t[virt].x[ei[1]])
+    # every leaf row equals its source row
+    assert torch.equal(t["object_virtual"].x, src["objects"].x)
+    assert torch.equal(t["room_virtual"].x, src["rooms"].x)
+
+
+# ------------------------------------------------------------------------------ container-order model
+def test_pyset_model_matches_this_cpython():
+    lib = htree.load_shared_object()
+    rng = random.Random(7)
+    for trial in range(200):
+        n_ops = rng.randint(1, 400)
+        universe = rng.choice([16, 64, 700, 5000])
+        s, ops, keys = set(), [], []
+        for _ in range(n_ops):
+            k = rng.randrange(universe)
+            if rng.random() < 0.7:
+                s.add(k), ops.append(0)
+            else:
+                s.discard(k), ops.append(1)
+            keys.append(k)
+        ops_a, keys_a = np.array(ops, np.int32), np.array(keys, np.int64)
+        out = np.zeros(len(s) + 1, np.int64)
+        n = lib.hg_pyset_trace(ops_a.ctypes.data, keys_a.ctypes.data, keys_a.ctypes.data, n_ops, out.ctypes.data, out.size)
+        assert n == len(s)
+        assert out[:n].tolist() == list(s), trial
+
+
+def test_pytuple_hash_matches_this_cpython():
+    lib = htree.load_shared_object()
+    rng = random.Random(11)
+    for _ in range(300):
+        t = tuple(rng.randrange(0, 3000) for _ in range(rng.randint(0, 9)))
+        a = np.array(t, np.int32)
+        assert lib.hg_pytuple_hash(a.ctypes.data, len(t)) == hash(t), t
