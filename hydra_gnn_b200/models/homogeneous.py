@@ -72,11 +72,12 @@ class HomogeneousNetwork(_Base):
         return PlanRequest(_REL, data.edge_index, n, n, False)
 
     @staticmethod
-    def _mask_rows(plan, name: str, mask: torch.Tensor) -> torch.Tensor:
-        """``nonzero(mask)`` as int32, computed once per plan (one host sync per batch)."""
+    def _mask_rows(plan, name: str, mask: torch.Tensor, negate: bool = False) -> torch.Tensor:
+        """``nonzero(mask)`` as int32, computed once per mask tensor (one host sync per batch); kept beside the
+        plan cache, keyed by the mask's identity, so that a forward whose plan is rebuilt stays capturable."""
         key = (name, mask.data_ptr(), mask._version)
         if plan.extra.get(name + "_key") != key:
-            plan.extra[name] = mask.nonzero(as_tuple=False).view(-1).to(torch.int32)
+            plan.extra[name] = (~mask if negate else mask).nonzero(as_tuple=False).view(-1).to(torch.int32)
             plan.extra[name + "_key"] = key
         return plan.extra[name]
 
@@ -114,10 +115,10 @@ class HomogeneousNetwork(_Base):
         plan = self._plans.get([self._main_request(data)])
         room_only = self.classification_task == "room"
         x = self._message_passing(data.x, data, plan, use_batch_norm=True, final_act=not room_only)
-        room_rows = self._mask_rows(plan, "room_rows", data.room_mask)
+        room_rows = self._mask_rows(self._plans, "room_rows", data.room_mask)
         if room_only:
             return ops.gather_rows(x, room_rows)
-        return self._heads(x, room_rows, self._mask_rows(plan, "not_room_rows", ~data.room_mask))
+        return self._heads(x, room_rows, self._mask_rows(self._plans, "not_room_rows", data.room_mask, negate=True))
 
 
 class HomogeneousNeuralTreeNetwork(HomogeneousNetwork):
@@ -157,11 +158,11 @@ class HomogeneousNeuralTreeNetwork(HomogeneousNetwork):
         x = self._message_passing(x, data, plan, use_batch_norm=False, final_act=False)
 
         pool = plan[(self._POOL, False)]
-        room_rows = self._mask_rows(plan, "room_rows", data.room_mask)
+        room_rows = self._mask_rows(self._plans, "room_rows", data.room_mask)
         if room_only:  # LeafPool evaluated only on the rows the caller keeps
             return ops.seg_reduce(x, pool, "mean", row_map=room_rows)
         # task "all": activation (+ dropout) after the pooling (:105-109)
-        object_rows = self._mask_rows(plan, "object_rows", data.object_mask)
+        object_rows = self._mask_rows(self._plans, "object_rows", data.object_mask)
         xr = self._drop(ops.seg_reduce(x, pool, "mean", row_map=room_rows, act=self._act_name))
         xo = self._drop(ops.seg_reduce(x, pool, "mean", row_map=object_rows, act=self._act_name))
         return (ops.linear([(xr, self.post_mp_room.weight)], self.post_mp_room.out_features,

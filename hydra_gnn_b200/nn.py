@@ -98,9 +98,11 @@ class PlanCache:
         self.overlap = True  # build on a side stream; joined by the first kernel that reads a CSR
         self._sig = None
         self._plan: Optional[GraphPlan] = None
+        self.extra: Dict[str, object] = {}  # per-batch derived index vectors (mask -> rows), keyed by tensor identity
 
     def clear(self):
         self._sig, self._plan = None, None
+        self.extra.clear()
 
     def join(self):
         """Joins a side-stream plan nobody consumed (keeps stream capture well formed)."""
