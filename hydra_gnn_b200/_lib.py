@@ -61,7 +61,21 @@ class LinearArgs(C.Structure):
                 ("w_prepacked", i32), ("reserved", i32)]
 
 
-_STRUCTS = [PlanRel, SegArgs, GatRel, GatArgs, LinSeg, LinearArgs]
+class GatTrainRel(C.Structure):
+    _fields_ = [("xs", vp), ("ldxs", i64), ("a_src", vp), ("lda_src", i64), ("a_dst", vp), ("lda_dst", i64),
+                ("rowptr", vp), ("col", vp), ("bias", vp), ("alpha", vp), ("dlogit", vp), ("rowptr_t", vp),
+                ("col_t", vp), ("pos_t", vp), ("dxs", vp), ("lddxs", i64), ("da_src", vp), ("ldda_src", i64),
+                ("da_dst", vp), ("ldda_dst", i64), ("n_src", i32), ("reserved", i32)]
+
+
+class GatTrainArgs(C.Structure):
+    _fields_ = [("rel", GatTrainRel * HG_MAX_RELATIONS), ("n_rel", i32), ("n_dst", i32), ("H", i32), ("C", i32),
+                ("concat", i32), ("group", i32), ("act", i32), ("neg_slope", f32), ("dropout_p", f32),
+                ("reserved", i32), ("seed", C.c_uint64), ("out", vp), ("ldout", i64), ("dout", vp), ("lddout", i64),
+                ("g", vp), ("ldg", i64), ("dbias", vp)]
+
+
+_STRUCTS = [PlanRel, SegArgs, GatRel, GatArgs, LinSeg, LinearArgs, GatTrainRel, GatTrainArgs]
 
 # name -> (restype, argtypes); every symbol declared in include/hydra_gnn_b200.h
 SYMBOLS = {
@@ -82,6 +96,11 @@ SYMBOLS = {
     "hg_gather_rows": (C.c_int, [vp, i64, vp, i64, i32, i32, vp, i64, vp]),
     "hg_collate_offsets": (C.c_int, [vp, i64, vp, vp, vp, i32, vp]),
     "hg_batch_vector": (C.c_int, [vp, i64, vp, i32, vp]),
+    "hg_gat_train_fwd": (C.c_int, [C.POINTER(GatTrainArgs), vp]),
+    "hg_gat_train_bwd": (C.c_int, [C.POINTER(GatTrainArgs), vp]),
+    "hg_csr_transpose_map": (C.c_int, [vp, vp, vp, i64, vp, vp, vp, i64, i32, vp, vp, vp]),
+    "hg_linear_wgrad": (C.c_int, [vp, i64, vp, i64, i32, i32, i32, vp, i64, i32, vp]),
+    "hg_adam_step": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, f32, i32, vp]),
 }
 
 _lock = threading.Lock()

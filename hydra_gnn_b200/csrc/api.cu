@@ -63,6 +63,8 @@ extern "C" int hg_sizeof(int which) {
         case 3: return static_cast<int>(sizeof(hg_gat_args));
         case 4: return static_cast<int>(sizeof(hg_lin_seg));
         case 5: return static_cast<int>(sizeof(hg_linear_args));
+        case 6: return static_cast<int>(sizeof(hg_gat_train_rel));
+        case 7: return static_cast<int>(sizeof(hg_gat_train_args));
         default: return -1;
     }
 }

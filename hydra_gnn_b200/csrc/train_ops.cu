@@ -1,0 +1,144 @@
+// Weight gradient of the projection (dW = dY^T X) and the Adam update (include/hydra_gnn_b200.h, "Training step").
+//
+// hg_linear_wgrad: fp32 FMA SGEMM, 64 x 64 output tiles, 4 x 4 micro-tiles, the M (row) dimension split across
+// CTAs so that the grid covers the 148 SMs several times; partial tiles are added with red.global.add.f32.
+// Both operands are read in their natural row-major layout (rows of dY give the N index, rows of X the K index),
+// so every global load is coalesced and no transpose is materialised.
+#include "hg_common.cuh"
+
+namespace hg {
+namespace {
+
+constexpr int kTN = 64, kTK = 64, kTM = 16, kWgThreads = 256;
+
+__global__ void __launch_bounds__(kWgThreads) k_wgrad(const float* __restrict__ dy, int64_t lddy,
+                                                      const float* __restrict__ x, int64_t ldx, int M, int N, int K,
+                                                      float* __restrict__ dw, int64_t lddw, int rows_per_split) {
+    __shared__ __align__(16) float sA[2][kTM][kTN];
+    __shared__ __align__(16) float sB[2][kTM][kTK];
+    const int tid = threadIdx.x;
+    const int n0 = blockIdx.x * kTN, k0 = blockIdx.y * kTK;
+    const int m_beg = blockIdx.z * rows_per_split;
+    const int m_end = min(M, m_beg + rows_per_split);
+    if (m_beg >= m_end) return;
+    const int lrow = tid >> 4, lcol = (tid & 15) * 4;  // loader: row of the m-tile, first of 4 columns
+    const int tn = (tid >> 4) * 4, tk = (tid & 15) * 4;  // micro-tile origin
+    float acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+    float ra[4], rb[4];
+    auto load = [&](int m0) {
+        const int m = m0 + lrow;
+        const bool ok = m < m_end;
+        const float* pa = dy + static_cast<int64_t>(m) * lddy + n0 + lcol;
+        const float* pb = x + static_cast<int64_t>(m) * ldx + k0 + lcol;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            ra[t] = (ok && n0 + lcol + t < N) ? __ldg(pa + t) : 0.f;
+            rb[t] = (ok && k0 + lcol + t < K) ? __ldg(pb + t) : 0.f;
+        }
+    };
+    load(m_beg);
+    int buf = 0;
+    for (int m0 = m_beg; m0 < m_end; m0 += kTM) {
+        *reinterpret_cast<float4*>(&sA[buf][lrow][lcol]) = make_float4(ra[0], ra[1], ra[2], ra[3]);
+        *reinterpret_cast<float4*>(&sB[buf][lrow][lcol]) = make_float4(rb[0], rb[1], rb[2], rb[3]);
+        __syncthreads();
+        if (m0 + kTM < m_end) load(m0 + kTM);
+#pragma unroll
+        for (int mm = 0; mm < kTM; ++mm) {
+            const float4 a4 = *reinterpret_cast<const float4*>(&sA[buf][mm][tn]);
+            const float4 b4 = *reinterpret_cast<const float4*>(&sB[buf][mm][tk]);
+            const float av[4] = {a4.x, a4.y, a4.z, a4.w};
+            const float bv[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(av[a], bv[b], acc[a][b]);
+        }
+        buf ^= 1;  // the next iteration writes the other buffer: one barrier per m-tile
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        const int n = n0 + tn + a;
+        if (n >= N) continue;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int k = k0 + tk + b;
+            if (k < K) atomicAdd(dw + static_cast<int64_t>(n) * lddw + k, acc[a][b]);
+        }
+    }
+}
+
+__global__ void k_zero_rows(float* __restrict__ p, int64_t ld, int N, int K) {
+    const int64_t total = static_cast<int64_t>(N) * K;
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total;
+         t += static_cast<int64_t>(gridDim.x) * blockDim.x)
+        p[(t / K) * ld + t % K] = 0.f;
+}
+
+__global__ void __launch_bounds__(256) k_adam(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                              float* __restrict__ v, int64_t n, float lr, float b1, float b2, float eps,
+                                              float wd, float gscale, float step_size, float inv_sqrt_bc2) {
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < n;
+         t += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const float pt = p[t];
+        const float gt = fmaf(wd, pt, g[t] * gscale);
+        const float mt = b1 * m[t] + (1.f - b1) * gt;
+        const float vt = b2 * v[t] + (1.f - b2) * gt * gt;
+        m[t] = mt;
+        v[t] = vt;
+        p[t] = pt - step_size * mt / (sqrtf(vt) * inv_sqrt_bc2 + eps);
+    }
+}
+
+}  // namespace
+}  // namespace hg
+
+extern "C" int hg_linear_wgrad(const float* dy, int64_t lddy, const float* x, int64_t ldx, int32_t M, int32_t N, int32_t K,
+                               float* dw, int64_t lddw, int32_t accumulate, void* stream_) {
+    using namespace hg;
+    if (M < 0 || N < 0 || K < 0 || lddy < N || ldx < K || lddw < K) return HG_EINVAL;
+    if (N == 0 || K == 0) return HG_OK;
+    if (!dw || (M > 0 && (!dy || !x))) return HG_EINVAL;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int sms = sm_count() > 0 ? sm_count() : 148;
+    if (!accumulate) {
+        const int64_t total = static_cast<int64_t>(N) * K;
+        const int64_t g = ceil_div<int64_t>(total, 256);
+        k_zero_rows<<<static_cast<unsigned>(g < sms * 8 ? g : sms * 8), 256, 0, stream>>>(dw, lddw, N, K);
+    }
+    if (M > 0) {
+        const int tn = ceil_div(N, kTN), tk = ceil_div(K, kTK);
+        int splits = ceil_div(sms * 4, tn * tk);
+        const int max_splits = ceil_div(M, 4 * kTM);
+        splits = splits < 1 ? 1 : (splits > max_splits ? max_splits : splits);
+        int rows = ceil_div(M, splits);
+        rows = ceil_div(rows, kTM) * kTM;
+        splits = ceil_div(M, rows);
+        k_wgrad<<<dim3(tn, tk, splits), kWgThreads, 0, stream>>>(dy, lddy, x, ldx, M, N, K, dw, lddw, rows);
+    }
+    return check_launch();
+}
+
+extern "C" int hg_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                            float beta1, float beta2, float eps, float weight_decay, float grad_scale, int32_t step,
+                            void* stream_) {
+    using namespace hg;
+    if (n < 0 || step < 1) return HG_EINVAL;
+    if (n == 0) return HG_OK;
+    if (!param || !grad || !exp_avg || !exp_avg_sq) return HG_EINVAL;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int sms = sm_count() > 0 ? sm_count() : 148;
+    // torch.optim.Adam (single-tensor path): step_size = lr / (1 - b1^t); denom = sqrt(v) / sqrt(1 - b2^t) + eps
+    const double bc1 = 1.0 - pow(static_cast<double>(beta1), step);
+    const double bc2 = 1.0 - pow(static_cast<double>(beta2), step);
+    const float step_size = static_cast<float>(lr / bc1);
+    const float inv_sqrt_bc2 = static_cast<float>(1.0 / sqrt(bc2));
+    const int64_t g = ceil_div<int64_t>(n, 256);
+    k_adam<<<static_cast<unsigned>(g < sms * 8 ? g : sms * 8), 256, 0, stream>>>(
+        param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, grad_scale, step_size, inv_sqrt_bc2);
+    return check_launch();
+}

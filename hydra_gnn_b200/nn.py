@@ -111,6 +111,9 @@ class PlanCache:
             j.wait()
 
     def get(self, requests: Sequence[PlanRequest]) -> GraphPlan:
+        if torch.is_grad_enabled():  # the backward maps the reversed CSR onto this one through perm
+            for r in requests:
+                r.want_perm = True
         sig = tuple(r.signature() for r in requests)
         if self.enabled and sig == self._sig and self._plan is not None:
             return self._plan
@@ -328,6 +331,10 @@ def run_gat_layer(convs: Dict[EdgeType, GATConv], rels: Sequence[EdgeType], x: D
     the biases and the activation in its epilogue."""
     if only_dst is not None:
         rels = [et for et in rels if et[2] in only_dst]
+    if (torch.is_grad_enabled() and any(p.requires_grad for et in rels for p in convs[et].parameters())) or \
+            any(convs[et].training and convs[et].dropout > 0 for et in rels):
+        from . import train  # training form: saved softmax weights, attention dropout, hand-written backward
+        return train.run_gat_layer_train(convs, rels, x, csr, act=act, group=group, edge_attr=edge_attr)
     pack = _gat_pack(owner, convs, rels, x, _gat_modes(convs, rels, x, group))
     device = next(iter(x.values())).device
     Y = {T: ops.linear([(x[T], W)], W.size(0), pack_cache=pack.wcache.setdefault(T, {})) for T, W in pack.W.items()}

@@ -161,6 +161,8 @@ class CSR:
     cap: int  # allocated entries; the live count is rowptr[-1] (kept on the device)
     self_loops: bool
     join: Optional[_Join] = None
+    edge_index: Optional[Tensor] = None  # kept when perm was requested: the training side is built from it
+    train: Optional["TrainCSR"] = None   # reversed CSR + position map (ensure_train_csr)
 
     def ready(self) -> "CSR":
         """Call before handing the arrays to a kernel on the current stream."""
@@ -236,7 +238,8 @@ def build_csr(specs: Sequence[CSRSpec], overlap: bool = False):
             r.n_edges, r.n_src, r.n_dst, r.self_loops = E, n_src, n_dst, int(s.self_loops)
             r.rowptr, r.col, r.perm, r.inv_sqrt_deg = ptr(rowptr), ptr(col), ptr(perm), ptr(norm)
             keep.append(ei)
-            out.append(CSR(rowptr, col, perm, norm, n_src, n_dst, cap, s.self_loops))
+            out.append(CSR(rowptr, col, perm, norm, n_src, n_dst, cap, s.self_loops,
+                           edge_index=ei if (s.want_perm and not s.transpose) else None))
         nbytes = h.hg_plan_workspace_bytes(rels, len(chunk))
         if nbytes == 0:
             raise RuntimeError("hg_plan_workspace_bytes rejected the plan (sizes out of int32 range?)")
@@ -489,3 +492,156 @@ def batch_vector(ptr_: Tensor, n_nodes: int) -> Tensor:
           lambda: h.hg_batch_vector(ptr(out), n_nodes, ptr(ptr_), ptr_.numel() - 1, stream_ptr()))
     _lib.launch_count += 1
     return out
+
+
+# ------------------------------------------------------------------------------ training step (configs[4])
+@dataclass
+class TrainCSR:
+    """Source-major side of a relation for the backward: CSR of the reversed relation and, per entry, its
+    position in the destination-major CSR (where alpha / dlogit live)."""
+    rowptr_t: Tensor
+    col_t: Tensor
+    pos_t: Tensor
+
+
+def ensure_train_csr(csrs: Sequence[CSR]) -> None:
+    """Builds (one plan call for all of them) the reversed CSRs of the relations that lack one."""
+    todo = [c for c in {id(c): c for c in csrs}.values() if c.train is None]
+    if not todo:
+        return
+    h = lib()
+    for c in todo:
+        if c.perm is None or c.edge_index is None:
+            raise RuntimeError("training needs a plan built with perm (build it with grad mode enabled)")
+        c.ready()
+    specs = [CSRSpec(c.edge_index, c.n_src, c.n_dst, c.self_loops, True, False, transpose=True) for c in todo]
+    rev, _ = build_csr(specs)
+    for c, t in zip(todo, rev):
+        E = c.edge_index.size(1)
+        n_loop = min(c.n_src, c.n_dst) if c.self_loops else 0
+        scratch = torch.empty(max(E + n_loop, 1), dtype=torch.int32, device=c.col.device)
+        pos_t = torch.empty(max(c.cap, 1), dtype=torch.int32, device=c.col.device)
+        # rowptr[-1] (the live entry count) stays on the device
+        _call("hg_csr_transpose_map", dict(cap=c.cap),
+              lambda: h.hg_csr_transpose_map(ptr(c.perm), ptr(c.col), c.rowptr.data_ptr() + 4 * c.n_dst, c.cap,
+                                             ptr(t.perm), ptr(t.col), t.rowptr.data_ptr() + 4 * t.n_dst, E, n_loop,
+                                             ptr(scratch), ptr(pos_t), stream_ptr()))
+        _lib.launch_count += 2
+        c.train = TrainCSR(t.rowptr, t.col, pos_t)
+
+
+def linear_wgrad(dy: Tensor, x: Tensor, out: Tensor = None, accumulate: bool = False) -> Tensor:
+    """``dW[N, K] = dy[M, N]^T @ x[M, K]`` (``hg_linear_wgrad``)."""
+    h = lib()
+    dy, x = _rows(dy, "dy"), _rows(x, "x")
+    M, N, K = dy.size(0), dy.size(1), x.size(1)
+    if x.size(0) != M:
+        raise ValueError("dy / x row counts differ")
+    if out is None:
+        out = torch.empty(N, K, dtype=torch.float32, device=x.device)
+        accumulate = False
+    meta = dict(M=M, N=N, K=K)
+    _call("hg_linear_wgrad", meta,
+          lambda: h.hg_linear_wgrad(ptr(dy), _ld(dy), ptr(x), _ld(x), M, N, K, ptr(out), _ld(out), int(accumulate),
+                                    stream_ptr()))
+    _lib.launch_count += 1 if accumulate else 2
+    return out
+
+
+def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, step: int, lr: float, beta1: float,
+              beta2: float, eps: float, weight_decay: float, grad_scale: float = 1.0) -> None:
+    h = lib()
+    for t in (param, grad, exp_avg, exp_avg_sq):
+        _f32(t, "adam operand")
+        if not t.is_contiguous() or t.numel() != param.numel():
+            raise ValueError("adam operands must be contiguous and of equal size")
+    _call("hg_adam_step", dict(n=param.numel()),
+          lambda: h.hg_adam_step(ptr(param), ptr(grad), ptr(exp_avg), ptr(exp_avg_sq), param.numel(), lr, beta1, beta2,
+                                 eps, weight_decay, grad_scale, step, stream_ptr()))
+    _lib.launch_count += 1
+
+
+@dataclass
+class GatTrainRelation:
+    """One relation of a training-form GAT group.  ``y_src`` / ``y_dst`` are the projection outputs of the source /
+    destination node type; the operands are column ranges of them (same layout for the gradients)."""
+    y_src: Tensor
+    y_dst: Tensor
+    xs_off: int
+    as_off: int
+    ad_off: int
+    csr: CSR
+    bias: Optional[Tensor] = None
+    alpha: Optional[Tensor] = None
+
+
+def _gat_train_args(rels: Sequence[GatTrainRelation], n_dst: int, H: int, Cc: int, concat: bool, group: str, act: str,
+                    neg_slope: float, dropout_p: float, seed: int, out: Tensor):
+    if not 1 <= len(rels) <= _lib.HG_MAX_RELATIONS:
+        raise ValueError("1..8 relations per destination type")
+    a = _lib.GatTrainArgs()
+    for k, r in enumerate(rels):
+        for t in (r.y_src, r.y_dst):
+            _f32(t, "y")
+            if t.dim() != 2 or (t.size(1) > 1 and t.stride(1) != 1):
+                raise ValueError("projection outputs must be 2-D with unit feature stride")
+        r.csr.ready()
+        if r.csr.n_dst != n_dst or r.y_dst.size(0) != n_dst or r.y_src.size(0) != r.csr.n_src:
+            raise ValueError("relation shapes do not match the CSR")
+        g = a.rel[k]
+        es = r.y_src.element_size()
+        g.xs, g.ldxs = r.y_src.data_ptr() + es * r.xs_off, _ld(r.y_src)
+        g.a_src, g.lda_src = r.y_src.data_ptr() + es * r.as_off, _ld(r.y_src)
+        g.a_dst, g.lda_dst = r.y_dst.data_ptr() + es * r.ad_off, _ld(r.y_dst)
+        g.rowptr, g.col, g.bias, g.alpha = ptr(r.csr.rowptr), ptr(r.csr.col), ptr(r.bias), ptr(r.alpha)
+        g.n_src = r.csr.n_src
+    a.n_rel, a.n_dst, a.H, a.C = len(rels), n_dst, H, Cc
+    a.concat, a.group, a.act, a.neg_slope = int(concat), GROUP[group], ACT[act], float(neg_slope)
+    a.dropout_p, a.seed = float(dropout_p), int(seed) & 0xFFFFFFFFFFFFFFFF
+    a.out, a.ldout = ptr(out), _ld(out)
+    return a
+
+
+def gat_train_fwd(rels: Sequence[GatTrainRelation], n_dst: int, H: int, Cc: int, concat: bool, *, group: str = "sum",
+                  act: str = None, neg_slope: float = 0.2, dropout_p: float = 0.0, seed: int = 0) -> Tensor:
+    """Training-form GAT aggregation (``hg_gat_train_fwd``); fills ``r.alpha`` ([cap, H]) of every relation."""
+    h = lib()
+    device = rels[0].y_src.device
+    out = torch.empty(n_dst, H * Cc if concat else Cc, dtype=torch.float32, device=device)
+    for r in rels:
+        if r.alpha is None:
+            r.alpha = torch.empty(max(r.csr.cap, 1), H, dtype=torch.float32, device=device)
+    a = _gat_train_args(rels, n_dst, H, Cc, concat, group, act, neg_slope, dropout_p, seed, out)
+    meta = dict(n_dst=n_dst, H=H, C=Cc, width=out.size(1), rels=[dict(n_src=r.csr.n_src, cap=r.csr.cap) for r in rels])
+    _call("hg_gat_train_fwd", meta, lambda: h.hg_gat_train_fwd(C.byref(a), stream_ptr()))
+    _lib.launch_count += 1
+    return out
+
+
+def gat_train_bwd(rels: Sequence[GatTrainRelation], dys: Sequence[tuple], n_dst: int, H: int, Cc: int, concat: bool,
+                  out: Tensor, dout: Tensor, *, group: str = "sum", act: str = None, neg_slope: float = 0.2,
+                  dropout_p: float = 0.0, seed: int = 0, dbias: Tensor = None) -> None:
+    """Backward of :func:`gat_train_fwd`.  ``dys[k] = (dY_src, dY_dst)``: gradient buffers with the layout of the
+    projection outputs; the relation's columns of them are overwritten."""
+    h = lib()
+    device = out.device
+    ensure_train_csr([r.csr for r in rels])
+    a = _gat_train_args(rels, n_dst, H, Cc, concat, group, act, neg_slope, dropout_p, seed, out)
+    dout = _rows(dout, "dout")
+    gbuf = torch.empty(n_dst, out.size(1), dtype=torch.float32, device=device)
+    keep = []
+    for k, (r, (dys_, dyd_)) in enumerate(zip(rels, dys)):
+        g = a.rel[k]
+        dl = torch.empty(max(r.csr.cap, 1), H, dtype=torch.float32, device=device)
+        keep.append(dl)
+        t = r.csr.train
+        g.dlogit, g.rowptr_t, g.col_t, g.pos_t = ptr(dl), ptr(t.rowptr_t), ptr(t.col_t), ptr(t.pos_t)
+        g.dxs, g.lddxs = dys_.data_ptr() + 4 * r.xs_off, _ld(dys_)
+        g.da_src, g.ldda_src = dys_.data_ptr() + 4 * r.as_off, _ld(dys_)
+        g.da_dst, g.ldda_dst = dyd_.data_ptr() + 4 * r.ad_off, _ld(dyd_)
+    a.dout, a.lddout = ptr(dout), _ld(dout)
+    a.g, a.ldg = ptr(gbuf), _ld(gbuf)
+    a.dbias = ptr(dbias)
+    meta = dict(n_dst=n_dst, H=H, C=Cc, width=out.size(1), rels=[dict(n_src=r.csr.n_src, cap=r.csr.cap) for r in rels])
+    _call("hg_gat_train_bwd", meta, lambda: h.hg_gat_train_bwd(C.byref(a), stream_ptr()))
+    _lib.launch_count += 2

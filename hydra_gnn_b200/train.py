@@ -1,0 +1,226 @@
+"""Training step of the GAT models (BASELINE.json configs[4]; reference: base_training_job.py:203-219 --
+``loss = model.loss(model(data), label, mask); loss.backward(); optimizer.step()``).
+
+``torch.autograd`` is the tape only: every gradient of a hot operator is produced by a hand-written kernel
+(``hg_gat_train_bwd``, ``hg_linear_wgrad``, ``hg_linear`` with the transposed weight) and the optimizer update by
+``hg_adam_step`` over one flat parameter buffer.  Parameter-space bookkeeping on tensors of a few hundred rows
+(stacking ``lin_src`` blocks and the folded attention rows into the per-node-type projection matrix) is left to
+torch's own differentiable ops, which also carries the gradient of the fold back to ``att_src`` / ``att_dst``.
+
+The training form keeps every relation project-first (the aggregate-first rewrite of the inference path would
+need the gradient of the re-arranged weights; not worth it while the weight gradient dominates the step).
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+from torch import Tensor, nn
+
+from . import ops
+from .ops import CSR, GatTrainRelation
+
+EdgeType = Tuple[str, str, str]
+
+
+def _pad4(n: int) -> int:
+    return (n + 3) // 4 * 4
+
+
+# =============================================================================== projection
+class _LinearFn(torch.autograd.Function):
+    """``y = x @ W^T`` on hg_linear; backward: ``dx = dy @ W`` (hg_linear), ``dW = dy^T @ x`` (hg_linear_wgrad)."""
+
+    @staticmethod
+    def forward(ctx, x: Tensor, W: Tensor):
+        ctx.save_for_backward(x, W)
+        return ops.linear([(x, W)], W.size(0))
+
+    @staticmethod
+    def backward(ctx, dy: Tensor):
+        x, W = ctx.saved_tensors
+        dx = dW = None
+        if ctx.needs_input_grad[0]:
+            dx = ops.linear([(dy, W.t().contiguous())], W.size(1))
+        if ctx.needs_input_grad[1]:
+            dW = ops.linear_wgrad(dy, x)
+        return dx, dW
+
+
+def linear(x: Tensor, W: Tensor) -> Tensor:
+    return _LinearFn.apply(x, W)
+
+
+# =============================================================================== GAT layer
+class _GatLayerFn(torch.autograd.Function):
+    """All destination types of one GAT layer.  Inputs: ``cfg`` (python description), then the projection outputs
+    ``Y_T`` (one per node type, in ``cfg.types`` order), then the relation biases.  Outputs: one tensor per
+    destination type.  The backward fills ONE gradient buffer per ``Y_T`` (each column range is owned by exactly one
+    relation role, so no accumulation across relations is needed)."""
+
+    @staticmethod
+    def forward(ctx, cfg, *tensors):
+        nT = len(cfg.types)
+        Y = dict(zip(cfg.types, tensors[:nT]))
+        biases = dict(zip(cfg.bias_rels, tensors[nT:]))
+        outs, saved_rels = [], []
+        for T in cfg.dsts:
+            rels = [GatTrainRelation(Y[et[0]], Y[T], cfg.xs_off[et], cfg.as_off[et], cfg.ad_off[et], cfg.csr[et],
+                                     biases.get(et)) for et in cfg.rels if et[2] == T]
+            out = ops.gat_train_fwd(rels, Y[T].size(0), cfg.H[T], cfg.C[T], cfg.concat[T], group=cfg.group, act=cfg.act,
+                                    neg_slope=cfg.slope[T], dropout_p=cfg.dropout[T], seed=cfg.seed[T])
+            outs.append(out)
+            saved_rels.append(rels)
+        ctx.cfg, ctx.saved_rels, ctx.Y = cfg, saved_rels, Y
+        ctx.save_for_backward(*outs)
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *douts):
+        cfg, Y = ctx.cfg, ctx.Y
+        outs = ctx.saved_tensors
+        dY = {T: torch.zeros_like(y) for T, y in Y.items()}
+        dbias: Dict[str, Tensor] = {}
+        for T, rels, out, dout in zip(cfg.dsts, ctx.saved_rels, outs, douts):
+            has_bias = any(r.bias is not None for r in rels)
+            db = torch.zeros(out.size(1), dtype=torch.float32, device=out.device) if has_bias else None
+            dbias[T] = db
+            dys = [(dY[et[0]], dY[T]) for et in cfg.rels if et[2] == T]
+            ops.gat_train_bwd(rels, dys, out.size(0), cfg.H[T], cfg.C[T], cfg.concat[T], out, dout.contiguous(),
+                              group=cfg.group, act=cfg.act, neg_slope=cfg.slope[T], dropout_p=cfg.dropout[T],
+                              seed=cfg.seed[T], dbias=db)
+        grads: List[Optional[Tensor]] = [None]
+        grads += [dY[T] for T in cfg.types]
+        used = set()
+        for et in cfg.bias_rels:  # the bias gradient is the same vector for every relation of a group
+            g = dbias[et[2]]
+            grads.append(g.clone() if et[2] in used else g)
+            used.add(et[2])
+        ctx.saved_rels = ctx.Y = None
+        return tuple(grads)
+
+
+class _LayerCfg:
+    pass
+
+
+def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeType], x: Dict[str, Tensor],
+                        csr: Dict[EdgeType, CSR], *, act: str = None, group: str = "sum",
+                        edge_attr=None) -> Dict[str, Tensor]:
+    """Differentiable form of ``nn.run_gat_layer`` (same HeteroConv semantics)."""
+    from .nn import GATConv
+
+    cfg = _LayerCfg()
+    cfg.rels = list(rels)
+    cfg.types = []
+    for s, _, d in rels:
+        for t in (s, d):
+            if t not in cfg.types:
+                cfg.types.append(t)
+    cfg.dsts = list(dict.fromkeys(et[2] for et in rels))
+    cfg.xs_off, cfg.as_off, cfg.ad_off, cfg.csr = {}, {}, {}, dict(csr)
+    cfg.H, cfg.C, cfg.concat, cfg.slope, cfg.dropout, cfg.seed = {}, {}, {}, {}, {}, {}
+    cfg.group, cfg.act = group, act
+    for et in rels:
+        c = convs[et]
+        if c.lin_edge is not None and edge_attr is not None and edge_attr.get(et) is not None:
+            raise NotImplementedError("training with edge attributes (GAT_edge) is not implemented")
+        T = et[2]
+        sig = (c.heads, c.out_channels, c.concat, c.negative_slope, c.dropout if c.training else 0.0)
+        if T in cfg.H and (cfg.H[T], cfg.C[T], cfg.concat[T], cfg.slope[T], cfg.dropout[T]) != sig:
+            raise NotImplementedError("relations targeting one node type must share heads/channels/concat/dropout")
+        cfg.H[T], cfg.C[T], cfg.concat[T], cfg.slope[T], cfg.dropout[T] = sig
+    for T in cfg.dsts:  # host-side draw from torch's CPU generator (torch.manual_seed makes a run repeatable)
+        cfg.seed[T] = int(torch.randint(0, 2 ** 62, (1,)).item()) if cfg.dropout[T] > 0 else 0
+
+    # per node type: [lin_src blocks of the relations leaving it | folded att_src rows | folded att_dst rows]
+    Y: Dict[str, Tensor] = {}
+    for T in cfg.types:
+        blocks, col = [], 0
+        for et in rels:
+            if et[0] != T:
+                continue
+            c = convs[et]
+            W = c.lin_src.weight
+            rows = c.heads * c.out_channels
+            blocks.append(W)
+            if _pad4(rows) != rows:
+                blocks.append(W.new_zeros(_pad4(rows) - rows, W.size(1)))
+            cfg.xs_off[et] = col
+            col += _pad4(rows)
+        for et in rels:
+            if et[0] != T:
+                continue
+            c = convs[et]
+            blocks.append(GATConv.fold(c.att_src, c.lin_src.weight, c.heads, c.out_channels))
+            cfg.as_off[et] = col
+            col += c.heads
+        for et in rels:
+            if et[2] != T:
+                continue
+            c = convs[et]
+            Wd = c.lin_src.weight if et[0] == et[2] else c.lin_dst.weight
+            blocks.append(GATConv.fold(c.att_dst, Wd, c.heads, c.out_channels))
+            cfg.ad_off[et] = col
+            col += c.heads
+        if _pad4(col) != col:
+            blocks.append(blocks[0].new_zeros(_pad4(col) - col, x[T].size(1)))
+        Y[T] = linear(x[T], torch.cat(blocks, dim=0))
+
+    cfg.bias_rels = [et for et in rels if convs[et].bias is not None]
+    outs = _GatLayerFn.apply(cfg, *[Y[T] for T in cfg.types], *[convs[et].bias for et in cfg.bias_rels])
+    return dict(zip(cfg.dsts, outs))
+
+
+# =============================================================================== optimizer
+class FlatAdam:
+    """``torch.optim.Adam(params, lr, weight_decay=...)`` (base_training_job.py:77-79) over ONE flat buffer:
+    after the first backward the live parameters (those that received a gradient -- PyG's dead ``lin_dst`` of
+    same-type relations never does, and torch's Adam skips ``grad is None``) are re-homed as views of
+    ``flat_param`` / ``flat_grad``, so a step is one ``hg_adam_step`` launch and a data-parallel gradient
+    exchange is one all-reduce of ``flat_grad``."""
+
+    def __init__(self, params, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.0):
+        seen, self.params = set(), []
+        for p in params:
+            if p.requires_grad and id(p) not in seen:
+                seen.add(id(p))
+                self.params.append(p)
+        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+        self.t = 0
+        self.flat_param = self.flat_grad = self.exp_avg = self.exp_avg_sq = None
+        self.live: List[nn.Parameter] = []
+
+    def _flatten(self):
+        self.live = [p for p in self.params if p.grad is not None]
+        if not self.live:
+            raise RuntimeError("FlatAdam.step() before any backward")
+        dev = self.live[0].device
+        n = sum(p.numel() for p in self.live)
+        self.flat_param = torch.empty(n, dtype=torch.float32, device=dev)
+        self.flat_grad = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
+        off = 0
+        with torch.no_grad():
+            for p in self.live:
+                k = p.numel()
+                self.flat_param[off:off + k].copy_(p.reshape(-1))
+                self.flat_grad[off:off + k].copy_(p.grad.reshape(-1))
+                p.data = self.flat_param[off:off + k].view(p.shape)
+                p.grad = self.flat_grad[off:off + k].view(p.shape)
+                off += k
+
+    def zero_grad(self):
+        if self.flat_grad is None:
+            for p in self.params:
+                p.grad = None
+        else:
+            self.flat_grad.zero_()
+
+    def step(self, grad_scale: float = 1.0):
+        if self.flat_param is None:
+            self._flatten()
+        self.t += 1
+        ops.adam_step(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.t, self.lr, self.betas[0],
+                      self.betas[1], self.eps, self.weight_decay, grad_scale)

@@ -65,7 +65,8 @@ HG_API int hg_abi_version(void);
 HG_API int hg_last_cuda_error(void);
 /* 0 if no usable device / kernel image for it; otherwise SM count of the current device */
 HG_API int hg_device_sm_count(void);
-/* sizeof of ABI struct #which (0 plan_rel, 1 seg_args, 2 gat_rel, 3 gat_args, 4 lin_seg, 5 linear_args) */
+/* sizeof of ABI struct #which (0 plan_rel, 1 seg_args, 2 gat_rel, 3 gat_args, 4 lin_seg, 5 linear_args,
+ * 6 gat_train_rel, 7 gat_train_args) */
 HG_API int hg_sizeof(int which);
 
 /* ------------------------------------------------------------------------------------
@@ -256,6 +257,89 @@ HG_API int hg_collate_offsets(int64_t* index, int64_t n_edges, const int64_t* ed
 
 /* batch[n] = g for ptr[g] <= n < ptr[g+1]: the `batch` vector of a collated node type (device int64). */
 HG_API int hg_batch_vector(int64_t* batch, int64_t n_nodes, const int64_t* ptr, int32_t n_graphs, void* stream);
+
+/* ====================================================================================
+ * Training step (BASELINE.json configs[4]; reference: base_training_job.py:203-219 --
+ * `loss.backward()` through the PyG layers, then `optimizer.step()` of torch.optim.Adam).
+ * The entry points below are the backward mirrors of K3/K4 and K6 plus the optimizer update.
+ * ==================================================================================== */
+
+/* ------------------------------------------------------------------------------------
+ * hg_gat_train_fwd / hg_gat_train_bwd -- GAT aggregation of every relation targeting ONE
+ * destination type, training form: same arithmetic as hg_gat_fused (project-first), plus
+ * attention dropout (GATConv(dropout=p): F.dropout on the softmax weights, models/utils.py:49-86)
+ * and the softmax weights saved for the backward.
+ *
+ *   forward :  w_e,h (softmax, saved in alpha)  ->  w'_e,h = w_e,h * keep(seed, r, e, h) / (1 - p)
+ *              out[i] = act( group_r ( concat_h|mean_h sum_e w'_e,h xs[col[e], h, :] + bias_r ) )
+ *   backward:  g[i]   = dout[i] * act'(out[i]) * (group == MEAN ? 1 / n_rel : 1)        (pass 1, by destination)
+ *              dbias += sum_i g[i]                      (same vector for every relation of the group)
+ *              dw'_e,h = <g_h[i], xs[col[e], h, :]>;  dw = dw' * keep / (1 - p)
+ *              ds_e,h = w_e,h (dw_e,h - sum_e' w_e',h dw_e',h) * leaky'(raw score)       -> dlogit[e, h]
+ *              da_dst[i, h] = sum_e ds_e,h
+ *              dxs[j, h, :] = sum_{e: col[e] = j} w'_e,h g_h[dst(e)]                      (pass 2, by source, over the
+ *              da_src[j, h] = sum_{e: col[e] = j} ds_e,h                                  transposed CSR; no atomics)
+ * keep() is a counter-based hash of (seed, relation slot, CSR position, head): the backward regenerates it.
+ * Every output column is written exactly once (plain stores).
+ * ---------------------------------------------------------------------------------- */
+typedef struct hg_gat_train_rel {
+    const float* xs;    int64_t ldxs;    /* [n_src, H*C] */
+    const float* a_src; int64_t lda_src; /* [n_src, H] */
+    const float* a_dst; int64_t lda_dst; /* [n_dst, H] */
+    const int32_t* rowptr; const int32_t* col; /* CSR by destination */
+    const float* bias;                   /* NULL | [out width] (forward only) */
+    float* alpha;                        /* [E', H]: written by fwd (before dropout), read by bwd */
+    /* ---- backward only ---- */
+    float* dlogit;                       /* [E', H] scratch: written by pass 1, read by pass 2 */
+    const int32_t* rowptr_t; const int32_t* col_t; /* CSR of the reversed relation (rows = sources, col = destination) */
+    const int32_t* pos_t;                /* [E'] position in the forward CSR of every entry of the reversed one */
+    float* dxs;    int64_t lddxs;        /* [n_src, H*C] */
+    float* da_src; int64_t ldda_src;     /* [n_src, H] */
+    float* da_dst; int64_t ldda_dst;     /* [n_dst, H] */
+    int32_t n_src; int32_t reserved;
+} hg_gat_train_rel;
+
+typedef struct hg_gat_train_args {
+    hg_gat_train_rel rel[HG_MAX_RELATIONS];
+    int32_t n_rel; int32_t n_dst;
+    int32_t H; int32_t C;
+    int32_t concat; int32_t group; int32_t act; float neg_slope;
+    float dropout_p; int32_t reserved;
+    uint64_t seed;
+    float* out; int64_t ldout;           /* fwd: written; bwd: read (activation derivative) */
+    const float* dout; int64_t lddout;   /* bwd: gradient w.r.t. out */
+    float* g; int64_t ldg;               /* bwd scratch [n_dst, out width] */
+    float* dbias;                        /* bwd: NULL | [out width], accumulated with atomics (caller zeroes) */
+} hg_gat_train_args;
+
+HG_API int hg_gat_train_fwd(const hg_gat_train_args* args_host, void* stream);
+HG_API int hg_gat_train_bwd(const hg_gat_train_args* args_host, void* stream);
+
+/* pos_t[q] = position in the forward CSR (perm / col, E' = *n_live entries) of entry q of the reversed CSR
+ * (perm_t / col_t, *n_live_t entries); both built by hg_plan_build from the same edge list with the same
+ * self_loops flag and perm requested.  scratch: int32 [n_edges + n_loop_nodes]. */
+HG_API int hg_csr_transpose_map(const int32_t* perm, const int32_t* col, const int32_t* n_live, int64_t cap,
+                                const int32_t* perm_t, const int32_t* col_t, const int32_t* n_live_t,
+                                int64_t n_edges, int32_t n_loop_nodes, int32_t* scratch, int32_t* pos_t, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * hg_linear_wgrad -- weight gradient of K6:  dW[N, K] (+)= dY[M, N]^T X[M, K]  (fp32 FMA, split over M,
+ * partial tiles added with atomics; `accumulate` = 0 zeroes dW first).  The input gradient dX = dY W is
+ * hg_linear with the transposed weight.  Replaces the autograd of torch.nn.Linear (cuBLAS SGEMM).
+ * ---------------------------------------------------------------------------------- */
+HG_API int hg_linear_wgrad(const float* dy, int64_t lddy, const float* x, int64_t ldx, int32_t M, int32_t N, int32_t K,
+                           float* dw, int64_t lddw, int32_t accumulate, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * hg_adam_step -- torch.optim.Adam (base_training_job.py:77-79: lr, weight_decay; betas (0.9, 0.999),
+ * eps 1e-8, amsgrad off) over ONE flat parameter buffer:
+ *   g = grad * grad_scale + weight_decay * p;  m = b1 m + (1-b1) g;  v = b2 v + (1-b2) g^2
+ *   p -= lr / (1 - b1^t) * m / (sqrt(v) / sqrt(1 - b2^t) + eps)
+ * `step` (t >= 1) is a host value.  grad_scale folds the 1 / world_size of a gradient all-reduce.
+ * ---------------------------------------------------------------------------------- */
+HG_API int hg_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                        float beta1, float beta2, float eps, float weight_decay, float grad_scale, int32_t step,
+                        void* stream);
 
 #ifdef __cplusplus
 }
