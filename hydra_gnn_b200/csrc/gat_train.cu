@@ -24,6 +24,15 @@ __device__ __forceinline__ float keep_scale(uint64_t seed, int r, int64_t idx, f
     return u >= p ? inv_keep : 0.f;
 }
 
+// The forward stores the softmax weight with the dropout decision in its sign bit (weights are >= 0): the hash is
+// evaluated once per (edge, head), by one lane; every later pass reads |alpha| and the sign.
+__device__ __forceinline__ float kept(float a_signed, float inv_keep) {
+    return (__float_as_uint(a_signed) >> 31) ? 0.f : a_signed * inv_keep;
+}
+__device__ __forceinline__ float keepf(float a_signed, float inv_keep) {
+    return (__float_as_uint(a_signed) >> 31) ? 0.f : inv_keep;
+}
+
 __device__ __forceinline__ float sel(const float (&v)[kMaxH], int h) {
     return h == 0 ? v[0] : (h == 1 ? v[1] : (h == 2 ? v[2] : v[3]));
 }
@@ -80,8 +89,12 @@ __global__ void __launch_bounds__(kThreads) k_fwd(const __grid_constant__ hg_gat
                 const float* as = R.a_src + static_cast<int64_t>(__ldg(R.col + p)) * R.lda_src;
 #pragma unroll
                 for (int h = 0; h < kMaxH; ++h)
-                    if (h < H)
-                        R.alpha[static_cast<int64_t>(p) * H + h] = expf(leaky(__ldg(as + h) + ad[h], slope) - m[h]) / sum[h];
+                    if (h < H) {
+                        const int64_t idx = static_cast<int64_t>(p) * H + h;
+                        float a = expf(leaky(__ldg(as + h) + ad[h], slope) - m[h]) / sum[h];
+                        if (drop && keep_scale(A.seed, r, idx, p_drop, inv_keep) == 0.f) a = -a;
+                        R.alpha[idx] = a;
+                    }
             }
             __syncwarp();
             for (int p = beg; p < end; ++p) {
@@ -92,7 +105,7 @@ __global__ void __launch_bounds__(kThreads) k_fwd(const __grid_constant__ hg_gat
                     wv[h] = 0.f;
                     if (h < H) {
                         const int64_t idx = static_cast<int64_t>(p) * H + h;
-                        wv[h] = R.alpha[idx] * (drop ? keep_scale(A.seed, r, idx, p_drop, inv_keep) : 1.f);
+                        wv[h] = kept(R.alpha[idx], inv_keep);
                     }
                 }
                 const float* xr = R.xs + static_cast<int64_t>(j) * R.ldxs;
@@ -195,8 +208,9 @@ __global__ void __launch_bounds__(kThreads) k_bwd_dst(const __grid_constant__ hg
                     if (h < H) {
                         const int64_t idx = static_cast<int64_t>(p) * H + h;
                         float da = warp_sum(part[h]);
-                        if (drop) da *= keep_scale(A.seed, r, idx, p_drop, inv_keep);
-                        t[h] = fmaf(R.alpha[idx], da, t[h]);
+                        const float a = R.alpha[idx];
+                        da *= keepf(a, inv_keep);
+                        t[h] = fmaf(fabsf(a), da, t[h]);
                         if (lane == 0) R.dlogit[idx] = da;
                     }
                 }
@@ -208,7 +222,7 @@ __global__ void __launch_bounds__(kThreads) k_bwd_dst(const __grid_constant__ hg
                 for (int h = 0; h < kMaxH; ++h) {
                     if (h < H) {
                         const int64_t idx = static_cast<int64_t>(p) * H + h;
-                        float ds = R.alpha[idx] * (R.dlogit[idx] - t[h]);
+                        float ds = fabsf(R.alpha[idx]) * (R.dlogit[idx] - t[h]);
                         ds *= (__ldg(as + h) + ad[h]) > 0.f ? 1.f : slope;
                         R.dlogit[idx] = ds;
                         dad[h] += ds;
@@ -267,7 +281,7 @@ __global__ void __launch_bounds__(kThreads) k_bwd_src(const __grid_constant__ hg
                 wv[h] = 0.f;
                 if (h < H) {
                     const int64_t idx = static_cast<int64_t>(p) * H + h;
-                    wv[h] = R.alpha[idx] * (drop ? keep_scale(A.seed, r, idx, p_drop, inv_keep) : 1.f) * invH;
+                    wv[h] = kept(R.alpha[idx], inv_keep) * invH;
                     das[h] += R.dlogit[idx];
                 }
             }
@@ -282,6 +296,459 @@ __global__ void __launch_bounds__(kThreads) k_bwd_src(const __grid_constant__ hg
             if (lane + 32 * k < HC) dx[lane + 32 * k] = acc[k];
         if (lane < H) R.da_src[static_cast<int64_t>(j) * R.ldda_src + lane] = sel(das, lane);
     }
+}
+
+
+// ------------------------------------------------------------------------------------------------------------------
+// Fast path (C % 4 == 0, 16-byte aligned rows): a half-warp per row, lanes own the float4 columns v = l + 16 k of the
+// H*C-wide row (k < NV), two rows per warp, two edges in flight per half-warp.  HK: C == 64, so the head of column
+// group k is k (no select chains).
+__device__ __forceinline__ float half_sum(float v, unsigned hm) {
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(hm, v, o);
+    return v;
+}
+__device__ __forceinline__ float half_max(float v, unsigned hm) {
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(hm, v, o));
+    return v;
+}
+__device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ void fma4(float4& a, float w, const float4& x) {
+    a.x = fmaf(w, x.x, a.x); a.y = fmaf(w, x.y, a.y); a.z = fmaf(w, x.z, a.z); a.w = fmaf(w, x.w, a.w);
+}
+__device__ __forceinline__ float dot4(const float4& a, const float4& b) {
+    return fmaf(a.x, b.x, fmaf(a.y, b.y, fmaf(a.z, b.z, a.w * b.w)));
+}
+
+template <int NV, bool HK>
+__global__ void __launch_bounds__(kThreads) k_fwd_v4(const __grid_constant__ hg_gat_train_args A) {
+    __shared__ __align__(16) float s_acc[kWarps][2][NV * 64];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, sub = lane >> 4, l = lane & 15;
+    const unsigned hm = sub ? 0xffff0000u : 0x0000ffffu;
+    const int H = A.H, C = A.C, HC4 = H * C / 4;
+    const int width = A.concat ? H * C : C;
+    const float slope = A.neg_slope, p_drop = A.dropout_p;
+    const bool drop = p_drop > 0.f;
+    const float inv_keep = drop ? 1.f / (1.f - p_drop) : 1.f;
+    int hk[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) hk[k] = HK ? k : ((l + 16 * k) < HC4 ? 4 * (l + 16 * k) / C : 0);
+    for (int i = (blockIdx.x * kWarps + w) * 2 + sub; i < A.n_dst; i += gridDim.x * kWarps * 2) {
+        float4 acc[NV];
+#pragma unroll
+        for (int k = 0; k < NV; ++k) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int r = 0; r < A.n_rel; ++r) {
+            const hg_gat_train_rel& R = A.rel[r];
+            const int beg = R.rowptr[i], end = R.rowptr[i + 1];
+            if (beg == end) continue;
+            float ad[kMaxH];
+#pragma unroll
+            for (int h = 0; h < kMaxH; ++h)
+                ad[h] = h < H ? __ldg(R.a_dst + static_cast<int64_t>(i) * R.lda_dst + h) : 0.f;
+            if (end - beg <= 16) {
+                // every lane owns at most one edge: logits, softmax and the dropout decision stay in registers,
+                // the gather takes (source id, weights) of edge t from lane t by shuffle
+                const int deg = end - beg, p = beg + l;
+                const bool mine = l < deg;
+                const int j = mine ? __ldg(R.col + p) : 0;
+                float sc[kMaxH], wv[kMaxH];
+#pragma unroll
+                for (int h = 0; h < kMaxH; ++h) {
+                    sc[h] = (mine && h < H) ? leaky(__ldg(R.a_src + static_cast<int64_t>(j) * R.lda_src + h) + ad[h], slope)
+                                            : -INFINITY;
+                    const float mx = half_max(sc[h], hm);
+                    const float e = (mine && h < H) ? expf(sc[h] - mx) : 0.f;
+                    const float sm = half_sum(e, hm) + 1e-16f;
+                    wv[h] = 0.f;
+                    if (mine && h < H) {
+                        const int64_t idx = static_cast<int64_t>(p) * H + h;
+                        float a = e / sm;
+                        if (drop && keep_scale(A.seed, r, idx, p_drop, inv_keep) == 0.f) a = -a;
+                        R.alpha[idx] = a;
+                        wv[h] = kept(a, inv_keep);
+                    }
+                }
+                for (int t = 0; t < deg; t += 2) {
+                    const int j0 = __shfl_sync(hm, j, t, 16), j1 = __shfl_sync(hm, j, t + 1 < deg ? t + 1 : t, 16);
+                    float w0[kMaxH], w1[kMaxH];
+#pragma unroll
+                    for (int h = 0; h < kMaxH; ++h) {
+                        w0[h] = __shfl_sync(hm, wv[h], t, 16);
+                        w1[h] = __shfl_sync(hm, wv[h], t + 1 < deg ? t + 1 : t, 16);
+                        if (t + 1 >= deg) w1[h] = 0.f;
+                    }
+                    const float* x0 = R.xs + static_cast<int64_t>(j0) * R.ldxs + 4 * l;
+                    const float* x1 = R.xs + static_cast<int64_t>(j1) * R.ldxs + 4 * l;
+                    float4 v0[NV], v1[NV];
+#pragma unroll
+                    for (int k = 0; k < NV; ++k) {
+                        const bool ok = HK || (l + 16 * k) < HC4;
+                        v0[k] = ok ? ldg4(x0 + 64 * k) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        v1[k] = ok ? ldg4(x1 + 64 * k) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+#pragma unroll
+                    for (int k = 0; k < NV; ++k) {
+                        fma4(acc[k], sel(w0, hk[k]), v0[k]);
+                        fma4(acc[k], sel(w1, hk[k]), v1[k]);
+                    }
+                }
+                continue;
+            }
+            float m[kMaxH], sum[kMaxH];
+#pragma unroll
+            for (int h = 0; h < kMaxH; ++h) {
+                m[h] = -INFINITY;
+                sum[h] = 0.f;
+            }
+            for (int p = beg + l; p < end; p += 16) {
+                const float* as = R.a_src + static_cast<int64_t>(__ldg(R.col + p)) * R.lda_src;
+#pragma unroll
+                for (int h = 0; h < kMaxH; ++h)
+                    if (h < H) m[h] = fmaxf(m[h], leaky(__ldg(as + h) + ad[h], slope));
+            }
+#pragma unroll
+            for (int h = 0; h < kMaxH; ++h) m[h] = half_max(m[h], hm);
+            for (int p = beg + l; p < end; p += 16) {
+                const float* as = R.a_src + static_cast<int64_t>(__ldg(R.col + p)) * R.lda_src;
+#pragma unroll
+                for (int h = 0; h < kMaxH; ++h)
+                    if (h < H) sum[h] += expf(leaky(__ldg(as + h) + ad[h], slope) - m[h]);
+            }
+#pragma unroll
+            for (int h = 0; h < kMaxH; ++h) sum[h] = half_sum(sum[h], hm) + 1e-16f;
+            for (int p = beg + l; p < end; p += 16) {
+                const float* as = R.a_src + static_cast<int64_t>(__ldg(R.col + p)) * R.lda_src;
+#pragma unroll
+                for (int h = 0; h < kMaxH; ++h)
+                    if (h < H) {
+                        const int64_t idx = static_cast<int64_t>(p) * H + h;
+                        float a = expf(leaky(__ldg(as + h) + ad[h], slope) - m[h]) / sum[h];
+                        if (drop && keep_scale(A.seed, r, idx, p_drop, inv_keep) == 0.f) a = -a;
+                        R.alpha[idx] = a;
+                    }
+            }
+            __syncwarp(hm);
+            for (int p = beg; p < end; p += 2) {
+                const bool two = p + 1 < end;
+                const int j0 = __ldg(R.col + p), j1 = two ? __ldg(R.col + p + 1) : j0;
+                float w0[kMaxH], w1[kMaxH];
+#pragma unroll
+                for (int h = 0; h < kMaxH; ++h) {
+                    w0[h] = w1[h] = 0.f;
+                    if (h < H) {
+                        const int64_t idx = static_cast<int64_t>(p) * H + h;
+                        w0[h] = kept(R.alpha[idx], inv_keep);
+                        if (two) w1[h] = kept(R.alpha[idx + H], inv_keep);
+                    }
+                }
+                const float* x0 = R.xs + static_cast<int64_t>(j0) * R.ldxs + 4 * l;
+                const float* x1 = R.xs + static_cast<int64_t>(j1) * R.ldxs + 4 * l;
+                float4 v0[NV], v1[NV];
+#pragma unroll
+                for (int k = 0; k < NV; ++k) {
+                    const bool ok = HK || (l + 16 * k) < HC4;
+                    v0[k] = ok ? ldg4(x0 + 64 * k) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    v1[k] = ok ? ldg4(x1 + 64 * k) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int k = 0; k < NV; ++k) {
+                    fma4(acc[k], sel(w0, hk[k]), v0[k]);
+                    fma4(acc[k], sel(w1, hk[k]), v1[k]);
+                }
+            }
+        }
+        float* sa = s_acc[w][sub];
+#pragma unroll
+        for (int k = 0; k < NV; ++k) *reinterpret_cast<float4*>(sa + 4 * (l + 16 * k)) = acc[k];
+        __syncwarp(hm);
+        for (int c = l; c < width; c += 16) {
+            float v;
+            if (A.concat) {
+                v = sa[c];
+            } else {
+                v = 0.f;
+                for (int h = 0; h < H; ++h) v += sa[h * C + c];
+                v /= static_cast<float>(H);
+            }
+            for (int r = 0; r < A.n_rel; ++r)
+                if (A.rel[r].bias) v += __ldg(A.rel[r].bias + c);
+            if (A.group == HG_GROUP_MEAN) v /= static_cast<float>(A.n_rel);
+            A.out[static_cast<int64_t>(i) * A.ldout + c] = apply_act(v, A.act);
+        }
+        __syncwarp(hm);
+    }
+}
+
+template <int NV, bool HK>
+__global__ void __launch_bounds__(kThreads) k_bwd_dst_v4(const __grid_constant__ hg_gat_train_args A) {
+    __shared__ __align__(16) float s_g[kWarps][2][NV * 64];
+    __shared__ float s_db[NV * 64];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, sub = lane >> 4, l = lane & 15;
+    const unsigned hm = sub ? 0xffff0000u : 0x0000ffffu;
+    const int H = A.H, C = A.C, HC4 = H * C / 4, C4 = C / 4;
+    const int width = A.concat ? H * C : C;
+    const float slope = A.neg_slope, p_drop = A.dropout_p;
+    const bool drop = p_drop > 0.f;
+    const float inv_keep = drop ? 1.f / (1.f - p_drop) : 1.f;
+    const float gscale = A.group == HG_GROUP_MEAN ? 1.f / static_cast<float>(A.n_rel) : 1.f;
+    const float invH = A.concat ? 1.f : 1.f / static_cast<float>(H);
+    for (int c = threadIdx.x; c < NV * 64; c += kThreads) s_db[c] = 0.f;
+    __syncthreads();
+    int hk[NV], gv[NV];  // head of column group k; float4 column of g it multiplies
+    float db[NV * 4];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        const int v = l + 16 * k;
+        hk[k] = HK ? k : (v < HC4 ? 4 * v / C : 0);
+        gv[k] = A.concat ? v : v - hk[k] * C4;
+    }
+#pragma unroll
+    for (int t = 0; t < NV * 4; ++t) db[t] = 0.f;
+    for (int i = (blockIdx.x * kWarps + w) * 2 + sub; i < A.n_dst; i += gridDim.x * kWarps * 2) {
+        float* sg = s_g[w][sub];
+#pragma unroll
+        for (int t = 0; t < NV * 4; ++t) {
+            const int c = l + 16 * t;
+            if (c < width) {
+                const float o = A.out[static_cast<int64_t>(i) * A.ldout + c];
+                float d = __ldg(A.dout + static_cast<int64_t>(i) * A.lddout + c);
+                if (A.act == HG_ACT_ELU) d *= o > 0.f ? 1.f : o + 1.f;
+                else if (A.act == HG_ACT_RELU) d = o > 0.f ? d : 0.f;
+                d *= gscale;
+                A.g[static_cast<int64_t>(i) * A.ldg + c] = d;
+                sg[c] = d;
+                db[t] += d;
+            }
+        }
+        __syncwarp(hm);
+        float4 gh[NV];
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            gh[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (HK || (l + 16 * k) < HC4) {
+                const float4 t4 = *reinterpret_cast<const float4*>(sg + 4 * gv[k]);
+                gh[k] = make_float4(t4.x * invH, t4.y * invH, t4.z * invH, t4.w * invH);
+            }
+        }
+        for (int r = 0; r < A.n_rel; ++r) {
+            const hg_gat_train_rel& R = A.rel[r];
+            const int beg = R.rowptr[i], end = R.rowptr[i + 1];
+            float ad[kMaxH], t[kMaxH], dad[kMaxH];
+#pragma unroll
+            for (int h = 0; h < kMaxH; ++h) {
+                ad[h] = h < H ? __ldg(R.a_dst + static_cast<int64_t>(i) * R.lda_dst + h) : 0.f;
+                t[h] = 0.f;
+                dad[h] = 0.f;
+            }
+            if (end - beg <= 16) {
+                // lane t owns edge t: its softmax weight, dropout decision and d(weight) stay in registers
+                const int deg = end - beg, p = beg + l;
+                const bool mine = l < deg;
+                const int j = mine ? __ldg(R.col + p) : 0;
+                float myda[kMaxH] = {0.f, 0.f, 0.f, 0.f};
+                for (int e = 0; e < deg; e += 2) {
+                    const bool two = e + 1 < deg;
+                    const int j0 = __shfl_sync(hm, j, e, 16), j1 = __shfl_sync(hm, j, two ? e + 1 : e, 16);
+                    const float* x0 = R.xs + static_cast<int64_t>(j0) * R.ldxs + 4 * l;
+                    const float* x1 = R.xs + static_cast<int64_t>(j1) * R.ldxs + 4 * l;
+                    float p0[kMaxH] = {0.f, 0.f, 0.f, 0.f}, p1[kMaxH] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int k = 0; k < NV; ++k) {
+                        if (HK || (l + 16 * k) < HC4) {
+                            const float d0 = dot4(gh[k], ldg4(x0 + 64 * k)), d1 = dot4(gh[k], ldg4(x1 + 64 * k));
+                            if (HK) {
+                                p0[k < kMaxH ? k : 0] += d0;
+                                p1[k < kMaxH ? k : 0] += d1;
+                            } else {
+#pragma unroll
+                                for (int h = 0; h < kMaxH; ++h) {
+                                    p0[h] += hk[k] == h ? d0 : 0.f;
+                                    p1[h] += hk[k] == h ? d1 : 0.f;
+                                }
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int h = 0; h < kMaxH; ++h) {
+                        if (h < H) {
+                            const float da0 = half_sum(p0[h], hm), da1 = half_sum(p1[h], hm);
+                            if (l == e) myda[h] = da0;
+                            if (two && l == e + 1) myda[h] = da1;
+                        }
+                    }
+                }
+#pragma unroll
+                for (int h = 0; h < kMaxH; ++h) {
+                    if (h < H) {
+                        const int64_t idx = static_cast<int64_t>(p) * H + h;
+                        const float a = mine ? R.alpha[idx] : 0.f;
+                        const float da = myda[h] * keepf(a, inv_keep);
+                        const float tt = half_sum(fabsf(a) * da, hm);
+                        float ds = 0.f;
+                        if (mine) {
+                            ds = fabsf(a) * (da - tt);
+                            ds *= (__ldg(R.a_src + static_cast<int64_t>(j) * R.lda_src + h) + ad[h]) > 0.f ? 1.f : slope;
+                            R.dlogit[idx] = ds;
+                        }
+                        const float v = half_sum(ds, hm);
+                        if (l == 0) R.da_dst[static_cast<int64_t>(i) * R.ldda_dst + h] = v;
+                    }
+                }
+                continue;
+            }
+            for (int p = beg; p < end; p += 2) {
+                const bool two = p + 1 < end;
+                const int j0 = __ldg(R.col + p), j1 = two ? __ldg(R.col + p + 1) : j0;
+                const float* x0 = R.xs + static_cast<int64_t>(j0) * R.ldxs + 4 * l;
+                const float* x1 = R.xs + static_cast<int64_t>(j1) * R.ldxs + 4 * l;
+                float p0[kMaxH] = {0.f, 0.f, 0.f, 0.f}, p1[kMaxH] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int k = 0; k < NV; ++k) {
+                    if (HK || (l + 16 * k) < HC4) {
+                        const float d0 = dot4(gh[k], ldg4(x0 + 64 * k)), d1 = dot4(gh[k], ldg4(x1 + 64 * k));
+                        if (HK) {
+                            p0[k < kMaxH ? k : 0] += d0;
+                            p1[k < kMaxH ? k : 0] += d1;
+                        } else {
+#pragma unroll
+                            for (int h = 0; h < kMaxH; ++h) {
+                                p0[h] += hk[k] == h ? d0 : 0.f;
+                                p1[h] += hk[k] == h ? d1 : 0.f;
+                            }
+                        }
+                    }
+                }
+#pragma unroll
+                for (int h = 0; h < kMaxH; ++h) {
+                    if (h < H) {
+                        const int64_t idx = static_cast<int64_t>(p) * H + h;
+                        float da0 = half_sum(p0[h], hm), da1 = half_sum(p1[h], hm);
+                        const float a0 = R.alpha[idx];
+                        da0 *= keepf(a0, inv_keep);
+                        t[h] = fmaf(fabsf(a0), da0, t[h]);
+                        if (l == 0) R.dlogit[idx] = da0;
+                        if (two) {
+                            const float a1 = R.alpha[idx + H];
+                            da1 *= keepf(a1, inv_keep);
+                            t[h] = fmaf(fabsf(a1), da1, t[h]);
+                            if (l == 0) R.dlogit[idx + H] = da1;
+                        }
+                    }
+                }
+            }
+            __syncwarp(hm);
+            for (int p = beg + l; p < end; p += 16) {
+                const float* as = R.a_src + static_cast<int64_t>(__ldg(R.col + p)) * R.lda_src;
+#pragma unroll
+                for (int h = 0; h < kMaxH; ++h) {
+                    if (h < H) {
+                        const int64_t idx = static_cast<int64_t>(p) * H + h;
+                        float ds = fabsf(R.alpha[idx]) * (R.dlogit[idx] - t[h]);
+                        ds *= (__ldg(as + h) + ad[h]) > 0.f ? 1.f : slope;
+                        R.dlogit[idx] = ds;
+                        dad[h] += ds;
+                    }
+                }
+            }
+#pragma unroll
+            for (int h = 0; h < kMaxH; ++h) {
+                if (h < H) {
+                    const float v = half_sum(dad[h], hm);
+                    if (l == 0) R.da_dst[static_cast<int64_t>(i) * R.ldda_dst + h] = v;
+                }
+            }
+            __syncwarp(hm);
+        }
+    }
+    if (A.dbias) {
+#pragma unroll
+        for (int t = 0; t < NV * 4; ++t)
+            if (l + 16 * t < width) atomicAdd(&s_db[l + 16 * t], db[t]);
+        __syncthreads();
+        for (int c = threadIdx.x; c < width; c += kThreads) atomicAdd(A.dbias + c, s_db[c]);
+    }
+}
+
+template <int NV, bool HK>
+__global__ void __launch_bounds__(kThreads) k_bwd_src_v4(const __grid_constant__ hg_gat_train_args A) {
+    const int r = blockIdx.y;
+    const hg_gat_train_rel& R = A.rel[r];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, sub = lane >> 4, l = lane & 15;
+    const int H = A.H, C = A.C, HC4 = H * C / 4, C4 = C / 4;
+    const float p_drop = A.dropout_p;
+    const bool drop = p_drop > 0.f;
+    const float inv_keep = drop ? 1.f / (1.f - p_drop) : 1.f;
+    const float invH = A.concat ? 1.f : 1.f / static_cast<float>(H);
+    const bool shared_g = HK && !A.concat;  // every column group reads the same float4 of g
+    int hk[NV], gv[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        const int v = l + 16 * k;
+        hk[k] = HK ? k : (v < HC4 ? 4 * v / C : 0);
+        gv[k] = A.concat ? v : v - hk[k] * C4;
+    }
+    for (int j = (blockIdx.x * kWarps + w) * 2 + sub; j < R.n_src; j += gridDim.x * kWarps * 2) {
+        float4 acc[NV];
+#pragma unroll
+        for (int k = 0; k < NV; ++k) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        float das[kMaxH] = {0.f, 0.f, 0.f, 0.f};
+        const int beg = R.rowptr_t[j], end = R.rowptr_t[j + 1];
+        for (int q = beg; q < end; q += 2) {
+            const bool two = q + 1 < end;
+            const int i0 = __ldg(R.col_t + q), i1 = two ? __ldg(R.col_t + q + 1) : i0;
+            const int p0 = __ldg(R.pos_t + q), p1 = two ? __ldg(R.pos_t + q + 1) : p0;
+            float w0[kMaxH], w1[kMaxH];
+#pragma unroll
+            for (int h = 0; h < kMaxH; ++h) {
+                w0[h] = w1[h] = 0.f;
+                if (h < H) {
+                    const int64_t a0 = static_cast<int64_t>(p0) * H + h, a1 = static_cast<int64_t>(p1) * H + h;
+                    w0[h] = kept(R.alpha[a0], inv_keep) * invH;
+                    das[h] += R.dlogit[a0];
+                    if (two) {
+                        w1[h] = kept(R.alpha[a1], inv_keep) * invH;
+                        das[h] += R.dlogit[a1];
+                    }
+                }
+            }
+            const float* g0 = A.g + static_cast<int64_t>(i0) * A.ldg;
+            const float* g1 = A.g + static_cast<int64_t>(i1) * A.ldg;
+            if (shared_g) {
+                const float4 u0 = ldg4(g0 + 4 * l), u1 = ldg4(g1 + 4 * l);
+#pragma unroll
+                for (int k = 0; k < NV; ++k) {
+                    fma4(acc[k], sel(w0, k), u0);
+                    fma4(acc[k], sel(w1, k), u1);
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < NV; ++k) {
+                    if (HK || (l + 16 * k) < HC4) {
+                        fma4(acc[k], sel(w0, hk[k]), ldg4(g0 + 4 * gv[k]));
+                        fma4(acc[k], sel(w1, hk[k]), ldg4(g1 + 4 * gv[k]));
+                    }
+                }
+            }
+        }
+        float* dx = R.dxs + static_cast<int64_t>(j) * R.lddxs + 4 * l;
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+            if (HK || (l + 16 * k) < HC4) *reinterpret_cast<float4*>(dx + 64 * k) = acc[k];
+        if (l < H) R.da_src[static_cast<int64_t>(j) * R.ldda_src + l] = sel(das, l);
+    }
+}
+
+bool v4_ok(const hg_gat_train_args* a, bool bwd) {
+    if (a->C % 4 != 0) return false;
+    auto al = [](const void* p, int64_t ld) { return aligned(p, 16) && ld % 4 == 0; };
+    for (int r = 0; r < a->n_rel; ++r) {
+        const hg_gat_train_rel& R = a->rel[r];
+        if (R.xs && !al(R.xs, R.ldxs)) return false;
+        if (bwd && R.dxs && !al(R.dxs, R.lddxs)) return false;
+    }
+    if (bwd && a->g && !al(a->g, a->ldg)) return false;
+    return true;
 }
 
 __global__ void k_map_a(const int32_t* __restrict__ perm, const int32_t* __restrict__ col, const int32_t* n_live,
@@ -325,6 +792,15 @@ unsigned row_grid(int64_t rows, int ctas_per_sm) {
     return static_cast<unsigned>(g < cap ? g : cap);
 }
 
+// fast path: NV = float4 column groups per lane (H*C <= 64 NV); HK when C == 64 and H == NV
+#define HG_NV_SWITCH(nv, hk, CALL)                       \
+    switch (nv) {                                        \
+        case 1: { if (hk) CALL(1, true); else CALL(1, false); break; } \
+        case 2: { if (hk) CALL(2, true); else CALL(2, false); break; } \
+        case 3: { if (hk) CALL(3, true); else CALL(3, false); break; } \
+        default: { if (hk) CALL(4, true); else CALL(4, false); break; } \
+    }
+
 #define HG_NE_SWITCH(ne, CALL)          \
     switch (ne) {                       \
         case 1: { CALL(1); break; }     \
@@ -345,6 +821,15 @@ extern "C" int hg_gat_train_fwd(const hg_gat_train_args* a, void* stream_) {
     if (a->n_dst == 0) return HG_OK;
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const int ne = ceil_div(a->H * a->C, 32);
+    if (v4_ok(a, false)) {
+        const int nv = ceil_div(a->H * a->C, 64);
+        const bool hk = a->C == 64 && a->H == nv;
+        const unsigned grid = row_grid(ceil_div(a->n_dst, 2), 64);
+#define CALL4(NV, HKV) k_fwd_v4<NV, HKV><<<grid, kThreads, 0, stream>>>(*a)
+        HG_NV_SWITCH(nv, hk, CALL4)
+#undef CALL4
+        return check_launch();
+    }
     const unsigned grid = row_grid(a->n_dst, 64);
 #define CALL(NE) k_fwd<NE><<<grid, kThreads, 0, stream>>>(*a)
     HG_NE_SWITCH(ne, CALL)
@@ -358,21 +843,39 @@ extern "C" int hg_gat_train_bwd(const hg_gat_train_args* a, void* stream_) {
     if (rc != HG_OK) return rc;
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const int ne = ceil_div(a->H * a->C, 32);
+    const bool fast = v4_ok(a, true);
+    const int nv = ceil_div(a->H * a->C, 64);
+    const bool hk = a->C == 64 && a->H == nv;
     if (a->n_dst > 0) {
-        const unsigned grid = row_grid(a->n_dst, 8);  // grid-stride: the bias gradient is reduced per block
+        // grid-stride: the bias gradient is reduced per block
+        if (fast) {
+            const unsigned grid = row_grid(ceil_div(a->n_dst, 2), 8);
+#define CALL4(NV, HKV) k_bwd_dst_v4<NV, HKV><<<grid, kThreads, 0, stream>>>(*a)
+            HG_NV_SWITCH(nv, hk, CALL4)
+#undef CALL4
+        } else {
+            const unsigned grid = row_grid(a->n_dst, 8);
 #define CALL(NE) k_bwd_dst<NE><<<grid, kThreads, 0, stream>>>(*a)
-        HG_NE_SWITCH(ne, CALL)
+            HG_NE_SWITCH(ne, CALL)
 #undef CALL
+        }
         rc = check_launch();
         if (rc != HG_OK) return rc;
     }
     int32_t max_src = 0;
     for (int r = 0; r < a->n_rel; ++r) max_src = a->rel[r].n_src > max_src ? a->rel[r].n_src : max_src;
     if (max_src > 0) {
-        const dim3 grid(row_grid(max_src, 64), a->n_rel);
+        if (fast) {
+            const dim3 grid(row_grid(ceil_div(max_src, 2), 64), a->n_rel);
+#define CALL4(NV, HKV) k_bwd_src_v4<NV, HKV><<<grid, kThreads, 0, stream>>>(*a)
+            HG_NV_SWITCH(nv, hk, CALL4)
+#undef CALL4
+        } else {
+            const dim3 grid(row_grid(max_src, 64), a->n_rel);
 #define CALL(NE) k_bwd_src<NE><<<grid, kThreads, 0, stream>>>(*a)
-        HG_NE_SWITCH(ne, CALL)
+            HG_NE_SWITCH(ne, CALL)
 #undef CALL
+        }
         rc = check_launch();
     }
     return rc;

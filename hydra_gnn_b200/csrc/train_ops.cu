@@ -6,6 +6,8 @@
 // so every global load is coalesced and no transpose is materialised.
 #include "hg_common.cuh"
 
+#include <cstdlib>
+
 namespace hg {
 namespace {
 
@@ -72,6 +74,118 @@ __global__ void __launch_bounds__(kWgThreads) k_wgrad(const float* __restrict__ 
     }
 }
 
+
+// ---- tensor-pipe variant: mma.sync m16n8k8 TF32 with the 3-term split (x = hi + lo, hi = mantissa truncated to
+// 10 bits, lo = x - hi exact; products lo*hi + hi*lo + hi*hi, fp32 accumulate) -- fp32-class accuracy, the same
+// scheme as the forward projection.  Roles: mma-M = n (rows of dW), mma-N = k (columns of dW), mma-K = m (the
+// reduced row index), so A(n, m) = dY[m][n] and B(m, k) = X[m][k] are both read from the m-major tiles as loaded.
+constexpr int kMN = 64, kMK = 64, kMM = 32, kMThreads = 128, kMLd = 72;  // 72: fragment reads hit 32 distinct banks
+
+__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
+    hi = __float_as_uint(x) & 0xffffe000u;
+    lo = __float_as_uint(x - __uint_as_float(hi));
+}
+
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+template <bool VEC2>
+__global__ void __launch_bounds__(kMThreads) k_wgrad_mma(const float* __restrict__ dy, int64_t lddy,
+                                                         const float* __restrict__ x, int64_t ldx, int M, int N, int K,
+                                                         float* __restrict__ dw, int64_t lddw, int rows_per_split) {
+    __shared__ __align__(16) float sA[2][kMM][kMLd];
+    __shared__ __align__(16) float sB[2][kMM][kMLd];
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int gid = lane >> 2, tig = lane & 3;
+    const int n0 = blockIdx.x * kMN, k0 = blockIdx.y * kMK;
+    const int m_beg = blockIdx.z * rows_per_split;
+    const int m_end = min(M, m_beg + rows_per_split);
+    if (m_beg >= m_end) return;
+    const int wn = (w >> 1) * 32, wk = (w & 1) * 32;
+    const int lcol = (tid & 31) * 2, lrow = tid >> 5;  // loader: 2 columns, rows lrow + 4 i
+    float acc[2][4][4];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int t = 0; t < 4; ++t) acc[i][j][t] = 0.f;
+    float2 ra[8], rb[8];
+    const bool a0ok = n0 + lcol < N, a1ok = n0 + lcol + 1 < N;
+    const bool b0ok = k0 + lcol < K, b1ok = k0 + lcol + 1 < K;
+    auto load = [&](int m0) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int m = m0 + lrow + 4 * i;
+            const bool ok = m < m_end;
+            const float* pa = dy + static_cast<int64_t>(m) * lddy + n0 + lcol;
+            const float* pb = x + static_cast<int64_t>(m) * ldx + k0 + lcol;
+            if (VEC2) {
+                ra[i] = (ok && a1ok) ? __ldg(reinterpret_cast<const float2*>(pa))
+                                     : make_float2((ok && a0ok) ? __ldg(pa) : 0.f, 0.f);
+                rb[i] = (ok && b1ok) ? __ldg(reinterpret_cast<const float2*>(pb))
+                                     : make_float2((ok && b0ok) ? __ldg(pb) : 0.f, 0.f);
+            } else {
+                ra[i] = make_float2((ok && a0ok) ? __ldg(pa) : 0.f, (ok && a1ok) ? __ldg(pa + 1) : 0.f);
+                rb[i] = make_float2((ok && b0ok) ? __ldg(pb) : 0.f, (ok && b1ok) ? __ldg(pb + 1) : 0.f);
+            }
+        }
+    };
+    load(m_beg);
+    int buf = 0;
+    for (int m0 = m_beg; m0 < m_end; m0 += kMM) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            *reinterpret_cast<float2*>(&sA[buf][lrow + 4 * i][lcol]) = ra[i];
+            *reinterpret_cast<float2*>(&sB[buf][lrow + 4 * i][lcol]) = rb[i];
+        }
+        __syncthreads();
+        if (m0 + kMM < m_end) load(m0 + kMM);
+#pragma unroll
+        for (int ks = 0; ks < kMM / 8; ++ks) {
+            const int r0 = ks * 8 + tig, r1 = r0 + 4;
+            uint32_t ah[2][4], al[2][4], bh[4][2], bl[4][2];
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int c = wn + i * 16 + gid;
+                split_tf32(sA[buf][r0][c], ah[i][0], al[i][0]);
+                split_tf32(sA[buf][r0][c + 8], ah[i][1], al[i][1]);
+                split_tf32(sA[buf][r1][c], ah[i][2], al[i][2]);
+                split_tf32(sA[buf][r1][c + 8], ah[i][3], al[i][3]);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int c = wk + j * 8 + gid;
+                split_tf32(sB[buf][r0][c], bh[j][0], bl[j][0]);
+                split_tf32(sB[buf][r1][c], bh[j][1], bl[j][1]);
+            }
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    mma_tf32(acc[i][j], al[i], bh[j]);
+                    mma_tf32(acc[i][j], ah[i], bl[j]);
+                    mma_tf32(acc[i][j], ah[i], bh[j]);
+                }
+        }
+        buf ^= 1;
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const int n = n0 + wn + i * 16 + gid + (t >> 1) * 8;
+                const int k = k0 + wk + j * 8 + 2 * tig + (t & 1);
+                if (n < N && k < K) atomicAdd(dw + static_cast<int64_t>(n) * lddw + k, acc[i][j][t]);
+            }
+}
+
 __global__ void k_zero_rows(float* __restrict__ p, int64_t ld, int N, int K) {
     const int64_t total = static_cast<int64_t>(N) * K;
     for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total;
@@ -111,14 +225,30 @@ extern "C" int hg_linear_wgrad(const float* dy, int64_t lddy, const float* x, in
         k_zero_rows<<<static_cast<unsigned>(g < sms * 8 ? g : sms * 8), 256, 0, stream>>>(dw, lddw, N, K);
     }
     if (M > 0) {
-        const int tn = ceil_div(N, kTN), tk = ceil_div(K, kTK);
-        int splits = ceil_div(sms * 4, tn * tk);
-        const int max_splits = ceil_div(M, 4 * kTM);
+        static const bool use_fma = getenv("HG_WGRAD_FMA") != nullptr;  // A/B: the CUDA-core variant
+        const int tn = ceil_div(N, kMN), tk = ceil_div(K, kMK);
+        // one wave: as many row splits as fit the resident CTA slots (a 2nd, nearly empty wave doubles the time)
+        static thread_local int occ_mma = 0, occ_fma = 0;
+        if (!occ_mma) {
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_mma, k_wgrad_mma<true>, kMThreads, 0);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_fma, k_wgrad, kWgThreads, 0);
+            occ_mma = occ_mma > 0 ? occ_mma : 1;
+            occ_fma = occ_fma > 0 ? occ_fma : 1;
+        }
+        int splits = sms * (use_fma ? occ_fma : occ_mma) / (tn * tk);
+        const int max_splits = ceil_div(M, 4 * kMM);
         splits = splits < 1 ? 1 : (splits > max_splits ? max_splits : splits);
         int rows = ceil_div(M, splits);
-        rows = ceil_div(rows, kTM) * kTM;
+        rows = ceil_div(rows, kMM) * kMM;
         splits = ceil_div(M, rows);
-        k_wgrad<<<dim3(tn, tk, splits), kWgThreads, 0, stream>>>(dy, lddy, x, ldx, M, N, K, dw, lddw, rows);
+        const dim3 grid(tn, tk, splits);
+        if (use_fma) {
+            k_wgrad<<<grid, kWgThreads, 0, stream>>>(dy, lddy, x, ldx, M, N, K, dw, lddw, rows);
+        } else if (lddy % 2 == 0 && ldx % 2 == 0 && aligned(dy, 8) && aligned(x, 8)) {
+            k_wgrad_mma<true><<<grid, kMThreads, 0, stream>>>(dy, lddy, x, ldx, M, N, K, dw, lddw, rows);
+        } else {
+            k_wgrad_mma<false><<<grid, kMThreads, 0, stream>>>(dy, lddy, x, ldx, M, N, K, dw, lddw, rows);
+        }
     }
     return check_launch();
 }

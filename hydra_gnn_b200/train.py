@@ -191,7 +191,10 @@ class FlatAdam:
         self.flat_param = self.flat_grad = self.exp_avg = self.exp_avg_sq = None
         self.live: List[nn.Parameter] = []
 
-    def _flatten(self):
+    def flatten(self):
+        """Idempotent; call after the first backward (``step`` does) and before a gradient all-reduce."""
+        if self.flat_param is not None:
+            return
         self.live = [p for p in self.params if p.grad is not None]
         if not self.live:
             raise RuntimeError("FlatAdam.step() before any backward")
@@ -219,8 +222,7 @@ class FlatAdam:
             self.flat_grad.zero_()
 
     def step(self, grad_scale: float = 1.0):
-        if self.flat_param is None:
-            self._flatten()
+        self.flatten()
         self.t += 1
         ops.adam_step(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.t, self.lr, self.betas[0],
                       self.betas[1], self.eps, self.weight_decay, grad_scale)
