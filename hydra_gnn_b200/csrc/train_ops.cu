@@ -163,14 +163,19 @@ __global__ void __launch_bounds__(kMThreads) k_wgrad_mma(const float* __restrict
                 split_tf32(sB[buf][r0][c], bh[j][0], bl[j][0]);
                 split_tf32(sB[buf][r1][c], bh[j][1], bl[j][1]);
             }
+            // term-major order: eight independent accumulators between two MMAs on the same one
 #pragma unroll
             for (int i = 0; i < 2; ++i)
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    mma_tf32(acc[i][j], al[i], bh[j]);
-                    mma_tf32(acc[i][j], ah[i], bl[j]);
-                    mma_tf32(acc[i][j], ah[i], bh[j]);
-                }
+                for (int j = 0; j < 4; ++j) mma_tf32(acc[i][j], al[i], bh[j]);
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) mma_tf32(acc[i][j], ah[i], bl[j]);
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) mma_tf32(acc[i][j], ah[i], bh[j]);
         }
         buf ^= 1;
     }

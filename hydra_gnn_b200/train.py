@@ -79,7 +79,11 @@ class _GatLayerFn(torch.autograd.Function):
     def backward(ctx, *douts):
         cfg, Y = ctx.cfg, ctx.Y
         outs = ctx.saved_tensors
-        dY = {T: torch.zeros_like(y) for T, y in Y.items()}
+        # every xs / a_src / a_dst column is written by exactly one relation role; only the pad columns need zeros
+        dY = {T: torch.empty_like(y) for T, y in Y.items()}
+        for T, spans in cfg.pad_cols.items():
+            for a, b in spans:
+                dY[T][:, a:b].zero_()
         dbias: Dict[str, Tensor] = {}
         for T, rels, out, dout in zip(cfg.dsts, ctx.saved_rels, outs, douts):
             has_bias = any(r.bias is not None for r in rels)
@@ -135,8 +139,10 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
 
     # per node type: [lin_src blocks of the relations leaving it | folded att_src rows | folded att_dst rows]
     Y: Dict[str, Tensor] = {}
+    cfg.pad_cols = {}
     for T in cfg.types:
         blocks, col = [], 0
+        pads = cfg.pad_cols.setdefault(T, [])
         for et in rels:
             if et[0] != T:
                 continue
@@ -146,6 +152,7 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
             blocks.append(W)
             if _pad4(rows) != rows:
                 blocks.append(W.new_zeros(_pad4(rows) - rows, W.size(1)))
+                pads.append((col + rows, col + _pad4(rows)))
             cfg.xs_off[et] = col
             col += _pad4(rows)
         for et in rels:
@@ -165,6 +172,7 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
             col += c.heads
         if _pad4(col) != col:
             blocks.append(blocks[0].new_zeros(_pad4(col) - col, x[T].size(1)))
+            pads.append((col, _pad4(col)))
         Y[T] = linear(x[T], torch.cat(blocks, dim=0))
 
     cfg.bias_rels = [et for et in rels if convs[et].bias is not None]
