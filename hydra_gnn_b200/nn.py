@@ -15,6 +15,8 @@ on a per-batch :class:`GraphPlan` (CSR per relation, built once by ``ops.build_c
 """
 from __future__ import annotations
 
+import os
+
 import math
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -213,6 +215,7 @@ def _pad4(n: int) -> int:
 
 
 AGG_FIRST_RATIO = 4  # a relation aggregates first when it has >= 4x fewer destinations than sources
+AGG_FIRST_WIDTH = float(os.environ.get("HG_AGG_FIRST_WIDTH", "1"))  # ... and raw rows at most this x the projected width
 
 
 def _gat_modes(convs, rels: Sequence[EdgeType], x: Dict[str, Tensor], group: str) -> Tuple[bool, ...]:
@@ -224,7 +227,7 @@ def _gat_modes(convs, rels: Sequence[EdgeType], x: Dict[str, Tensor], group: str
     if group != "sum":
         return tuple(False for _ in rels)
     return tuple(x[et[2]].size(0) * AGG_FIRST_RATIO <= x[et[0]].size(0)
-                 and x[et[0]].size(1) <= convs[et].heads * convs[et].out_channels for et in rels)
+                 and x[et[0]].size(1) <= AGG_FIRST_WIDTH * convs[et].heads * convs[et].out_channels for et in rels)
 
 
 class _GatPack:
