@@ -15,6 +15,7 @@ from __future__ import annotations
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
+import torch.nn.functional as F
 from torch import Tensor, nn
 
 from . import ops
@@ -124,13 +125,18 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
     cfg.dsts = list(dict.fromkeys(et[2] for et in rels))
     cfg.xs_off, cfg.as_off, cfg.ad_off, cfg.csr = {}, {}, {}, dict(csr)
     cfg.H, cfg.C, cfg.concat, cfg.slope, cfg.dropout, cfg.seed = {}, {}, {}, {}, {}, {}
-    cfg.group, cfg.act = group, act
+    cfg.group, cfg.act, cfg.C_real = group, act, {}
     for et in rels:
         c = convs[et]
         if c.lin_edge is not None and edge_attr is not None and edge_attr.get(et) is not None:
             raise NotImplementedError("training with edge attributes (GAT_edge) is not implemented")
         T = et[2]
-        sig = (c.heads, c.out_channels, c.concat, c.negative_slope, c.dropout if c.training else 0.0)
+        # head mean with C % 4 != 0 (the 26-class layer): the per-head blocks of the projection are padded to a multiple
+        # of 4 channels (zero weight rows, zero bias) so the float4 kernels apply; the pad columns of the output are 0
+        # and sliced away below
+        Cp = _pad4(c.out_channels) if (not c.concat or c.heads == 1) else c.out_channels
+        cfg.C_real[T] = c.out_channels
+        sig = (c.heads, Cp, c.concat, c.negative_slope, c.dropout if c.training else 0.0)
         if T in cfg.H and (cfg.H[T], cfg.C[T], cfg.concat[T], cfg.slope[T], cfg.dropout[T]) != sig:
             raise NotImplementedError("relations targeting one node type must share heads/channels/concat/dropout")
         cfg.H[T], cfg.C[T], cfg.concat[T], cfg.slope[T], cfg.dropout[T] = sig
@@ -148,7 +154,10 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
                 continue
             c = convs[et]
             W = c.lin_src.weight
-            rows = c.heads * c.out_channels
+            Cp = cfg.C[et[2]]
+            if Cp != c.out_channels:
+                W = F.pad(W.view(c.heads, c.out_channels, -1), (0, 0, 0, Cp - c.out_channels)).reshape(c.heads * Cp, -1)
+            rows = c.heads * Cp
             blocks.append(W)
             if _pad4(rows) != rows:
                 blocks.append(W.new_zeros(_pad4(rows) - rows, W.size(1)))
@@ -176,8 +185,15 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
         Y[T] = linear(x[T], torch.cat(blocks, dim=0))
 
     cfg.bias_rels = [et for et in rels if convs[et].bias is not None]
-    outs = _GatLayerFn.apply(cfg, *[Y[T] for T in cfg.types], *[convs[et].bias for et in cfg.bias_rels])
-    return dict(zip(cfg.dsts, outs))
+    biases = []
+    for et in cfg.bias_rels:
+        b, width = convs[et].bias, (cfg.H[et[2]] * cfg.C[et[2]] if cfg.concat[et[2]] else cfg.C[et[2]])
+        biases.append(b if b.numel() == width else F.pad(b, (0, width - b.numel())))
+    outs = _GatLayerFn.apply(cfg, *[Y[T] for T in cfg.types], *biases)
+    res = {}
+    for T, o in zip(cfg.dsts, outs):
+        res[T] = o if cfg.C[T] == cfg.C_real[T] else o[:, :cfg.C_real[T]]
+    return res
 
 
 # =============================================================================== optimizer

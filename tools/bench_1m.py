@@ -1,0 +1,107 @@
+"""BASELINE.json configs[3]: 1M synthetic scene graphs sharded by graph across the GPUs of one box, heterogeneous GAT
+(M-GAT) forward in micro-batches of 16,384 graphs, ONE NCCL gather of the room logits at the end.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/bench_1m.py \
+        [--total 1000000] [--micro 16384] [--repeat 3]
+
+Rank r owns graph ids [r T/W, (r+1) T/W) (dist.shard_range); its micro-batches are generated once (host, untimed) and
+kept resident in HBM.  Timed region (CUDA events between two barriers, max over ranks): every micro-batch forward
+(plan rebuilt per micro-batch) + the ragged logit gather.  One JSON line on rank 0.
+"""
+import argparse, json, os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import torch.distributed as dist
+
+from bench import M_GAT, ClockSampler
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--total", type=int, default=1_000_000)
+    ap.add_argument("--micro", type=int, default=16384)
+    ap.add_argument("--repeat", type=int, default=3)
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29533")
+    dist.init_process_group("nccl" if world > 1 else "gloo", rank=rank, world_size=world,
+                            **({"device_id": dev} if world > 1 else {}))
+
+    import hydra_gnn_b200 as hg
+    from hydra_gnn_b200 import _lib, synth
+    from hydra_gnn_b200.dist import LogitGather, shard_range
+
+    lo, hi = shard_range(args.total, rank, world)
+    t0 = time.perf_counter()
+    micro, rooms = [], 0
+    for a in range(lo, hi, args.micro):
+        host = synth.synth_mp3d_batch(range(a, min(a + args.micro, hi)))
+        d = hg.data.HeteroData()
+        for t in host.node_types:
+            d[t].x = host[t].x.to(dev)
+        for t in host.edge_types:
+            d[t].edge_index = host[t].edge_index.to(dev)
+        micro.append((d, rooms, host["rooms"].x.size(0)))
+        rooms += host["rooms"].x.size(0)
+    t_gen = time.perf_counter() - t0
+    net = synth.random_state_dict_(hg.HeterogeneousNetwork(**M_GAT), seed=0).eval().to(dev)
+    net.plan_cache.enabled = False
+    logits = torch.empty(rooms, 26, dtype=torch.float32, device=dev)
+    gather = LogitGather(26).prepare(rooms, dev) if world > 1 else None
+
+    def job():
+        for d, off, n in micro:
+            logits[off:off + n].copy_(net(d))
+        if gather is not None:
+            gather(logits)
+
+    def fence():
+        dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    job()  # warm-up: weight images, workspaces, NCCL channels
+    fence()
+    l0 = _lib.launch_count
+    times = []
+    with ClockSampler(local) as clocks:
+        for _ in range(args.repeat):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            fence()
+            e0.record()
+            job()
+            e1.record()
+            fence()
+            times.append(e0.elapsed_time(e1))
+    launches = _lib.launch_count - l0
+    t = torch.tensor(times, device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    times = sorted(t.tolist())
+    ms = times[len(times) // 2]
+    n_rooms_all = sum(gather.counts) if gather is not None else rooms
+    if rank == 0:
+        got = gather.unpad() if gather is not None else logits
+        assert got.size(0) == n_rooms_all and bool(torch.isfinite(got).all())
+        # graph order check: this rank's rows come first and equal its local logits
+        assert torch.equal(got[:rooms], logits)
+        print(json.dumps({
+            "metric": "scene_graphs_per_s_forward", "value": args.total / (ms / 1e3), "unit": "graphs/s", "n_gpus": world,
+            "ms_per_job": ms, "ms_all_repeats": times, "higher_is_better": True, "scaling": "strong", "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": "configs[3]: 1M synthetic MP3D-shaped scene graphs sharded by graph, M-GAT forward in "
+                                   f"micro-batches of {args.micro}, one NCCL gather of the room logits",
+                       "total_graphs": args.total, "micro_batch": args.micro, "micro_batches_per_rank": len(micro),
+                       "rooms_total": n_rooms_all, "gathered_bytes": n_rooms_all * 26 * 4,
+                       "collective": "all_gather_into_tensor(max-padded room logits)" if world > 1 else "none",
+                       "cuda_graph": False, "host_generation_s_per_rank": round(t_gen, 1)},
+            "gpu_launches": launches, "clocks": clocks.summary()}), flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
