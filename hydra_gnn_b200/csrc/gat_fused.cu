@@ -121,9 +121,15 @@ __device__ __noinline__ void slow_row(const GatParams& P, int64_t i, int lane, i
                     const int32_t j = __ldg(Rl.col + e);
                     float sc = __ldg(Rl.a_src + static_cast<int64_t>(j) * Rl.lda_src + h) + ad;
                     if (Rl.a_edge) sc += __ldg(Rl.a_edge + static_cast<int64_t>(e) * H + h);
-                    const float w = __expf(leaky(sc, A.neg_slope) - m) * inv;
+                    float w = __expf(leaky(sc, A.neg_slope) - m) * inv;
+                    float a_saved = w;
+                    if (A.dropout_p > 0.f) {  // training forward: decision in the sign bit of the saved weight
+                        w *= dropout_keep_scale(A.dropout_seed, r, static_cast<int64_t>(e) * H + h, A.dropout_p,
+                                                1.f / (1.f - A.dropout_p));
+                        if (w == 0.f) a_saved = -a_saved;
+                    }
                     if (A.alpha_saved[r] && (head_mean ? (lane == 0 && oc0 == 0 && f_begin == 0) : (live && f % C == 0)))
-                        A.alpha_saved[r][static_cast<int64_t>(e) * H + h] = w;
+                        A.alpha_saved[r][static_cast<int64_t>(e) * H + h] = a_saved;
                     if (live) {
                         float val[VEC];
                         ldg_vec<VEC>(Rl.xs + static_cast<int64_t>(j) * Rl.ldxs + src_f, val);
@@ -278,6 +284,17 @@ k_gat_fused(const __grid_constant__ GatParams P) {
             }
             const float inv = 1.f / (l + 1e-16f);
             float* alpha = (P.f_begin == 0) ? A.alpha_saved[r] : nullptr;
+            if (A.dropout_p > 0.f) {  // training forward (uniform branch; inference passes 0)
+                const float inv_keep = 1.f / (1.f - A.dropout_p);
+                for (int e = beg; e < end; ++e) {
+                    const float a = w[e << hsh] * inv;
+                    const int64_t idx = static_cast<int64_t>(e0 + e) * H + h;
+                    const float ks = dropout_keep_scale(A.dropout_seed, r, idx, A.dropout_p, inv_keep);
+                    w[e << hsh] = a * ks;
+                    if (alpha) alpha[idx] = ks == 0.f ? -a : a;
+                }
+                continue;
+            }
             for (int e = beg; e < end; ++e) {
                 const float a = w[e << hsh] * inv;
                 w[e << hsh] = a;

@@ -14,16 +14,6 @@ constexpr int kWarps = 8;
 constexpr int kThreads = kWarps * kWarp;
 constexpr int kMaxH = 4;
 
-__device__ __forceinline__ float keep_scale(uint64_t seed, int r, int64_t idx, float p, float inv_keep) {
-    // splitmix64 of (seed, relation slot, CSR position * H + head): regenerated identically by the backward
-    uint64_t z = seed + 0x9E3779B97F4A7C15ull * (static_cast<uint64_t>(idx) * HG_MAX_RELATIONS + r + 1);
-    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-    z ^= z >> 31;
-    const float u = static_cast<float>(z >> 40) * (1.0f / 16777216.0f);
-    return u >= p ? inv_keep : 0.f;
-}
-
 // The forward stores the softmax weight with the dropout decision in its sign bit (weights are >= 0): the hash is
 // evaluated once per (edge, head), by one lane; every later pass reads |alpha| and the sign.
 __device__ __forceinline__ float kept(float a_signed, float inv_keep) {
@@ -92,7 +82,7 @@ __global__ void __launch_bounds__(kThreads) k_fwd(const __grid_constant__ hg_gat
                     if (h < H) {
                         const int64_t idx = static_cast<int64_t>(p) * H + h;
                         float a = expf(leaky(__ldg(as + h) + ad[h], slope) - m[h]) / sum[h];
-                        if (drop && keep_scale(A.seed, r, idx, p_drop, inv_keep) == 0.f) a = -a;
+                        if (drop && dropout_keep_scale(A.seed, r, idx, p_drop, inv_keep) == 0.f) a = -a;
                         R.alpha[idx] = a;
                     }
             }
@@ -364,7 +354,7 @@ __global__ void __launch_bounds__(kThreads) k_fwd_v4(const __grid_constant__ hg_
                     if (mine && h < H) {
                         const int64_t idx = static_cast<int64_t>(p) * H + h;
                         float a = e / sm;
-                        if (drop && keep_scale(A.seed, r, idx, p_drop, inv_keep) == 0.f) a = -a;
+                        if (drop && dropout_keep_scale(A.seed, r, idx, p_drop, inv_keep) == 0.f) a = -a;
                         R.alpha[idx] = a;
                         wv[h] = kept(a, inv_keep);
                     }
@@ -424,7 +414,7 @@ __global__ void __launch_bounds__(kThreads) k_fwd_v4(const __grid_constant__ hg_
                     if (h < H) {
                         const int64_t idx = static_cast<int64_t>(p) * H + h;
                         float a = expf(leaky(__ldg(as + h) + ad[h], slope) - m[h]) / sum[h];
-                        if (drop && keep_scale(A.seed, r, idx, p_drop, inv_keep) == 0.f) a = -a;
+                        if (drop && dropout_keep_scale(A.seed, r, idx, p_drop, inv_keep) == 0.f) a = -a;
                         R.alpha[idx] = a;
                     }
             }
@@ -481,7 +471,7 @@ __global__ void __launch_bounds__(kThreads) k_fwd_v4(const __grid_constant__ hg_
 }
 
 template <int NV, bool HK>
-__global__ void __launch_bounds__(kThreads) k_bwd_dst_v4(const __grid_constant__ hg_gat_train_args A) {
+__global__ void __launch_bounds__(kThreads, 4) k_bwd_dst_v4(const __grid_constant__ hg_gat_train_args A) {
     __shared__ __align__(16) float s_g[kWarps][2][NV * 64];
     __shared__ float s_db[NV * 64];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, sub = lane >> 4, l = lane & 15;
@@ -509,6 +499,7 @@ __global__ void __launch_bounds__(kThreads) k_bwd_dst_v4(const __grid_constant__
         float* sg = s_g[w][sub];
 #pragma unroll
         for (int t = 0; t < NV * 4; ++t) {
+            if (16 * t >= width) break;  // uniform
             const int c = l + 16 * t;
             if (c < width) {
                 const float o = A.out[static_cast<int64_t>(i) * A.ldout + c];
@@ -849,6 +840,7 @@ extern "C" int hg_gat_train_bwd(const hg_gat_train_args* a, void* stream_) {
     if (a->n_dst > 0) {
         // grid-stride: the bias gradient is reduced per block
         if (fast) {
+            // grid-stride over whole waves: 4 resident CTAs per SM (launch bounds), two waves' worth of CTAs
             const unsigned grid = row_grid(ceil_div(a->n_dst, 2), 8);
 #define CALL4(NV, HKV) k_bwd_dst_v4<NV, HKV><<<grid, kThreads, 0, stream>>>(*a)
             HG_NV_SWITCH(nv, hk, CALL4)

@@ -62,6 +62,18 @@ __device__ __forceinline__ float apply_act(float v, int act) {
     return v;
 }
 
+
+// Attention-dropout decision of (relation slot r, flat index idx = CSR position * H + head): splitmix64 of the seed
+// and the counter.  Returns 1/(1-p) when kept, 0 when dropped.
+__device__ __forceinline__ float dropout_keep_scale(uint64_t seed, int r, int64_t idx, float p, float inv_keep) {
+    uint64_t z = seed + 0x9E3779B97F4A7C15ull * (static_cast<uint64_t>(idx) * HG_MAX_RELATIONS + r + 1);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    const float u = static_cast<float>(z >> 40) * (1.0f / 16777216.0f);
+    return u >= p ? inv_keep : 0.f;
+}
+
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));

@@ -12,6 +12,7 @@ need the gradient of the re-arranged weights; not worth it while the weight grad
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
@@ -68,8 +69,8 @@ class _GatLayerFn(torch.autograd.Function):
         for T in cfg.dsts:
             rels = [GatTrainRelation(Y[et[0]], Y[T], cfg.xs_off[et], cfg.as_off[et], cfg.ad_off[et], cfg.csr[et],
                                      biases.get(et)) for et in cfg.rels if et[2] == T]
-            out = ops.gat_train_fwd(rels, Y[T].size(0), cfg.H[T], cfg.C[T], cfg.concat[T], group=cfg.group, act=cfg.act,
-                                    neg_slope=cfg.slope[T], dropout_p=cfg.dropout[T], seed=cfg.seed[T])
+            out = _forward_group(rels, Y[T].size(0), cfg.H[T], cfg.C[T], cfg.concat[T], cfg.group, cfg.act,
+                                 cfg.slope[T], cfg.dropout[T], cfg.seed[T])
             outs.append(out)
             saved_rels.append(rels)
         ctx.cfg, ctx.saved_rels, ctx.Y = cfg, saved_rels, Y
@@ -103,6 +104,27 @@ class _GatLayerFn(torch.autograd.Function):
             used.add(et[2])
         ctx.saved_rels = ctx.Y = None
         return tuple(grads)
+
+
+TILE_FORWARD = os.environ.get("HG_TRAIN_TILE_FWD", "1") != "0"  # training forward through the inference tile kernel (hg_gat_fused + dropout + saved weights)
+
+
+def _forward_group(rels: Sequence[GatTrainRelation], n_dst: int, H: int, C: int, concat: bool, group: str, act: str,
+                   slope: float, dropout_p: float, seed: int) -> Tensor:
+    """Forward of one destination type.  Default: ``hg_gat_fused`` (the tile kernel of the inference path) with the
+    softmax weights saved for the backward and attention dropout applied in its softmax stage; ``TILE_FORWARD =
+    False`` selects ``hg_gat_train_fwd`` (row-per-half-warp kernel, same results up to the fast exp)."""
+    if not TILE_FORWARD:
+        return ops.gat_train_fwd(rels, n_dst, H, C, concat, group=group, act=act, neg_slope=slope, dropout_p=dropout_p,
+                                 seed=seed)
+    HC = H * C
+    fused = []
+    for r in rels:
+        r.alpha = torch.empty(max(r.csr.cap, 1), H, dtype=torch.float32, device=r.y_src.device)
+        fused.append(ops.GatRelation(r.y_src[:, r.xs_off: r.xs_off + HC], r.y_src[:, r.as_off: r.as_off + H],
+                                     r.y_dst[:, r.ad_off: r.ad_off + H], r.csr, r.bias, None, r.alpha))
+    return ops.gat_fused(fused, n_dst, H, C, concat, group=group, act=act, neg_slope=slope, dropout_p=dropout_p,
+                         seed=seed)
 
 
 class _LayerCfg:

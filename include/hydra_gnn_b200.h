@@ -176,12 +176,17 @@ typedef struct hg_gat_args {
     int32_t act;        /* HG_ACT_* */
     float neg_slope;
     float* out; int64_t ldout;
-    float* alpha_saved[HG_MAX_RELATIONS]; /* NULL | [E', H] softmax weights (for backward) */
+    float* alpha_saved[HG_MAX_RELATIONS]; /* NULL | [E', H] softmax weights (for hg_gat_train_bwd) */
     const float* addend; int64_t ldadd;   /* NULL | [n_dst, out width]: added after the group, before act
                                              (output of aggregate-first relations of the same dst type) */
     int32_t src_shared; /* 1: aggregate-first form -- xs is [n_src, C], ONE row shared by all heads;
                            out[i, h, :] = sum_e w_eh xs[col[e], :], width H*C (requires concat = 1) */
-    int32_t reserved;
+    float dropout_p;    /* training forward only (0 for inference): attention dropout, GATConv(dropout=p) --
+                           w_e,h is zeroed with probability p (counter-based hash of seed, relation slot, CSR
+                           position, head) and scaled by 1/(1-p) otherwise; alpha_saved then holds the softmax weight
+                           BEFORE dropout with the decision in its sign bit (negative = dropped), the encoding
+                           hg_gat_train_bwd reads */
+    uint64_t dropout_seed;
 } hg_gat_args;
 
 HG_API int hg_gat_fused(const hg_gat_args* args_host, void* stream);

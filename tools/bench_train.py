@@ -45,8 +45,8 @@ def key(name, m):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--graphs", type=int, default=8192)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--dropout", type=float, default=0.4)
     ap.add_argument("--cpu-graphs", type=int, default=512)
     ap.add_argument("--no-cpu", action="store_true")
