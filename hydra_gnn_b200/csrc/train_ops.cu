@@ -94,7 +94,7 @@ __device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], 
 }
 
 template <bool VEC2>
-__global__ void __launch_bounds__(kMThreads) k_wgrad_mma(const float* __restrict__ dy, int64_t lddy,
+__global__ void __launch_bounds__(kMThreads, 4) k_wgrad_mma(const float* __restrict__ dy, int64_t lddy,
                                                          const float* __restrict__ x, int64_t ldx, int M, int N, int K,
                                                          float* __restrict__ dw, int64_t lddw, int rows_per_split) {
     __shared__ __align__(16) float sA[2][kMM][kMLd];
@@ -115,25 +115,48 @@ __global__ void __launch_bounds__(kMThreads) k_wgrad_mma(const float* __restrict
 #pragma unroll
             for (int t = 0; t < 4; ++t) acc[i][j][t] = 0.f;
     float2 ra[8], rb[8];
-    const bool a0ok = n0 + lcol < N, a1ok = n0 + lcol + 1 < N;
-    const bool b0ok = k0 + lcol < K, b1ok = k0 + lcol + 1 < K;
+    // Column clamp instead of predicates: dW[n][k] depends on column n of dY and column k of X only, so a clamped
+    // (in-bounds, wrong) column only feeds accumulators that are never stored.  Rows are predicated in the one partial
+    // stage at the end of the row range.
+    const int ca = VEC2 ? min(n0 + lcol, (N - 2) & ~1) : min(n0 + lcol, N - 1);
+    const int cb = VEC2 ? min(k0 + lcol, (K - 2) & ~1) : min(k0 + lcol, K - 1);
+    const int ca1 = min(n0 + lcol + 1, N - 1), cb1 = min(k0 + lcol + 1, K - 1);  // scalar variant
+    const float* pa = dy + static_cast<int64_t>(m_beg + lrow) * lddy;
+    const float* pb = x + static_cast<int64_t>(m_beg + lrow) * ldx;
     auto load = [&](int m0) {
+        if (m0 + kMM <= m_end) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const int m = m0 + lrow + 4 * i;
-            const bool ok = m < m_end;
-            const float* pa = dy + static_cast<int64_t>(m) * lddy + n0 + lcol;
-            const float* pb = x + static_cast<int64_t>(m) * ldx + k0 + lcol;
-            if (VEC2) {
-                ra[i] = (ok && a1ok) ? __ldg(reinterpret_cast<const float2*>(pa))
-                                     : make_float2((ok && a0ok) ? __ldg(pa) : 0.f, 0.f);
-                rb[i] = (ok && b1ok) ? __ldg(reinterpret_cast<const float2*>(pb))
-                                     : make_float2((ok && b0ok) ? __ldg(pb) : 0.f, 0.f);
-            } else {
-                ra[i] = make_float2((ok && a0ok) ? __ldg(pa) : 0.f, (ok && a1ok) ? __ldg(pa + 1) : 0.f);
-                rb[i] = make_float2((ok && b0ok) ? __ldg(pb) : 0.f, (ok && b1ok) ? __ldg(pb + 1) : 0.f);
+            for (int i = 0; i < 8; ++i) {
+                if (VEC2) {
+                    ra[i] = __ldg(reinterpret_cast<const float2*>(pa + static_cast<int64_t>(4 * i) * lddy + ca));
+                    rb[i] = __ldg(reinterpret_cast<const float2*>(pb + static_cast<int64_t>(4 * i) * ldx + cb));
+                } else {
+                    ra[i] = make_float2(__ldg(pa + static_cast<int64_t>(4 * i) * lddy + ca),
+                                        __ldg(pa + static_cast<int64_t>(4 * i) * lddy + ca1));
+                    rb[i] = make_float2(__ldg(pb + static_cast<int64_t>(4 * i) * ldx + cb),
+                                        __ldg(pb + static_cast<int64_t>(4 * i) * ldx + cb1));
+                }
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const bool ok = m0 + lrow + 4 * i < m_end;
+                ra[i] = rb[i] = make_float2(0.f, 0.f);
+                if (ok) {
+                    if (VEC2) {
+                        ra[i] = __ldg(reinterpret_cast<const float2*>(pa + static_cast<int64_t>(4 * i) * lddy + ca));
+                        rb[i] = __ldg(reinterpret_cast<const float2*>(pb + static_cast<int64_t>(4 * i) * ldx + cb));
+                    } else {
+                        ra[i] = make_float2(__ldg(pa + static_cast<int64_t>(4 * i) * lddy + ca),
+                                            __ldg(pa + static_cast<int64_t>(4 * i) * lddy + ca1));
+                        rb[i] = make_float2(__ldg(pb + static_cast<int64_t>(4 * i) * ldx + cb),
+                                            __ldg(pb + static_cast<int64_t>(4 * i) * ldx + cb1));
+                    }
+                }
             }
         }
+        pa += static_cast<int64_t>(kMM) * lddy;
+        pb += static_cast<int64_t>(kMM) * ldx;
     };
     load(m_beg);
     int buf = 0;
@@ -249,7 +272,7 @@ extern "C" int hg_linear_wgrad(const float* dy, int64_t lddy, const float* x, in
         const dim3 grid(tn, tk, splits);
         if (use_fma) {
             k_wgrad<<<grid, kWgThreads, 0, stream>>>(dy, lddy, x, ldx, M, N, K, dw, lddw, rows);
-        } else if (lddy % 2 == 0 && ldx % 2 == 0 && aligned(dy, 8) && aligned(x, 8)) {
+        } else if (N >= 2 && K >= 2 && lddy % 2 == 0 && ldx % 2 == 0 && aligned(dy, 8) && aligned(x, 8)) {
             k_wgrad_mma<true><<<grid, kMThreads, 0, stream>>>(dy, lddy, x, ldx, M, N, K, dw, lddw, rows);
         } else {
             k_wgrad_mma<false><<<grid, kMThreads, 0, stream>>>(dy, lddy, x, ldx, M, N, K, dw, lddw, rows);
