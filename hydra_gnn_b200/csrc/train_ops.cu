@@ -214,6 +214,36 @@ __global__ void __launch_bounds__(kMThreads, 4) k_wgrad_mma(const float* __restr
             }
 }
 
+// g = dy * act'(y), dbias += column sums of g.  Block = 32 columns x 8 rows, grid-stride over rows.
+__global__ void __launch_bounds__(256) k_act_bwd(const float* __restrict__ dy, int64_t lddy, const float* __restrict__ y,
+                                                 int64_t ldy, int64_t M, int N, int act, float* __restrict__ g,
+                                                 int64_t ldg, float* __restrict__ dbias) {
+    __shared__ float s_sum[8][33];
+    const int c = blockIdx.y * 32 + threadIdx.x;
+    float acc = 0.f;
+    if (c < N) {
+        for (int64_t m = static_cast<int64_t>(blockIdx.x) * 8 + threadIdx.y; m < M; m += static_cast<int64_t>(gridDim.x) * 8) {
+            float d = dy[m * lddy + c];
+            if (act != HG_ACT_NONE) {
+                const float o = __ldg(y + m * ldy + c);
+                if (act == HG_ACT_ELU) d *= o > 0.f ? 1.f : o + 1.f;
+                else d = o > 0.f ? d : 0.f;
+            }
+            if (g) g[m * ldg + c] = d;
+            acc += d;
+        }
+    }
+    if (!dbias) return;
+    s_sum[threadIdx.y][threadIdx.x] = acc;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < N) {
+        float t = 0.f;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) t += s_sum[r][threadIdx.x];
+        atomicAdd(dbias + c, t);
+    }
+}
+
 __global__ void k_zero_rows(float* __restrict__ p, int64_t ld, int N, int K) {
     const int64_t total = static_cast<int64_t>(N) * K;
     for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total;
@@ -298,5 +328,23 @@ extern "C" int hg_adam_step(float* param, const float* grad, float* exp_avg, flo
     const int64_t g = ceil_div<int64_t>(n, 256);
     k_adam<<<static_cast<unsigned>(g < sms * 8 ? g : sms * 8), 256, 0, stream>>>(
         param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, grad_scale, step_size, inv_sqrt_bc2);
+    return check_launch();
+}
+
+extern "C" int hg_act_bwd(const float* dy, int64_t lddy, const float* y, int64_t ldy, int64_t M, int32_t N, int32_t act,
+                          float* g, int64_t ldg, float* dbias, void* stream_) {
+    using namespace hg;
+    if (M < 0 || N < 0) return HG_EINVAL;
+    if (M == 0 || N == 0 || (!g && !dbias)) return HG_OK;
+    if (!dy || (act != HG_ACT_NONE && !y)) return HG_EINVAL;
+    if (act == HG_ACT_NONE && !dbias && g == dy) return HG_OK;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int sms = sm_count() > 0 ? sm_count() : 148;
+    const int cols = ceil_div(N, 32);
+    int64_t gx = ceil_div<int64_t>(M, 8);
+    const int64_t cap = ceil_div<int64_t>(static_cast<int64_t>(sms) * 8, cols);
+    gx = gx < cap ? gx : cap;
+    k_act_bwd<<<dim3(static_cast<unsigned>(gx > 0 ? gx : 1), cols), dim3(32, 8), 0, stream>>>(dy, lddy, y, ldy, M, N, act, g,
+                                                                                          ldg, dbias);
     return check_launch();
 }

@@ -144,5 +144,5 @@ class HeterogeneousNeuralTreeNetwork(_Base):
                 x_dict = self._drop(x_dict)
 
         from .. import ops
-        outs = [ops.seg_reduce(x_dict[et[0]], plan[(et, False)], "mean") for et, _ in pools]
+        outs = [hnn.seg_reduce(x_dict[et[0]], plan[(et, False)], "mean") for et, _ in pools]
         return outs[0] if room_only else (outs[0], outs[1])

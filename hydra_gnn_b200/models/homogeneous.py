@@ -105,11 +105,9 @@ class HomogeneousNetwork(_Base):
         return x
 
     def _heads(self, x, room_rows, object_rows):
-        xr, xo = ops.gather_rows(x, room_rows), ops.gather_rows(x, object_rows)
-        return (ops.linear([(xr, self.post_mp_room.weight)], self.post_mp_room.out_features,
-                           bias=self.post_mp_room.bias),
-                ops.linear([(xo, self.post_mp_object.weight)], self.post_mp_object.out_features,
-                           bias=self.post_mp_object.bias))
+        xr, xo = hnn.gather_rows(x, room_rows), hnn.gather_rows(x, object_rows)
+        return (hnn.linear(xr, self.post_mp_room.weight, self.post_mp_room.bias),
+                hnn.linear(xo, self.post_mp_object.weight, self.post_mp_object.bias))
 
     def _forward(self, data):
         plan = self._plans.get([self._main_request(data)])
@@ -117,7 +115,7 @@ class HomogeneousNetwork(_Base):
         x = self._message_passing(data.x, data, plan, use_batch_norm=True, final_act=not room_only)
         room_rows = self._mask_rows(self._plans, "room_rows", data.room_mask)
         if room_only:
-            return ops.gather_rows(x, room_rows)
+            return hnn.gather_rows(x, room_rows)
         return self._heads(x, room_rows, self._mask_rows(self._plans, "not_room_rows", data.room_mask, negate=True))
 
 
@@ -160,12 +158,10 @@ class HomogeneousNeuralTreeNetwork(HomogeneousNetwork):
         pool = plan[(self._POOL, False)]
         room_rows = self._mask_rows(self._plans, "room_rows", data.room_mask)
         if room_only:  # LeafPool evaluated only on the rows the caller keeps
-            return ops.seg_reduce(x, pool, "mean", row_map=room_rows)
+            return hnn.seg_reduce(x, pool, "mean", row_map=room_rows)
         # task "all": activation (+ dropout) after the pooling (:105-109)
         object_rows = self._mask_rows(self._plans, "object_rows", data.object_mask)
-        xr = self._drop(ops.seg_reduce(x, pool, "mean", row_map=room_rows, act=self._act_name))
-        xo = self._drop(ops.seg_reduce(x, pool, "mean", row_map=object_rows, act=self._act_name))
-        return (ops.linear([(xr, self.post_mp_room.weight)], self.post_mp_room.out_features,
-                           bias=self.post_mp_room.bias),
-                ops.linear([(xo, self.post_mp_object.weight)], self.post_mp_object.out_features,
-                           bias=self.post_mp_object.bias))
+        xr = self._drop(hnn.seg_reduce(x, pool, "mean", row_map=room_rows, act=self._act_name))
+        xo = self._drop(hnn.seg_reduce(x, pool, "mean", row_map=object_rows, act=self._act_name))
+        return (hnn.linear(xr, self.post_mp_room.weight, self.post_mp_room.bias),
+                hnn.linear(xo, self.post_mp_object.weight, self.post_mp_object.bias))

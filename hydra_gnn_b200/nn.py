@@ -25,6 +25,7 @@ import torch.nn as nn
 from torch import Tensor
 
 from . import ops
+from . import train as _train
 from .ops import CSR, CSRSpec, GatRelation
 
 EdgeType = Tuple[str, str, str]
@@ -414,6 +415,8 @@ class SAGEConv(nn.Module):
 def run_sage(conv: SAGEConv, x_src: Tensor, x_dst: Tensor, csr: CSR, act: str = None) -> Tensor:
     """Homogeneous / single-relation SAGE.  Aggregate-first when in <= out (fewer gathered bytes),
     project-first otherwise (``lin_l(mean x) = mean(x W_l^T) + b``: same value, 1e-7 rounding)."""
+    if _train.wants_grad(x_src, x_dst, *conv.parameters()):
+        return _train.run_sage_train(conv, x_src, x_dst, csr, act=act)
     d_in, d_out = conv.in_channels[0], conv.out_channels
     if d_in <= d_out or x_src is not x_dst:
         mean = ops.seg_reduce(x_src, csr, "mean")
@@ -432,6 +435,8 @@ def run_hetero_sage(convs: Dict[EdgeType, SAGEConv], rels: Sequence[EdgeType], x
     concatenation [mean_r1 | mean_r2 | ... | x_dst] (root weights and biases pre-summed)."""
     if only_dst is not None:
         rels = [et for et in rels if et[2] in only_dst]
+    if _train.wants_grad(*x.values(), *[p for et in rels for p in convs[et].parameters()]):
+        return _train.run_hetero_sage_train(convs, rels, x, csr, act=act, group=group)
     out: Dict[str, Tensor] = {}
     for T in dict.fromkeys(et[2] for et in rels):
         mine = [et for et in rels if et[2] == T]
@@ -477,6 +482,8 @@ class GCNConv(nn.Module):
 
 
 def run_gcn(conv: GCNConv, x: Tensor, csr: CSR, act: str = None) -> Tensor:
+    if _train.wants_grad(x, *conv.parameters()):
+        return _train.run_gcn_train(conv, x, csr, act=act)
     y = ops.linear([(x, conv.lin.weight)], conv.out_channels, pack_cache=_wcache(conv, "lin"))
     return ops.seg_reduce(y, csr, "sum", src_scale=csr.inv_sqrt_deg, dst_scale=csr.inv_sqrt_deg, bias=conv.bias, act=act)
 
@@ -605,4 +612,25 @@ class LeafPool(nn.Module):
     def forward(self, x: Tensor, edge_index: Tensor, num_out: int = None) -> Tensor:
         n = x.size(0) if num_out is None else num_out
         plan = self._plans.get([PlanRequest("_", edge_index, x.size(0), n)])
-        return ops.seg_reduce(x, plan[("_", False)], self.aggr)
+        return _train.seg_reduce(x, plan[("_", False)], self.aggr)
+
+
+# =============================================================================== dispatchers used by the model classes
+def seg_reduce(x: Tensor, csr: CSR, op: str = "sum", **kw) -> Tensor:
+    """``ops.seg_reduce``; records the backward (reversed-CSR gather) when a gradient is wanted."""
+    return _train.seg_reduce(x, csr, op, **kw)
+
+
+def gather_rows(x: Tensor, rows: Tensor, act: str = None) -> Tensor:
+    """``act(x[rows])`` -- the ``x[room_mask]`` selection; under autograd the selection is torch's index_select
+    (its backward is the index_add of the reference) and the activation torch's."""
+    if not _train.wants_grad(x):
+        return ops.gather_rows(x, rows, act=act)
+    y = x.index_select(0, rows.long())
+    return y if act is None else (torch.relu(y) if act == "relu" else torch.nn.functional.elu(y))
+
+
+def linear(x: Tensor, weight: Tensor, bias: Tensor = None, act: str = None) -> Tensor:
+    if _train.wants_grad(x, weight, bias):
+        return _train.linear_multi([(x, weight)], bias, act)
+    return ops.linear([(x, weight)], weight.size(0), bias=bias, act=act)

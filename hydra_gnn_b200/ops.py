@@ -646,3 +646,31 @@ def gat_train_bwd(rels: Sequence[GatTrainRelation], dys: Sequence[tuple], n_dst:
     meta = dict(n_dst=n_dst, H=H, C=Cc, width=out.size(1), rels=[dict(n_src=r.csr.n_src, cap=r.csr.cap) for r in rels])
     _call("hg_gat_train_bwd", meta, lambda: h.hg_gat_train_bwd(C.byref(a), stream_ptr()))
     _lib.launch_count += 2
+
+
+def act_bwd(dy: Tensor, y: Tensor, act: str = None, want_g: bool = True, want_dbias: bool = False):
+    """``g = dy * act'(y)`` (``y`` = the activation's output) and/or ``dbias = g.sum(0)`` (``hg_act_bwd``).
+    Returns ``(g, dbias)``; with no activation ``g`` is ``dy`` itself."""
+    h = lib()
+    dy = _rows(dy, "dy")
+    M, N = dy.shape
+    code = ACT[act]
+    g = dy
+    if code != 0 and want_g:
+        g = torch.empty(M, N, dtype=torch.float32, device=dy.device)
+    dbias = torch.zeros(N, dtype=torch.float32, device=dy.device) if want_dbias else None
+    if code != 0 or want_dbias:
+        y = _rows(y, "y") if code != 0 else None
+        _call("hg_act_bwd", dict(M=M, N=N),
+              lambda: h.hg_act_bwd(ptr(dy), _ld(dy), ptr(y), _ld(y) if y is not None else 0, M, N, code,
+                                   ptr(g) if (code != 0 and want_g) else None, _ld(g), ptr(dbias), stream_ptr()))
+        _lib.launch_count += 1
+    return g, dbias
+
+
+def reversed_csr(csr: CSR) -> CSR:
+    """The by-source CSR of a relation (rows = its sources, col = destination ids) as a CSR object for
+    :func:`seg_reduce` -- the scatter direction of every aggregation backward."""
+    ensure_train_csr([csr])
+    t = csr.train
+    return CSR(t.rowptr_t, t.col_t, None, None, csr.n_dst, csr.n_src, csr.cap, csr.self_loops)

@@ -272,3 +272,106 @@ class FlatAdam:
         self.t += 1
         ops.adam_step(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.t, self.lr, self.betas[0],
                       self.betas[1], self.eps, self.weight_decay, grad_scale)
+
+
+# =============================================================================== SAGE / GCN / LeafPool (a3, a6, a8)
+def wants_grad(*tensors) -> bool:
+    return torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors)
+
+
+class _LinearMultiFn(torch.autograd.Function):
+    """``y = act(sum_s x_s @ W_s^T + bias)`` (the K-segmented hg_linear).  Backward: ``g = dy * act'(y)`` and the bias
+    gradient in one ``hg_act_bwd`` pass, ``dx_s = g @ W_s`` (hg_linear), ``dW_s = g^T @ x_s`` (hg_linear_wgrad)."""
+
+    @staticmethod
+    def forward(ctx, act, n_seg, *tensors):
+        xs, Ws, bias = tensors[:n_seg], tensors[n_seg:2 * n_seg], tensors[2 * n_seg]
+        y = ops.linear(list(zip(xs, Ws)), Ws[0].size(0), bias=bias, act=act)
+        ctx.act, ctx.n_seg, ctx.has_bias = act, n_seg, bias is not None
+        ctx.save_for_backward(y, *xs, *Ws)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        n = ctx.n_seg
+        y, xs, Ws = ctx.saved_tensors[0], ctx.saved_tensors[1:1 + n], ctx.saved_tensors[1 + n:]
+        need = ctx.needs_input_grad[2:]
+        g, dbias = ops.act_bwd(dy.contiguous(), y, ctx.act, want_dbias=ctx.has_bias and need[2 * n])
+        dxs = [ops.linear([(g, W.t().contiguous())], W.size(1)) if need[k] else None for k, W in enumerate(Ws)]
+        dWs = [ops.linear_wgrad(g, x) if need[n + k] else None for k, x in enumerate(xs)]
+        return (None, None, *dxs, *dWs, dbias)
+
+
+def linear_multi(segments, bias: Optional[Tensor] = None, act: str = None) -> Tensor:
+    xs, Ws = [x for x, _ in segments], [w for _, w in segments]
+    return _LinearMultiFn.apply(act, len(segments), *xs, *Ws, bias)
+
+
+class _SegReduceFn(torch.autograd.Function):
+    """``out = act(dst_scale * reduce(src_scale * x[col]) + bias)`` (hg_seg_reduce, sum | mean, optional ``row_map``).
+    Backward: ``g = dout * act'(out)`` (hg_act_bwd, + bias gradient), then the SAME kernel over the reversed CSR:
+    ``dx[j] = src_scale[j] * sum_{i <- j} (dst_scale[i] / deg[i]) g[i]`` -- a gather, no atomics."""
+
+    @staticmethod
+    def forward(ctx, x, bias, csr, op, src_scale, dst_scale, row_map, act):
+        out = ops.seg_reduce(x, csr, op, src_scale=src_scale, dst_scale=dst_scale, row_map=row_map, bias=bias, act=act)
+        ctx.csr, ctx.op, ctx.src_scale, ctx.dst_scale, ctx.row_map, ctx.act = csr, op, src_scale, dst_scale, row_map, act
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(out)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (out,) = ctx.saved_tensors
+        csr = ctx.csr
+        g, dbias = ops.act_bwd(dout.contiguous(), out, ctx.act, want_dbias=ctx.has_bias and ctx.needs_input_grad[1])
+        dx = None
+        if ctx.needs_input_grad[0]:
+            if ctx.row_map is not None:  # rows the forward did not compute carry no gradient
+                full = torch.zeros(csr.n_dst, g.size(1), dtype=torch.float32, device=g.device)
+                full.index_copy_(0, ctx.row_map.long(), g)
+                g = full
+            scale = ctx.dst_scale
+            if ctx.op == "mean":
+                csr.ready()
+                inv_deg = (csr.rowptr[1:] - csr.rowptr[:-1]).clamp(min=1).to(torch.float32).reciprocal()
+                scale = inv_deg if scale is None else scale * inv_deg
+            dx = ops.seg_reduce(g, ops.reversed_csr(csr), "sum", src_scale=scale, dst_scale=ctx.src_scale)
+        return dx, dbias, None, None, None, None, None, None
+
+
+def seg_reduce(x: Tensor, csr: CSR, op: str = "sum", *, src_scale: Tensor = None, dst_scale: Tensor = None,
+               row_map: Tensor = None, bias: Tensor = None, act: str = None) -> Tensor:
+    """``ops.seg_reduce`` that records its backward when a gradient is wanted (sum / mean)."""
+    if not wants_grad(x, bias):
+        return ops.seg_reduce(x, csr, op, src_scale=src_scale, dst_scale=dst_scale, row_map=row_map, bias=bias, act=act)
+    if op not in ("sum", "add", "mean"):
+        raise NotImplementedError("backward of the max aggregation is not implemented")
+    return _SegReduceFn.apply(x, bias, csr, op, src_scale, dst_scale, row_map, act)
+
+
+def run_sage_train(conv, x_src: Tensor, x_dst: Tensor, csr: CSR, act: str = None) -> Tensor:
+    """SAGEConv, differentiable: ``lin_l(mean_j x_j) + lin_r(x_i)`` as one K-segmented projection."""
+    mean = seg_reduce(x_src, csr, "mean")
+    return linear_multi([(mean, conv.lin_l.weight), (x_dst, conv.lin_r.weight)], conv.lin_l.bias, act)
+
+
+def run_hetero_sage_train(convs, rels: Sequence[EdgeType], x: Dict[str, Tensor], csr: Dict[EdgeType, CSR], *,
+                          act: str = None, group: str = "sum") -> Dict[str, Tensor]:
+    out: Dict[str, Tensor] = {}
+    for T in dict.fromkeys(et[2] for et in rels):
+        mine = [et for et in rels if et[2] == T]
+        scale = 1.0 / len(mine) if group == "mean" else 1.0
+        w_root = sum(convs[et].lin_r.weight for et in mine) * scale  # parameter-space ops: torch autograd
+        biases = [convs[et].lin_l.bias for et in mine if convs[et].lin_l.bias is not None]
+        bias = (sum(biases) * scale) if biases else None
+        segs = [(seg_reduce(x[et[0]], csr[et], "mean"),
+                 convs[et].lin_l.weight * scale if scale != 1.0 else convs[et].lin_l.weight) for et in mine]
+        segs.append((x[T], w_root))
+        out[T] = linear_multi(segs, bias, act)
+    return out
+
+
+def run_gcn_train(conv, x: Tensor, csr: CSR, act: str = None) -> Tensor:
+    y = linear_multi([(x, conv.lin.weight)])
+    return seg_reduce(y, csr, "sum", src_scale=csr.inv_sqrt_deg, dst_scale=csr.inv_sqrt_deg, bias=conv.bias, act=act)

@@ -346,6 +346,12 @@ HG_API int hg_adam_step(float* param, const float* grad, float* exp_avg, float* 
                         float beta1, float beta2, float eps, float weight_decay, float grad_scale, int32_t step,
                         void* stream);
 
+/* g[m, c] = dy[m, c] * act'(y[m, c]) and dbias[c] += sum_m g[m, c] (either output may be NULL; `g` may alias `dy`).
+ * y is the activation's OUTPUT (ELU: y > 0 ? 1 : y + 1; ReLU: y > 0).  Backward of the fused bias + activation
+ * epilogues of hg_linear / hg_seg_reduce (autograd of F.relu / F.elu + the bias broadcast in the reference). */
+HG_API int hg_act_bwd(const float* dy, int64_t lddy, const float* y, int64_t ldy, int64_t M, int32_t N, int32_t act,
+                      float* g, int64_t ldg, float* dbias /* NULL | [N], accumulated (caller zeroes) */, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

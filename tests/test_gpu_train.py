@@ -149,3 +149,90 @@ def test_adam_kernel_matches_torch():
         opt.step()
         ops.adam_step(pd, g.cuda(), m, v, t, 3e-3, 0.9, 0.999, 1e-8, 1e-2)
     assert float((pd.cpu() - ref.detach()).abs().max()) <= 1e-6
+
+
+# ------------------------------------------------------------------------------ the other model families (a3, a6, a8, a9)
+def _compare_grads(ref, net, run_ref, run_net, min_checked):
+    ref.zero_grad(set_to_none=True)
+    net.zero_grad(set_to_none=True)
+    want = run_ref()
+    got = run_net()
+    wants, gots = (want if isinstance(want, tuple) else (want,)), (got if isinstance(got, tuple) else (got,))
+    torch.manual_seed(3)
+    probes = [torch.randn_like(w) for w in wants]  # fixed linear functional of the outputs
+    sum((w * p).sum() for w, p in zip(wants, probes)).backward()
+    sum((g * p.cuda()).sum() for g, p in zip(gots, probes)).backward()
+    for w, g in zip(wants, gots):
+        _grad_close(g, w, "output", rtol=1e-4)
+    ref_p, got_p = dict(ref.named_parameters()), dict(net.named_parameters())
+    floor = 1e-3 * max(float(p.grad.abs().max()) for p in ref_p.values() if p.grad is not None)
+    checked = 0
+    for name, p in ref_p.items():
+        if p.grad is None:
+            g = got_p[name].grad
+            assert g is None or float(g.abs().max()) == 0.0, name
+            continue
+        assert got_p[name].grad is not None, f"{name}: no gradient"
+        _grad_close(got_p[name].grad, p.grad, name, floor=floor)
+        checked += 1
+    assert checked >= min_checked, checked
+
+
+def test_hetero_sage_gradients_match_oracle():
+    kw = dict(input_dim_dict={"objects": 306, "rooms": 6}, output_dim_dict={"rooms": 15, "objects": 35},
+              conv_block="GraphSAGE", hidden_dim=64, num_layers=3, dropout=0.0)
+    host = synth.synth_mp3d_batch(range(24))
+    ref, net = _pair(kw)
+    dev = clone_data(host, "cuda")
+    _compare_grads(ref, net, lambda: ref(clone_data(host)), lambda: net(dev), 20)
+
+
+@pytest.mark.parametrize("conv_block", ["GCN", "GraphSAGE", "GAT"])
+def test_homogeneous_gradients_match_oracle(conv_block):
+    from hydra_gnn_b200 import convert
+    kw = dict(input_dim=306, output_dim=26, conv_block=conv_block, hidden_dim=64, num_layers=3, dropout=0.0,
+              GAT_hidden_dims=[32, 32], GAT_heads=[2, 2, 1], GAT_concats=[True, True, False])
+    hom = convert.dsg_to_homogeneous(synth.synth_mp3d_batch(range(24)))
+    ref, net = _pair(kw, "HomogeneousNetwork")
+    dev = clone_data(hom, "cuda")
+    _compare_grads(ref, net, lambda: ref(clone_data(hom)), lambda: net(dev), 6)
+
+
+@pytest.mark.parametrize("conv_block", ["GCN", "GraphSAGE"])
+def test_homogeneous_neural_tree_gradients_match_oracle(conv_block):
+    from hydra_gnn_b200 import convert, htree
+    from hydra_gnn_b200.data import Batch
+    trees = [htree.generate_htree(synth.synth_mp3d_batch([g])) for g in range(6)]
+    hom = Batch.from_data_list([convert.heterogeneous_htree_to_homogeneous(t) for t in trees])
+    kw = dict(input_dim=306, output_dim=26, conv_block=conv_block, hidden_dim=32, num_layers=3, dropout=0.0,
+              disable_initialization=True)
+    ref, net = _pair(kw, "HomogeneousNeuralTreeNetwork")
+    dev = clone_data(hom, "cuda")
+    _compare_grads(ref, net, lambda: ref(clone_data(hom)), lambda: net(dev), 6)
+
+
+@pytest.mark.parametrize("pre_mp", [False, True])
+def test_heterogeneous_neural_tree_gat_gradients_match_oracle(pre_mp):
+    from hydra_gnn_b200 import htree
+    from hydra_gnn_b200.data import Batch
+    trees = [htree.generate_htree(synth.synth_mp3d_batch([g])) for g in range(6)]
+    het = Batch.from_data_list(trees)
+    dims = {"object": 306, "room": 6, "object-room": 6, "room-room": 6, "object_virtual": 306, "room_virtual": 6}
+    kw = dict(input_dim_dict=dims, output_dim=26, conv_block="GAT", GAT_hidden_dims=[32, 32], GAT_heads=[2, 2, 2],
+              GAT_concats=[False] * 3, dropout=0.0, disable_initialization=not pre_mp)
+    ref, net = _pair(kw, "HeterogeneousNeuralTreeNetwork")
+    dev = clone_data(het, "cuda")
+    _compare_grads(ref, net, lambda: ref(clone_data(het)), lambda: net(dev), 20)
+
+
+def test_act_bwd_kernel():
+    torch.manual_seed(0)
+    dy = torch.randn(1001, 70, device="cuda")
+    x = torch.randn(1001, 70, device="cuda")
+    for act, f in (("elu", torch.nn.functional.elu), ("relu", torch.relu), (None, lambda t: t)):
+        xr = x.clone().requires_grad_(True)
+        y = f(xr)
+        y.backward(dy)
+        g, db = ops.act_bwd(dy, y.detach(), act, want_dbias=True)
+        assert torch.allclose(g, xr.grad, rtol=1e-6, atol=1e-6)
+        assert torch.allclose(db, xr.grad.sum(0), rtol=1e-4, atol=1e-4)
