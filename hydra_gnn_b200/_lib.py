@@ -48,7 +48,7 @@ class GatArgs(C.Structure):
     _fields_ = [("rel", GatRel * HG_MAX_RELATIONS), ("n_rel", i32), ("n_dst", i32), ("H", i32), ("C", i32),
                 ("concat", i32), ("group", i32), ("act", i32), ("neg_slope", f32), ("out", vp), ("ldout", i64),
                 ("alpha_saved", vp * HG_MAX_RELATIONS), ("addend", vp), ("ldadd", i64), ("src_shared", i32),
-                ("dropout_p", f32), ("dropout_seed", C.c_uint64)]
+                ("dropout_p", f32), ("dropout_seed", C.c_uint64), ("dropout_seed_dev", vp)]
 
 
 class LinSeg(C.Structure):

@@ -124,7 +124,8 @@ __device__ __noinline__ void slow_row(const GatParams& P, int64_t i, int lane, i
                     float w = __expf(leaky(sc, A.neg_slope) - m) * inv;
                     float a_saved = w;
                     if (A.dropout_p > 0.f) {  // training forward: decision in the sign bit of the saved weight
-                        w *= dropout_keep_scale(A.dropout_seed, r, static_cast<int64_t>(e) * H + h, A.dropout_p,
+                        w *= dropout_keep_scale(A.dropout_seed + (A.dropout_seed_dev ? *A.dropout_seed_dev : 0ull), r,
+                                                static_cast<int64_t>(e) * H + h, A.dropout_p,
                                                 1.f / (1.f - A.dropout_p));
                         if (w == 0.f) a_saved = -a_saved;
                     }
@@ -286,10 +287,11 @@ k_gat_fused(const __grid_constant__ GatParams P) {
             float* alpha = (P.f_begin == 0) ? A.alpha_saved[r] : nullptr;
             if (A.dropout_p > 0.f) {  // training forward (uniform branch; inference passes 0)
                 const float inv_keep = 1.f / (1.f - A.dropout_p);
+                const uint64_t seed = A.dropout_seed + (A.dropout_seed_dev ? *A.dropout_seed_dev : 0ull);
                 for (int e = beg; e < end; ++e) {
                     const float a = w[e << hsh] * inv;
                     const int64_t idx = static_cast<int64_t>(e0 + e) * H + h;
-                    const float ks = dropout_keep_scale(A.dropout_seed, r, idx, A.dropout_p, inv_keep);
+                    const float ks = dropout_keep_scale(seed, r, idx, A.dropout_p, inv_keep);
                     w[e << hsh] = a * ks;
                     if (alpha) alpha[idx] = ks == 0.f ? -a : a;
                 }

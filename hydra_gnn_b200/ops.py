@@ -305,7 +305,7 @@ class GatRelation:
 
 def gat_fused(rels: Sequence[GatRelation], n_dst: int, H: int, Cc: int, concat: bool, *, group: str = "sum",
               act: str = None, neg_slope: float = 0.2, out: Tensor = None, addend: Tensor = None,
-              src_shared: bool = False, dropout_p: float = 0.0, seed: int = 0) -> Tensor:
+              src_shared: bool = False, dropout_p: float = 0.0, seed: int = 0, seed_dev: Tensor = None) -> Tensor:
     """Fused GAT aggregation of every relation targeting one node type (``hg_gat_fused``).
 
     ``src_shared=True`` is the aggregate-first form: ``xs`` is ``[n_src, C]`` (one row shared by all
@@ -350,6 +350,10 @@ def gat_fused(rels: Sequence[GatRelation], n_dst: int, H: int, Cc: int, concat: 
         a.addend, a.ldadd = ptr(addend), _ld(addend)
     a.src_shared = int(src_shared)
     a.dropout_p, a.dropout_seed = float(dropout_p), int(seed) & 0xFFFFFFFFFFFFFFFF
+    if seed_dev is not None:
+        if seed_dev.dtype != torch.int64 or seed_dev.numel() != 1 or not seed_dev.is_cuda:
+            raise TypeError("seed_dev must be a CUDA int64 scalar")
+        a.dropout_seed_dev = ptr(seed_dev)
     meta = dict(n_dst=n_dst, H=H, C=Cc, concat=bool(concat), width=width, src_width=Cc if src_shared else H * Cc,
                 addend=addend is not None,
                 rels=[dict(n_src=r.xs.size(0), cap=r.csr.cap, edge=r.a_edge is not None) for r in rels])

@@ -106,6 +106,28 @@ class _GatLayerFn(torch.autograd.Function):
         return tuple(grads)
 
 
+# Device-resident dropout seed (CUDA-graph training): when set, every attention-dropout kernel adds this scalar to its
+# (static) per-call salt, so a replayed graph draws a new mask each step; ``advance_seed()`` belongs inside the graph.
+_DEVICE_SEED: Optional[Tensor] = None
+_salt = 0
+
+
+def enable_device_seed(device, seed: int = 0) -> Tensor:
+    global _DEVICE_SEED
+    _DEVICE_SEED = torch.full((1,), int(seed), dtype=torch.int64, device=device)
+    return _DEVICE_SEED
+
+
+def disable_device_seed() -> None:
+    global _DEVICE_SEED
+    _DEVICE_SEED = None
+
+
+def advance_seed() -> None:
+    if _DEVICE_SEED is not None:
+        _DEVICE_SEED.add_(0x632BE5AB)  # odd stride; the kernels hash (seed, relation, edge, head)
+
+
 TILE_FORWARD = os.environ.get("HG_TRAIN_TILE_FWD", "1") != "0"  # training forward through the inference tile kernel (hg_gat_fused + dropout + saved weights)
 
 
@@ -115,6 +137,8 @@ def _forward_group(rels: Sequence[GatTrainRelation], n_dst: int, H: int, C: int,
     softmax weights saved for the backward and attention dropout applied in its softmax stage; ``TILE_FORWARD =
     False`` selects ``hg_gat_train_fwd`` (row-per-half-warp kernel, same results up to the fast exp)."""
     if not TILE_FORWARD:
+        if _DEVICE_SEED is not None and dropout_p > 0:
+            raise NotImplementedError("the device-resident dropout seed needs the tile forward (HG_TRAIN_TILE_FWD=1)")
         return ops.gat_train_fwd(rels, n_dst, H, C, concat, group=group, act=act, neg_slope=slope, dropout_p=dropout_p,
                                  seed=seed)
     HC = H * C
@@ -124,7 +148,7 @@ def _forward_group(rels: Sequence[GatTrainRelation], n_dst: int, H: int, C: int,
         fused.append(ops.GatRelation(r.y_src[:, r.xs_off: r.xs_off + HC], r.y_src[:, r.as_off: r.as_off + H],
                                      r.y_dst[:, r.ad_off: r.ad_off + H], r.csr, r.bias, None, r.alpha))
     return ops.gat_fused(fused, n_dst, H, C, concat, group=group, act=act, neg_slope=slope, dropout_p=dropout_p,
-                         seed=seed)
+                         seed=seed, seed_dev=_DEVICE_SEED if dropout_p > 0 else None)
 
 
 class _LayerCfg:
@@ -162,8 +186,15 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
         if T in cfg.H and (cfg.H[T], cfg.C[T], cfg.concat[T], cfg.slope[T], cfg.dropout[T]) != sig:
             raise NotImplementedError("relations targeting one node type must share heads/channels/concat/dropout")
         cfg.H[T], cfg.C[T], cfg.concat[T], cfg.slope[T], cfg.dropout[T] = sig
-    for T in cfg.dsts:  # host-side draw from torch's CPU generator (torch.manual_seed makes a run repeatable)
-        cfg.seed[T] = int(torch.randint(0, 2 ** 62, (1,)).item()) if cfg.dropout[T] > 0 else 0
+    global _salt
+    for T in cfg.dsts:
+        if cfg.dropout[T] <= 0:
+            cfg.seed[T] = 0
+        elif _DEVICE_SEED is not None:  # static salt per call site; the device scalar makes it fresh per step
+            _salt += 1
+            cfg.seed[T] = (_salt * 0x9E3779B97F4A7C15) & 0x3FFFFFFFFFFFFFFF
+        else:  # host-side draw from torch's CPU generator (torch.manual_seed makes a run repeatable)
+            cfg.seed[T] = int(torch.randint(0, 2 ** 62, (1,)).item())
 
     # per node type: [lin_src blocks of the relations leaving it | folded att_src rows | folded att_dst rows]
     Y: Dict[str, Tensor] = {}

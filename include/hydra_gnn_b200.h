@@ -187,6 +187,9 @@ typedef struct hg_gat_args {
                            BEFORE dropout with the decision in its sign bit (negative = dropped), the encoding
                            hg_gat_train_bwd reads */
     uint64_t dropout_seed;
+    const uint64_t* dropout_seed_dev; /* NULL | device scalar added to dropout_seed when the kernel runs: a captured
+                                         CUDA graph of a training step draws a fresh mask on every replay (the
+                                         caller advances the scalar inside the graph) */
 } hg_gat_args;
 
 HG_API int hg_gat_fused(const hg_gat_args* args_host, void* stream);

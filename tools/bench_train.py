@@ -50,6 +50,7 @@ def main():
     ap.add_argument("--dropout", type=float, default=0.4)
     ap.add_argument("--cpu-graphs", type=int, default=512)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch every step eagerly instead of replaying a CUDA graph")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -62,6 +63,7 @@ def main():
     import hydra_gnn_b200 as hg
     from hydra_gnn_b200 import _lib, ops, synth
     from hydra_gnn_b200.dist import shard_range
+    from hydra_gnn_b200 import train as hgt
     from hydra_gnn_b200.train import FlatAdam
 
     G = args.graphs
@@ -85,7 +87,12 @@ def main():
     net.plan_cache.enabled = False  # plan (forward + reversed CSRs) rebuilt every step
     opt = FlatAdam(net.parameters(), lr=1e-3, weight_decay=1e-3)
 
+    use_graph = not args.no_graph
+    if use_graph:  # dropout masks must change on every replay: the seed lives on the device
+        hgt.enable_device_seed(dev, 20240229 + rank)
+
     def step():
+        hgt.advance_seed()
         opt.zero_grad()
         logits = net(data)
         # global masked mean: local sum / global count, gradients summed over ranks
@@ -101,6 +108,25 @@ def main():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
+
+    eager_step = step
+    side = torch.cuda.Stream(dev)
+    side.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.stream(side):  # eager warm-up: flattens the parameters, sizes workspaces, primes NCCL
+        for _ in range(3):
+            step()
+    torch.cuda.current_stream(dev).wait_stream(side)
+    fence()
+    if use_graph:
+        # the whole step (plan, forward, loss, backward, gradient all-reduce, Adam) as ONE CUDA graph
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            static_loss = eager_step()
+        fence()
+
+        def step():
+            graph.replay()
+            return static_loss
 
     for _ in range(max(args.warmup, 3)):
         step()
@@ -123,7 +149,7 @@ def main():
     t_eager0 = torch.cuda.Event(enable_timing=True); t_eager1 = torch.cuda.Event(enable_timing=True)
     t_eager0.record()
     for _ in range(args.steps):
-        step()
+        eager_step()
     t_eager1.record()
     fence()
     ops.PARALLEL_BRANCHES, net.plan_cache.overlap = saved
@@ -161,7 +187,7 @@ def main():
                                    f"{args.dropout}) + masked CE + backward + gradient all-reduce + Adam, {G} graphs per GPU",
                        "graphs_per_gpu": G, "objects": int(host["objects"].x.size(0)), "rooms": int(host["rooms"].x.size(0)),
                        "collective": "all_reduce(flat gradient, %d floats)" % opt.flat_grad.numel() if world > 1 else "none",
-                       "cuda_graph": False},
+                       "cuda_graph": use_graph},
             "gpu_launches": launches, "clocks": clocks.summary(),
             "our_kernels_share_of_step": round(ours_ms / ms_prof, 4),
             "loss_last_step": final_loss, "kernels": table,
