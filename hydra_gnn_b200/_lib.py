@@ -101,7 +101,7 @@ SYMBOLS = {
     "hg_csr_transpose_map": (C.c_int, [vp, vp, vp, i64, vp, vp, vp, i64, i32, vp, vp, vp]),
     "hg_linear_wgrad": (C.c_int, [vp, i64, vp, i64, i32, i32, i32, vp, i64, i32, vp]),
     "hg_act_bwd": (C.c_int, [vp, i64, vp, i64, i64, i32, i32, vp, i64, vp, vp]),
-    "hg_adam_step": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, f32, i32, vp]),
+    "hg_adam_step": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, f32, i32, vp, vp]),
 }
 
 _lock = threading.Lock()

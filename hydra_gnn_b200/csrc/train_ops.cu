@@ -253,7 +253,13 @@ __global__ void k_zero_rows(float* __restrict__ p, int64_t ld, int N, int K) {
 
 __global__ void __launch_bounds__(256) k_adam(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                               float* __restrict__ v, int64_t n, float lr, float b1, float b2, float eps,
-                                              float wd, float gscale, float step_size, float inv_sqrt_bc2) {
+                                              float wd, float gscale, int step, const int32_t* __restrict__ step_dev) {
+    // torch.optim.Adam (single-tensor path): step_size = lr / (1 - b1^t); denom = sqrt(v) / sqrt(1 - b2^t) + eps
+    const int t_step = step_dev ? *step_dev : step;
+    const double bc1 = 1.0 - pow(static_cast<double>(b1), static_cast<double>(t_step));
+    const double bc2 = 1.0 - pow(static_cast<double>(b2), static_cast<double>(t_step));
+    const float step_size = static_cast<float>(static_cast<double>(lr) / bc1);
+    const float inv_sqrt_bc2 = static_cast<float>(1.0 / sqrt(bc2));
     for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < n;
          t += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const float pt = p[t];
@@ -313,21 +319,16 @@ extern "C" int hg_linear_wgrad(const float* dy, int64_t lddy, const float* x, in
 
 extern "C" int hg_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                             float beta1, float beta2, float eps, float weight_decay, float grad_scale, int32_t step,
-                            void* stream_) {
+                            const int32_t* step_dev, void* stream_) {
     using namespace hg;
-    if (n < 0 || step < 1) return HG_EINVAL;
+    if (n < 0 || (!step_dev && step < 1)) return HG_EINVAL;
     if (n == 0) return HG_OK;
     if (!param || !grad || !exp_avg || !exp_avg_sq) return HG_EINVAL;
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const int sms = sm_count() > 0 ? sm_count() : 148;
-    // torch.optim.Adam (single-tensor path): step_size = lr / (1 - b1^t); denom = sqrt(v) / sqrt(1 - b2^t) + eps
-    const double bc1 = 1.0 - pow(static_cast<double>(beta1), step);
-    const double bc2 = 1.0 - pow(static_cast<double>(beta2), step);
-    const float step_size = static_cast<float>(lr / bc1);
-    const float inv_sqrt_bc2 = static_cast<float>(1.0 / sqrt(bc2));
     const int64_t g = ceil_div<int64_t>(n, 256);
     k_adam<<<static_cast<unsigned>(g < sms * 8 ? g : sms * 8), 256, 0, stream>>>(
-        param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, grad_scale, step_size, inv_sqrt_bc2);
+        param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, grad_scale, step, step_dev);
     return check_launch();
 }
 

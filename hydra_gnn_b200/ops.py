@@ -554,7 +554,8 @@ def linear_wgrad(dy: Tensor, x: Tensor, out: Tensor = None, accumulate: bool = F
 
 
 def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, step: int, lr: float, beta1: float,
-              beta2: float, eps: float, weight_decay: float, grad_scale: float = 1.0) -> None:
+              beta2: float, eps: float, weight_decay: float, grad_scale: float = 1.0, step_dev: Tensor = None) -> None:
+    """``step_dev``: CUDA int32 scalar holding t (>= 1), read by the kernel instead of the host value ``step``."""
     h = lib()
     for t in (param, grad, exp_avg, exp_avg_sq):
         _f32(t, "adam operand")
@@ -562,7 +563,7 @@ def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, 
             raise ValueError("adam operands must be contiguous and of equal size")
     _call("hg_adam_step", dict(n=param.numel()),
           lambda: h.hg_adam_step(ptr(param), ptr(grad), ptr(exp_avg), ptr(exp_avg_sq), param.numel(), lr, beta1, beta2,
-                                 eps, weight_decay, grad_scale, step, stream_ptr()))
+                                 eps, weight_decay, grad_scale, step, ptr(step_dev), stream_ptr()))
     _lib.launch_count += 1
 
 

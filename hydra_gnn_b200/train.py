@@ -281,7 +281,8 @@ class FlatAdam:
         self.flat_grad = torch.zeros(n, dtype=torch.float32, device=dev)
         self.exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
         self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
-        off = 0
+        self.t_dev = torch.full((1,), self.t, dtype=torch.int32, device=dev)  # step count t, device-resident so a
+        off = 0                                                               # captured step advances it on replay
         with torch.no_grad():
             for p in self.live:
                 k = p.numel()
@@ -300,9 +301,10 @@ class FlatAdam:
 
     def step(self, grad_scale: float = 1.0):
         self.flatten()
-        self.t += 1
+        self.t += 1  # host mirror (not advanced by graph replays); the kernel reads the device counter
+        self.t_dev.add_(1)
         ops.adam_step(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.t, self.lr, self.betas[0],
-                      self.betas[1], self.eps, self.weight_decay, grad_scale)
+                      self.betas[1], self.eps, self.weight_decay, grad_scale, step_dev=self.t_dev)
 
 
 # =============================================================================== SAGE / GCN / LeafPool (a3, a6, a8)

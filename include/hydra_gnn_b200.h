@@ -347,7 +347,8 @@ HG_API int hg_linear_wgrad(const float* dy, int64_t lddy, const float* x, int64_
  * ---------------------------------------------------------------------------------- */
 HG_API int hg_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                         float beta1, float beta2, float eps, float weight_decay, float grad_scale, int32_t step,
-                        void* stream);
+                        const int32_t* step_dev /* NULL | device scalar t >= 1 used instead of `step` (a captured
+                        CUDA graph of the training step advances it inside the graph) */, void* stream);
 
 /* g[m, c] = dy[m, c] * act'(y[m, c]) and dbias[c] += sum_m g[m, c] (either output may be NULL; `g` may alias `dy`).
  * y is the activation's OUTPUT (ELU: y > 0 ? 1 : y + 1; ReLU: y > 0).  Backward of the fused bias + activation

@@ -236,3 +236,73 @@ def test_act_bwd_kernel():
         g, db = ops.act_bwd(dy, y.detach(), act, want_dbias=True)
         assert torch.allclose(g, xr.grad, rtol=1e-6, atol=1e-6)
         assert torch.allclose(db, xr.grad.sum(0), rtol=1e-4, atol=1e-4)
+
+
+def test_training_step_as_cuda_graph():
+    """The whole step (plan, forward, loss, backward, Adam) captured once and replayed: with dropout = 0 the replayed
+    trajectory tracks the eager one; with dropout the device-resident seed gives a different mask on every replay."""
+    from hydra_gnn_b200 import train as hgt
+    host = synth.synth_mp3d_batch(range(32))
+    labels = host["rooms"].y.long().cuda()
+    dev = clone_data(host, "cuda")
+
+    def build(p):
+        _, net = _pair(dict(M_GAT, dropout=p))
+        net.plan_cache.enabled = False
+        return net, FlatAdam(net.parameters(), lr=1e-3)
+
+    def make_step(net, opt):
+        def step():
+            hgt.advance_seed()
+            opt.zero_grad()
+            loss = net.loss(net(dev), labels)
+            loss.backward()
+            opt.step()
+            return loss
+        return step
+
+    def capture(step):
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                step()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            loss = step()
+        torch.cuda.synchronize()
+        return g, loss
+
+    try:
+        hgt.enable_device_seed(torch.device("cuda"), 5)
+        # dropout 0: graph replay == eager (2 warm-up + 1 capture-free + 3 replays vs 5 eager steps)
+        net_e, opt_e = build(0.0)
+        step_e = make_step(net_e, opt_e)
+        for _ in range(5):
+            step_e()
+        net_g, opt_g = build(0.0)
+        g, _ = capture(make_step(net_g, opt_g))  # 2 eager warm-up steps; the capture itself executes nothing
+        for _ in range(3):
+            g.replay()
+        torch.cuda.synchronize()
+        assert int(opt_g.t_dev) == 5  # 2 eager steps + 3 replays (the traced call only records)
+        lr, steps = 1e-3, 5
+        got_p = dict(net_g.named_parameters())
+        for name, p in net_e.named_parameters():
+            err = (got_p[name].detach() - p.detach()).abs()
+            assert float(err.max()) <= 0.25 * lr * steps, f"{name}: max err {float(err.max()):.3e}"
+            assert float(err.mean()) <= 0.005 * lr * steps, f"{name}: mean err {float(err.mean()):.3e}"
+        # dropout: successive replays see different masks
+        net_d, opt_d = build(0.4)
+        net_d._drop = lambda x: x
+        gd, loss_d = capture(make_step(net_d, opt_d))
+        seen = []
+        for _ in range(3):
+            gd.replay()
+            torch.cuda.synchronize()
+            seen.append(float(loss_d.detach()))
+        assert len(set(seen)) == 3, seen
+    finally:
+        hgt.disable_device_seed()
