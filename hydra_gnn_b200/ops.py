@@ -42,8 +42,9 @@ def _call(name: str, meta, fn):
 def _require_no_grad(*tensors):
     if torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors):
         raise NotImplementedError(
-            "hydra_gnn_b200 kernels are forward-only in this build; call under torch.no_grad() "
-            "(backward kernels belong to the training config, see DESIGN.md)")
+            "this operator has no backward here: the raw ops are forward-only, gradients are recorded by "
+            "hydra_gnn_b200.train (GAT / GraphSAGE / GCN model classes; GIN and GAT_edge training are not implemented). "
+            "Call under torch.no_grad() or model.eval() with frozen parameters")
 
 
 def _f32(t: Tensor, name: str) -> Tensor:

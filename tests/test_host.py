@@ -254,3 +254,66 @@ def test_checkpoint_keys_of_newer_pyg_are_accepted():
     other.load_state_dict(new, strict=True)
     for k, v in other.state_dict().items():
         assert torch.equal(v, sd[k] * 2.0), k
+
+
+# ------------------------------------------------------------------------------ training plumbing (host side)
+def test_flat_adam_rehomes_live_parameters_as_views():
+    """FlatAdam.flatten(): parameters that received a gradient become views of ONE flat buffer (so a step is one kernel
+    and a gradient exchange one all-reduce); dead parameters (no gradient, like PyG's unused lin_dst) stay out."""
+    from hydra_gnn_b200.train import FlatAdam
+    torch.manual_seed(0)
+    a, b, dead = (torch.nn.Parameter(torch.randn(3, 4)), torch.nn.Parameter(torch.randn(5)),
+                  torch.nn.Parameter(torch.randn(2)))
+    before = [a.detach().clone(), b.detach().clone()]
+    opt = FlatAdam([a, b, dead, a], lr=1e-3)  # a listed twice: shared parameters are taken once
+    ((a * 2).sum() + (b * 3).sum()).backward()
+    opt.flatten()
+    assert opt.flat_param.numel() == 17 and [id(p) for p in opt.live] == [id(a), id(b)]
+    assert torch.equal(a.detach(), before[0]) and torch.equal(b.detach(), before[1])
+    assert a.data_ptr() == opt.flat_param.data_ptr() and b.data_ptr() == opt.flat_param[12:].data_ptr()
+    assert torch.equal(opt.flat_grad, torch.cat([torch.full((12,), 2.0), torch.full((5,), 3.0)]))
+    opt.zero_grad()
+    assert float(a.grad.abs().sum()) == 0.0 and a.grad.data_ptr() == opt.flat_grad.data_ptr()
+    ((a * 5).sum()).backward()  # autograd accumulates in place into the view
+    assert torch.equal(opt.flat_grad[:12], torch.full((12,), 5.0)) and dead.grad is None
+
+
+def _gloo_grad_worker(rank, world, port, out):
+    import torch.distributed as dist
+    from hydra_gnn_b200.train import FlatAdam
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(0)  # identical replicas
+        w = torch.nn.Parameter(torch.randn(4, 3))
+        b = torch.nn.Parameter(torch.randn(4))
+        opt = FlatAdam([w, b])
+        x = torch.arange(6, dtype=torch.float32).reshape(2, 3) + rank  # each rank its own shard
+        n_global = 2.0 * world
+        ((x @ w.t() + b).sum() / n_global).backward()  # local sum / global count
+        opt.flatten()
+        dist.all_reduce(opt.flat_grad)  # the one collective of the training step
+        out.put((rank, opt.flat_grad.clone(), w.grad.clone()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_world2_gradient_all_reduce_gives_the_global_mean():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q, world, port = ctx.Queue(), 2, 29611
+    procs = [ctx.Process(target=_gloo_grad_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = sorted([q.get(timeout=120) for _ in range(world)], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+    torch.manual_seed(0)
+    w = torch.randn(4, 3, requires_grad=True)
+    b = torch.randn(4, requires_grad=True)
+    x = torch.cat([torch.arange(6, dtype=torch.float32).reshape(2, 3) + r for r in range(world)])
+    ((x @ w.t() + b).sum() / x.size(0)).backward()
+    want = torch.cat([w.grad.reshape(-1), b.grad.reshape(-1)])
+    for _, flat, wg in got:
+        assert torch.allclose(flat, want, rtol=1e-6, atol=1e-6)
+        assert torch.allclose(wg, w.grad, rtol=1e-6, atol=1e-6)  # the parameter's .grad is a view of the reduced buffer
