@@ -16,6 +16,62 @@ enum NodeClass : uint8_t { kLeaf = 0, kClique = 1, kVirtual = 2 };           // 
 enum NodeKind : uint8_t { kObject = 0, kRoom = 1, kObjectRoom = 2, kRoomRoom = 3,
                           kObjectVirtual = 4, kRoomVirtual = 5, kNoKind = 255 };  // attribute "node_type"
 
+// Adjacency list with inline storage for 8 neighbours: H-tree and scene-graph degrees are small and the builder makes
+// ~200 graph copies per scene graph, so a heap allocation per adjacency list dominated its time.
+struct NbrList {
+    static constexpr uint32_t kInline = 8;
+    int inl[kInline];
+    int* heap = nullptr;
+    uint32_t sz = 0, cap = kInline;
+
+    NbrList() = default;
+    NbrList(const NbrList& o) { assign(o); }
+    NbrList(NbrList&& o) noexcept { steal(o); }
+    NbrList& operator=(const NbrList& o) { if (this != &o) { release(); assign(o); } return *this; }
+    NbrList& operator=(NbrList&& o) noexcept { if (this != &o) { release(); steal(o); } return *this; }
+    ~NbrList() { release(); }
+
+    int* data() { return heap ? heap : inl; }
+    const int* data() const { return heap ? heap : inl; }
+    int* begin() { return data(); }
+    int* end() { return data() + sz; }
+    const int* begin() const { return data(); }
+    const int* end() const { return data() + sz; }
+    size_t size() const { return sz; }
+    bool empty() const { return sz == 0; }
+    int operator[](size_t i) const { return data()[i]; }
+    void push_back(int v) {
+        if (sz == cap) grow(cap * 2);
+        data()[sz++] = v;
+    }
+    void erase(int* first, int* last) {  // only the erase(remove(...), end()) idiom is used
+        (void)last;
+        sz = static_cast<uint32_t>(first - data());
+    }
+    std::vector<int> to_vector() const { return std::vector<int>(begin(), end()); }
+
+ private:
+    void grow(uint32_t ncap) {
+        int* p = new int[ncap];
+        std::copy(begin(), end(), p);
+        delete[] heap;
+        heap = p;
+        cap = ncap;
+    }
+    void assign(const NbrList& o) {
+        heap = nullptr; cap = kInline; sz = 0;
+        if (o.sz > kInline) { heap = new int[o.sz]; cap = o.sz; }
+        std::copy(o.begin(), o.end(), data());
+        sz = o.sz;
+    }
+    void steal(NbrList& o) {
+        heap = o.heap; sz = o.sz; cap = o.cap;
+        if (!heap) std::copy(o.inl, o.inl + o.sz, inl);
+        o.heap = nullptr; o.sz = 0; o.cap = kInline;
+    }
+    void release() { delete[] heap; heap = nullptr; }
+};
+
 struct Attr {
     uint8_t cls = kLeaf;
     uint8_t kind = kNoKind;
@@ -24,18 +80,71 @@ struct Attr {
     std::vector<int> list;
 };
 
+// key -> slot tables are as long as the largest key (H-tree node ids reach the hundreds) while most of the ~200 graphs
+// built per scene graph have a handful of nodes: the tables are recycled through a thread-local pool (all entries -1
+// when pooled; a graph resets only the keys it used), which removes a multi-KB allocation + fill per graph.
+inline std::vector<std::vector<int>>& slot_pool() {
+    thread_local std::vector<std::vector<int>> pool;
+    return pool;
+}
+
 struct Graph {
     std::vector<int> order;              // node keys in dict order (nodes are never removed)
     std::vector<int> slot_of;            // key -> slot, -1 when absent (keys are small non-negative ints)
-    std::vector<std::vector<int>> adj;   // per slot: neighbour keys in dict order
+    int key_hi = 0;                      // 1 + largest key present
+
+    Graph() { take_slots(); }
+    Graph(const Graph& o) : order(o.order), key_hi(o.key_hi), adj(o.adj), attr(o.attr) {
+        take_slots();
+        if (slot_of.size() < (size_t)key_hi) slot_of.resize(key_hi, -1);
+        for (size_t s = 0; s < order.size(); ++s) slot_of[order[s]] = (int)s;
+    }
+    Graph(Graph&& o) noexcept
+        : order(std::move(o.order)), slot_of(std::move(o.slot_of)), key_hi(o.key_hi), adj(std::move(o.adj)),
+          attr(std::move(o.attr)) {
+        o.order.clear(); o.slot_of.clear(); o.key_hi = 0;
+    }
+    Graph& operator=(const Graph& o) {
+        if (this != &o) { Graph t(o); *this = std::move(t); }
+        return *this;
+    }
+    Graph& operator=(Graph&& o) noexcept {
+        if (this != &o) {
+            give_slots();
+            order = std::move(o.order); slot_of = std::move(o.slot_of); key_hi = o.key_hi;
+            adj = std::move(o.adj); attr = std::move(o.attr);
+            o.order.clear(); o.slot_of.clear(); o.key_hi = 0;
+        }
+        return *this;
+    }
+    ~Graph() { give_slots(); }
+    size_t key_span() const { return (size_t)key_hi; }  // size of a scratch array indexed by node key
+
+ private:
+    void take_slots() {
+        auto& pool = slot_pool();
+        if (!pool.empty()) { slot_of = std::move(pool.back()); pool.pop_back(); }
+    }
+    void give_slots() {
+        if (slot_of.empty()) return;
+        for (int k : order) slot_of[k] = -1;
+        auto& pool = slot_pool();
+        if (pool.size() < 64) pool.push_back(std::move(slot_of));
+        slot_of.clear();
+    }
+
+ public:
+    std::vector<NbrList> adj;            // per slot: neighbour keys in dict order
     std::vector<Attr> attr;              // per slot
 
     size_t n() const { return order.size(); }
-    bool has_node(int k) const { return k >= 0 && (size_t)k < slot_of.size() && slot_of[k] >= 0; }
+    void reserve(size_t n) { order.reserve(n); adj.reserve(n); attr.reserve(n); }
+    bool has_node(int k) const { return k >= 0 && k < key_hi && slot_of[k] >= 0; }
     int slot(int k) const { return slot_of[k]; }
     int add_node(int k) {
         if ((size_t)k >= slot_of.size()) slot_of.resize(std::max<size_t>(k + 1, slot_of.size() * 2), -1);
         if (slot_of[k] < 0) {
+            if (k >= key_hi) key_hi = k + 1;
             slot_of[k] = (int)order.size();
             order.push_back(k);
             adj.emplace_back();
@@ -46,7 +155,7 @@ struct Graph {
     int add_node(int k, const Attr& a) { int s = add_node(k); attr[s] = a; return s; }
     const Attr& at(int k) const { return attr[slot_of[k]]; }
     Attr& at(int k) { return attr[slot_of[k]]; }
-    const std::vector<int>& nbrs(int k) const { return adj[slot_of[k]]; }
+    const NbrList& nbrs(int k) const { return adj[slot_of[k]]; }
     bool has_edge(int u, int v) const {
         if (!has_node(u)) return false;
         const auto& a = adj[slot_of[u]];
@@ -69,7 +178,7 @@ struct Graph {
     }
     // EdgeView.__iter__: node order x adjacency order, an edge reported from its first endpoint only
     template <class F> void each_edge(F&& f) const {
-        std::vector<char> seen(slot_of.size(), 0);
+        std::vector<char> seen(key_span(), 0);
         for (size_t s = 0; s < order.size(); ++s) {
             for (int v : adj[s]) if (!seen[v]) f(order[s], v);
             seen[order[s]] = 1;
@@ -116,6 +225,7 @@ inline GL subview(const GL& g, const std::vector<int>& seq) {
 inline Graph copy_of(const GL& g) {
     Graph h;
     std::vector<int> nodes = g.node_list();
+    h.reserve(nodes.size());
     for (int k : nodes) h.add_node(k, g.root->at(k));
     for (int u : nodes) g.each_nbr(u, [&](int v) { h.add_edge(u, v); });
     return h;
@@ -124,6 +234,7 @@ inline Graph copy_of(const GL& g) {
 // relabel_nodes(G, mapping, copy=True) for a total mapping given as a function
 template <class M> inline Graph relabel_copy(const Graph& g, M&& map) {
     Graph h;
+    h.reserve(g.n());
     for (int k : g.order) h.add_node(map(k));
     for (int k : g.order) h.at(map(k)) = g.at(k);
     g.each_edge([&](int u, int v) { h.add_edge(map(u), map(v)); });
@@ -143,7 +254,7 @@ inline void absorb(Graph& r, const Graph& g, bool overwrite_attrs_of_existing) {
 // nx.connected_components(G): one PySet per component, filled in BFS order (components._plain_bfs)
 inline std::vector<PySet> connected_components(const GL& g) {
     std::vector<PySet> out;
-    std::vector<char> seen(g.root->slot_of.size(), 0);
+    std::vector<char> seen(g.root->key_span(), 0);
     size_t n = g.count(), n_seen = 0;
     std::vector<int> nodes = g.node_list();
     for (int v : nodes) {

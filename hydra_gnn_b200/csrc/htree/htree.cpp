@@ -40,10 +40,10 @@ struct HTreeAcc {
     std::vector<int> roots;
 
     void add_object_jth(Graph& ojth, const std::vector<int>& oroots, int room) {
-        std::vector<char> is_root(ojth.slot_of.size(), 0);
+        std::vector<char> is_root(ojth.key_span(), 0);
         for (int r : oroots) is_root[r] = 1;
         for (int r : oroots) {
-            std::vector<int> nb = ojth.nbrs(r);
+            std::vector<int> nb = ojth.nbrs(r).to_vector();
             for (int v : nb) if (is_root[v]) ojth.remove_edge(r, v);
         }
         for (int root : roots) {
@@ -132,7 +132,7 @@ Tree build_tree(int32_t n_nodes, const uint8_t* is_room, const int64_t* edge_ind
         }
         // nx.disjoint_union(htree, acc.jth): both relabelled to consecutive integers, then union_all
         const int first = (int)htree.n();
-        std::vector<int> pos_h(htree.slot_of.size(), -1), pos_j(acc.jth.slot_of.size(), -1);
+        std::vector<int> pos_h(htree.key_span(), -1), pos_j(acc.jth.key_span(), -1);
         for (size_t s = 0; s < htree.n(); ++s) pos_h[htree.order[s]] = (int)s;
         for (size_t s = 0; s < acc.jth.n(); ++s) pos_j[acc.jth.order[s]] = first + (int)s;
         Graph a = relabel_copy(htree, [&](int k) { return pos_h[k]; });
@@ -150,7 +150,7 @@ Tree build_tree(int32_t n_nodes, const uint8_t* is_room, const int64_t* edge_ind
     std::vector<int> order = htree.order;
     std::vector<Attr> attr(offset);
     std::vector<std::vector<int>> out_nbrs(offset);
-    for (size_t s = 0; s < htree.n(); ++s) { attr[htree.order[s]] = htree.attr[s]; out_nbrs[htree.order[s]] = htree.adj[s]; }
+    for (size_t s = 0; s < htree.n(); ++s) { attr[htree.order[s]] = htree.attr[s]; out_nbrs[htree.order[s]] = htree.adj[s].to_vector(); }
     auto ensure = [&](int key) {
         if ((size_t)key >= attr.size()) { attr.resize(key + 1); out_nbrs.resize(key + 1); }
     };

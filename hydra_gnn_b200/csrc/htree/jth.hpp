@@ -226,13 +226,13 @@ inline Jth generate_jth(const GL& g, bool original) {
             for (int k : fresh) u.add_edge(k, anode);
         } else {
             Jth sub = generate_jth(sg, false);
-            std::vector<char> is_root(sub.g.slot_of.size(), 0);
+            std::vector<char> is_root(sub.g.key_span(), 0);
             for (int r : sub.roots) is_root[r] = 1;
             for (int r : sub.roots) {  // remove the tree structure among the roots of this layer
-                std::vector<int> nb = sub.g.nbrs(r);
+                std::vector<int> nb = sub.g.nbrs(r).to_vector();
                 for (int v : nb) if (is_root[v]) sub.g.remove_edge(r, v);
             }
-            std::vector<int> new_index(sub.g.slot_of.size(), -1), roots_new;
+            std::vector<int> new_index(sub.g.key_span(), -1), roots_new;
             for (int k : sub.g.order) {
                 new_index[k] = next_index;
                 if (is_root[k]) roots_new.push_back(next_index);
