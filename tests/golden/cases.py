@@ -199,3 +199,39 @@ def load_golden_logits():
         keys = sorted(k for k in z.files if k.split("|")[0] == case)
         out[case] = [torch.from_numpy(z[k]) for k in keys]
     return out
+
+
+# ------------------------------------------------------------------------------ gradient fingerprints (training parity)
+def grad_fingerprint(model, inp):
+    """Three float64 numbers per parameter -- sum, l2 norm and the dot product with a fixed pseudo-random vector -- of the
+    gradient of a fixed linear functional of the model's outputs (eval mode: dropout off, so the forward is
+    deterministic; autograd does not care).  Small enough to commit, sharp enough to pin a backward."""
+    import zlib
+
+    model.zero_grad(set_to_none=True)
+    out = model(inp)
+    outs = list(out) if isinstance(out, (tuple, list)) else [out]
+    g = torch.Generator().manual_seed(1234)
+    sum((o * torch.randn(o.shape, generator=g).to(o.device)).sum() for o in outs).backward()
+    fp = {}
+    for name, p in sorted(model.named_parameters()):
+        if p.grad is None:
+            fp[name] = np.full(3, np.nan)
+            continue
+        gr = p.grad.detach().double().cpu().reshape(-1)
+        probe = torch.randn(gr.numel(), generator=torch.Generator().manual_seed(zlib.crc32(name.encode())),
+                            dtype=torch.float64)
+        fp[name] = np.array([float(gr.sum()), float(gr.norm()), float(gr.dot(probe))])
+    return fp
+
+
+def load_golden_grads():
+    path = os.path.join(HERE, "grads.npz")
+    if not os.path.exists(path):
+        return {}
+    z = np.load(path)
+    out = {}
+    for k in z.files:
+        case, name = k.split("|", 1)
+        out.setdefault(case, {})[name] = z[k]
+    return out

@@ -15,7 +15,7 @@ torch_geometric is not installable here, so those files run on ``oracle.pyg`` (t
 the PyG 2.3.1 operators, registered under the name ``torch_geometric``); if the real package ever
 is importable it is used instead and ``meta.json`` records ``pyg-<version>``.
 
-Outputs: stanford3dsg.npz, htree_synth.npz, htree_stanford.npz, convert_golden.npz, logits.npz,
+Outputs: stanford3dsg.npz, htree_synth.npz, htree_stanford.npz, convert_golden.npz, logits.npz, grads.npz,
 htree_sha256.json, meta.json.
 """
 from __future__ import annotations
@@ -204,6 +204,15 @@ def main():
             logits[f"{case}|{k}"] = o.numpy().astype(np.float32)
         print(f"{case:18s} {cls:32s} -> {[tuple(o.shape) for o in outs]}")
     np.savez_compressed(os.path.join(HERE, "logits.npz"), **logits)
+
+    # ---- 6. gradient fingerprints of the reference's own model classes (training parity)
+    grads = {}
+    for case, (cls, kw, inp) in cases.CASES.items():
+        model = cases.build_model(ref_models, case)
+        for name, v in cases.grad_fingerprint(model, cases.build_input(inp)).items():
+            grads[f"{case}|{name}"] = v
+        print(f"{case:18s} gradient fingerprint of {sum(1 for k in grads if k.startswith(case + '|'))} parameters")
+    np.savez_compressed(os.path.join(HERE, "grads.npz"), **grads)
 
     with open(os.path.join(HERE, "meta.json"), "w") as f:
         json.dump(meta, f, indent=1, sort_keys=True)
