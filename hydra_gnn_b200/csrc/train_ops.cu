@@ -308,7 +308,8 @@ extern "C" int hg_linear_wgrad(const float* dy, int64_t lddy, const float* x, in
         const dim3 grid(tn, tk, splits);
         if (use_fma) {
             k_wgrad<<<grid, kWgThreads, 0, stream>>>(dy, lddy, x, ldx, M, N, K, dw, lddw, rows);
-        } else if (N >= 2 && K >= 2 && lddy % 2 == 0 && ldx % 2 == 0 && aligned(dy, 8) && aligned(x, 8)) {
+        } else if (N % 2 == 0 && K % 2 == 0 && lddy % 2 == 0 && ldx % 2 == 0 && aligned(dy, 8) && aligned(x, 8)) {
+            // float2 loads: with an odd width the last column would share its pair with the clamp and load the wrong one
             k_wgrad_mma<true><<<grid, kMThreads, 0, stream>>>(dy, lddy, x, ldx, M, N, K, dw, lddw, rows);
         } else {
             k_wgrad_mma<false><<<grid, kMThreads, 0, stream>>>(dy, lddy, x, ldx, M, N, K, dw, lddw, rows);
