@@ -111,3 +111,102 @@ def heterogeneous_htree_to_homogeneous(data: HeteroData) -> Data:
     out.room_mask = out.node_type == rv
     out.object_mask = out.node_type == ov
     return out
+
+
+def batched_htree_to_homogeneous(batch: HeteroData) -> Data:
+    """``Batch.from_data_list([heterogeneous_htree_to_homogeneous(t) for t in trees])`` computed from
+    ``batch = Batch.from_data_list(trees)`` (or ``htree.generate_htree_batch``) in one pass of tensor ops
+    instead of a Python loop over graphs (mp3d_dataset.py:72-119 applied per graph, then PyG's collate):
+    graph g's nodes are its node types in store order, its edges the relations in store order, split into
+    init / pool / tree by the endpoint types.  Bit-identical to the per-graph route (tests/test_host.py)."""
+    node_types = [t for t in batch.node_types if "x" in batch[t]]
+    assert "object_virtual" in node_types and "room_virtual" in node_types
+    dev = batch[node_types[0]].x.device
+    ptrs = {}
+    for t in node_types:
+        st = batch[t]
+        if "ptr" in st:
+            ptrs[t] = st.ptr.long().to(dev)
+        else:
+            ptrs[t] = torch.tensor([0, int(st.num_nodes)], dtype=torch.long, device=dev)
+    G = int(ptrs[node_types[0]].numel()) - 1
+    type_off, cum = {}, torch.zeros(G, dtype=torch.long, device=dev)
+    for t in node_types:
+        type_off[t] = cum
+        cum = cum + (ptrs[t][1:] - ptrs[t][:-1])
+    ptr = torch.zeros(G + 1, dtype=torch.long, device=dev)
+    ptr[1:] = cum.cumsum(0)
+    N = int(ptr[-1])
+    # homogeneous index of every node of every type
+    graph_of, place = {}, {}
+    for t in node_types:
+        n = int(ptrs[t][-1])
+        g = torch.repeat_interleave(torch.arange(G, device=dev), ptrs[t][1:] - ptrs[t][:-1], output_size=n)
+        graph_of[t] = g
+        place[t] = ptr[:-1][g] + type_off[t][g] + (torch.arange(n, device=dev) - ptrs[t][g])
+    out = Data()
+    # ---- edges: per graph, relations in store order (a stable sort by (graph, relation))
+    rels = [et for et in batch.edge_types if "edge_index" in batch[et]]
+    K = len(batch.edge_types)
+    virtual = ("object_virtual", "room_virtual")
+    src, dst, keys, init, pool = [], [], [], [], []
+    for k, et in enumerate(batch.edge_types):
+        if et not in rels:
+            continue
+        ei = batch[et].edge_index.long()
+        src.append(place[et[0]][ei[0]])
+        dst.append(place[et[2]][ei[1]])
+        keys.append(graph_of[et[0]][ei[0]] * K + k)
+        init.append(torch.full((ei.size(1),), et[0] in virtual, dtype=torch.bool, device=dev))
+        pool.append(torch.full((ei.size(1),), et[2] in virtual, dtype=torch.bool, device=dev))
+    tree = None
+    if rels:
+        order = torch.sort(torch.cat(keys), stable=True).indices
+        edges = torch.stack([torch.cat(src), torch.cat(dst)])[:, order]
+        init, pool = torch.cat(init)[order], torch.cat(pool)[order]
+        tree = ~(init | pool)
+        out.edge_index = edges[:, tree]
+    # ---- node attributes present in every store with one trailing shape (x zero-padded to the widest)
+    width = max(int(batch[t].x.size(1)) for t in node_types)
+    first = batch[node_types[0]]
+    names = [k for k, v in first.items() if torch.is_tensor(v) and v.dim() >= 1 and k not in ("batch", "ptr")]
+    if "y" in batch["room_virtual"] and "y" not in names:
+        names.append("y")
+    for key in names:
+        vals = []
+        for t in node_types:
+            w = batch[t].get(key)
+            if key == "y" and w is None and "y" in batch["room_virtual"]:
+                y = batch["room_virtual"].y
+                w = -torch.ones(int(ptrs[t][-1]), dtype=y.dtype, device=dev)
+            if not torch.is_tensor(w):
+                vals = None
+                break
+            vals.append(w)
+        if vals is None:
+            continue
+        trail = (width,) if key == "x" else tuple(vals[0].shape[1:])
+        if key != "x" and any(tuple(w.shape[1:]) != trail for w in vals):
+            continue
+        buf = torch.zeros((N,) + trail, dtype=vals[0].dtype, device=dev)
+        for t, w in zip(node_types, vals):
+            if key == "x":
+                buf[place[t], : w.size(1)] = w
+            else:
+                buf[place[t]] = w
+        out[key] = buf
+    if rels and all("edge_attr" in batch[et] for et in rels):
+        out.edge_attr = torch.cat([batch[et].edge_attr for et in rels], dim=0)[order][tree, :]
+    node_type = torch.empty(N, dtype=torch.long, device=dev)
+    for i, t in enumerate(node_types):
+        node_type[place[t]] = i
+    out.node_type = node_type
+    if rels:
+        out.init_edge_index = edges[:, init]
+        out.pool_edge_index = edges[:, pool]
+    out.room_mask = node_type == node_types.index("room_virtual")
+    out.object_mask = node_type == node_types.index("object_virtual")
+    out.batch = torch.repeat_interleave(torch.arange(G, device=dev), ptr[1:] - ptr[:-1], output_size=N)
+    out.ptr = ptr
+    out.num_graphs = G
+    return out

@@ -150,6 +150,35 @@ def test_batched_build_equals_collate_of_single_builds():
         assert torch.equal(a[key], b[key]), key
 
 
+def test_batched_homogeneous_conversion_equals_per_graph_route():
+    """convert.batched_htree_to_homogeneous(one batched H-tree) == Batch.from_data_list of the reference's per-graph
+    heterogeneous_htree_to_homogeneous (mp3d_dataset.py:72-119; train_mp3d.py:134-135 applies it per graph and the
+    DataLoader collates): every attribute, bit for bit, with and without the `y` fill of -1."""
+    ids = list(range(40))
+    for with_y in (False, True):
+        trees = [htree.generate_htree(synth.synth_mp3d_batch([i])) for i in ids]
+        whole = htree.generate_htree_batch(synth.synth_mp3d_batch(ids))
+        if with_y:
+            for t in trees + [whole]:
+                t["room_virtual"].y = t["room_virtual"].label.long()
+        want = Batch.from_data_list([convert.heterogeneous_htree_to_homogeneous(t) for t in trees])
+        got = convert.batched_htree_to_homogeneous(whole)
+        assert sorted(want.keys()) == sorted(got.keys())
+        assert ("y" in got) == with_y
+        for key in want.keys():
+            a, b = want[key], got[key]
+            if torch.is_tensor(a):
+                assert a.dtype == b.dtype and torch.equal(a, b), key
+            else:
+                assert a == b, key
+    # a single un-batched tree (no ptr) is the one-graph case
+    one = htree.generate_htree(synth.synth_mp3d_batch([3]))
+    want = convert.heterogeneous_htree_to_homogeneous(htree.generate_htree(synth.synth_mp3d_batch([3])))
+    got = convert.batched_htree_to_homogeneous(one)
+    for key in want.keys():
+        assert torch.equal(want[key], got[key]), key
+
+
 def test_htree_structure_invariants_on_a_larger_batch():
     """Size-independent properties at a size the reference takes minutes for (256 graphs): the leaves of every H-tree cover every source node at least once, virtual nodes are one per source node in source order."""
     ids = list(range(1000, 1256))

@@ -65,11 +65,11 @@ def main():
     t2 = time.perf_counter()
     out["htree_builder"] = {"seconds_batched_call": round(t2 - t1, 3), "graphs_per_s": round(args.graphs / (t2 - t1)),
                             "threads": os.cpu_count(), "synth_seconds": round(t1 - t0, 3)}
-    # the homogeneous form needs per-graph conversion + collate (reference order of the flat numbering)
-    singles = [synth.synth_mp3d_batch([g]) for g in range(args.graphs)]
-    trees = [htree.generate_htree(s) for s in singles]
-    hom = Batch.from_data_list([convert.heterogeneous_htree_to_homogeneous(t) for t in trees])
-    del singles, trees
+    # the homogeneous form (reference: per-graph conversion + collate) from the batched H-tree in one pass;
+    # tests/test_htree.py pins it bit-exactly to the per-graph route, and --check below uses that route
+    t3 = time.perf_counter()
+    hom = convert.batched_htree_to_homogeneous(het)
+    out["htree_builder"]["homogeneous_conversion_seconds"] = round(time.perf_counter() - t3, 3)
     out["sizes"] = {"hetero_nodes": {t: int(het[t].x.size(0)) for t in het.node_types},
                     "hetero_edges": {et[1]: int(het[et].edge_index.size(1)) for et in het.edge_types},
                     "homogeneous_nodes": int(hom.x.size(0)), "tree_edges": int(hom.edge_index.size(1)),
