@@ -9,6 +9,11 @@
 #include <cstdlib>
 
 namespace hg {
+
+// wgrad_tc.cu: the tcgen05 variant (opt-in, HG_WGRAD_TC=1)
+int wgrad_tc(const float* dy, int64_t lddy, const float* x, int64_t ldx, int32_t M, int32_t N, int32_t K, float* dw,
+             int64_t lddw, cudaStream_t stream);
+
 namespace {
 
 constexpr int kTN = 64, kTK = 64, kTM = 16, kWgThreads = 256;
@@ -289,6 +294,12 @@ extern "C" int hg_linear_wgrad(const float* dy, int64_t lddy, const float* x, in
         k_zero_rows<<<static_cast<unsigned>(g < sms * 8 ? g : sms * 8), 256, 0, stream>>>(dw, lddw, N, K);
     }
     if (M > 0) {
+        // opt-in tcgen05 variant (not yet run on hardware, see wgrad_tc.cu); read per call so one process can A/B
+        const char* tc_env = getenv("HG_WGRAD_TC");
+        if (tc_env && tc_env[0] == '1') {
+            const int rc = check_launch();  // the zeroing launch
+            return rc != HG_OK ? rc : wgrad_tc(dy, lddy, x, ldx, M, N, K, dw, lddw, stream);
+        }
         static const bool use_fma = getenv("HG_WGRAD_FMA") != nullptr;  // A/B: the CUDA-core variant
         const int tn = ceil_div(N, kMN), tk = ceil_div(K, kMK);
         // one wave: as many row splits as fit the resident CTA slots (a 2nd, nearly empty wave doubles the time)
