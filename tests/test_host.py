@@ -42,6 +42,41 @@ def test_library_exports_every_declared_symbol():
         assert h.hg_sizeof(which) == ctypes.sizeof(st)
 
 
+def test_training_entry_points_reject_bad_arguments_on_the_host():
+    """Error behaviour of the training ABI (include/hydra_gnn_b200.h): argument checks run before any CUDA call and
+    return the documented negative codes (no launch, so this runs without a GPU)."""
+    import ctypes as C
+
+    h = _lib.load_shared_object()
+    EINVAL, EUNSUPPORTED = -1, -6
+    assert h.hg_strerror(EINVAL) == b"invalid argument" and b"unsupported" in h.hg_strerror(EUNSUPPORTED)
+    # hg_linear_wgrad: negative sizes, leading dimensions shorter than the row
+    assert h.hg_linear_wgrad(None, 0, None, 0, -1, 4, 4, None, 4, 0, None) == EINVAL
+    assert h.hg_linear_wgrad(None, 2, None, 4, 8, 4, 4, None, 4, 0, None) == EINVAL
+    assert h.hg_linear_wgrad(None, 4, None, 4, 8, 4, 4, None, 2, 0, None) == EINVAL
+    assert h.hg_linear_wgrad(None, 4, None, 4, 8, 4, 4, None, 4, 0, None) == EINVAL  # NULL dW
+    assert h.hg_linear_wgrad(None, 4, None, 4, 8, 0, 4, None, 4, 0, None) == 0       # empty product: nothing to do
+    # hg_adam_step: n < 0; step < 1 without a device counter
+    assert h.hg_adam_step(None, None, None, None, -1, 0.1, 0.9, 0.999, 1e-8, 0.0, 1.0, 1, None, None) == EINVAL
+    assert h.hg_adam_step(None, None, None, None, 5, 0.1, 0.9, 0.999, 1e-8, 0.0, 1.0, 0, None, None) == EINVAL
+    assert h.hg_adam_step(None, None, None, None, 0, 0.1, 0.9, 0.999, 1e-8, 0.0, 1.0, 1, None, None) == 0
+    # hg_gat_train_*: NULL, head / width limits of the kernels, dropout probability outside [0, 1)
+    assert h.hg_gat_train_fwd(None, None) == EINVAL and h.hg_gat_train_bwd(None, None) == EINVAL
+    a = _lib.GatTrainArgs()
+    a.n_rel, a.n_dst, a.H, a.C = 1, 0, 5, 8
+    assert h.hg_gat_train_fwd(C.byref(a), None) == EUNSUPPORTED   # more than 4 heads
+    a.H, a.C = 4, 65
+    assert h.hg_gat_train_fwd(C.byref(a), None) == EUNSUPPORTED   # H * C > 256
+    a.H, a.C, a.dropout_p = 2, 8, 1.0
+    assert h.hg_gat_train_fwd(C.byref(a), None) == EINVAL
+    a.dropout_p, a.n_rel = 0.0, 0
+    assert h.hg_gat_train_fwd(C.byref(a), None) == EINVAL
+    assert h.hg_csr_transpose_map(None, None, None, -1, None, None, None, 0, 0, None, None, None) == EINVAL
+    assert h.hg_csr_transpose_map(None, None, None, 0, None, None, None, 0, 0, None, None, None) == 0
+    assert h.hg_act_bwd(None, 0, None, 0, -1, 4, 0, None, 0, None, None) == EINVAL
+    assert h.hg_act_bwd(None, 0, None, 0, 0, 4, 0, None, 0, None, None) == 0
+
+
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
 def test_product_fails_loudly_without_gpu():
     net = hg.HeterogeneousNetwork(**cases.CASES["mgat"][1]).eval()
