@@ -177,13 +177,13 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
         if c.lin_edge is not None and edge_attr is not None and edge_attr.get(et) is not None:
             raise NotImplementedError("training with edge attributes (GAT_edge) is not implemented")
         T = et[2]
-        if c.heads > 4 or c.heads * _pad4(c.out_channels) > 256:
-            raise NotImplementedError(f"GAT training kernels take heads <= 4 and heads * channels <= 256 (got {c.heads} x "
-                                      f"{c.out_channels}: e.g. the 306-channel pre_mp of the homogeneous Neural Tree)")
         # head mean with C % 4 != 0 (the 26-class layer): the per-head blocks of the projection are padded to a multiple
         # of 4 channels (zero weight rows, zero bias) so the float4 kernels apply; the pad columns of the output are 0
         # and sliced away below
         Cp = _pad4(c.out_channels) if (not c.concat or c.heads == 1) else c.out_channels
+        if c.heads > 4 or c.heads * Cp > 256:  # the limits hg_gat_train_fwd / _bwd validate (HG_EUNSUPPORTED)
+            raise NotImplementedError(f"GAT training kernels take heads <= 4 and heads * channels <= 256 (got {c.heads} x "
+                                      f"{c.out_channels}: e.g. the 306-channel pre_mp of the homogeneous Neural Tree)")
         cfg.C_real[T] = c.out_channels
         sig = (c.heads, Cp, c.concat, c.negative_slope, c.dropout if c.training else 0.0)
         if T in cfg.H and (cfg.H[T], cfg.C[T], cfg.concat[T], cfg.slope[T], cfg.dropout[T]) != sig:
