@@ -7,7 +7,14 @@
 // (4 * out-width bytes per edge).
 #include "hg_common.cuh"
 
+#include <cstdlib>
+
 namespace hg {
+
+// gat_train_tile.cu: pass 1 of the backward as a tile kernel (opt-in, HG_GAT_BWD_TILE=1)
+bool gat_bwd_dst_tile_ok(const hg_gat_train_args* a);
+int gat_bwd_dst_tile(const hg_gat_train_args* a, cudaStream_t stream);
+
 namespace {
 
 constexpr int kWarps = 8;
@@ -839,7 +846,11 @@ extern "C" int hg_gat_train_bwd(const hg_gat_train_args* a, void* stream_) {
     const bool hk = a->C == 64 && a->H == nv;
     if (a->n_dst > 0) {
         // grid-stride: the bias gradient is reduced per block
-        if (fast) {
+        const char* tile_env = getenv("HG_GAT_BWD_TILE");  // opt-in, not yet run on hardware (gat_train_tile.cu)
+        if (tile_env && tile_env[0] == '1' && gat_bwd_dst_tile_ok(a)) {
+            rc = gat_bwd_dst_tile(a, stream);
+            if (rc != HG_OK) return rc;
+        } else if (fast) {
             // grid-stride over whole waves: 4 resident CTAs per SM (launch bounds), two waves' worth of CTAs
             const unsigned grid = row_grid(ceil_div(a->n_dst, 2), 8);
 #define CALL4(NV, HKV) k_bwd_dst_v4<NV, HKV><<<grid, kThreads, 0, stream>>>(*a)
