@@ -50,15 +50,23 @@ struct HTreeAcc {
             Attr& a = jth.at(root);
             if (!a.is_list) { a.is_list = true; a.list.assign(1, a.single); }
             if (std::find(a.list.begin(), a.list.end(), room) == a.list.end()) continue;
-            Graph g = copy_of(whole(ojth));
+            // g = ojth.copy(); relabel to base.. (new_labels = dict(zip(range(n), range(base, base + n))));
+            // self.jth = nx.compose(self.jth, g).  The reference rebuilds the whole accumulated tree here; every such
+            // rebuild (copy / relabel / compose) re-adds edges in EdgeView order, which keeps, for every node, the
+            // relative order of its LATER neighbours (later in node order) and nothing else of the adjacency order --
+            // and that is all the final node / edge lists depend on (they are produced by one more EdgeView pass in
+            // disjoint_union).  Appending the relabelled nodes and edges in place preserves exactly that, without
+            // the O(|jth|) rebuild per object component.
             const int base = (int)jth.n();
-            // new_labels = dict(zip(range(n), range(base, base + n)))
-            const int n = (int)g.n();
-            Graph rel = relabel_copy(g, [&](int k) { return k < n ? base + k : k; });
-            Graph merged;  // nx.compose(self.jth, g)
-            absorb(merged, jth, false);
-            absorb(merged, rel, false);
-            jth = std::move(merged);
+            const int n = (int)ojth.n();
+            auto map = [&](int k) { return k < n ? base + k : k; };
+            for (int k : ojth.order) {
+                const int mk = map(k);
+                const bool had = jth.has_node(mk);
+                const int s = jth.add_node(mk);
+                if (!had) jth.attr[s] = ojth.at(k);
+            }
+            ojth.each_edge([&](int u, int v) { jth.add_edge(map(u), map(v)); });
             for (int r : oroots) jth.add_edge(root, base + r);
         }
     }
