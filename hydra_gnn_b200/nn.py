@@ -506,6 +506,9 @@ class GINConv(nn.Module):
 
 
 def run_gin(conv: GINConv, x: Tensor, csr: CSR, act: str = None, bn: "BatchNorm" = None) -> Tensor:
+    bn_train = bn is not None and bn.module.training
+    if bn_train or _train.wants_grad(x, *conv.parameters(), *(bn.parameters() if bn is not None else ())):
+        return _train.run_gin_train(conv, x, csr, act=act, bn=bn)
     h = ops.seg_reduce(x, csr, "sum", x_self=x, self_coef=conv.eps, self_coef_add=1.0)
     layers = list(conv.nn)
     lin_idx = [k for k, m in enumerate(layers) if isinstance(m, nn.Linear)]

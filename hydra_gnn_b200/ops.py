@@ -43,7 +43,7 @@ def _require_no_grad(*tensors):
     if torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors):
         raise NotImplementedError(
             "this operator has no backward here: the raw ops are forward-only, gradients are recorded by "
-            "hydra_gnn_b200.train (GAT / GraphSAGE / GCN model classes; GIN and GAT_edge training are not implemented). "
+            "hydra_gnn_b200.train (GAT / GraphSAGE / GCN / GIN model classes; GAT_edge training is not implemented). "
             "Call under torch.no_grad() or model.eval() with frozen parameters")
 
 

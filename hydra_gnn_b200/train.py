@@ -411,3 +411,34 @@ def run_hetero_sage_train(convs, rels: Sequence[EdgeType], x: Dict[str, Tensor],
 def run_gcn_train(conv, x: Tensor, csr: CSR, act: str = None) -> Tensor:
     y = linear_multi([(x, conv.lin.weight)])
     return seg_reduce(y, csr, "sum", src_scale=csr.inv_sqrt_deg, dst_scale=csr.inv_sqrt_deg, bias=conv.bias, act=act)
+
+
+def run_gin_train(conv, x: Tensor, csr: CSR, act: str = None, bn=None) -> Tensor:
+    """GINConv, differentiable: ``nn((1 + eps) x_i + sum_j x_j)`` -- the neighbour sum is
+    ``hg_seg_reduce`` (backward: the same kernel over the reversed CSR), the self term is a torch elementwise op
+    (it carries the gradient of a trainable ``eps``), every Linear of the MLP is ``hg_linear`` with its ReLU fused.
+    ``bn`` (HomogeneousNetwork, homogeneous_network.py:94-97,133-134): PyG ``BatchNorm`` between the last Linear and
+    the layer's activation -- batch statistics in training mode, torch's ``BatchNorm1d`` (library call; GIN is on
+    none of the benchmark configurations)."""
+    h = seg_reduce(x, csr, "sum") + (1.0 + conv.eps) * x
+    layers = list(conv.nn)
+    lin_idx = [k for k, m in enumerate(layers) if isinstance(m, nn.Linear)]
+    for k, m in enumerate(layers):
+        if isinstance(m, nn.Linear):
+            last = k == lin_idx[-1]
+            fuse_relu = (not last) and k + 1 < len(layers) and isinstance(layers[k + 1], nn.ReLU)
+            fused = "relu" if fuse_relu else (act if (last and bn is None) else None)
+            h = linear_multi([(h, m.weight)], m.bias, fused)
+        elif isinstance(m, nn.ReLU):
+            continue  # fused into the preceding projection
+        else:
+            raise NotImplementedError(f"GINConv.nn may hold Linear / ReLU only, got {type(m).__name__}")
+    if bn is not None:
+        h = bn.module(h)
+        if act == "relu":
+            h = torch.relu(h)
+        elif act == "elu":
+            h = torch.nn.functional.elu(h)
+        elif act is not None:
+            raise NotImplementedError(f"activation {act!r}")
+    return h

@@ -1,0 +1,226 @@
+"""Host logic of the training glue (hydra_gnn_b200/train.py) on CPU: the autograd Functions composed over plain-torch
+stand-ins of the CUDA operators (tests/cpu_backend.py) must reproduce the outputs AND the gradients of the oracle's
+layers (oracle/pyg/nn.py, PyG 2.3.1 semantics) -- what each Function saves, which operand receives which gradient, how
+degrees / normalisation / row maps / a trainable eps enter the backward.  The kernels are checked on the GPU
+(tests/test_gpu_train.py); this file needs none.
+"""
+import os
+import sys
+
+import pytest
+import torch
+from torch import nn
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+import cpu_backend as cb  # noqa: E402
+from hydra_gnn_b200 import nn as hnn, train  # noqa: E402
+from oracle.pyg import nn as onn  # noqa: E402  (checker)
+
+
+def _graph(n_src, n_dst, n_edges, seed, bipartite=False):
+    g = torch.Generator().manual_seed(seed)
+    src = torch.randint(0, n_src, (n_edges,), generator=g)
+    dst = torch.randint(0, max(n_dst - 3, 1), (n_edges,), generator=g)  # the last rows stay isolated
+    if not bipartite:
+        keep = src != dst
+        src, dst = src[keep], dst[keep]
+    ei = torch.unique(torch.stack([src, dst]), dim=1)  # simple graph
+    return ei[:, torch.randperm(ei.size(1), generator=g)]  # unsorted, as the loaders emit it
+
+
+def _pair(oracle_conv, product_conv):
+    missing = product_conv.load_state_dict(oracle_conv.state_dict(), strict=False)
+    assert not missing.missing_keys, missing
+    return oracle_conv, product_conv
+
+
+def _check(out_ref, out, params_ref, params, inputs_ref, inputs, seed=0):
+    torch.testing.assert_close(out, out_ref, rtol=1e-5, atol=1e-6)
+    w = torch.randn(out_ref.shape, generator=torch.Generator().manual_seed(seed))
+    (out_ref * w).sum().backward()
+    (out * w).sum().backward()
+    for a, b in zip(inputs_ref, inputs):
+        torch.testing.assert_close(b.grad, a.grad, rtol=1e-4, atol=1e-6)
+    ref = dict(params_ref)
+    n = 0
+    for name, p in params:
+        if name in ref and ref[name].grad is not None:
+            assert p.grad is not None, name
+            torch.testing.assert_close(p.grad, ref[name].grad, rtol=1e-4, atol=1e-6, msg=lambda m, name=name: f"{name}: {m}")
+            n += 1
+    assert n > 0
+
+
+@pytest.mark.parametrize("act", [None, "relu", "elu"])
+def test_sage_layer_gradients(act):
+    torch.manual_seed(1)
+    ei = _graph(40, 40, 160, 1)
+    o, p = _pair(onn.SAGEConv(12, 20), hnn.SAGEConv(12, 20))
+    x_ref = torch.randn(40, 12, requires_grad=True)
+    x = x_ref.detach().clone().requires_grad_(True)
+    with cb.patched_ops():
+        out = train.run_sage_train(p, x, x, cb.build_csr(ei, 40, 40), act=act)
+        _check(cb._act(o(x_ref, ei), act), out, o.named_parameters(), p.named_parameters(), [x_ref], [x])
+
+
+def test_bipartite_sage_layer_gradients():
+    torch.manual_seed(2)
+    ei = _graph(30, 17, 90, 2, bipartite=True)
+    o, p = _pair(onn.SAGEConv((9, 5), 11), hnn.SAGEConv((9, 5), 11))
+    xs_ref, xd_ref = torch.randn(30, 9, requires_grad=True), torch.randn(17, 5, requires_grad=True)
+    xs, xd = xs_ref.detach().clone().requires_grad_(True), xd_ref.detach().clone().requires_grad_(True)
+    with cb.patched_ops():
+        out = train.run_sage_train(p, xs, xd, cb.build_csr(ei, 30, 17), act="relu")
+        _check(torch.relu(o((xs_ref, xd_ref), ei)), out, o.named_parameters(), p.named_parameters(),
+               [xs_ref, xd_ref], [xs, xd])
+
+
+@pytest.mark.parametrize("group", ["sum", "mean"])
+def test_hetero_sage_group_gradients(group):
+    """Two relations into one node type: the root weights / biases are combined in parameter space (torch autograd),
+    the neighbour means go through one K-segmented projection."""
+    torch.manual_seed(3)
+    ets = [("a", "r1", "b"), ("b", "r2", "b")]
+    ei = {ets[0]: _graph(25, 18, 70, 3, bipartite=True), ets[1]: _graph(18, 18, 60, 4)}
+    dims = {"a": 7, "b": 6}
+    oc = {et: onn.SAGEConv((dims[et[0]], dims[et[2]]), 10) for et in ets}
+    pc = {et: hnn.SAGEConv((dims[et[0]], dims[et[2]]), 10) for et in ets}
+    for et in ets:
+        _pair(oc[et], pc[et])
+    x_ref = {"a": torch.randn(25, 7, requires_grad=True), "b": torch.randn(18, 6, requires_grad=True)}
+    x = {k: v.detach().clone().requires_grad_(True) for k, v in x_ref.items()}
+    outs = [oc[et]((x_ref[et[0]], x_ref[et[2]]), ei[et]) for et in ets]
+    ref = torch.nn.functional.elu(sum(outs) / (len(outs) if group == "mean" else 1))
+    with cb.patched_ops():
+        csr = {et: cb.build_csr(ei[et], x[et[0]].size(0), 18) for et in ets}
+        out = train.run_hetero_sage_train(pc, ets, x, csr, act="elu", group=group)["b"]
+        named_ref = [(f"{et[1]}.{n}", q) for et in ets for n, q in oc[et].named_parameters()]
+        named = [(f"{et[1]}.{n}", q) for et in ets for n, q in pc[et].named_parameters()]
+        _check(ref, out, named_ref, named, [x_ref["a"], x_ref["b"]], [x["a"], x["b"]])
+
+
+@pytest.mark.parametrize("act", [None, "relu"])
+def test_gcn_layer_gradients(act):
+    torch.manual_seed(5)
+    ei = _graph(36, 36, 150, 5)
+    o, p = _pair(onn.GCNConv(8, 14), hnn.GCNConv(8, 14))
+    x_ref = torch.randn(36, 8, requires_grad=True)
+    x = x_ref.detach().clone().requires_grad_(True)
+    with cb.patched_ops():
+        csr = cb.build_csr(ei, 36, 36, self_loops=True, norm=True)
+        out = train.run_gcn_train(p, x, csr, act=act)
+        _check(cb._act(o(x_ref, ei), act), out, o.named_parameters(), p.named_parameters(), [x_ref], [x])
+
+
+def _mlp(i, h, o):
+    return nn.Sequential(nn.Linear(i, h), nn.ReLU(), nn.Linear(h, o))
+
+
+@pytest.mark.parametrize("train_eps", [False, True])
+@pytest.mark.parametrize("act", [None, "elu"])
+def test_gin_layer_gradients(train_eps, act):
+    torch.manual_seed(6)
+    ei = _graph(33, 33, 120, 6)
+    o, p = _pair(onn.GINConv(_mlp(7, 16, 9), eps=0.3, train_eps=train_eps),
+                 hnn.GINConv(_mlp(7, 16, 9), eps=0.3, train_eps=train_eps))
+    x_ref = torch.randn(33, 7, requires_grad=True)
+    x = x_ref.detach().clone().requires_grad_(True)
+    with cb.patched_ops():
+        out = train.run_gin_train(p, x, cb.build_csr(ei, 33, 33), act=act)
+        _check(cb._act(o(x_ref, ei), act), out, o.named_parameters(), p.named_parameters(), [x_ref], [x])
+    if train_eps:
+        assert p.eps.grad is not None and p.eps.grad.abs().item() > 0
+
+
+def test_gin_layer_with_batch_norm_in_training_mode():
+    """HomogeneousNetwork's GIN layers: conv -> BatchNorm (batch statistics) -> activation
+    (homogeneous_network.py:94-97,133-134); running statistics advance exactly as the oracle's do."""
+    torch.manual_seed(7)
+    ei = _graph(50, 50, 200, 7)
+    o, p = _pair(onn.GINConv(_mlp(6, 12, 12), eps=0.0, train_eps=True), hnn.GINConv(_mlp(6, 12, 12), eps=0.0, train_eps=True))
+    obn, pbn = onn.BatchNorm(12), hnn.BatchNorm(12)
+    pbn.load_state_dict(obn.state_dict())
+    obn.train(), pbn.train()
+    x_ref = torch.randn(50, 6, requires_grad=True)
+    x = x_ref.detach().clone().requires_grad_(True)
+    with cb.patched_ops():
+        out = train.run_gin_train(p, x, cb.build_csr(ei, 50, 50), act="relu", bn=pbn)
+        ref = torch.relu(obn(o(x_ref, ei)))
+        named_ref = list(o.named_parameters()) + [("bn." + n, q) for n, q in obn.named_parameters()]
+        named = list(p.named_parameters()) + [("bn." + n, q) for n, q in pbn.named_parameters()]
+        _check(ref, out, named_ref, named, [x_ref], [x])
+    torch.testing.assert_close(pbn.module.running_mean, obn.module.running_mean)
+    torch.testing.assert_close(pbn.module.running_var, obn.module.running_var)
+
+
+def test_run_gin_dispatches_to_the_training_form():
+    """nn.run_gin takes the differentiable route when a gradient is wanted or the BatchNorm is in training mode
+    (the inference route folds running statistics into the projection's epilogue and refuses batch statistics)."""
+    torch.manual_seed(8)
+    ei = _graph(20, 20, 60, 8)
+    conv, bn = hnn.GINConv(_mlp(5, 8, 8), train_eps=True), hnn.BatchNorm(8)
+    x = torch.randn(20, 5)
+    with cb.patched_ops():
+        csr = cb.build_csr(ei, 20, 20)
+        y = hnn.run_gin(conv, x, csr, act="relu", bn=bn.train())
+        assert y.requires_grad and y.shape == (20, 8)
+        with torch.no_grad():
+            y2 = hnn.run_gin(conv, x, csr, act="relu", bn=bn.train())  # batch statistics, no tape
+        assert not y2.requires_grad
+        torch.testing.assert_close(y2, y.detach())
+
+
+def test_seg_reduce_row_map_gradient_reaches_only_mapped_rows():
+    """LeafPool / last-layer row selection: rows the forward did not compute carry no gradient."""
+    torch.manual_seed(9)
+    ei = _graph(28, 28, 100, 9)
+    x_ref = torch.randn(28, 5, requires_grad=True)
+    x = x_ref.detach().clone().requires_grad_(True)
+    rows = torch.tensor([3, 0, 11, 12, 20], dtype=torch.int32)
+    bias_ref = torch.randn(5, requires_grad=True)
+    bias = bias_ref.detach().clone().requires_grad_(True)
+    src, dst = ei[0], ei[1]
+    deg = torch.bincount(dst, minlength=28).clamp(min=1).float()
+    full = torch.zeros(28, 5).index_add(0, dst, x_ref.index_select(0, src)) / deg[:, None]
+    ref = torch.relu(full.index_select(0, rows.long()) + bias_ref)
+    with cb.patched_ops():
+        out = train.seg_reduce(x, cb.build_csr(ei, 28, 28), "mean", row_map=rows, bias=bias, act="relu")
+        _check(ref, out, [("bias", bias_ref)], [("bias", bias)], [x_ref], [x])
+
+
+# ------------------------------------------------------------------------------ whole models against the REFERENCE's gradients
+sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+import numpy as np  # noqa: E402
+
+import cases  # noqa: E402
+import hydra_gnn_b200 as hg  # noqa: E402
+
+_NON_GAT_CASES = ["msage_all", "nt_hom_gcn", "nt_hom_sage", "hom_gcn", "hom_gin", "hom_sage_all"]
+
+
+@pytest.mark.parametrize("case", _NON_GAT_CASES)
+def test_model_glue_reproduces_reference_gradient_fingerprints(case):
+    """The product's model classes (plan requests, layer wiring, row selection, heads, the autograd Functions), run over
+    the CPU stand-ins, against tests/golden/grads.npz -- gradient fingerprints computed by the REFERENCE's own model
+    classes (make_golden.py step 6).  GAT cases need the GAT kernels and are checked on the GPU only."""
+    golden = cases.load_golden_grads()[case]
+    with cb.patched_ops():
+        model = cases.build_model(hg, case).train()  # train(): the forward records a tape; dropout off as in the golden run
+        model.dropout = 0.0
+        for m in model.modules():
+            if isinstance(m, hnn.BatchNorm):
+                m.eval()  # running statistics, as in the golden (eval-mode) run
+        fp = cases.grad_fingerprint(model, cases.build_input(cases.CASES[case][2]))
+    checked = 0
+    for name, want in golden.items():
+        got = fp[name]
+        if np.isnan(want).all():
+            assert np.isnan(got).all(), name
+            continue
+        assert abs(want[1]) > 0 or np.allclose(got, 0), name
+        np.testing.assert_allclose(got, want, rtol=0, atol=2e-5 * max(abs(want[1]), 1e-12), err_msg=name)
+        checked += 1
+    assert checked >= 6
