@@ -243,11 +243,8 @@ bool gat_bwd_dst_tile_ok(const hg_gat_train_args* a) {
 int gat_bwd_dst_tile(const hg_gat_train_args* a, cudaStream_t stream) {
     const int width = a->concat ? a->H * a->C : a->C;
     const size_t smem = tile_smem_bytes(a->n_rel, width);
-    static thread_local size_t smem_set = 0;
-    if (smem > smem_set) {
-        HG_CUDA_TRY(cudaFuncSetAttribute(k_bwd_dst_tile, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-        smem_set = smem;
-    }
+    // per call, as linear_tc.cu does: the attribute belongs to the current device's context, not to the thread
+    HG_CUDA_TRY(cudaFuncSetAttribute(k_bwd_dst_tile, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     const int sms = sm_count() > 0 ? sm_count() : 148;
     const int64_t tiles = ceil_div<int64_t>(a->n_dst, kTile);
     const int64_t cap = static_cast<int64_t>(sms) * 8;  // grid-stride: the bias gradient is reduced per CTA

@@ -265,11 +265,8 @@ int wgrad_tc(const float* dy, int64_t lddy, const float* x, int64_t ldx, int32_t
     P.kb_per_split = ceil_div(P.n_kb_total, splits);
     splits = ceil_div(P.n_kb_total, P.kb_per_split);
     const size_t smem = stages * stage_bytes + fixed;
-    static thread_local size_t smem_set = 0;
-    if (smem > smem_set) {
-        HG_CUDA_TRY(cudaFuncSetAttribute(k_wgrad_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-        smem_set = smem;
-    }
+    // per call, as linear_tc.cu does: the attribute belongs to the current device's context, not to the thread
+    HG_CUDA_TRY(cudaFuncSetAttribute(k_wgrad_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     k_wgrad_tc<<<static_cast<unsigned>(tiles * splits), kThreadsW, smem, stream>>>(P);
     return check_launch();
 }
