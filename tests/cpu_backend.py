@@ -135,6 +135,67 @@ def gather_rows(x, rows, act=None, out=None):
     return _act(x.index_select(0, rows.long()), act)
 
 
+def _gat_group(views, n_dst, H, C, concat, group, act, slope):
+    """PyG GATConv per relation (section 9.2 of SURVEY.md) summed / averaged over the relations of one destination
+    type.  views: (xs [n_src, H*C], a_src [n_src, H], a_dst [n_dst, H], csr, bias).  Returns (out, [alpha [E', H]])."""
+    total, alphas = 0, []
+    for xs, a_s, a_d, csr, bias in views:
+        col = csr.col.long()
+        deg = (csr.rowptr[1:] - csr.rowptr[:-1]).long()
+        row_of = torch.repeat_interleave(torch.arange(n_dst), deg)
+        e = torch.nn.functional.leaky_relu(a_s.index_select(0, col) + a_d.index_select(0, row_of), slope)
+        m = torch.full((n_dst, H), float("-inf")).scatter_reduce(0, row_of[:, None].expand(-1, H), e.detach(), "amax")
+        p = torch.exp(e - m.index_select(0, row_of))
+        denom = torch.zeros(n_dst, H).index_add(0, row_of, p)
+        alpha = p / (denom.index_select(0, row_of) + 1e-16)
+        msg = xs.index_select(0, col).view(-1, H, C) * alpha[:, :, None]
+        out = torch.zeros(n_dst, H, C).index_add(0, row_of, msg)
+        out = out.reshape(n_dst, H * C) if concat else out.mean(1)
+        if bias is not None:
+            out = out + bias
+        total = total + out
+        alphas.append(alpha)
+    if group == "mean":
+        total = total / len(views)
+    return _act(total, act), alphas
+
+
+def gat_fused(rels, n_dst, H, Cc, concat, *, group="sum", act=None, neg_slope=0.2, out=None, addend=None,
+              src_shared=False, dropout_p=0.0, seed=0, seed_dev=None):
+    """``ops.gat_fused`` in its training-forward use (saved softmax weights, no attention dropout here)."""
+    assert dropout_p == 0.0 and not src_shared and addend is None and all(r.a_edge is None for r in rels)
+    res, alphas = _gat_group([(r.xs, r.a_src, r.a_dst, r.csr, r.bias) for r in rels], n_dst, H, Cc, concat, group, act,
+                             neg_slope)
+    for r, a in zip(rels, alphas):
+        if r.alpha_out is not None:
+            r.alpha_out[: a.size(0)].copy_(a)
+    return res
+
+
+def gat_train_bwd(rels, dys, n_dst, H, Cc, concat, out, dout, *, group="sum", act=None, neg_slope=0.2, dropout_p=0.0,
+                  seed=0, dbias=None):
+    """``ops.gat_train_bwd``: overwrites each relation's column ranges of (dY_src, dY_dst); ``dbias`` accumulates."""
+    assert dropout_p == 0.0
+    HC = H * Cc
+    with torch.enable_grad():
+        leaves, views = [], []
+        for r in rels:
+            xs = r.y_src[:, r.xs_off: r.xs_off + HC].detach().clone().requires_grad_(True)
+            a_s = r.y_src[:, r.as_off: r.as_off + H].detach().clone().requires_grad_(True)
+            a_d = r.y_dst[:, r.ad_off: r.ad_off + H].detach().clone().requires_grad_(True)
+            leaves += [xs, a_s, a_d]
+            views.append((xs, a_s, a_d, r.csr, None))
+        pre, _ = _gat_group(views, n_dst, H, Cc, concat, group, None, neg_slope)
+        g = act_bwd(dout, out, act)[0] if act is not None else dout
+        grads = torch.autograd.grad(pre, leaves, g)
+    for k, (r, (dys_, dyd_)) in enumerate(zip(rels, dys)):
+        dys_[:, r.xs_off: r.xs_off + HC] = grads[3 * k]
+        dys_[:, r.as_off: r.as_off + H] = grads[3 * k + 1]
+        dyd_[:, r.ad_off: r.ad_off + H] = grads[3 * k + 2]
+    if dbias is not None:
+        dbias += g.sum(0) * (1.0 / len(rels) if group == "mean" else 1.0)
+
+
 def build_csr_specs(specs, overlap=False):
     """``ops.build_csr``: one CSR per CSRSpec + the status word (edges with endpoints out of range: none here)."""
     out = []
@@ -152,7 +213,8 @@ def patched_ops():
     """Swap the stand-ins into ``hydra_gnn_b200.ops`` for the duration of a test."""
     from hydra_gnn_b200 import ops
 
-    names = ("seg_reduce", "linear", "linear_wgrad", "act_bwd", "reversed_csr", "gather_rows", "build_csr")
+    names = ("seg_reduce", "linear", "linear_wgrad", "act_bwd", "reversed_csr", "gather_rows", "build_csr", "gat_fused",
+             "gat_train_bwd")
     standin = dict(globals(), build_csr=build_csr_specs)
     saved = {n: getattr(ops, n) for n in names}
     try:
