@@ -160,6 +160,8 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
                         edge_attr=None) -> Dict[str, Tensor]:
     """Differentiable form of ``nn.run_gat_layer`` (same HeteroConv semantics)."""
     from .nn import GATConv
+    if any(convs[et].heads == 1 and _pad4(convs[et].out_channels) > 256 for et in rels):
+        return _run_wide_single_head(convs, rels, x, csr, act=act, group=group, edge_attr=edge_attr)
 
     cfg = _LayerCfg()
     cfg.rels = list(rels)
@@ -224,7 +226,8 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
             if et[0] != T:
                 continue
             c = convs[et]
-            blocks.append(GATConv.fold(c.att_src, c.lin_src.weight, c.heads, c.out_channels))
+            fs = getattr(c, "fold_src", None)  # a channel chunk of a wide conv carries the whole conv's folded rows
+            blocks.append(fs if fs is not None else GATConv.fold(c.att_src, c.lin_src.weight, c.heads, c.out_channels))
             cfg.as_off[et] = col
             col += c.heads
         for et in rels:
@@ -232,7 +235,8 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
                 continue
             c = convs[et]
             Wd = c.lin_src.weight if et[0] == et[2] else c.lin_dst.weight
-            blocks.append(GATConv.fold(c.att_dst, Wd, c.heads, c.out_channels))
+            fd = getattr(c, "fold_dst", None)
+            blocks.append(fd if fd is not None else GATConv.fold(c.att_dst, Wd, c.heads, c.out_channels))
             cfg.ad_off[et] = col
             col += c.heads
         if _pad4(col) != col:
@@ -250,6 +254,55 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
     for T, o in zip(cfg.dsts, outs):
         res[T] = o if cfg.C[T] == cfg.C_real[T] else o[:, :cfg.C_real[T]]
     return res
+
+
+class _Rows:
+    """Stands where ``run_gat_layer_train`` reads ``conv.lin_src.weight``."""
+
+    def __init__(self, weight: Tensor):
+        self.weight = weight
+
+
+class _ChannelChunk:
+    """Output channels [a, b) of a single-head GATConv as a conv of its own: its rows of the projection and of the
+    bias, and the attention logits of the WHOLE conv (``fold_src`` / ``fold_dst``, read by the packing above)."""
+
+    def __init__(self, conv, a: int, b: int, same_type: bool):
+        from .nn import GATConv
+        C = conv.out_channels
+        self.heads, self.out_channels, self.concat = 1, b - a, conv.concat
+        self.negative_slope, self.dropout, self.training, self.lin_edge = conv.negative_slope, 0.0, conv.training, None
+        self.lin_src = _Rows(conv.lin_src.weight[a:b])
+        self.lin_dst = self.lin_src
+        self.att_src = self.att_dst = None
+        self.bias = conv.bias[a:b] if conv.bias is not None else None
+        self.fold_src = GATConv.fold(conv.att_src, conv.lin_src.weight, 1, C)
+        self.fold_dst = GATConv.fold(conv.att_dst, conv.lin_src.weight if same_type else conv.lin_dst.weight, 1, C)
+
+
+def _run_wide_single_head(convs, rels, x, csr, *, act, group, edge_attr):
+    """A single-head GAT layer wider than the training kernels' 256 columns (the 306-channel ``pre_mp`` of the
+    homogeneous Neural Tree, homogeneous_neural_tree_network.py:63-66,86): with one head the softmax weights are shared
+    by every channel, so the layer is computed in channel chunks -- each chunk a GAT layer over its own columns of the
+    projection with the attention logits of the whole conv -- and the chunks are concatenated.  Exact: the aggregation
+    is per channel, and the softmax backward is linear in ``d alpha = sum_c g_c xs_c``, so the per-chunk contributions to
+    the attention gradients add up in parameter space (torch autograd sums them through the shared folded rows)."""
+    if len(rels) != 1:
+        raise NotImplementedError("a single-head GAT layer wider than 256 channels must be the only relation of its layer")
+    et = rels[0]
+    c = convs[et]
+    if c.training and c.dropout > 0:
+        raise NotImplementedError("attention dropout on a channel-chunked GAT layer (every chunk must draw the same mask)")
+    if c.lin_edge is not None and edge_attr is not None and edge_attr.get(et) is not None:
+        raise NotImplementedError("training with edge attributes (GAT_edge) is not implemented")
+    C = c.out_channels
+    n_chunks = -(-_pad4(C) // 256)
+    step = _pad4(-(-C // n_chunks))
+    outs = []
+    for a in range(0, C, step):
+        chunk = _ChannelChunk(c, a, min(a + step, C), et[0] == et[2])
+        outs.append(run_gat_layer_train({et: chunk}, [et], x, csr, act=act, group=group)[et[2]])
+    return {et[2]: torch.cat(outs, dim=1)}
 
 
 # =============================================================================== optimizer

@@ -322,3 +322,20 @@ def test_homogeneous_gin_gradients_match_oracle():
     for a, b in zip(ref.batch_norms, net.batch_norms):  # running statistics advanced alike (the last one is never applied)
         torch.testing.assert_close(b.module.running_mean.cpu(), a.module.running_mean, rtol=1e-4, atol=1e-5)
         torch.testing.assert_close(b.module.running_var.cpu(), a.module.running_var, rtol=1e-4, atol=1e-5)
+
+
+def test_homogeneous_neural_tree_wide_pre_mp_gradients_match_oracle():
+    """The 306-channel single-head ``pre_mp`` of the homogeneous Neural Tree (homogeneous_neural_tree_network.py:63-66,
+    86) is wider than the GAT training kernels' 256 columns: computed in channel chunks that share the attention logits
+    (train._run_wide_single_head).  Like the GIN test above it was added after the round's GPU budget was spent: the
+    glue reproduces the reference's gradient fingerprints on CPU (tests/test_train_glue.py, case nt_hom_gcn_init), the
+    kernels are the ones the tests above exercise at other widths."""
+    from hydra_gnn_b200 import convert, htree
+    from hydra_gnn_b200.data import Batch
+    trees = [htree.generate_htree(synth.synth_mp3d_batch([g])) for g in range(6)]
+    hom = Batch.from_data_list([convert.heterogeneous_htree_to_homogeneous(t) for t in trees])
+    kw = dict(input_dim=306, output_dim=26, conv_block="GCN", hidden_dim=32, num_layers=3, dropout=0.0,
+              disable_initialization=False)
+    ref, net = _pair(kw, "HomogeneousNeuralTreeNetwork")
+    dev = clone_data(hom, "cuda")
+    _compare_grads(ref, net, lambda: ref(clone_data(hom)), lambda: net(dev), 8)

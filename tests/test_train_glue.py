@@ -198,10 +198,11 @@ import numpy as np  # noqa: E402
 import cases  # noqa: E402
 import hydra_gnn_b200 as hg  # noqa: E402
 
-# every golden case the training path supports (hom_gat: 6 heads, nt_hom_gcn_init: a 306-channel pre_mp -- both outside
-# the GAT training kernels' limits, they raise NotImplementedError; mgat_edge / hom_gat_edge: GAT_edge gradients not built)
+# every golden case the training path supports (hom_gat: 6 heads, outside the GAT training kernels' limit, raises
+# NotImplementedError; mgat_edge / hom_gat_edge: GAT_edge gradients not built).  nt_hom_gcn_init carries the 306-channel
+# single-head pre_mp, computed in channel chunks (train._run_wide_single_head)
 _TRAINABLE_CASES = ["mgat", "msage_all", "nt_het_gat", "nt_het_gat_init", "nt_het_sage_all", "nt_hom_gcn", "nt_hom_sage",
-                    "nt_hom_gat_all", "hom_gcn", "hom_gin", "hom_sage_all"]
+                    "nt_hom_gcn_init", "nt_hom_gat_all", "hom_gcn", "hom_gin", "hom_sage_all"]
 
 
 @pytest.mark.parametrize("case", _TRAINABLE_CASES)
@@ -234,7 +235,7 @@ def test_model_glue_reproduces_reference_gradient_fingerprints(case):
     assert checked >= 6
 
 
-@pytest.mark.parametrize("case", ["hom_gat", "nt_hom_gcn_init", "mgat_edge"])
+@pytest.mark.parametrize("case", ["hom_gat", "mgat_edge", "hom_gat_edge"])
 def test_unsupported_training_shapes_raise(case):
     """Shapes outside the training kernels raise instead of returning wrong gradients."""
     with cb.patched_ops():
