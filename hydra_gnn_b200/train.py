@@ -162,6 +162,8 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
     from .nn import GATConv
     if any(convs[et].heads == 1 and _pad4(convs[et].out_channels) > 256 for et in rels):
         return _run_wide_single_head(convs, rels, x, csr, act=act, group=group, edge_attr=edge_attr)
+    if any(convs[et].heads > 4 or convs[et].heads * _kernel_channels(convs[et]) > 256 for et in rels):
+        return _run_head_groups(convs, rels, x, csr, act=act, group=group, edge_attr=edge_attr)
 
     cfg = _LayerCfg()
     cfg.rels = list(rels)
@@ -254,6 +256,63 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
     for T, o in zip(cfg.dsts, outs):
         res[T] = o if cfg.C[T] == cfg.C_real[T] else o[:, :cfg.C_real[T]]
     return res
+
+
+def _kernel_channels(c) -> int:
+    """Channels per head as the kernels see them (head mean with C % 4 != 0 is padded, see run_gat_layer_train)."""
+    return _pad4(c.out_channels) if (not c.concat or c.heads == 1) else c.out_channels
+
+
+class _HeadGroup:
+    """Heads [h0, h1) of a GATConv as a conv of its own (heads attend independently: own rows of the projections, of the
+    attention vectors and -- concat -- of the bias).  Head mean: the caller weights the group by (h1 - h0) / H, and the
+    bias rides on the first group, pre-scaled so that the weighting restores it."""
+
+    def __init__(self, conv, h0: int, h1: int, first: bool):
+        H, C = conv.heads, conv.out_channels
+        self.heads, self.out_channels, self.concat = h1 - h0, C, conv.concat
+        self.negative_slope, self.dropout, self.training, self.lin_edge = conv.negative_slope, conv.dropout, conv.training, None
+        self.lin_src = _Rows(conv.lin_src.weight[h0 * C: h1 * C])
+        self.lin_dst = self.lin_src if conv.lin_dst is conv.lin_src else _Rows(conv.lin_dst.weight[h0 * C: h1 * C])
+        self.att_src, self.att_dst = conv.att_src[:, h0:h1], conv.att_dst[:, h0:h1]
+        if conv.bias is None:
+            self.bias = None
+        elif conv.concat:
+            self.bias = conv.bias[h0 * C: h1 * C]
+        else:
+            self.bias = conv.bias * (H / (h1 - h0)) if first else None
+
+
+def _run_head_groups(convs, rels, x, csr, *, act, group, edge_attr):
+    """A GAT layer with more heads (or more heads x channels) than one launch of the training kernels takes
+    (heads <= 4, heads x channels <= 256; the reference's configs go to 6 heads): the heads are split into groups, each
+    group is a GAT layer of its own over its rows of the parameters, and the groups are concatenated (concat) or
+    averaged with weights |group| / H (head mean) before the activation.  Exact: heads do not interact before that."""
+    heads = {convs[et].heads for et in rels}
+    concat = {bool(convs[et].concat) for et in rels}
+    if len(heads) != 1 or len(concat) != 1:
+        raise NotImplementedError("splitting heads into groups needs every relation of the layer to share heads / concat")
+    for et in rels:
+        if convs[et].lin_edge is not None and edge_attr is not None and edge_attr.get(et) is not None:
+            raise NotImplementedError("training with edge attributes (GAT_edge) is not implemented")
+    H, is_concat = heads.pop(), concat.pop()
+    per = min(4, 256 // max(_kernel_channels(convs[et]) for et in rels))
+    if per < 1:
+        raise NotImplementedError("GAT training kernels take heads x channels <= 256 with more than one head")
+    n_groups = -(-H // per)
+    size = -(-H // n_groups)
+    parts: Dict[str, List[Tensor]] = {}
+    for k, h0 in enumerate(range(0, H, size)):
+        h1 = min(h0 + size, H)
+        res = run_gat_layer_train({et: _HeadGroup(convs[et], h0, h1, k == 0) for et in rels}, rels, x, csr, act=None,
+                                  group=group)
+        for T, o in res.items():
+            parts.setdefault(T, []).append(o if is_concat else o * ((h1 - h0) / H))
+    out = {}
+    for T, ps in parts.items():
+        o = torch.cat(ps, dim=1) if is_concat else sum(ps)
+        out[T] = o if act is None else (torch.relu(o) if act == "relu" else F.elu(o))
+    return out
 
 
 class _Rows:

@@ -339,3 +339,15 @@ def test_homogeneous_neural_tree_wide_pre_mp_gradients_match_oracle():
     ref, net = _pair(kw, "HomogeneousNeuralTreeNetwork")
     dev = clone_data(hom, "cuda")
     _compare_grads(ref, net, lambda: ref(clone_data(hom)), lambda: net(dev), 8)
+
+
+@pytest.mark.parametrize("heads,concats", [([6, 6, 6], [False, False, False]), ([5, 5, 5], [True, True, False])])
+def test_mgat_with_five_and_six_heads_gradients_match_oracle(heads, concats):
+    """5 and 6 heads (half of the reference's shipped configs) exceed the 4 heads one launch of the training kernels
+    takes: the layer runs as head groups (train._run_head_groups).  Added after the round's GPU budget was spent, like the
+    two tests above: glue pinned on CPU (tests/test_train_glue.py), kernels exercised above at 1-4 heads."""
+    kw = dict(M_GAT, GAT_heads=heads, GAT_concats=concats)
+    host = synth.synth_mp3d_batch(range(24))
+    ref, net = _pair(kw)
+    dev = clone_data(host, "cuda")
+    _compare_grads(ref, net, lambda: ref(clone_data(host)), lambda: net(dev), 20)

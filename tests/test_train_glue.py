@@ -198,11 +198,11 @@ import numpy as np  # noqa: E402
 import cases  # noqa: E402
 import hydra_gnn_b200 as hg  # noqa: E402
 
-# every golden case the training path supports (hom_gat: 6 heads, outside the GAT training kernels' limit, raises
-# NotImplementedError; mgat_edge / hom_gat_edge: GAT_edge gradients not built).  nt_hom_gcn_init carries the 306-channel
-# single-head pre_mp, computed in channel chunks (train._run_wide_single_head)
+# every golden case the training path supports (mgat_edge / hom_gat_edge: GAT_edge gradients not built).  nt_hom_gcn_init
+# carries the 306-channel single-head pre_mp, computed in channel chunks (train._run_wide_single_head); hom_gat has 6
+# heads, computed in two groups of 3 (train._run_head_groups)
 _TRAINABLE_CASES = ["mgat", "msage_all", "nt_het_gat", "nt_het_gat_init", "nt_het_sage_all", "nt_hom_gcn", "nt_hom_sage",
-                    "nt_hom_gcn_init", "nt_hom_gat_all", "hom_gcn", "hom_gin", "hom_sage_all"]
+                    "nt_hom_gcn_init", "nt_hom_gat_all", "hom_gcn", "hom_gin", "hom_sage_all", "hom_gat"]
 
 
 @pytest.mark.parametrize("case", _TRAINABLE_CASES)
@@ -235,7 +235,7 @@ def test_model_glue_reproduces_reference_gradient_fingerprints(case):
     assert checked >= 6
 
 
-@pytest.mark.parametrize("case", ["hom_gat", "mgat_edge", "hom_gat_edge"])
+@pytest.mark.parametrize("case", ["mgat_edge", "hom_gat_edge"])
 def test_unsupported_training_shapes_raise(case):
     """Shapes outside the training kernels raise instead of returning wrong gradients."""
     with cb.patched_ops():
@@ -243,3 +243,37 @@ def test_unsupported_training_shapes_raise(case):
         model.dropout = 0.0
         with pytest.raises(NotImplementedError):
             model(cases.build_input(cases.CASES[case][2]))
+
+
+@pytest.mark.parametrize("heads,concats", [([6, 6, 6], [False, False, False]), ([5, 5, 5], [True, True, False]),
+                                           ([6, 6], [True, False])])
+def test_hetero_gat_with_more_heads_than_one_launch_takes(heads, concats):
+    """The reference's configs go to 5 and 6 heads (config/mp3d/*.yaml) while one launch of the GAT training kernels
+    takes 4: the layer is split into head groups (train._run_head_groups).  Heterogeneous GAT, head mean with the
+    26 -> 28 channel padding and concat, against the oracle's autograd."""
+    from oracle import models as om
+    from hydra_gnn_b200 import synth
+
+    kw = dict(input_dim_dict={"objects": 306, "rooms": 6}, output_dim=26, conv_block="GAT",
+              GAT_hidden_dims=[64] * (len(heads) - 1), GAT_heads=heads, GAT_concats=concats, dropout=0.0)
+    ref = synth.random_state_dict_(om.HeterogeneousNetwork(**kw), seed=0).train()
+    net = hg.HeterogeneousNetwork(**kw)
+    net.load_state_dict(ref.state_dict())
+    net.train()
+    data = synth.synth_mp3d_batch(range(6))
+    with cb.patched_ops():
+        want, got = ref(synth.synth_mp3d_batch(range(6))), net(data)
+        torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
+        probe = torch.randn(want.shape, generator=torch.Generator().manual_seed(3))
+        (want * probe).sum().backward()
+        (got * probe).sum().backward()
+    ref_p, got_p = dict(ref.named_parameters()), dict(net.named_parameters())
+    scale = max(float(p.grad.abs().max()) for p in ref_p.values() if p.grad is not None)
+    checked = 0
+    for name, p in ref_p.items():
+        if p.grad is None:
+            assert got_p[name].grad is None or float(got_p[name].grad.abs().max()) == 0.0, name
+            continue
+        torch.testing.assert_close(got_p[name].grad, p.grad, rtol=5e-4, atol=1e-5 * scale, msg=lambda m, name=name: f"{name}: {m}")
+        checked += 1
+    assert checked >= 20
