@@ -289,6 +289,9 @@ HG_API int hg_batch_vector(int64_t* batch, int64_t n_nodes, const int64_t* ptr, 
  *              da_src[j, h] = sum_{e: col[e] = j} ds_e,h                                  transposed CSR; no atomics)
  * keep() is a counter-based hash of (seed, relation slot, CSR position, head): the backward regenerates it.
  * Every output column is written exactly once (plain stores).
+ * Limits of one call: H <= 4 and H * C <= 256 (HG_EUNSUPPORTED beyond).  Heads attend independently and, with one head, the
+ * softmax backward is linear in dw, so a caller covers wider layers exactly by head groups / channel chunks over its own
+ * rows of the parameters (hydra_gnn_b200/train.py: _run_head_groups, _run_wide_single_head).
  * ---------------------------------------------------------------------------------- */
 typedef struct hg_gat_train_rel {
     const float* xs;    int64_t ldxs;    /* [n_src, H*C] */
