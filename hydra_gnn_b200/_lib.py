@@ -65,7 +65,7 @@ class GatTrainRel(C.Structure):
     _fields_ = [("xs", vp), ("ldxs", i64), ("a_src", vp), ("lda_src", i64), ("a_dst", vp), ("lda_dst", i64),
                 ("rowptr", vp), ("col", vp), ("bias", vp), ("alpha", vp), ("dlogit", vp), ("rowptr_t", vp),
                 ("col_t", vp), ("pos_t", vp), ("dxs", vp), ("lddxs", i64), ("da_src", vp), ("ldda_src", i64),
-                ("da_dst", vp), ("ldda_dst", i64), ("n_src", i32), ("reserved", i32)]
+                ("da_dst", vp), ("ldda_dst", i64), ("n_src", i32), ("reserved", i32), ("a_edge", vp)]
 
 
 class GatTrainArgs(C.Structure):

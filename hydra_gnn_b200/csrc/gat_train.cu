@@ -135,7 +135,8 @@ __global__ void __launch_bounds__(kThreads) k_fwd(const __grid_constant__ hg_gat
 }
 
 // Pass 1 of the backward: by destination row.
-template <int NE>
+// EDGE: the raw score carries an edge term (GAT_edge): leaky' is taken at a_src + a_dst + a_edge
+template <int NE, bool EDGE>
 __global__ void __launch_bounds__(kThreads) k_bwd_dst(const __grid_constant__ hg_gat_train_args A) {
     __shared__ float s_g[kWarps][NE * kWarp];
     __shared__ float s_db[NE * kWarp];
@@ -220,7 +221,9 @@ __global__ void __launch_bounds__(kThreads) k_bwd_dst(const __grid_constant__ hg
                     if (h < H) {
                         const int64_t idx = static_cast<int64_t>(p) * H + h;
                         float ds = fabsf(R.alpha[idx]) * (R.dlogit[idx] - t[h]);
-                        ds *= (__ldg(as + h) + ad[h]) > 0.f ? 1.f : slope;
+                        float raw = __ldg(as + h) + ad[h];
+                        if constexpr (EDGE) raw += __ldg(R.a_edge + idx);
+                        ds *= raw > 0.f ? 1.f : slope;
                         R.dlogit[idx] = ds;
                         dad[h] += ds;
                     }
@@ -477,7 +480,7 @@ __global__ void __launch_bounds__(kThreads) k_fwd_v4(const __grid_constant__ hg_
     }
 }
 
-template <int NV, bool HK>
+template <int NV, bool HK, bool EDGE>
 __global__ void __launch_bounds__(kThreads, 4) k_bwd_dst_v4(const __grid_constant__ hg_gat_train_args A) {
     __shared__ __align__(16) float s_g[kWarps][2][NV * 64];
     __shared__ float s_db[NV * 64];
@@ -586,7 +589,9 @@ __global__ void __launch_bounds__(kThreads, 4) k_bwd_dst_v4(const __grid_constan
                         float ds = 0.f;
                         if (mine) {
                             ds = fabsf(a) * (da - tt);
-                            ds *= (__ldg(R.a_src + static_cast<int64_t>(j) * R.lda_src + h) + ad[h]) > 0.f ? 1.f : slope;
+                            float raw = __ldg(R.a_src + static_cast<int64_t>(j) * R.lda_src + h) + ad[h];
+                            if constexpr (EDGE) raw += __ldg(R.a_edge + idx);
+                            ds *= raw > 0.f ? 1.f : slope;
                             R.dlogit[idx] = ds;
                         }
                         const float v = half_sum(ds, hm);
@@ -643,7 +648,9 @@ __global__ void __launch_bounds__(kThreads, 4) k_bwd_dst_v4(const __grid_constan
                     if (h < H) {
                         const int64_t idx = static_cast<int64_t>(p) * H + h;
                         float ds = fabsf(R.alpha[idx]) * (R.dlogit[idx] - t[h]);
-                        ds *= (__ldg(as + h) + ad[h]) > 0.f ? 1.f : slope;
+                        float raw = __ldg(as + h) + ad[h];
+                        if constexpr (EDGE) raw += __ldg(R.a_edge + idx);
+                        ds *= raw > 0.f ? 1.f : slope;
                         R.dlogit[idx] = ds;
                         dad[h] += ds;
                     }
@@ -780,6 +787,9 @@ int validate(const hg_gat_train_args* a, bool bwd) {
         if (bwd && (!R.rowptr_t || R.n_src < 0)) return HG_EINVAL;
     }
     if (bwd && a->n_dst > 0 && (!a->dout || !a->g)) return HG_EINVAL;
+    bool edge = false, no_edge = false;
+    for (int r = 0; r < a->n_rel; ++r) (a->rel[r].a_edge ? edge : no_edge) = true;
+    if (edge && (no_edge || !bwd)) return HG_EUNSUPPORTED;  // all relations or none; forward with edges: hg_gat_fused
     return HG_OK;
 }
 
@@ -842,6 +852,7 @@ extern "C" int hg_gat_train_bwd(const hg_gat_train_args* a, void* stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const int ne = ceil_div(a->H * a->C, 32);
     const bool fast = v4_ok(a, true);
+    const bool edge = a->rel[0].a_edge != nullptr;  // validate(): all relations or none
     const int nv = ceil_div(a->H * a->C, 64);
     const bool hk = a->C == 64 && a->H == nv;
     if (a->n_dst > 0) {
@@ -853,12 +864,20 @@ extern "C" int hg_gat_train_bwd(const hg_gat_train_args* a, void* stream_) {
         } else if (fast) {
             // grid-stride over whole waves: 4 resident CTAs per SM (launch bounds), two waves' worth of CTAs
             const unsigned grid = row_grid(ceil_div(a->n_dst, 2), 8);
-#define CALL4(NV, HKV) k_bwd_dst_v4<NV, HKV><<<grid, kThreads, 0, stream>>>(*a)
+#define CALL4(NV, HKV)                                                                     \
+    do {                                                                                   \
+        if (edge) k_bwd_dst_v4<NV, HKV, true><<<grid, kThreads, 0, stream>>>(*a);          \
+        else k_bwd_dst_v4<NV, HKV, false><<<grid, kThreads, 0, stream>>>(*a);              \
+    } while (0)
             HG_NV_SWITCH(nv, hk, CALL4)
 #undef CALL4
         } else {
             const unsigned grid = row_grid(a->n_dst, 8);
-#define CALL(NE) k_bwd_dst<NE><<<grid, kThreads, 0, stream>>>(*a)
+#define CALL(NE)                                                                 \
+    do {                                                                         \
+        if (edge) k_bwd_dst<NE, true><<<grid, kThreads, 0, stream>>>(*a);        \
+        else k_bwd_dst<NE, false><<<grid, kThreads, 0, stream>>>(*a);            \
+    } while (0)
             HG_NE_SWITCH(ne, CALL)
 #undef CALL
         }

@@ -81,7 +81,8 @@ __device__ __noinline__ void slow_row(const hg_gat_train_args& A, const float* s
             float dad = 0.f;
             for (int p = beg + lane; p < end; p += 32) {
                 const int64_t idx = static_cast<int64_t>(p) * H + h;
-                const float raw = __ldg(R.a_src + static_cast<int64_t>(__ldg(R.col + p)) * R.lda_src + h) + ad;
+                float raw = __ldg(R.a_src + static_cast<int64_t>(__ldg(R.col + p)) * R.lda_src + h) + ad;
+                if (R.a_edge) raw += __ldg(R.a_edge + idx);
                 const float ds = fabsf(R.alpha[idx]) * (R.dlogit[idx] - t) * (raw > 0.f ? 1.f : A.neg_slope);
                 R.dlogit[idx] = ds;
                 dad += ds;
@@ -160,8 +161,11 @@ __global__ void __launch_bounds__(kTThreads, 4) k_bwd_dst_tile(const __grid_cons
                 for (int h = 0; h < kHs; ++h) {
                     float a = 0.f;
                     if (h < H) {
-                        a = Rl.alpha[static_cast<int64_t>(e0 + e) * H + h];
-                        if (__ldg(as + h) + adr[h] > 0.f) flags |= 1u << (8 + h);
+                        const int64_t idx = static_cast<int64_t>(e0 + e) * H + h;
+                        a = Rl.alpha[idx];
+                        float raw = __ldg(as + h) + adr[h];
+                        if (Rl.a_edge) raw += __ldg(Rl.a_edge + idx);
+                        if (raw > 0.f) flags |= 1u << (8 + h);
                     }
                     al[h] = a;
                 }

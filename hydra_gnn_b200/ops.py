@@ -43,7 +43,7 @@ def _require_no_grad(*tensors):
     if torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors):
         raise NotImplementedError(
             "this operator has no backward here: the raw ops are forward-only, gradients are recorded by "
-            "hydra_gnn_b200.train (GAT / GraphSAGE / GCN / GIN model classes; GAT_edge training is not implemented). "
+            "hydra_gnn_b200.train (every conv block of the four model classes). "
             "Call under torch.no_grad() or model.eval() with frozen parameters")
 
 
@@ -580,6 +580,7 @@ class GatTrainRelation:
     csr: CSR
     bias: Optional[Tensor] = None
     alpha: Optional[Tensor] = None
+    a_edge: Optional[Tensor] = None  # [cap, H] contiguous, CSR order (GAT_edge): backward only, forward = gat_fused
 
 
 def _gat_train_args(rels: Sequence[GatTrainRelation], n_dst: int, H: int, Cc: int, concat: bool, group: str, act: str,
@@ -629,7 +630,9 @@ def gat_train_bwd(rels: Sequence[GatTrainRelation], dys: Sequence[tuple], n_dst:
                   out: Tensor, dout: Tensor, *, group: str = "sum", act: str = None, neg_slope: float = 0.2,
                   dropout_p: float = 0.0, seed: int = 0, dbias: Tensor = None) -> None:
     """Backward of :func:`gat_train_fwd`.  ``dys[k] = (dY_src, dY_dst)``: gradient buffers with the layout of the
-    projection outputs; the relation's columns of them are overwritten."""
+    projection outputs; the relation's columns of them are overwritten.  Returns the per-relation ``dlogit`` buffers
+    ([cap, H], CSR order): the gradient of the raw scores, i.e. of ``a_edge`` for a relation that carries one (rows past
+    the live entry count are zero for those)."""
     h = lib()
     device = out.device
     ensure_train_csr([r.csr for r in rels])
@@ -639,8 +642,13 @@ def gat_train_bwd(rels: Sequence[GatTrainRelation], dys: Sequence[tuple], n_dst:
     keep = []
     for k, (r, (dys_, dyd_)) in enumerate(zip(rels, dys)):
         g = a.rel[k]
-        dl = torch.empty(max(r.csr.cap, 1), H, dtype=torch.float32, device=device)
+        alloc = torch.zeros if r.a_edge is not None else torch.empty
+        dl = alloc(max(r.csr.cap, 1), H, dtype=torch.float32, device=device)
         keep.append(dl)
+        if r.a_edge is not None:
+            if r.a_edge.dtype != torch.float32 or not r.a_edge.is_contiguous() or r.a_edge.shape != dl.shape:
+                raise ValueError("a_edge must be contiguous float32 [cap, H]")
+            g.a_edge = ptr(r.a_edge)
         t = r.csr.train
         g.dlogit, g.rowptr_t, g.col_t, g.pos_t = ptr(dl), ptr(t.rowptr_t), ptr(t.col_t), ptr(t.pos_t)
         g.dxs, g.lddxs = dys_.data_ptr() + 4 * r.xs_off, _ld(dys_)
@@ -652,6 +660,7 @@ def gat_train_bwd(rels: Sequence[GatTrainRelation], dys: Sequence[tuple], n_dst:
     meta = dict(n_dst=n_dst, H=H, C=Cc, width=out.size(1), rels=[dict(n_src=r.csr.n_src, cap=r.csr.cap) for r in rels])
     _call("hg_gat_train_bwd", meta, lambda: h.hg_gat_train_bwd(C.byref(a), stream_ptr()))
     _lib.launch_count += 2
+    return keep
 
 
 def act_bwd(dy: Tensor, y: Tensor, act: str = None, want_g: bool = True, want_dbias: bool = False):

@@ -54,6 +54,35 @@ def linear(x: Tensor, W: Tensor) -> Tensor:
 
 
 # =============================================================================== GAT layer
+class _EdgeLogitsFn(torch.autograd.Function):
+    """``a_edge[p, h] = <edge_attr[perm[p]], v[h]>`` in CSR order (``hg_edge_logits``; added self loops take ``fill`` or 0).
+    ``v = W_edge^T att_edge`` is folded in parameter space (torch autograd carries its gradient to ``lin_edge.weight`` and
+    ``att_edge``).  Backward: ``dv[h] = sum_p da_edge[p, h] * edge_attr[perm[p]]`` -- a gather of the 3-wide attribute rows
+    into CSR order and one ``hg_linear_wgrad``; the incoming gradient is zero past the live entry count."""
+
+    @staticmethod
+    def forward(ctx, v, edge_attr, csr, H, fill):
+        ctx.csr, ctx.fill = csr, fill
+        ctx.save_for_backward(edge_attr)
+        return ops.edge_logits(edge_attr, csr, v.contiguous(), H, fill=fill)
+
+    @staticmethod
+    def backward(ctx, da):
+        (edge_attr,) = ctx.saved_tensors
+        csr = ctx.csr
+        n = min(da.size(0), csr.perm.numel())  # an empty relation still has a 1-row buffer
+        if n == 0:
+            return da.new_zeros(da.size(1), edge_attr.size(1)), None, None, None, None
+        da = da[:n]
+        perm = csr.perm[:n].long()
+        live = torch.arange(n, device=da.device) < csr.rowptr[-1]
+        real = live & (perm >= 0)
+        rows = edge_attr.index_select(0, torch.where(real, perm, torch.zeros_like(perm))) * real[:, None].to(da.dtype)
+        if ctx.fill is not None:
+            rows = rows + (live & (perm < 0))[:, None].to(da.dtype) * ctx.fill
+        return ops.linear_wgrad(da.contiguous(), rows.contiguous()), None, None, None, None
+
+
 class _GatLayerFn(torch.autograd.Function):
     """All destination types of one GAT layer.  Inputs: ``cfg`` (python description), then the projection outputs
     ``Y_T`` (one per node type, in ``cfg.types`` order), then the relation biases.  Outputs: one tensor per
@@ -62,13 +91,14 @@ class _GatLayerFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, cfg, *tensors):
-        nT = len(cfg.types)
+        nT, nB = len(cfg.types), len(cfg.bias_rels)
         Y = dict(zip(cfg.types, tensors[:nT]))
-        biases = dict(zip(cfg.bias_rels, tensors[nT:]))
+        biases = dict(zip(cfg.bias_rels, tensors[nT:nT + nB]))
+        edges = dict(zip(cfg.edge_rels, tensors[nT + nB:]))  # [cap, H] edge terms of the raw scores (GAT_edge)
         outs, saved_rels = [], []
         for T in cfg.dsts:
             rels = [GatTrainRelation(Y[et[0]], Y[T], cfg.xs_off[et], cfg.as_off[et], cfg.ad_off[et], cfg.csr[et],
-                                     biases.get(et)) for et in cfg.rels if et[2] == T]
+                                     biases.get(et), None, edges.get(et)) for et in cfg.rels if et[2] == T]
             out = _forward_group(rels, Y[T].size(0), cfg.H[T], cfg.C[T], cfg.concat[T], cfg.group, cfg.act,
                                  cfg.slope[T], cfg.dropout[T], cfg.seed[T])
             outs.append(out)
@@ -87,14 +117,18 @@ class _GatLayerFn(torch.autograd.Function):
             for a, b in spans:
                 dY[T][:, a:b].zero_()
         dbias: Dict[str, Tensor] = {}
+        dedge: Dict[EdgeType, Tensor] = {}
         for T, rels, out, dout in zip(cfg.dsts, ctx.saved_rels, outs, douts):
             has_bias = any(r.bias is not None for r in rels)
             db = torch.zeros(out.size(1), dtype=torch.float32, device=out.device) if has_bias else None
             dbias[T] = db
-            dys = [(dY[et[0]], dY[T]) for et in cfg.rels if et[2] == T]
-            ops.gat_train_bwd(rels, dys, out.size(0), cfg.H[T], cfg.C[T], cfg.concat[T], out, dout.contiguous(),
-                              group=cfg.group, act=cfg.act, neg_slope=cfg.slope[T], dropout_p=cfg.dropout[T],
-                              seed=cfg.seed[T], dbias=db)
+            mine = [et for et in cfg.rels if et[2] == T]
+            dys = [(dY[et[0]], dY[T]) for et in mine]
+            dlogits = ops.gat_train_bwd(rels, dys, out.size(0), cfg.H[T], cfg.C[T], cfg.concat[T], out, dout.contiguous(),
+                                        group=cfg.group, act=cfg.act, neg_slope=cfg.slope[T], dropout_p=cfg.dropout[T],
+                                        seed=cfg.seed[T], dbias=db)
+            for et, dl in zip(mine, dlogits):
+                dedge[et] = dl  # the gradient of the raw scores IS the gradient of their edge term
         grads: List[Optional[Tensor]] = [None]
         grads += [dY[T] for T in cfg.types]
         used = set()
@@ -102,6 +136,7 @@ class _GatLayerFn(torch.autograd.Function):
             g = dbias[et[2]]
             grads.append(g.clone() if et[2] in used else g)
             used.add(et[2])
+        grads += [dedge[et] for et in cfg.edge_rels]
         ctx.saved_rels = ctx.Y = None
         return tuple(grads)
 
@@ -137,6 +172,8 @@ def _forward_group(rels: Sequence[GatTrainRelation], n_dst: int, H: int, C: int,
     softmax weights saved for the backward and attention dropout applied in its softmax stage; ``TILE_FORWARD =
     False`` selects ``hg_gat_train_fwd`` (row-per-half-warp kernel, same results up to the fast exp)."""
     if not TILE_FORWARD:
+        if any(r.a_edge is not None for r in rels):
+            raise NotImplementedError("edge attributes need the tile forward (HG_TRAIN_TILE_FWD=1)")
         if _DEVICE_SEED is not None and dropout_p > 0:
             raise NotImplementedError("the device-resident dropout seed needs the tile forward (HG_TRAIN_TILE_FWD=1)")
         return ops.gat_train_fwd(rels, n_dst, H, C, concat, group=group, act=act, neg_slope=slope, dropout_p=dropout_p,
@@ -146,7 +183,7 @@ def _forward_group(rels: Sequence[GatTrainRelation], n_dst: int, H: int, C: int,
     for r in rels:
         r.alpha = torch.empty(max(r.csr.cap, 1), H, dtype=torch.float32, device=r.y_src.device)
         fused.append(ops.GatRelation(r.y_src[:, r.xs_off: r.xs_off + HC], r.y_src[:, r.as_off: r.as_off + H],
-                                     r.y_dst[:, r.ad_off: r.ad_off + H], r.csr, r.bias, None, r.alpha))
+                                     r.y_dst[:, r.ad_off: r.ad_off + H], r.csr, r.bias, r.a_edge, r.alpha))
     return ops.gat_fused(fused, n_dst, H, C, concat, group=group, act=act, neg_slope=slope, dropout_p=dropout_p,
                          seed=seed, seed_dev=_DEVICE_SEED if dropout_p > 0 else None)
 
@@ -178,8 +215,6 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
     cfg.group, cfg.act, cfg.C_real = group, act, {}
     for et in rels:
         c = convs[et]
-        if c.lin_edge is not None and edge_attr is not None and edge_attr.get(et) is not None:
-            raise NotImplementedError("training with edge attributes (GAT_edge) is not implemented")
         T = et[2]
         # head mean with C % 4 != 0 (the 26-class layer): the per-head blocks of the projection are padded to a multiple
         # of 4 channels (zero weight rows, zero bias) so the float4 kernels apply; the pad columns of the output are 0
@@ -246,12 +281,24 @@ def run_gat_layer_train(convs: Dict[EdgeType, nn.Module], rels: Sequence[EdgeTyp
             pads.append((col, _pad4(col)))
         Y[T] = linear(x[T], torch.cat(blocks, dim=0))
 
+    # GAT_edge: the edge term of the raw scores, a_edge[p, h] = <edge_attr[perm[p]], (W_edge^T att_edge)[h]>, per relation
+    cfg.edge_rels = [et for et in rels if convs[et].lin_edge is not None and edge_attr is not None
+                     and edge_attr.get(et) is not None]
+    for T in cfg.dsts:
+        mine = [et for et in rels if et[2] == T]
+        if 0 < sum(et in cfg.edge_rels for et in mine) < len(mine):
+            raise NotImplementedError("relations targeting one node type must all carry edge attributes, or none")
+    a_edges = []
+    for et in cfg.edge_rels:
+        c = convs[et]
+        v = GATConv.fold(c.att_edge, c.lin_edge.weight, c.heads, c.out_channels)  # [H, edge_dim], parameter space
+        a_edges.append(_EdgeLogitsFn.apply(v, edge_attr[et], csr[et], c.heads, c.fill_vector(x[et[2]].device)))
     cfg.bias_rels = [et for et in rels if convs[et].bias is not None]
     biases = []
     for et in cfg.bias_rels:
         b, width = convs[et].bias, (cfg.H[et[2]] * cfg.C[et[2]] if cfg.concat[et[2]] else cfg.C[et[2]])
         biases.append(b if b.numel() == width else F.pad(b, (0, width - b.numel())))
-    outs = _GatLayerFn.apply(cfg, *[Y[T] for T in cfg.types], *biases)
+    outs = _GatLayerFn.apply(cfg, *[Y[T] for T in cfg.types], *biases, *a_edges)
     res = {}
     for T, o in zip(cfg.dsts, outs):
         res[T] = o if cfg.C[T] == cfg.C_real[T] else o[:, :cfg.C_real[T]]
@@ -271,7 +318,10 @@ class _HeadGroup:
     def __init__(self, conv, h0: int, h1: int, first: bool):
         H, C = conv.heads, conv.out_channels
         self.heads, self.out_channels, self.concat = h1 - h0, C, conv.concat
-        self.negative_slope, self.dropout, self.training, self.lin_edge = conv.negative_slope, conv.dropout, conv.training, None
+        self.negative_slope, self.dropout, self.training = conv.negative_slope, conv.dropout, conv.training
+        self.lin_edge = None if conv.lin_edge is None else _Rows(conv.lin_edge.weight[h0 * C: h1 * C])
+        self.att_edge = None if conv.lin_edge is None else conv.att_edge[:, h0:h1]
+        self.fill_vector = conv.fill_vector
         self.lin_src = _Rows(conv.lin_src.weight[h0 * C: h1 * C])
         self.lin_dst = self.lin_src if conv.lin_dst is conv.lin_src else _Rows(conv.lin_dst.weight[h0 * C: h1 * C])
         self.att_src, self.att_dst = conv.att_src[:, h0:h1], conv.att_dst[:, h0:h1]
@@ -292,9 +342,6 @@ def _run_head_groups(convs, rels, x, csr, *, act, group, edge_attr):
     concat = {bool(convs[et].concat) for et in rels}
     if len(heads) != 1 or len(concat) != 1:
         raise NotImplementedError("splitting heads into groups needs every relation of the layer to share heads / concat")
-    for et in rels:
-        if convs[et].lin_edge is not None and edge_attr is not None and edge_attr.get(et) is not None:
-            raise NotImplementedError("training with edge attributes (GAT_edge) is not implemented")
     H, is_concat = heads.pop(), concat.pop()
     per = min(4, 256 // max(_kernel_channels(convs[et]) for et in rels))
     if per < 1:
@@ -305,7 +352,7 @@ def _run_head_groups(convs, rels, x, csr, *, act, group, edge_attr):
     for k, h0 in enumerate(range(0, H, size)):
         h1 = min(h0 + size, H)
         res = run_gat_layer_train({et: _HeadGroup(convs[et], h0, h1, k == 0) for et in rels}, rels, x, csr, act=None,
-                                  group=group)
+                                  group=group, edge_attr=edge_attr)
         for T, o in res.items():
             parts.setdefault(T, []).append(o if is_concat else o * ((h1 - h0) / H))
     out = {}

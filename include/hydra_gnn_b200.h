@@ -308,6 +308,8 @@ typedef struct hg_gat_train_rel {
     float* da_src; int64_t ldda_src;     /* [n_src, H] */
     float* da_dst; int64_t ldda_dst;     /* [n_dst, H] */
     int32_t n_src; int32_t reserved;
+    const float* a_edge;                 /* bwd: NULL | [E', H] in CSR order, the edge term of the raw score (GAT_edge: the
+                                          * forward is hg_gat_fused with the same a_edge); its gradient IS dlogit */
 } hg_gat_train_rel;
 
 typedef struct hg_gat_train_args {

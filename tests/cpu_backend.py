@@ -38,17 +38,20 @@ def build_csr(edge_index: Tensor, n_src: int, n_dst: int, self_loops: bool = Fal
     """hg_plan_build's contract: stable sort by destination; ``self_loops`` appends one (i, i) entry per node that has
     none (the test graphs carry no self loops); ``norm``: inv_sqrt_deg = in-degree^-1/2 counted over the final rows."""
     src, dst = edge_index[0].long(), edge_index[1].long()
+    eid = torch.arange(src.numel())  # original edge id of every entry, -1 for an added self loop
     if self_loops:
         assert n_src == n_dst and not bool((src == dst).any())
         loop = torch.arange(n_dst)
         src, dst = torch.cat([src, loop]), torch.cat([dst, loop])
+        eid = torch.cat([eid, torch.full((n_dst,), -1, dtype=torch.long)])
     order = torch.sort(dst, stable=True).indices
     col = src[order].to(torch.int32)
+    perm = eid[order].to(torch.int32)
     counts = torch.bincount(dst, minlength=n_dst)
     rowptr = torch.zeros(n_dst + 1, dtype=torch.int32)
     rowptr[1:] = counts.cumsum(0).to(torch.int32)
     isd = counts.clamp(min=1).float().rsqrt() if norm else None
-    return CpuCSR(rowptr, col, None, isd, n_src, n_dst, int(col.numel()), self_loops,
+    return CpuCSR(rowptr, col, perm, isd, n_src, n_dst, int(col.numel()), self_loops,
                   edge_index=torch.stack([src, dst]))
 
 
@@ -139,11 +142,14 @@ def _gat_group(views, n_dst, H, C, concat, group, act, slope):
     """PyG GATConv per relation (section 9.2 of SURVEY.md) summed / averaged over the relations of one destination
     type.  views: (xs [n_src, H*C], a_src [n_src, H], a_dst [n_dst, H], csr, bias).  Returns (out, [alpha [E', H]])."""
     total, alphas = 0, []
-    for xs, a_s, a_d, csr, bias in views:
+    for xs, a_s, a_d, csr, bias, *rest in views:
         col = csr.col.long()
         deg = (csr.rowptr[1:] - csr.rowptr[:-1]).long()
         row_of = torch.repeat_interleave(torch.arange(n_dst), deg)
-        e = torch.nn.functional.leaky_relu(a_s.index_select(0, col) + a_d.index_select(0, row_of), slope)
+        raw = a_s.index_select(0, col) + a_d.index_select(0, row_of)
+        if rest and rest[0] is not None:
+            raw = raw + rest[0][: col.numel()]  # edge term, CSR order
+        e = torch.nn.functional.leaky_relu(raw, slope)
         m = torch.full((n_dst, H), float("-inf")).scatter_reduce(0, row_of[:, None].expand(-1, H), e.detach(), "amax")
         p = torch.exp(e - m.index_select(0, row_of))
         denom = torch.zeros(n_dst, H).index_add(0, row_of, p)
@@ -163,9 +169,9 @@ def _gat_group(views, n_dst, H, C, concat, group, act, slope):
 def gat_fused(rels, n_dst, H, Cc, concat, *, group="sum", act=None, neg_slope=0.2, out=None, addend=None,
               src_shared=False, dropout_p=0.0, seed=0, seed_dev=None):
     """``ops.gat_fused`` in its training-forward use (saved softmax weights, no attention dropout here)."""
-    assert dropout_p == 0.0 and not src_shared and addend is None and all(r.a_edge is None for r in rels)
-    res, alphas = _gat_group([(r.xs, r.a_src, r.a_dst, r.csr, r.bias) for r in rels], n_dst, H, Cc, concat, group, act,
-                             neg_slope)
+    assert dropout_p == 0.0 and not src_shared and addend is None
+    res, alphas = _gat_group([(r.xs, r.a_src, r.a_dst, r.csr, r.bias, r.a_edge) for r in rels], n_dst, H, Cc, concat,
+                             group, act, neg_slope)
     for r, a in zip(rels, alphas):
         if r.alpha_out is not None:
             r.alpha_out[: a.size(0)].copy_(a)
@@ -183,17 +189,29 @@ def gat_train_bwd(rels, dys, n_dst, H, Cc, concat, out, dout, *, group="sum", ac
             xs = r.y_src[:, r.xs_off: r.xs_off + HC].detach().clone().requires_grad_(True)
             a_s = r.y_src[:, r.as_off: r.as_off + H].detach().clone().requires_grad_(True)
             a_d = r.y_dst[:, r.ad_off: r.ad_off + H].detach().clone().requires_grad_(True)
-            leaves += [xs, a_s, a_d]
-            views.append((xs, a_s, a_d, r.csr, None))
+            # the gradient of the raw scores (dlogit) through a zero edge term when the relation has none
+            a_e = (r.a_edge if r.a_edge is not None else torch.zeros(r.csr.cap, H)).detach().clone().requires_grad_(True)
+            leaves += [xs, a_s, a_d, a_e]
+            views.append((xs, a_s, a_d, r.csr, None, a_e))
         pre, _ = _gat_group(views, n_dst, H, Cc, concat, group, None, neg_slope)
         g = act_bwd(dout, out, act)[0] if act is not None else dout
         grads = torch.autograd.grad(pre, leaves, g)
     for k, (r, (dys_, dyd_)) in enumerate(zip(rels, dys)):
-        dys_[:, r.xs_off: r.xs_off + HC] = grads[3 * k]
-        dys_[:, r.as_off: r.as_off + H] = grads[3 * k + 1]
-        dyd_[:, r.ad_off: r.ad_off + H] = grads[3 * k + 2]
+        dys_[:, r.xs_off: r.xs_off + HC] = grads[4 * k]
+        dys_[:, r.as_off: r.as_off + H] = grads[4 * k + 1]
+        dyd_[:, r.ad_off: r.ad_off + H] = grads[4 * k + 2]
     if dbias is not None:
         dbias += g.sum(0) * (1.0 / len(rels) if group == "mean" else 1.0)
+    return [grads[4 * k + 3] for k in range(len(rels))]
+
+
+def edge_logits(edge_attr, csr, v, H, fill=None):
+    """a_edge[p, h] = <edge_attr[perm[p]], v[h]> in CSR order; added self loops: <fill, v[h]> or 0."""
+    perm = csr.perm.long()
+    rows = edge_attr.index_select(0, perm.clamp(min=0)) * (perm >= 0)[:, None].float()
+    if fill is not None:
+        rows = rows + (perm < 0)[:, None].float() * fill
+    return rows @ v.t()
 
 
 def build_csr_specs(specs, overlap=False):
@@ -214,7 +232,7 @@ def patched_ops():
     from hydra_gnn_b200 import ops
 
     names = ("seg_reduce", "linear", "linear_wgrad", "act_bwd", "reversed_csr", "gather_rows", "build_csr", "gat_fused",
-             "gat_train_bwd")
+             "gat_train_bwd", "edge_logits")
     standin = dict(globals(), build_csr=build_csr_specs)
     saved = {n: getattr(ops, n) for n in names}
     try:

@@ -351,3 +351,18 @@ def test_mgat_with_five_and_six_heads_gradients_match_oracle(heads, concats):
     ref, net = _pair(kw)
     dev = clone_data(host, "cuda")
     _compare_grads(ref, net, lambda: ref(clone_data(host)), lambda: net(dev), 20)
+
+
+@pytest.mark.parametrize("heads,concats", [([3, 3, 3], [False, False, False]), ([6, 6, 6], [True, True, False])])
+def test_mgat_edge_gradients_match_oracle(heads, concats):
+    """GAT_edge (what every shipped MP3D config trains): the edge term of the raw scores is a differentiable input of the
+    layer, its gradient is the kernels' dlogit, and leaky' in pass 1 is taken at a_src + a_dst + a_edge (the EDGE
+    instantiations of k_bwd_dst / k_bwd_dst_v4).  Added after the round's GPU budget was spent, like the tests above:
+    glue pinned on CPU against the reference's fingerprints (cases mgat_edge, hom_gat_edge); the EDGE kernels differ
+    from the verified ones by one load per (edge, head) and had not run on a GPU when this was committed."""
+    kw = dict(M_GAT, input_dim_dict={"objects": 303, "rooms": 3}, conv_block="GAT_edge", GAT_heads=heads,
+              GAT_concats=concats)
+    host = synth.synth_mp3d_batch(range(24), relative_pos=True)
+    ref, net = _pair(kw)
+    dev = clone_data(host, "cuda")
+    _compare_grads(ref, net, lambda: ref(clone_data(host)), lambda: net(dev), 30)

@@ -198,11 +198,13 @@ import numpy as np  # noqa: E402
 import cases  # noqa: E402
 import hydra_gnn_b200 as hg  # noqa: E402
 
-# every golden case the training path supports (mgat_edge / hom_gat_edge: GAT_edge gradients not built).  nt_hom_gcn_init
+# every golden case of tests/golden/cases.py.  mgat_edge / hom_gat_edge: the edge term of the raw scores is a
+# differentiable input of the layer (train._EdgeLogitsFn), its gradient is the kernels' dlogit.  nt_hom_gcn_init
 # carries the 306-channel single-head pre_mp, computed in channel chunks (train._run_wide_single_head); hom_gat has 6
 # heads, computed in two groups of 3 (train._run_head_groups)
 _TRAINABLE_CASES = ["mgat", "msage_all", "nt_het_gat", "nt_het_gat_init", "nt_het_sage_all", "nt_hom_gcn", "nt_hom_sage",
-                    "nt_hom_gcn_init", "nt_hom_gat_all", "hom_gcn", "hom_gin", "hom_sage_all", "hom_gat"]
+                    "nt_hom_gcn_init", "nt_hom_gat_all", "hom_gcn", "hom_gin", "hom_sage_all", "hom_gat", "mgat_edge",
+                    "hom_gat_edge"]
 
 
 @pytest.mark.parametrize("case", _TRAINABLE_CASES)
@@ -235,14 +237,38 @@ def test_model_glue_reproduces_reference_gradient_fingerprints(case):
     assert checked >= 6
 
 
-@pytest.mark.parametrize("case", ["mgat_edge", "hom_gat_edge"])
-def test_unsupported_training_shapes_raise(case):
-    """Shapes outside the training kernels raise instead of returning wrong gradients."""
+def test_all_golden_cases_are_trainable():
+    assert sorted(_TRAINABLE_CASES) == sorted(cases.CASES)
+
+
+def test_six_head_gat_edge_runs_as_head_groups():
+    """GAT_edge with 6 heads (config/mp3d/*_gt*.yaml pairs GAT_edge with 5 and 6 heads): head groups carry their rows of
+    lin_edge / att_edge; against the oracle's autograd."""
+    from oracle import models as om
+    from hydra_gnn_b200 import synth
+
+    kw = dict(input_dim_dict={"objects": 303, "rooms": 3}, output_dim=26, conv_block="GAT_edge", GAT_hidden_dims=[64],
+              GAT_heads=[6, 6], GAT_concats=[True, False], dropout=0.0)
+    ref = synth.random_state_dict_(om.HeterogeneousNetwork(**kw), seed=0).train()
+    net = hg.HeterogeneousNetwork(**kw)
+    net.load_state_dict(ref.state_dict())
+    net.train()
     with cb.patched_ops():
-        model = cases.build_model(hg, case).train()
-        model.dropout = 0.0
-        with pytest.raises(NotImplementedError):
-            model(cases.build_input(cases.CASES[case][2]))
+        want = ref(synth.synth_mp3d_batch(range(6), relative_pos=True))
+        got = net(synth.synth_mp3d_batch(range(6), relative_pos=True))
+        torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
+        probe = torch.randn(want.shape, generator=torch.Generator().manual_seed(3))
+        (want * probe).sum().backward()
+        (got * probe).sum().backward()
+    ref_p, got_p = dict(ref.named_parameters()), dict(net.named_parameters())
+    scale = max(float(p.grad.abs().max()) for p in ref_p.values() if p.grad is not None)
+    checked = 0
+    for name, p in ref_p.items():
+        if p.grad is None:
+            continue
+        torch.testing.assert_close(got_p[name].grad, p.grad, rtol=5e-4, atol=1e-5 * scale, msg=lambda m, name=name: f"{name}: {m}")
+        checked += "edge" in name
+    assert checked >= 8  # lin_edge.weight and att_edge of the live relations
 
 
 @pytest.mark.parametrize("heads,concats", [([6, 6, 6], [False, False, False]), ([5, 5, 5], [True, True, False]),
