@@ -214,6 +214,16 @@ def edge_logits(edge_attr, csr, v, H, fill=None):
     return rows @ v.t()
 
 
+def adam_step(param, grad, exp_avg, exp_avg_sq, step, lr, beta1, beta2, eps, weight_decay, grad_scale=1.0, step_dev=None):
+    """hg_adam_step = torch.optim.Adam's single-tensor update (L2 weight decay added to the gradient), in place."""
+    t = int(step_dev) if step_dev is not None else step
+    g = grad * grad_scale + weight_decay * param
+    exp_avg.mul_(beta1).add_(g, alpha=1 - beta1)
+    exp_avg_sq.mul_(beta2).addcmul_(g, g, value=1 - beta2)
+    denom = exp_avg_sq.sqrt() / (1 - beta2 ** t) ** 0.5 + eps
+    param.addcdiv_(exp_avg, denom, value=-lr / (1 - beta1 ** t))
+
+
 def build_csr_specs(specs, overlap=False):
     """``ops.build_csr``: one CSR per CSRSpec + the status word (edges with endpoints out of range: none here)."""
     out = []
@@ -232,7 +242,7 @@ def patched_ops():
     from hydra_gnn_b200 import ops
 
     names = ("seg_reduce", "linear", "linear_wgrad", "act_bwd", "reversed_csr", "gather_rows", "build_csr", "gat_fused",
-             "gat_train_bwd", "edge_logits")
+             "gat_train_bwd", "edge_logits", "adam_step")
     standin = dict(globals(), build_csr=build_csr_specs)
     saved = {n: getattr(ops, n) for n in names}
     try:

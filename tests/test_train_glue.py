@@ -303,3 +303,43 @@ def test_hetero_gat_with_more_heads_than_one_launch_takes(heads, concats):
         torch.testing.assert_close(got_p[name].grad, p.grad, rtol=5e-4, atol=1e-5 * scale, msg=lambda m, name=name: f"{name}: {m}")
         checked += 1
     assert checked >= 20
+
+
+@pytest.mark.parametrize("conv_block,heads", [("GAT", [3, 3, 3]), ("GAT_edge", [6, 6, 6])])
+def test_training_steps_track_torch_adam(conv_block, heads):
+    """Whole steps -- forward, masked cross-entropy (label 25 ignored, base_training_job.py:63), backward, FlatAdam over the
+    re-homed flat buffers (weight decay as in base_training_job.py:77-79) -- against the oracle model under
+    torch.optim.Adam: the parameters after 4 steps."""
+    from oracle import models as om
+    from hydra_gnn_b200 import synth
+    from hydra_gnn_b200.train import FlatAdam
+
+    edge = conv_block == "GAT_edge"
+    kw = dict(input_dim_dict={"objects": 303, "rooms": 3} if edge else {"objects": 306, "rooms": 6}, output_dim=26,
+              conv_block=conv_block, GAT_hidden_dims=[64, 64], GAT_heads=heads, GAT_concats=[False] * 3, dropout=0.0)
+    ref = synth.random_state_dict_(om.HeterogeneousNetwork(**kw), seed=0).train()
+    net = hg.HeterogeneousNetwork(**kw)
+    net.load_state_dict(ref.state_dict())
+    net.train()
+    data = lambda: synth.synth_mp3d_batch(range(8), relative_pos=edge)  # noqa: E731
+    y = data()["rooms"].y.long()
+    mask = y != 25
+    lr, wd, steps = 1e-2, 1e-3, 4
+    opt_ref = torch.optim.Adam(ref.parameters(), lr=lr, weight_decay=wd)
+    with cb.patched_ops():
+        opt = FlatAdam(net.parameters(), lr=lr, weight_decay=wd)
+        for _ in range(steps):
+            opt_ref.zero_grad()
+            ref.loss(ref(data()), y, mask).backward()
+            opt_ref.step()
+            opt.zero_grad()
+            net.loss(net(data()), y, mask).backward()
+            opt.step()
+    got = dict(net.named_parameters())
+    start = synth.random_state_dict_(om.HeterogeneousNetwork(**kw), seed=0).state_dict()
+    moved = 0
+    for name, p in ref.named_parameters():
+        err = float((got[name].detach() - p.detach()).abs().max())
+        assert err <= 0.05 * lr * steps, f"{name}: {err:.3e}"  # Adam normalises: compare in units of the step size
+        moved += float((p.detach() - start[name]).abs().max()) > 0
+    assert moved >= 20
