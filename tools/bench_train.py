@@ -50,6 +50,9 @@ def main():
     ap.add_argument("--dropout", type=float, default=0.4)
     ap.add_argument("--cpu-graphs", type=int, default=512)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--edge-attr", action="store_true",
+                    help="M-GATe: conv_block GAT_edge on 303 / 3-d inputs with relative-position edge attributes (what the "
+                         "reference's MP3D configs train); first GPU run pending, see DESIGN.md section 4.4")
     ap.add_argument("--no-graph", action="store_true", help="launch every step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--graph", action="store_true",
                     help="N > 1 only: capture the step (NCCL all-reduce included) as a CUDA graph -- EXPERIMENTAL, a first "
@@ -71,12 +74,14 @@ def main():
 
     G = args.graphs
     lo, hi = shard_range(G * world, rank, world)
-    host = synth.synth_mp3d_batch(range(lo, hi))
+    host = synth.synth_mp3d_batch(range(lo, hi), relative_pos=args.edge_attr)
     data = hg.data.HeteroData()
     for t in host.node_types:
         data[t].x = host[t].x.to(dev)
     for t in host.edge_types:
         data[t].edge_index = host[t].edge_index.to(dev)
+        if args.edge_attr:
+            data[t].edge_attr = host[t].edge_attr.to(dev)
     labels = host["rooms"].y.long().to(dev)
     mask = labels != 25  # base_training_job.py:63 ignored_label
     keep_rows = mask.nonzero().view(-1)
@@ -86,6 +91,8 @@ def main():
     n_global = float(n_local.item())
 
     kw = dict(M_GAT, dropout=args.dropout)
+    if args.edge_attr:
+        kw.update(conv_block="GAT_edge", input_dim_dict={"objects": 303, "rooms": 3})
     net = synth.random_state_dict_(hg.HeterogeneousNetwork(**kw), seed=0).train().to(dev)
     net.plan_cache.enabled = False  # plan (forward + reversed CSRs) rebuilt every step
     opt = FlatAdam(net.parameters(), lr=1e-3, weight_decay=1e-3)
@@ -189,7 +196,8 @@ def main():
             "metric": "scene_graphs_per_s_train_step", "value": G * world * args.steps / (ms / 1e3), "unit": "graphs/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "configs[4]: heterogeneous GAT (M-GAT) training step: forward (dropout "
+            "config": {"workload": ("configs[4] variant M-GATe (GAT_edge): " if args.edge_attr else "configs[4]: ") +
+                                   "heterogeneous GAT (M-GAT) training step: forward (dropout "
                                    f"{args.dropout}) + masked CE + backward + gradient all-reduce + Adam, {G} graphs per GPU",
                        "graphs_per_gpu": G, "objects": int(host["objects"].x.size(0)), "rooms": int(host["rooms"].x.size(0)),
                        "collective": "all_reduce(flat gradient, %d floats)" % opt.flat_grad.numel() if world > 1 else "none",
@@ -204,7 +212,7 @@ def main():
             n = min(args.cpu_graphs, G)
             ref = synth.random_state_dict_(om.HeterogeneousNetwork(**kw), seed=0).train()
             o = torch.optim.Adam(ref.parameters(), lr=1e-3, weight_decay=1e-3)
-            d = synth.synth_mp3d_batch(range(n))
+            d = synth.synth_mp3d_batch(range(n), relative_pos=args.edge_attr)
             y = d["rooms"].y.long()
             mk = y != 25
             def cpu_step():
