@@ -92,7 +92,7 @@ SYMBOLS = {
     "hg_linear_pack_weights": (C.c_int, [C.POINTER(LinearArgs), vp, C.c_size_t, vp]),
     "hg_linear": (C.c_int, [C.POINTER(LinearArgs), vp, C.c_size_t, vp]),
     "hg_edge_logits": (C.c_int, [vp, i64, i32, vp, vp, i64, vp, vp, i32, vp, vp]),
-    "hg_relative_pos": (C.c_int, [vp, vp, vp, vp, i64, vp, vp]),
+    "hg_relative_pos": (C.c_int, [vp, i64, vp, i64, vp, vp, i64, vp, vp, vp]),
     "hg_gather_rows": (C.c_int, [vp, i64, vp, i64, i32, i32, vp, i64, vp]),
     "hg_collate_offsets": (C.c_int, [vp, i64, vp, vp, vp, i32, vp]),
     "hg_batch_vector": (C.c_int, [vp, i64, vp, i32, vp]),

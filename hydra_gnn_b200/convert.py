@@ -210,3 +210,23 @@ def batched_htree_to_homogeneous(batch: HeteroData) -> Data:
     out.ptr = ptr
     out.num_graphs = G
     return out
+
+
+def compute_relative_pos(data: HeteroData) -> HeteroData:
+    """``Hydra_mp3d_data.compute_relative_pos`` (mp3d_dataset.py:298-319), in place: the three position columns are
+    dropped from every node type's ``x`` and every relation gets ``edge_attr = pos_dst[edge_index[1]] -
+    pos_src[edge_index[0]]``.  Device-resident data (the batches the models consume) goes through ``hg_relative_pos``
+    -- one launch per relation, bit-identical to the indexing expression; host tensors (dataset preparation, as in the
+    reference) are indexed in place where they live."""
+    if data.edge_attr_dict:
+        raise Warning("Cannot compute relative pos as edge_attr -- edge_attr is not empty.")  # mp3d_dataset.py:304-307
+    for t in data.x_dict:
+        data[t].x = data[t].x[:, 3:]
+    for et, ei in data.edge_index_dict.items():
+        ps, pd = data[et[0]].pos, data[et[2]].pos
+        if ei.is_cuda:
+            from . import ops
+            data[et].edge_attr = ops.relative_pos(ps, pd, ei)
+        else:
+            data[et].edge_attr = pd[ei[1]] - ps[ei[0]]
+    return data

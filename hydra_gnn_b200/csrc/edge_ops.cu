@@ -29,10 +29,18 @@ k_edge_logits(const float* __restrict__ attr, int64_t ld, int D, const int32_t* 
 
 __global__ void __launch_bounds__(kThreads)
 k_relative_pos(const float* __restrict__ ps, const float* __restrict__ pd, const int64_t* __restrict__ src,
-               const int64_t* __restrict__ dst, int64_t E, float* __restrict__ out) {
+               const int64_t* __restrict__ dst, int64_t E, int64_t n_src, int64_t n_dst, float* __restrict__ out,
+               int32_t* __restrict__ status) {
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
     for (int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; e < E; e += stride) {
         const int64_t s = src[e], d = dst[e];
+        if (static_cast<uint64_t>(s) >= static_cast<uint64_t>(n_src) ||
+            static_cast<uint64_t>(d) >= static_cast<uint64_t>(n_dst)) {  // never dereferenced: NaN row + counted
+#pragma unroll
+            for (int c = 0; c < 3; ++c) out[e * 3 + c] = __int_as_float(0x7fc00000);
+            if (status) atomicAdd(status, 1);
+            continue;
+        }
 #pragma unroll
         for (int c = 0; c < 3; ++c) out[e * 3 + c] = __ldg(pd + d * 3 + c) - __ldg(ps + s * 3 + c);
     }
@@ -102,14 +110,15 @@ extern "C" int hg_edge_logits(const float* edge_attr, int64_t ld_attr, int32_t D
     return check_launch();
 }
 
-extern "C" int hg_relative_pos(const float* pos_src, const float* pos_dst, const int64_t* src, const int64_t* dst,
-                               int64_t E, float* edge_attr, void* stream_) {
+extern "C" int hg_relative_pos(const float* pos_src, int64_t n_src, const float* pos_dst, int64_t n_dst,
+                               const int64_t* src, const int64_t* dst, int64_t E, float* edge_attr, int32_t* status,
+                               void* stream_) {
     using namespace hg;
-    if (E < 0) return HG_EINVAL;
+    if (E < 0 || n_src < 0 || n_dst < 0) return HG_EINVAL;
     if (E == 0) return HG_OK;
-    if (!pos_src || !pos_dst || !src || !dst || !edge_attr) return HG_EINVAL;
-    k_relative_pos<<<grid_for(E), kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(pos_src, pos_dst, src, dst, E,
-                                                                                      edge_attr);
+    if (!src || !dst || !edge_attr || (n_src > 0 && !pos_src) || (n_dst > 0 && !pos_dst)) return HG_EINVAL;
+    k_relative_pos<<<grid_for(E), kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(pos_src, pos_dst, src, dst, E, n_src,
+                                                                                      n_dst, edge_attr, status);
     return check_launch();
 }
 

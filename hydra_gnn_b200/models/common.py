@@ -120,6 +120,14 @@ class _Base(nn.Module):
     def plan_cache(self) -> hnn.PlanCache:
         return self._plans
 
+    def train(self, mode: bool = True):
+        """``net.train()`` / ``net.eval()`` (base_training_job.py:203,248): besides the mode flag, drops the packed weight
+        images, so the validation pass after an epoch of optimizer steps -- which update the weights in place, possibly
+        inside a replayed CUDA graph -- folds the CURRENT weights."""
+        if mode != self.training:
+            hnn.invalidate_weight_caches(self)
+        return super().train(mode)
+
     @property
     def _act_name(self) -> str:
         return "elu" if self.conv_block[:3] == "GAT" else "relu"

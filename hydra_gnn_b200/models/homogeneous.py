@@ -73,13 +73,8 @@ class HomogeneousNetwork(_Base):
 
     @staticmethod
     def _mask_rows(plan, name: str, mask: torch.Tensor, negate: bool = False) -> torch.Tensor:
-        """``nonzero(mask)`` as int32, computed once per mask tensor (one host sync per batch); kept beside the
-        plan cache, keyed by the mask's identity, so that a forward whose plan is rebuilt stays capturable."""
-        key = (name, mask.data_ptr(), mask._version)
-        if plan.extra.get(name + "_key") != key:
-            plan.extra[name] = (~mask if negate else mask).nonzero(as_tuple=False).view(-1).to(torch.int32)
-            plan.extra[name + "_key"] = key
-        return plan.extra[name]
+        """``nonzero(mask)`` as int32, once per mask tensor (``PlanCache.mask_rows``)."""
+        return plan.mask_rows(name, mask, negate)
 
     # ------------------------------------------------------------------ layers
     def _message_passing(self, x, data, plan, use_batch_norm: bool, final_act: bool):

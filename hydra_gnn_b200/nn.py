@@ -87,9 +87,19 @@ class PlanRequest:
         self.self_loops, self.want_perm, self.want_norm = bool(self_loops), bool(want_perm), bool(want_norm)
 
     def signature(self):
+        """Shape / version part of the cache key.  The ADDRESS of ``edge_index`` only identifies a tensor while that
+        tensor is alive (the allocator recycles freed blocks), so :class:`PlanCache` also holds a reference to the tensor
+        the plan was built from and compares storage identity against it (``same_tensor``)."""
         ei = self.edge_index
-        return (self.key, ei.data_ptr(), tuple(ei.shape), ei._version, self.n_src, self.n_dst, self.self_loops,
+        return (self.key, tuple(ei.shape), tuple(ei.stride()), ei._version, self.n_src, self.n_dst, self.self_loops,
                 self.want_perm, self.want_norm)
+
+
+def same_tensor(a: Tensor, b: Tensor) -> bool:
+    """``b`` is (a view of) the tensor ``a`` we kept alive: same storage address, offset, layout and version.  Because
+    ``a`` is referenced by the cache its memory cannot have been freed and handed to another tensor."""
+    return a is b or (a.data_ptr() == b.data_ptr() and a.shape == b.shape and a.stride() == b.stride()
+                      and a.dtype == b.dtype and a._version == b._version)
 
 
 class PlanCache:
@@ -101,10 +111,11 @@ class PlanCache:
         self.overlap = True  # build on a side stream; joined by the first kernel that reads a CSR
         self._sig = None
         self._plan: Optional[GraphPlan] = None
-        self.extra: Dict[str, object] = {}  # per-batch derived index vectors (mask -> rows), keyed by tensor identity
+        self._built_from: List[Tensor] = []  # the edge_index tensors of the cached plan, kept alive (see same_tensor)
+        self.extra: Dict[str, object] = {}  # per-batch derived index vectors (mask -> rows), see mask_rows
 
     def clear(self):
-        self._sig, self._plan = None, None
+        self._sig, self._plan, self._built_from = None, None, []
         self.extra.clear()
 
     def join(self):
@@ -118,7 +129,8 @@ class PlanCache:
             for r in requests:
                 r.want_perm = True
         sig = tuple(r.signature() for r in requests)
-        if self.enabled and sig == self._sig and self._plan is not None:
+        if self.enabled and sig == self._sig and self._plan is not None and \
+                all(same_tensor(a, r.edge_index) for a, r in zip(self._built_from, requests)):
             return self._plan
         plan = GraphPlan()
         specs = [CSRSpec(r.edge_index, r.n_src, r.n_dst, r.self_loops, r.want_perm, r.want_norm) for r in requests]
@@ -126,8 +138,21 @@ class PlanCache:
         self._pending = csrs[0].join if csrs else None
         for r, c in zip(requests, csrs):
             plan.csr[(r.key, r.self_loops)] = c
-        self._sig, self._plan = (sig, plan) if self.enabled else (None, None)
+        if self.enabled:
+            self._sig, self._plan, self._built_from = sig, plan, [r.edge_index for r in requests]
+        else:
+            self._sig, self._plan, self._built_from = None, None, []
         return plan
+
+    def mask_rows(self, name: str, mask: Tensor, negate: bool = False) -> Tensor:
+        """``nonzero(mask)`` as int32, computed once per mask tensor (one host sync per batch).  The entry keeps the
+        mask it was computed from alive and is matched by storage identity + version (``same_tensor``): a fresh
+        batch's mask can land at a recycled address with ``_version == 0``, so an address alone is not a key."""
+        hit = self.extra.get(name)
+        if hit is None or hit[1] != mask._version or not same_tensor(hit[0], mask):
+            rows = (~mask if negate else mask).nonzero(as_tuple=False).view(-1).to(torch.int32)
+            hit = self.extra[name] = (mask, mask._version, rows)  # the version AT BUILD TIME (hit[0] may be `mask` itself)
+        return hit[2]
 
 
 def _wcache(owner, site: str) -> dict:
@@ -136,7 +161,19 @@ def _wcache(owner, site: str) -> dict:
 
 
 def _param_signature(params: Sequence[Optional[Tensor]]):
-    return tuple((p.data_ptr(), p._version) if p is not None else None for p in params)
+    """Identity of a set of weights for the packed-image caches.  ``ops.param_generation()`` is part of it because an
+    optimizer that updates parameters through raw pointers (``train.FlatAdam`` -> hg_adam_step) changes neither
+    ``data_ptr`` nor ``_version``."""
+    return (ops.param_generation(),) + tuple((p.data_ptr(), p._version) if p is not None else None for p in params)
+
+
+def invalidate_weight_caches(module: nn.Module) -> None:
+    """Drops every packed / folded weight image below ``module`` (GAT projection packs, SAGE root sums, the TF32
+    hi/lo images of ``ops.linear``).  Called on every ``train()`` / ``eval()`` switch of a model."""
+    for m in module.modules():
+        for name in ("_pack", "_wpack", "_sage_pack"):
+            if name in m.__dict__:
+                m.__dict__[name] = None if name == "_pack" else {}
 
 
 # =============================================================================== GAT
@@ -183,18 +220,25 @@ class GATConv(nn.Module):
         return (att.reshape(H, C, 1) * weight.reshape(H, C, -1)).sum(dim=1)
 
     def fill_vector(self, device) -> Optional[Tensor]:
-        """Edge attribute given to added self loops (None = zeros)."""
+        """Edge attribute given to added self loops (None = zeros).  Decided ONCE on the host value (the reference passes
+        a CPU float64 ``zeros(3)``, models/utils.py:125-126) and cached per device: no copy and no sync per forward, so
+        a GAT_edge forward stays CUDA-graph capturable."""
         fv = self.fill_value
         if self.edge_dim is None or fv is None:
             return None
-        if isinstance(fv, Tensor):
-            v = fv.to(device=device, dtype=torch.float32).reshape(-1)
-            return v if bool((v != 0).any()) else None
-        if isinstance(fv, (int, float)):
-            return torch.full((self.edge_dim,), float(fv), device=device) if fv != 0 else None
-        raise NotImplementedError(
-            f"GATConv(edge_dim, fill_value={fv!r}): only constant / tensor fill values are supported "
-            "(the reference uses zeros(3), models/utils.py:125-126)")
+        cache = self.__dict__.setdefault("_fill_cache", {})
+        key = str(device)
+        if key not in cache:
+            if isinstance(fv, Tensor):
+                host = fv.detach().to(device="cpu", dtype=torch.float32).reshape(-1)
+                cache[key] = host.to(device) if bool((host != 0).any()) else None
+            elif isinstance(fv, (int, float)):
+                cache[key] = torch.full((self.edge_dim,), float(fv), device=device) if fv != 0 else None
+            else:
+                raise NotImplementedError(
+                    f"GATConv(edge_dim, fill_value={fv!r}): only constant / tensor fill values are supported "
+                    "(the reference uses zeros(3), models/utils.py:125-126)")
+        return cache[key]
 
     def forward(self, x, edge_index: Tensor, edge_attr: Tensor = None, act: str = None) -> Tensor:
         """Stand-alone call (single relation).  ``x``: Tensor or ``(x_src, x_dst)``."""

@@ -28,6 +28,20 @@ def set_profile_sink(sink):
     _profile_sink = sink
 
 
+# Generation of "parameters changed behind torch's back": bumped by every optimizer step that writes weights through raw
+# pointers (train.FlatAdam -> hg_adam_step leaves data_ptr and _version untouched).  Part of every packed-weight cache key.
+_param_generation = 0
+
+
+def param_generation() -> int:
+    return _param_generation
+
+
+def bump_param_generation() -> None:
+    global _param_generation
+    _param_generation += 1
+
+
 def _call(name: str, meta, fn):
     if _profile_sink is None:
         check(fn(), name)
@@ -403,7 +417,7 @@ def linear(segments: Sequence, N: int, *, bias: Tensor = None, scale: Tensor = N
     nbytes = h.hg_linear_workspace_bytes(C.byref(a))
     ws = None
     if nbytes and pack_cache is not None:
-        key = (N, tuple((w.data_ptr(), w._version, w.size(1), _ld(w)) for _, w in keep))
+        key = (N, _param_generation, tuple((w.data_ptr(), w._version, w.size(1), _ld(w)) for _, w in keep))
         ws = pack_cache.get(key)
         if ws is None:
             pack_cache.clear()  # one live image per owner: older weight versions are dead
@@ -441,16 +455,22 @@ def edge_logits(edge_attr: Tensor, csr: CSR, v: Tensor, H: int, fill: Tensor = N
     return out
 
 
-def relative_pos(pos_src: Tensor, pos_dst: Tensor, edge_index: Tensor) -> Tensor:
-    """``edge_attr = pos_dst[edge_index[1]] - pos_src[edge_index[0]]`` (mp3d_dataset.py:316-319)."""
+def relative_pos(pos_src: Tensor, pos_dst: Tensor, edge_index: Tensor, status: Tensor = None) -> Tensor:
+    """``edge_attr = pos_dst[edge_index[1]] - pos_src[edge_index[0]]`` (mp3d_dataset.py:316-319), bit-identical to
+    the torch expression.  ``status``: optional CUDA int32[1] that receives the number of edges with an endpoint out of
+    range (their rows are NaN; torch would raise) -- read it only where a sync is acceptable."""
     h = lib()
     pos_src, pos_dst = _f32(pos_src, "pos_src").contiguous(), _f32(pos_dst, "pos_dst").contiguous()
+    if pos_src.dim() != 2 or pos_src.size(1) != 3 or pos_dst.dim() != 2 or pos_dst.size(1) != 3:
+        raise ValueError("pos must be [n, 3]")
+    if edge_index.dtype != torch.int64 or edge_index.dim() != 2 or edge_index.size(0) != 2 or not edge_index.is_cuda:
+        raise TypeError("edge_index must be a CUDA int64 [2, E] tensor")
     ei = edge_index.contiguous()
     E = ei.size(1)
     out = torch.empty(E, 3, dtype=torch.float32, device=ei.device)
     _call("hg_relative_pos", dict(E=E),
-          lambda: h.hg_relative_pos(ptr(pos_src), ptr(pos_dst), ei.data_ptr(), ei.data_ptr() + 8 * E, E, ptr(out),
-                                    stream_ptr()))
+          lambda: h.hg_relative_pos(ptr(pos_src), pos_src.size(0), ptr(pos_dst), pos_dst.size(0), ei.data_ptr(),
+                                    ei.data_ptr() + 8 * E, E, ptr(out), ptr(status), stream_ptr()))
     _lib.launch_count += 1
     return out
 

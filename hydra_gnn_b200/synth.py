@@ -152,16 +152,21 @@ def synth_mp3d_batch(graph_ids, seed: int = SEED, with_word2vec: bool = True, re
     for et, ei in zip(EDGE_TYPES, (oo, rr, o2r, r2o)):
         data[et].edge_index = torch.from_numpy(np.ascontiguousarray(ei.astype(np.int64)))
     data.num_graphs = G
-    if relative_pos:
+    from .convert import compute_relative_pos
+
+    def rel_pos():  # GAT_edge variant (mp3d_dataset.py:298-319); the sliced x made contiguous for the projections
+        compute_relative_pos(data)
         for nt in ("objects", "rooms"):
-            data[nt].x = data[nt].x[:, 3:].contiguous()
-        for et in EDGE_TYPES:
-            ei = data[et].edge_index
-            data[et].edge_attr = data[et[2]].pos[ei[1]] - data[et[0]].pos[ei[0]]
+            data[nt].x = data[nt].x.contiguous()
+
+    if relative_pos and device is None:
+        rel_pos()
     if pin:
         data.pin_memory()
     if device is not None:
         data.to(device)
+        if relative_pos:  # the batch lives on the device: hg_relative_pos, bit-identical to the host expression
+            rel_pos()
     return data
 
 

@@ -454,19 +454,49 @@ class FlatAdam:
                 p.grad = self.flat_grad[off:off + k].view(p.shape)
                 off += k
 
-    def zero_grad(self):
+    @property
+    def param_groups(self):
+        """One group, torch.optim style (``lr`` is read from here at every eager step, so a ``StepLR``-like scheduler that
+        rewrites ``param_groups[0]['lr']`` works; a captured CUDA graph bakes the value it was captured with)."""
+        if "_groups" not in self.__dict__:
+            self._groups = [{"params": self.params, "lr": self.lr, "betas": self.betas, "eps": self.eps,
+                             "weight_decay": self.weight_decay}]
+        return self._groups
+
+    def zero_grad(self, set_to_none: bool = False):
         if self.flat_grad is None:
             for p in self.params:
                 p.grad = None
         else:
             self.flat_grad.zero_()
 
+    def _rebind_grads(self):
+        """``net.zero_grad()`` (set_to_none) or ``p.grad = None`` detaches a parameter from ``flat_grad``; the next
+        backward then writes a fresh ``.grad`` tensor.  Re-home it (copy + rebind) instead of stepping on stale data."""
+        off = 0
+        for p in self.live:
+            k = p.numel()
+            view = self.flat_grad[off:off + k]
+            if p.grad is None:
+                view.zero_()
+                p.grad = view.view(p.shape)
+            elif p.grad.data_ptr() != view.data_ptr():
+                with torch.no_grad():
+                    view.copy_(p.grad.reshape(-1))
+                p.grad = view.view(p.shape)
+            off += k
+
     def step(self, grad_scale: float = 1.0):
         self.flatten()
+        if not (self.flat_param.is_cuda and torch.cuda.is_current_stream_capturing()):
+            self._rebind_grads()
+        g = self.param_groups[0]
+        self.lr, self.weight_decay = g["lr"], g["weight_decay"]
         self.t += 1  # host mirror (not advanced by graph replays); the kernel reads the device counter
         self.t_dev.add_(1)
         ops.adam_step(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.t, self.lr, self.betas[0],
                       self.betas[1], self.eps, self.weight_decay, grad_scale, step_dev=self.t_dev)
+        ops.bump_param_generation()  # weights changed through a raw pointer: every packed-weight cache key moves on
 
 
 # =============================================================================== SAGE / GCN / LeafPool (a3, a6, a8)

@@ -241,13 +241,16 @@ HG_API int hg_linear(const hg_linear_args* args_host, void* workspace, size_t wo
  * heterogeneous_network.py:68-79; mp3d_dataset.py:298-319).
  *   hg_edge_logits: a_edge[p, h] = perm[p] >= 0 ? dot(edge_attr[perm[p], :D], v[h, :D]) : fill_h
  *   with v = folded (lin_edge^T att_edge) [H, D]; fill_h = dot(fill[:D], v[h]) (loops).
- *   hg_relative_pos: edge_attr[e, :] = pos_dst[dst[e], :3] - pos_src[src[e], :3]
+ *   hg_relative_pos: edge_attr[e, :] = pos_dst[dst[e], :3] - pos_src[src[e], :3]   (compute_relative_pos,
+ *   mp3d_dataset.py:316-319; exact fp32 subtraction, bit-identical to the torch expression)
  * ---------------------------------------------------------------------------------- */
 HG_API int hg_edge_logits(const float* edge_attr, int64_t ld_attr, int32_t D, const int32_t* perm, const int32_t* rowptr_last,
                    int64_t cap, const float* v /* [H, D] */, const float* fill /* NULL | [D] */, int32_t H,
                    float* a_edge /* [cap, H] */, void* stream);
-HG_API int hg_relative_pos(const float* pos_src, const float* pos_dst, const int64_t* src, const int64_t* dst, int64_t E,
-                    float* edge_attr /* [E, 3] */, void* stream);
+HG_API int hg_relative_pos(const float* pos_src /* [n_src, 3] */, int64_t n_src, const float* pos_dst /* [n_dst, 3] */,
+                    int64_t n_dst, const int64_t* src, const int64_t* dst, int64_t E, float* edge_attr /* [E, 3] */,
+                    int32_t* status /* NULL | [1]: += number of edges with an endpoint outside [0, n) -- their rows are
+                                       NaN, nothing is dereferenced (the caller zeroes it) */, void* stream);
 
 /* out[r, :F] = act(x[idx[r], :F]) -- the `x[room_mask, :]` / `x[object_mask, :]` row selection of
  * homogeneous_network.py:139-145 and homogeneous_neural_tree_network.py:103-109 (idx = nonzero(mask),

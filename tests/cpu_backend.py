@@ -168,10 +168,18 @@ def _gat_group(views, n_dst, H, C, concat, group, act, slope):
 
 def gat_fused(rels, n_dst, H, Cc, concat, *, group="sum", act=None, neg_slope=0.2, out=None, addend=None,
               src_shared=False, dropout_p=0.0, seed=0, seed_dev=None):
-    """``ops.gat_fused`` in its training-forward use (saved softmax weights, no attention dropout here)."""
-    assert dropout_p == 0.0 and not src_shared and addend is None
-    res, alphas = _gat_group([(r.xs, r.a_src, r.a_dst, r.csr, r.bias, r.a_edge) for r in rels], n_dst, H, Cc, concat,
-                             group, act, neg_slope)
+    """``ops.gat_fused`` (no attention dropout here).  ``src_shared`` (the aggregate-first form of the header): xs is
+    [n_src, C], every head weighs the SAME row, output [n_dst, H*C]; ``addend`` joins after the relation group, before
+    the activation."""
+    assert dropout_p == 0.0
+    views = []
+    for r in rels:
+        xs = r.xs.repeat(1, H) if src_shared else r.xs  # [n_src, H*C] with the shared row under every head
+        views.append((xs, r.a_src, r.a_dst, r.csr, r.bias, r.a_edge))
+    res, alphas = _gat_group(views, n_dst, H, Cc, True if src_shared else concat, group, None, neg_slope)
+    if addend is not None:
+        res = res + addend
+    res = _act(res, act)
     for r, a in zip(rels, alphas):
         if r.alpha_out is not None:
             r.alpha_out[: a.size(0)].copy_(a)

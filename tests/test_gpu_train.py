@@ -308,14 +308,9 @@ def test_training_step_as_cuda_graph():
         hgt.disable_device_seed()
 
 
-# The tests below cover compositions written after this round's GPU budget was spent: their host glue is pinned on CPU
-# against the reference's gradient fingerprints (tests/test_train_glue.py) and their kernels are exercised above (GAT_edge
-# adds one load per edge to pass 1), but none of them had run on a GPU when committed.  Non-strict xfail: the run reports
-# XPASS / XFAIL per test without hiding either outcome; drop the marker once a GPU run has confirmed them.
-_FIRST_GPU_RUN_PENDING = pytest.mark.xfail(strict=False, reason="first GPU run pending (CPU-pinned in tests/test_train_glue.py)")
+# Compositions of the verified kernels: GIN + BatchNorm, the wide pre_mp, head groups, GAT_edge (first GPU run: round 2).
 
 
-@_FIRST_GPU_RUN_PENDING
 def test_homogeneous_gin_gradients_match_oracle():
     """GIN (a7) training: neighbour sum + trainable eps + MLP + BatchNorm with batch statistics (homogeneous_network.py:
     94-97,133-134).  Kept last in this file: it was added after the round's GPU budget was spent -- its host glue is
@@ -332,7 +327,6 @@ def test_homogeneous_gin_gradients_match_oracle():
         torch.testing.assert_close(b.module.running_var.cpu(), a.module.running_var, rtol=1e-4, atol=1e-5)
 
 
-@_FIRST_GPU_RUN_PENDING
 def test_homogeneous_neural_tree_wide_pre_mp_gradients_match_oracle():
     """The 306-channel single-head ``pre_mp`` of the homogeneous Neural Tree (homogeneous_neural_tree_network.py:63-66,
     86) is wider than the GAT training kernels' 256 columns: computed in channel chunks that share the attention logits
@@ -350,7 +344,6 @@ def test_homogeneous_neural_tree_wide_pre_mp_gradients_match_oracle():
     _compare_grads(ref, net, lambda: ref(clone_data(hom)), lambda: net(dev), 8)
 
 
-@_FIRST_GPU_RUN_PENDING
 @pytest.mark.parametrize("heads,concats", [([6, 6, 6], [False, False, False]), ([5, 5, 5], [True, True, False])])
 def test_mgat_with_five_and_six_heads_gradients_match_oracle(heads, concats):
     """5 and 6 heads (half of the reference's shipped configs) exceed the 4 heads one launch of the training kernels
@@ -363,7 +356,6 @@ def test_mgat_with_five_and_six_heads_gradients_match_oracle(heads, concats):
     _compare_grads(ref, net, lambda: ref(clone_data(host)), lambda: net(dev), 20)
 
 
-@_FIRST_GPU_RUN_PENDING
 @pytest.mark.parametrize("heads,concats", [([3, 3, 3], [False, False, False]), ([6, 6, 6], [True, True, False])])
 def test_mgat_edge_gradients_match_oracle(heads, concats):
     """GAT_edge (what every shipped MP3D config trains): the edge term of the raw scores is a differentiable input of the
@@ -377,3 +369,44 @@ def test_mgat_edge_gradients_match_oracle(heads, concats):
     ref, net = _pair(kw)
     dev = clone_data(host, "cuda")
     _compare_grads(ref, net, lambda: ref(clone_data(host)), lambda: net(dev), 30)
+
+
+def test_eval_after_flat_adam_steps_uses_the_updated_weights_on_the_gpu():
+    """base_training_job.py:197-232 trains an epoch, then ``net.eval()`` + validation, every epoch.  hg_adam_step writes
+    the weights through a raw pointer (no ``data_ptr`` / ``_version`` change), so the packed TF32 images and the folded GAT
+    projections must be rebuilt: each eval must equal a cold model with the same weights."""
+    host = synth.synth_mp3d_batch(range(32))
+    labels = host["rooms"].y.long().cuda()
+    mask = labels != 25
+    net = synth.random_state_dict_(hg.HeterogeneousNetwork(**M_GAT), seed=0).cuda()
+    opt = FlatAdam(net.parameters(), lr=1e-2)
+    dev = clone_data(host, "cuda")
+
+    def cold_eval():
+        fresh = hg.HeterogeneousNetwork(**M_GAT)
+        fresh.load_state_dict({k: v.detach().cpu().clone() for k, v in net.state_dict().items()})
+        return fresh.eval().cuda()(dev)
+
+    seen = []
+    for steps in (1, 3):
+        net.train()
+        for _ in range(steps):
+            opt.zero_grad()
+            net.loss(net(dev), labels, mask).backward()
+            opt.step()
+        net.eval()
+        got = net(dev)
+        assert torch.equal(got, cold_eval())
+        seen.append(got.clone())
+    assert float((seen[0] - seen[1]).abs().max()) > 1e-3
+    # a step taken while the model stays in eval mode (no train()/eval() switch): the generation counter moves the keys
+    with torch.enable_grad():
+        net.train()
+        opt.zero_grad()
+        net.loss(net(dev), labels, mask).backward()
+    net.eval()
+    before = net(dev).clone()
+    opt.step()
+    after = net(dev)
+    assert float((before - after).abs().max()) > 1e-4
+    assert torch.equal(after, cold_eval())

@@ -352,3 +352,27 @@ def test_gloo_world2_gradient_all_reduce_gives_the_global_mean():
     for _, flat, wg in got:
         assert torch.allclose(flat, want, rtol=1e-6, atol=1e-6)
         assert torch.allclose(wg, w.grad, rtol=1e-6, atol=1e-6)  # the parameter's .grad is a view of the reduced buffer
+
+
+def test_plan_cache_keys_hold_their_tensors_so_recycled_addresses_cannot_alias():
+    """A fresh batch's ``room_mask`` / ``edge_index`` is ``_version`` 0 and can land in the allocator block a freed one
+    just left: ``(data_ptr, _version)`` alone is not an identity.  The caches keep the keyed tensor alive and compare
+    against it."""
+    from hydra_gnn_b200.nn import PlanCache, same_tensor
+
+    pc = PlanCache()
+    a = torch.tensor([True, False, True, False])
+    b = torch.tensor([False, True, True, True])
+    for k in range(20):  # alternating fresh clones: temporaries are freed and their blocks reused
+        m = (a if k % 2 == 0 else b).clone()
+        rows = pc.mask_rows("room_rows", m)
+        assert rows.tolist() == m.nonzero().view(-1).tolist(), k
+        del m
+    m = a.clone()
+    r1 = pc.mask_rows("room_rows", m)
+    assert pc.mask_rows("room_rows", m) is r1            # same tensor: cached
+    assert pc.mask_rows("room_rows", m[:]) is r1         # a full view of it too
+    m[1] = True                                          # in-place edit bumps the version
+    assert pc.mask_rows("room_rows", m).tolist() == [0, 1, 2]
+    e = torch.zeros(2, 3, dtype=torch.long)
+    assert same_tensor(e, e) and same_tensor(e, e.view(2, 3)) and not same_tensor(e, e.clone())

@@ -343,3 +343,86 @@ def test_training_steps_track_torch_adam(conv_block, heads):
         assert err <= 0.05 * lr * steps, f"{name}: {err:.3e}"  # Adam normalises: compare in units of the step size
         moved += float((p.detach() - start[name]).abs().max()) > 0
     assert moved >= 20
+
+
+def test_eval_after_flat_adam_steps_uses_the_updated_weights():
+    """The reference loop trains an epoch, then ``net.eval()`` + validation, every epoch (base_training_job.py:197-232).
+    FlatAdam updates the weights through a raw pointer (neither ``data_ptr`` nor ``_version`` of a parameter moves), so
+    every packed-weight cache must be keyed on more than those: step, eval, step, eval -- each eval must equal the eval of a
+    fresh model holding the same weights (cold caches)."""
+    from hydra_gnn_b200 import synth
+    from hydra_gnn_b200.train import FlatAdam
+
+    kw = dict(input_dim_dict={"objects": 306, "rooms": 6}, output_dim=26, conv_block="GAT", GAT_hidden_dims=[64, 64],
+              GAT_heads=[3, 3, 3], GAT_concats=[False] * 3, dropout=0.0)
+    net = synth.random_state_dict_(hg.HeterogeneousNetwork(**kw), seed=0)
+    data = lambda: synth.synth_mp3d_batch(range(8))  # noqa: E731
+    y = data()["rooms"].y.long()
+    mask = y != 25
+
+    def cold_eval():
+        fresh = hg.HeterogeneousNetwork(**kw)
+        fresh.load_state_dict({k: v.clone() for k, v in net.state_dict().items()})
+        return fresh.eval()(data())
+
+    from hydra_gnn_b200 import ops
+    saved = ops.PARALLEL_BRANCHES
+    ops.PARALLEL_BRANCHES = False  # the inference path forks side streams for independent branches: none on a CPU
+    try:
+        _eval_after_steps(net, data, y, mask, cold_eval, FlatAdam)
+    finally:
+        ops.PARALLEL_BRANCHES = saved
+
+
+def _eval_after_steps(net, data, y, mask, cold_eval, FlatAdam):
+    with cb.patched_ops():
+        opt = FlatAdam(net.parameters(), lr=1e-2)
+        seen = []
+        for steps in (1, 3):
+            net.train()
+            for _ in range(steps):
+                opt.zero_grad()
+                net.loss(net(data()), y, mask).backward()
+                opt.step()
+            net.eval()
+            got = net(data())
+            assert torch.equal(got, net(data()))  # warm caches agree with themselves ...
+            torch.testing.assert_close(got, cold_eval(), rtol=0, atol=0)  # ... and with a cold model
+            seen.append(got)
+        assert float((seen[0] - seen[1]).abs().max()) > 1e-3  # the weights did move between the two evals
+        # same without the train()/eval() switch in between (generation counter in the cache keys)
+        opt.zero_grad()
+        with torch.enable_grad():
+            net.train()
+            net.loss(net(data()), y, mask).backward()
+        net.eval()
+        before = net(data())
+        opt.step()  # eval mode, no mode switch after the step
+        after = net(data())
+        assert float((before - after).abs().max()) > 1e-4
+        torch.testing.assert_close(after, cold_eval(), rtol=0, atol=0)
+
+
+def test_flat_adam_survives_zero_grad_set_to_none_and_exposes_param_groups():
+    """``net.zero_grad()`` (set_to_none) detaches the parameters from the flat gradient buffer; the next step must use the
+    fresh gradients, not stale flat contents.  ``param_groups[0]['lr']`` drives the step size (StepLR in the reference)."""
+    from hydra_gnn_b200.train import FlatAdam
+
+    lin_a, lin_b = torch.nn.Linear(3, 2), torch.nn.Linear(3, 2)
+    lin_b.load_state_dict(lin_a.state_dict())
+    x = torch.randn(5, 3)
+    with cb.patched_ops():
+        opt = FlatAdam(lin_a.parameters(), lr=1e-2)
+        ref = torch.optim.Adam(lin_b.parameters(), lr=1e-2)
+        for k in range(4):
+            lin_a.zero_grad()  # set_to_none=True: p.grad rebound by the next backward
+            ref.zero_grad()
+            (lin_a(x) ** 2).sum().backward()
+            (lin_b(x) ** 2).sum().backward()
+            if k == 2:
+                opt.param_groups[0]["lr"] = 1e-3
+                ref.param_groups[0]["lr"] = 1e-3
+            opt.step()
+            ref.step()
+    torch.testing.assert_close(lin_a.weight, lin_b.weight, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(lin_a.bias, lin_b.bias, rtol=1e-5, atol=1e-6)
