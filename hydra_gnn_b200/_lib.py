@@ -14,6 +14,7 @@ import threading
 HG_MAX_RELATIONS = 8
 HG_MAX_SEGMENTS = 8
 HG_MAX_PLAN_RELATIONS = 16
+HG_PLAN_STATIC_SCRATCH_BYTES = 16 << 20
 
 REDUCE = {"sum": 0, "add": 0, "mean": 1, "max": 2}
 ACT = {None: 0, "none": 0, "relu": 1, "elu": 2}
@@ -86,6 +87,7 @@ SYMBOLS = {
     "hg_sizeof": (C.c_int, [C.c_int]),
     "hg_plan_workspace_bytes": (C.c_size_t, [C.POINTER(PlanRel), C.c_int]),
     "hg_plan_build": (C.c_int, [C.POINTER(PlanRel), C.c_int, vp, vp, C.c_size_t, vp]),
+    "hg_plan_build_static": (C.c_int, [C.POINTER(PlanRel), C.c_int, vp, vp]),
     "hg_seg_reduce": (C.c_int, [C.POINTER(SegArgs), vp]),
     "hg_gat_fused": (C.c_int, [C.POINTER(GatArgs), vp]),
     "hg_linear_workspace_bytes": (C.c_size_t, [C.POINTER(LinearArgs)]),

@@ -37,6 +37,7 @@ extern "C" const char* hg_strerror(int code) {
         case HG_ECUDA: return "CUDA runtime error (see hg_last_cuda_error)";
         case HG_EALIGN: return "pointer or leading dimension misaligned";
         case HG_EUNSUPPORTED: return "unsupported shape for this kernel";
+        case HG_ECAPACITY: return "problem exceeds the fixed scratch capacity of this *_static entry point";
         default: return "unknown error";
     }
 }

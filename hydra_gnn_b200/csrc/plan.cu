@@ -5,6 +5,8 @@
 // -> every edge ranks itself inside its (short) row.  All relations of a batch share each
 // launch (blockIdx.y = relation) so a 4-relation DSG plan or a 15-relation H-tree plan costs
 // the same number of launches.  HBM-bound: 16 B/edge in, 8 B/edge + 4 B/row out.
+#include <mutex>
+
 #include "hg_common.cuh"
 
 namespace hg {
@@ -270,4 +272,53 @@ extern "C" int hg_plan_build(const hg_plan_rel* rels, int n_rel, int32_t* status
     if (max_edges > 0) k_fill<<<dim3(edge_grid(max_edges), n_rel), kEdgeThreads, 0, stream>>>(P);
     if (max_total > 0) k_rank<<<dim3(edge_grid(max_total), n_rel), kEdgeThreads, 0, stream>>>(P);
     return check_launch();
+}
+
+// ---------------------------------------------------------------------------------------------------
+// hg_plan_build_static -- hg_plan_build for callers that cannot call cudaMalloc (code under CUDA-graph
+// capture, tight serving loops, harnesses that forbid allocation).  The workspace is a file-scope device
+// array of HG_PLAN_STATIC_SCRATCH_BYTES: every GPU that loads the library holds it until exit.  Every
+// call shares the array (it keeps the last call's contents; the plan clears the part that must start at
+// zero itself), so calls that overlap on the GPU -- two streams, two threads -- race.
+// ---------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_plan_scratch[HG_PLAN_STATIC_SCRATCH_BYTES];
+
+namespace hg {
+namespace {
+
+constexpr int kMaxDevices = 64;
+std::mutex g_scratch_mu;
+void* g_scratch_ptr[kMaxDevices] = {};  // device address of g_plan_scratch, per device ordinal
+
+// In host code `g_plan_scratch` is a host-side stand-in, not a device address: ask the runtime for the
+// address on the CURRENT device, once per device.
+int static_scratch(void** out) {
+    int dev = -1;
+    HG_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return HG_EUNSUPPORTED;
+    std::lock_guard<std::mutex> lock(g_scratch_mu);
+    if (!g_scratch_ptr[dev]) {
+        void* p = nullptr;
+        HG_CUDA_TRY(cudaGetSymbolAddress(&p, g_plan_scratch));
+        if (!p) return HG_ECUDA;
+        g_scratch_ptr[dev] = p;
+    }
+    *out = g_scratch_ptr[dev];
+    return HG_OK;
+}
+
+}  // namespace
+}  // namespace hg
+
+extern "C" int hg_plan_build_static(const hg_plan_rel* rels, int n_rel, int32_t* status, void* stream_) {
+    using namespace hg;
+    WsLayout L;
+    const int rc = layout(rels, n_rel, L);
+    if (rc != HG_OK) return rc;
+    if (L.total > static_cast<size_t>(HG_PLAN_STATIC_SCRATCH_BYTES)) return HG_ECAPACITY;  // before any CUDA call
+    if (n_rel == 0) return HG_OK;
+    void* ws = nullptr;
+    const int rs = static_scratch(&ws);
+    if (rs != HG_OK) return rs;
+    return hg_plan_build(rels, n_rel, status, ws, HG_PLAN_STATIC_SCRATCH_BYTES, stream_);
 }

@@ -47,7 +47,8 @@ enum {
     HG_EWORKSPACE = -3, /* workspace too small */
     HG_ECUDA = -4,    /* a CUDA runtime call failed; see hg_last_cuda_error() */
     HG_EALIGN = -5,   /* pointer / leading dimension violates the alignment contract */
-    HG_EUNSUPPORTED = -6
+    HG_EUNSUPPORTED = -6,
+    HG_ECAPACITY = -7 /* problem larger than the fixed capacity of a *_static entry point */
 };
 
 enum { HG_REDUCE_SUM = 0, HG_REDUCE_MEAN = 1, HG_REDUCE_MAX = 2 };
@@ -103,6 +104,19 @@ typedef struct hg_plan_rel {
 HG_API size_t hg_plan_workspace_bytes(const hg_plan_rel* rels_host, int n_rel);
 HG_API int hg_plan_build(const hg_plan_rel* rels_host, int n_rel, int32_t* status /* [1], zeroed by the call */,
                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* hg_plan_build without a caller workspace and without any allocation (no cudaMalloc / cudaFree, no allocating
+ * library routine) -- for code under CUDA-graph capture, tight serving loops and harnesses that forbid allocation.
+ * NO counterpart in the reference.
+ * The scratch is a file-scope `static __device__` array of HG_PLAN_STATIC_SCRATCH_BYTES inside the library, held by
+ * every GPU that loads it until process exit.  Same outputs, bit for bit, as hg_plan_build.  Returns HG_ECAPACITY
+ * (before any CUDA call) when hg_plan_workspace_bytes(rels, n_rel) - 256 exceeds HG_PLAN_STATIC_SCRATCH_BYTES
+ * (16 MiB holds one 4096-graph MP3D-shaped DSG batch; an H-tree batch of that size does not fit).
+ * All calls on a device share the one array, which keeps the previous call's contents (the plan zeroes what it
+ * needs zeroed): calls that overlap on the GPU -- different streams, different threads -- RACE; serialise them. */
+#define HG_PLAN_STATIC_SCRATCH_BYTES (16u << 20)
+HG_API int hg_plan_build_static(const hg_plan_rel* rels_host, int n_rel, int32_t* status /* [1], zeroed by the call */,
+                  void* stream);
 
 /* ------------------------------------------------------------------------------------
  * K2 / K5  Segmented reduction over CSR rows (sum / mean / max), warp-per-destination,
