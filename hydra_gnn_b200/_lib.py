@@ -14,6 +14,7 @@ import threading
 HG_MAX_RELATIONS = 8
 HG_MAX_SEGMENTS = 8
 HG_MAX_PLAN_RELATIONS = 16
+HG_TILE_ROWS = 32
 HG_PLAN_STATIC_SCRATCH_BYTES = 16 << 20
 
 REDUCE = {"sum": 0, "add": 0, "mean": 1, "max": 2}
@@ -31,7 +32,7 @@ vp, i32, i64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
 class PlanRel(C.Structure):
     _fields_ = [("src", vp), ("dst", vp), ("n_edges", i64), ("n_src", i32), ("n_dst", i32),
                 ("self_loops", i32), ("reserved", i32), ("rowptr", vp), ("col", vp), ("perm", vp),
-                ("inv_sqrt_deg", vp)]
+                ("inv_sqrt_deg", vp), ("tile_win", vp)]
 
 
 class SegArgs(C.Structure):
@@ -42,7 +43,7 @@ class SegArgs(C.Structure):
 
 class GatRel(C.Structure):
     _fields_ = [("xs", vp), ("ldxs", i64), ("a_src", vp), ("lda_src", i64), ("a_dst", vp), ("lda_dst", i64),
-                ("a_edge", vp), ("rowptr", vp), ("col", vp), ("bias", vp)]
+                ("a_edge", vp), ("rowptr", vp), ("col", vp), ("bias", vp), ("tile_win", vp)]
 
 
 class GatArgs(C.Structure):

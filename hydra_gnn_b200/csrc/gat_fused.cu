@@ -23,7 +23,9 @@
 // src_shared = 1 is the aggregate-first form: xs is [n_src, C] (ONE row shared by all heads) and the
 // output is [n_dst, H*C] with out[i, h, :] = sum_e w_eh xs[j, :]; the projection is applied afterwards
 // to the aggregated rows (used when a relation has far fewer destinations than sources).
-#include "hg_common.cuh"
+#include <cstdlib>
+
+#include "tc_common.cuh"
 
 namespace hg {
 namespace {
@@ -51,6 +53,7 @@ struct GatParams {
     int32_t f_begin;    // first column of this launch (wide rows are split over launches);
     int32_t f_count;    // columns of this launch.  OUTPUT columns, except MODE 2: columns of the source row
     int32_t n_bias;     // staged bias values: f_count (MODE 2: H * f_count, head-major)
+    int32_t wrows;      // window kernel: source rows the shared-memory window holds (all relations of a tile)
 };
 
 __device__ __forceinline__ float leaky(float v, float slope) { return v > 0.f ? v : v * slope; }
@@ -436,7 +439,7 @@ k_gat_fused(const __grid_constant__ GatParams P) {
                     const float* bp = S.bias + (MODE == 2 ? h * P.f_count : 0) + lc;
                     float o[VEC];
 #pragma unroll
-                    for (int v = 0; v < VEC; ++v) o[v] = (acc[h][k][v] * hscale + bp[v]) * gscale;
+                    for (int v = 0; v < VEC; ++v) o[v] = __fmul_rn(__fadd_rn(__fmul_rn(acc[h][k][v], hscale), bp[v]), gscale);
                     if (addp) {
                         float av[VEC];
                         ldg_vec<VEC>(addp + oc, av);
@@ -527,6 +530,480 @@ int dispatch_special(GatParams& P, cudaStream_t stream) {
     return HG_EUNSUPPORTED;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Window variant (v9) -- head-mean, C = 64, H <= 4, R <= 4, inference (no alpha_saved / dropout).
+//
+// A batch of scene graphs is a disjoint union in graph order and object-object edges stay inside a room, so the
+// sources of a tile of 32 consecutive destination rows are a window of a few dozen consecutive rows of xs (the plan
+// records {first row, rows} per tile: hg_plan_rel.tile_win).  The v6 kernel above gathers those rows with
+// per-thread LDG.128 and is bound by instruction issue and by the latency of its L1 misses (ncu, round 1: 80 M
+// warp instructions, IPC 1.9, 45 % of the warps active, DRAM traffic 1.07x the algorithmic bytes).  A first window
+// kernel with CTA-wide phases (stage / softmax / gather between __syncthreads) reached only 143 us: 39 % of its warp
+// samples sat at barriers and 24 % behind the staging loads (col -> a_src: dependent DRAM round trips per tile).
+// Here one persistent CTA per SM is warp-specialised and nothing in it meets at a CTA barrier:
+//   window warp     per tile, in tile order: waits for a free window stage (ring of 3) and issues one cp.async.bulk
+//                   per window row (H*C*4 = 768 B each; rows of a column slice of the projection output: pitch ldxs,
+//                   16-byte aligned) onto the stage's `win_full` mbarrier: the HBM/L2 stream of a tile costs ~50
+//                   instructions instead of 300 loads and runs up to three tiles ahead of the gather;
+//   edge producers  6 warps, each with its OWN edge stage and every 6th tile (so six tiles are being staged while one
+//                   is gathered: the DRAM round trips overlap): lanes = edges: neighbour id -> byte offset of its row
+//                   in the window (or -1 - id for a source outside the staged rows: that edge is gathered from global
+//                   memory, so ANY graph is handled) and the raw logits of all heads as one float4; then lanes =
+//                   rows: softmax in three passes over the row's float4 logits; arrive on the stage's `edge_full`;
+//   consumers       8 warps, tile by tile: wait `edge_full` and `win_full`; 8 threads per row, each owning float4
+//                   chunks q and q + 8 of the 64 output columns: per edge one LDS of the offset, one LDS.128 of the
+//                   weights, 2 H LDS.128 of the source row, 8 H FFMA (same accumulation order as v6: the two kernels
+//                   agree bit for bit); one lane per warp releases both stages, then the epilogue runs from registers.
+// All relations of a tile share one edge pool and one window pool (packed per tile).
+// Tiles whose edges exceed the pool (hub rows) take v6's warp-per-row path in the consumer warps.
+// ---------------------------------------------------------------------------------------------------
+constexpr int kWinConsumerWarps = 8, kWinProducerWarps = 6, kWinStages = 3;
+constexpr int kWinThreads = (kWinConsumerWarps + kWinProducerWarps + 1) * 32;  // 480
+constexpr int kWinC = 64;               // channels per head (8 threads x 2 float4 chunks)
+constexpr int kWinBytes = 43008;        // window pool of one stage: 56 rows at H = 3
+constexpr int kWinEdges = 448;          // edge pool of one stage (all relations of a tile)
+constexpr int kWinMaxRel = 4;
+constexpr int kWinBars = 2 * kWinProducerWarps + 2 * kWinStages;
+
+// one edge stage: weights float4[ecap] | destination logits float4[rmax][32] | offsets int[ecap] |
+// pool-relative rowptr int[rmax][33] (padded to 16 B) | control int[4] {hub, window rows, any source outside}
+__host__ __device__ inline uint32_t win_edge_stage_bytes(int ecap, int rmax) {
+    return static_cast<uint32_t>(ecap * 16 + rmax * kMaxTile * 16 + ecap * 4 + (rmax * (kMaxTile + 1) * 4 + 15) / 16 * 16 + 16);
+}
+__host__ __device__ inline size_t win_smem_bytes(int wrows, int rowb, int ecap, int rmax) {
+    return static_cast<size_t>(kWinStages) * wrows * rowb + static_cast<size_t>(kWinProducerWarps) * win_edge_stage_bytes(ecap, rmax) +
+           kWinC * 4 + kWinBars * 8 + 16;
+}
+
+__device__ __forceinline__ float ex2_ftz(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// edge ranges and window slices of a tile, packed (uniform loads; every role computes the same values)
+template <int ROWB, int RMAX>
+struct WinTile {
+    int e0[RMAX], ne[RMAX], eb[RMAX], wlo[RMAX], wn[RMAX], wb[RMAX];
+    int tot, used;
+    __device__ __forceinline__ void load(const hg_gat_args& A, int64_t tile, int64_t t0, int rows, int wrows) {
+        tot = 0;
+        used = 0;
+#pragma unroll
+        for (int r = 0; r < RMAX; ++r) {
+            e0[r] = ne[r] = eb[r] = wlo[r] = wn[r] = wb[r] = 0;
+            if (r < A.n_rel) {
+                const hg_gat_rel& Rl = A.rel[r];
+                e0[r] = __ldg(Rl.rowptr + t0);
+                ne[r] = __ldg(Rl.rowptr + t0 + rows) - e0[r];
+                eb[r] = tot;
+                tot += ne[r];
+                if (Rl.tile_win) {
+                    const int2 w = __ldg(reinterpret_cast<const int2*>(Rl.tile_win) + tile);
+                    wlo[r] = w.x;
+                    wn[r] = w.y < wrows - used ? w.y : wrows - used;
+                    wb[r] = used * ROWB;
+                    used += wn[r];
+                }
+            }
+        }
+    }
+};
+
+template <int HT, int RMAX>
+__global__ void __launch_bounds__(kWinThreads, 1)
+k_gat_window(const __grid_constant__ GatParams P) {
+    extern __shared__ __align__(128) uint8_t s_raw[];
+    constexpr int ROWB = HT * kWinC * 4;  // bytes of one window row
+    const hg_gat_args& A = P.a;
+    const int R = A.n_rel;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t win_bytes = static_cast<uint32_t>(P.wrows) * ROWB;
+    const uint32_t est_bytes = win_edge_stage_bytes(P.cap, RMAX);
+    uint8_t* const edge0 = s_raw + static_cast<size_t>(kWinStages) * win_bytes;
+    uint8_t* const tail = edge0 + static_cast<size_t>(kWinProducerWarps) * est_bytes;
+    float* const s_bias = reinterpret_cast<float*>(tail);
+    uint64_t* const s_bar = reinterpret_cast<uint64_t*>(tail + kWinC * 4);
+    const uint32_t bar_a = tc::smem_u32(s_bar);
+    const uint32_t edge_full = bar_a, edge_empty = bar_a + 8 * kWinProducerWarps;
+    const uint32_t win_full = bar_a + 16 * kWinProducerWarps, win_empty = win_full + 8 * kWinStages;
+    // offsets inside an edge stage
+    const uint32_t o_ad = static_cast<uint32_t>(P.cap) * 16;
+    const uint32_t o_off = o_ad + RMAX * kMaxTile * 16;
+    const uint32_t o_rp = o_off + static_cast<uint32_t>(P.cap) * 4;
+    const uint32_t o_ctl = o_rp + (RMAX * (kMaxTile + 1) * 4 + 15) / 16 * 16;
+
+    if (tid < kWinC) {
+        float b = 0.f;
+        for (int r = 0; r < R; ++r)
+            if (A.rel[r].bias) b += __ldg(A.rel[r].bias + tid);
+        s_bias[tid] = b;
+    }
+    if (tid == 0) {
+        for (int s = 0; s < kWinProducerWarps; ++s) {
+            tc::mbar_init(s_bar + s, 1);                                        // edge_full: lane 0 of the producer warp
+            tc::mbar_init(s_bar + kWinProducerWarps + s, kWinConsumerWarps);    // edge_empty: one lane per consumer warp
+        }
+        for (int s = 0; s < kWinStages; ++s) {
+            tc::mbar_init(s_bar + 2 * kWinProducerWarps + s, 1);                // win_full: one arrive (+ the copies' bytes)
+            tc::mbar_init(s_bar + 2 * kWinProducerWarps + kWinStages + s, kWinConsumerWarps);  // win_empty
+        }
+        tc::fence_barrier_init();
+    }
+    __syncthreads();
+    const int64_t n_tiles = ceil_div<int64_t>(A.n_dst, kMaxTile);
+    const int n_k = static_cast<int>((n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x);  // tiles of this CTA
+
+    if (warp == kWinConsumerWarps + kWinProducerWarps) {
+        // ================================================================== window warp
+        int ws = 0;
+        uint32_t wph = 0;
+        for (int k = 0; k < n_k; ++k) {
+            const int64_t tile = blockIdx.x + static_cast<int64_t>(k) * gridDim.x, t0 = tile * kMaxTile;
+            const int rows = (A.n_dst - t0 < kMaxTile) ? static_cast<int>(A.n_dst - t0) : kMaxTile;
+            WinTile<ROWB, RMAX> T;
+            T.load(A, tile, t0, rows, P.wrows);  // issued before the wait: in flight while the stage drains
+            tc::mbar_wait(win_empty + 8 * ws, wph ^ 1u);
+            if (T.tot > P.cap || T.used == 0) {  // hub tile / no window: complete the phase without bytes
+                if (lane == 0) tc::mbar_arrive(win_full + 8 * ws);
+            } else {
+                if (lane == 0) tc::mbar_arrive_expect_tx(win_full + 8 * ws, static_cast<uint32_t>(T.used) * ROWB);
+                __syncwarp();
+                const uint32_t win_a = tc::smem_u32(s_raw) + ws * win_bytes;
+#pragma unroll
+                for (int r = 0; r < RMAX; ++r) {
+                    if (r < R && T.wn[r] > 0) {
+                        const size_t pitch = static_cast<size_t>(A.rel[r].ldxs) * 4;
+                        const char* src = reinterpret_cast<const char*>(A.rel[r].xs) + static_cast<size_t>(T.wlo[r]) * pitch;
+                        for (int row = lane; row < T.wn[r]; row += 32)
+                            tc::bulk_g2s(win_a + T.wb[r] + row * ROWB, src + static_cast<size_t>(row) * pitch, ROWB, win_full + 8 * ws);
+                    }
+                }
+            }
+            __syncwarp();
+            if (++ws == kWinStages) ws = 0, wph ^= 1u;
+        }
+        return;
+    }
+
+    if (warp >= kWinConsumerWarps) {
+        // ================================================================== edge producers: warp p, tiles k = p, p + 6, ...
+        const int p = warp - kWinConsumerWarps;
+        uint8_t* const st = edge0 + static_cast<size_t>(p) * est_bytes;
+        float4* const s_w = reinterpret_cast<float4*>(st);
+        float4* const s_ad = reinterpret_cast<float4*>(st + o_ad);
+        int32_t* const s_off = reinterpret_cast<int32_t*>(st + o_off);
+        int32_t* const s_rp = reinterpret_cast<int32_t*>(st + o_rp);
+        int32_t* const s_ctl = reinterpret_cast<int32_t*>(st + o_ctl);
+        uint32_t eph = 0;
+        for (int k = p; k < n_k; k += kWinProducerWarps, eph ^= 1u) {
+            const int64_t tile = blockIdx.x + static_cast<int64_t>(k) * gridDim.x, t0 = tile * kMaxTile;
+            const int rows = (A.n_dst - t0 < kMaxTile) ? static_cast<int>(A.n_dst - t0) : kMaxTile;
+            WinTile<ROWB, RMAX> T;
+            T.load(A, tile, t0, rows, P.wrows);
+            tc::mbar_wait(edge_empty + 8 * p, eph ^ 1u);  // stage free (the first pass is on the fresh barrier)
+            if (T.tot > P.cap) {  // hub tile (uniform): the consumers stream it from global memory
+                if (lane == 0) {
+                    s_ctl[0] = 1, s_ctl[1] = 0, s_ctl[2] = 0;
+                    tc::mbar_arrive(edge_full + 8 * p);
+                }
+                __syncwarp();
+                continue;
+            }
+            // ---- stage: pool-relative rowptr slices, destination logits ...
+            for (int idx = lane; idx < R * (kMaxTile + 1); idx += 32) {
+                const int r = idx / (kMaxTile + 1), tt = idx - r * (kMaxTile + 1);
+                int d = 0;
+#pragma unroll
+                for (int rr = 0; rr < RMAX; ++rr)
+                    if (rr == r) d = T.eb[rr] - T.e0[rr];
+                s_rp[idx] = __ldg(A.rel[r].rowptr + t0 + min(tt, rows)) + d;
+            }
+#pragma unroll
+            for (int r = 0; r < RMAX; ++r) {
+                if (r < R && lane < rows) {
+                    const hg_gat_rel& Rl = A.rel[r];
+                    const float* ap = Rl.a_dst + (t0 + lane) * Rl.lda_dst;
+                    float v[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int h = 0; h < HT; ++h) v[h] = __ldg(ap + h);
+                    s_ad[r * kMaxTile + lane] = make_float4(v[0], v[1], v[2], v[3]);
+                }
+            }
+            // ---- ... and, lanes = edges in batches of 4 x 32 (all neighbour ids of a batch in flight, then all logits)
+            bool miss = false;
+#pragma unroll
+            for (int r = 0; r < RMAX; ++r) {
+                if (r < R) {
+                    const hg_gat_rel& Rl = A.rel[r];
+                    const float* __restrict__ a_src = Rl.a_src;
+                    const float* __restrict__ a_edge = Rl.a_edge;
+                    const int64_t lda = Rl.lda_src;
+                    const int n = T.ne[r];
+                    for (int base = 0; base < n; base += 128) {
+                        int32_t j[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int e = base + u * 32 + lane;
+                            j[u] = e < n ? __ldg(Rl.col + T.e0[r] + e) : -1;
+                        }
+                        float v[4][4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+#pragma unroll
+                            for (int h = 0; h < 4; ++h) v[u][h] = 0.f;
+                            if (j[u] >= 0) {
+                                const float* src = a_src + static_cast<int64_t>(j[u]) * lda;
+#pragma unroll
+                                for (int h = 0; h < HT; ++h) v[u][h] = __ldg(src + h);
+                                if (a_edge) {
+                                    const float* ae = a_edge + static_cast<int64_t>(T.e0[r] + base + u * 32 + lane) * HT;
+#pragma unroll
+                                    for (int h = 0; h < HT; ++h) v[u][h] += __ldg(ae + h);
+                                }
+                            }
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            if (j[u] >= 0) {
+                                const int e = T.eb[r] + base + u * 32 + lane;
+                                const uint32_t d = static_cast<uint32_t>(j[u] - T.wlo[r]);
+                                const bool in = d < static_cast<uint32_t>(T.wn[r]);
+                                miss = miss || !in;
+                                s_off[e] = in ? static_cast<int32_t>(T.wb[r] + d * ROWB) : -1 - j[u];
+                                s_w[e] = make_float4(v[u][0], v[u][1], v[u][2], v[u][3]);
+                            }
+                        }
+                    }
+                }
+            }
+            const bool any_miss = __any_sync(0xffffffffu, miss);
+            __syncwarp();  // the stores above are ordered before the reads below (other lanes' edges)
+
+            // ---- softmax in place: lanes = rows, relation by relation; all heads of an edge are one float4
+#pragma unroll
+            for (int r = 0; r < RMAX; ++r) {
+                if (r < R && lane < rows) {
+                    const int beg = s_rp[r * (kMaxTile + 1) + lane], end = s_rp[r * (kMaxTile + 1) + lane + 1];
+                    const float4 ad4 = s_ad[r * kMaxTile + lane];
+                    const float ad[4] = {ad4.x, ad4.y, ad4.z, ad4.w};
+                    float m[HT], l[HT];
+#pragma unroll
+                    for (int h = 0; h < HT; ++h) m[h] = -INFINITY, l[h] = 0.f;
+                    for (int e = beg; e < end; ++e) {
+                        float4 w4 = s_w[e];
+                        float v[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+                        for (int h = 0; h < HT; ++h) {
+                            v[h] = leaky(v[h] + ad[h], A.neg_slope);
+                            m[h] = fmaxf(m[h], v[h]);
+                        }
+                        s_w[e] = make_float4(v[0], v[1], v[2], v[3]);
+                    }
+                    for (int e = beg; e < end; ++e) {
+                        float4 w4 = s_w[e];
+                        float v[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+                        for (int h = 0; h < HT; ++h) {
+                            v[h] = __expf(v[h] - m[h]);
+                            l[h] += v[h];
+                        }
+                        s_w[e] = make_float4(v[0], v[1], v[2], v[3]);
+                    }
+                    float inv[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int h = 0; h < HT; ++h) inv[h] = 1.f / (l[h] + 1e-16f);
+                    for (int e = beg; e < end; ++e) {
+                        float4 w4 = s_w[e];
+                        s_w[e] = make_float4(w4.x * inv[0], w4.y * inv[1], w4.z * inv[2], w4.w * inv[3]);
+                    }
+                }
+            }
+            if (lane == 0) s_ctl[0] = 0, s_ctl[1] = T.used, s_ctl[2] = any_miss ? 1 : 0;
+            __syncwarp();  // every lane's stage writes are ordered before lane 0's releasing arrive
+            if (lane == 0) tc::mbar_arrive(edge_full + 8 * p);
+        }
+        return;
+    }
+
+    // ====================================================================== consumers
+    const int q = tid & 7, t = tid >> 3;  // chunk pair / destination row of the tile
+    const float gscale = (A.group == HG_GROUP_MEAN) ? 1.f / static_cast<float>(R) : 1.f;
+    const float hscale = 1.f / static_cast<float>(HT);
+    int es = 0, ws = 0;
+    uint32_t eph = 0, wph = 0;
+    for (int k = 0; k < n_k; ++k) {
+        const int64_t tile = blockIdx.x + static_cast<int64_t>(k) * gridDim.x, t0 = tile * kMaxTile;
+        const int rows = (A.n_dst - t0 < kMaxTile) ? static_cast<int>(A.n_dst - t0) : kMaxTile;
+        const uint8_t* const st = edge0 + static_cast<size_t>(es) * est_bytes;
+        const float4* const s_w = reinterpret_cast<const float4*>(st);
+        const int32_t* const s_off = reinterpret_cast<const int32_t*>(st + o_off);
+        const int32_t* const s_rp = reinterpret_cast<const int32_t*>(st + o_rp);
+        const int32_t* const s_ctl = reinterpret_cast<const int32_t*>(st + o_ctl);
+        const uint32_t b_ef = edge_full + 8 * es, b_ee = edge_empty + 8 * es, b_wf = win_full + 8 * ws, b_we = win_empty + 8 * ws;
+        const uint8_t* const wq = s_raw + static_cast<size_t>(ws) * win_bytes + q * 16;
+
+        tc::mbar_wait(b_ef, eph);
+        tc::mbar_wait(b_wf, wph);
+        const int hub = s_ctl[0], any_miss = s_ctl[2];
+        if (++es == kWinProducerWarps) es = 0, eph ^= 1u;
+        if (++ws == kWinStages) ws = 0, wph ^= 1u;
+        if (hub) {  // uniform: warp per row straight from global memory
+            for (int tt = warp; tt < rows; tt += kWinConsumerWarps) slow_row<4>(P, t0 + tt, lane, 0, kWinC);
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(b_ee), tc::mbar_arrive(b_we);
+            continue;
+        }
+        float acc[2][4];
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk)
+#pragma unroll
+            for (int v = 0; v < 4; ++v) acc[kk][v] = 0.f;
+        if (t < rows) {
+#pragma unroll
+            for (int r = 0; r < RMAX; ++r) {
+                if (r < R) {
+                    const int beg = s_rp[r * (kMaxTile + 1) + t], end = s_rp[r * (kMaxTile + 1) + t + 1];
+                    if (!any_miss) {  // every source of the tile is in the window: no per-edge branch
+#pragma unroll 2
+                        for (int e = beg; e < end; ++e) {
+                            const int32_t off = s_off[e];
+                            const float4 wa = s_w[e];
+                            const float wv[4] = {wa.x, wa.y, wa.z, wa.w};
+                            float4 val[HT][2];
+#pragma unroll
+                            for (int hh = 0; hh < HT; ++hh) {
+                                val[hh][0] = *reinterpret_cast<const float4*>(wq + off + hh * (kWinC * 4));
+                                val[hh][1] = *reinterpret_cast<const float4*>(wq + off + hh * (kWinC * 4) + 128);
+                            }
+#pragma unroll
+                            for (int hh = 0; hh < HT; ++hh)
+#pragma unroll
+                                for (int kk = 0; kk < 2; ++kk) {
+                                    acc[kk][0] = fmaf(wv[hh], val[hh][kk].x, acc[kk][0]);
+                                    acc[kk][1] = fmaf(wv[hh], val[hh][kk].y, acc[kk][1]);
+                                    acc[kk][2] = fmaf(wv[hh], val[hh][kk].z, acc[kk][2]);
+                                    acc[kk][3] = fmaf(wv[hh], val[hh][kk].w, acc[kk][3]);
+                                }
+                        }
+                    } else {
+                        const char* xg = reinterpret_cast<const char*>(A.rel[r].xs) + q * 16;
+                        const uint32_t pitch = static_cast<uint32_t>(A.rel[r].ldxs) * 4u;
+                        for (int e = beg; e < end; ++e) {
+                            const int32_t off = s_off[e];
+                            const float4 wa = s_w[e];
+                            const float wv[4] = {wa.x, wa.y, wa.z, wa.w};
+                            float4 val[HT][2];
+                            if (off >= 0) {
+#pragma unroll
+                                for (int hh = 0; hh < HT; ++hh) {
+                                    val[hh][0] = *reinterpret_cast<const float4*>(wq + off + hh * (kWinC * 4));
+                                    val[hh][1] = *reinterpret_cast<const float4*>(wq + off + hh * (kWinC * 4) + 128);
+                                }
+                            } else {  // source outside the staged window
+                                const char* row = xg + static_cast<uint64_t>(static_cast<uint32_t>(-1 - off)) * pitch;
+#pragma unroll
+                                for (int hh = 0; hh < HT; ++hh) {
+                                    val[hh][0] = __ldg(reinterpret_cast<const float4*>(row + hh * (kWinC * 4)));
+                                    val[hh][1] = __ldg(reinterpret_cast<const float4*>(row + hh * (kWinC * 4) + 128));
+                                }
+                            }
+#pragma unroll
+                            for (int hh = 0; hh < HT; ++hh)
+#pragma unroll
+                                for (int kk = 0; kk < 2; ++kk) {
+                                    acc[kk][0] = fmaf(wv[hh], val[hh][kk].x, acc[kk][0]);
+                                    acc[kk][1] = fmaf(wv[hh], val[hh][kk].y, acc[kk][1]);
+                                    acc[kk][2] = fmaf(wv[hh], val[hh][kk].z, acc[kk][2]);
+                                    acc[kk][3] = fmaf(wv[hh], val[hh][kk].w, acc[kk][3]);
+                                }
+                        }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(b_ee), tc::mbar_arrive(b_we);  // release: this warp no longer reads the stages
+        if (t >= rows) continue;
+        // ---- epilogue: head mean, summed biases, group mean, addend, activation, one store per chunk
+        // (FMUL then FADD like v6's SASS, so the two kernels round identically)
+        const int64_t i = t0 + t;
+        const float* __restrict__ addp = A.addend ? A.addend + i * A.ldadd : nullptr;
+        float* __restrict__ outp = A.out + i * A.ldout;
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk) {
+            const int oc = (q + kk * 8) * 4;
+            const float4 b4 = *reinterpret_cast<const float4*>(s_bias + oc);
+            const float bv[4] = {b4.x, b4.y, b4.z, b4.w};
+            float o[4];
+#pragma unroll
+            for (int v = 0; v < 4; ++v) o[v] = __fmul_rn(__fadd_rn(__fmul_rn(acc[kk][v], hscale), bv[v]), gscale);
+            if (addp) {
+                float av[4];
+                ldg_vec<4>(addp + oc, av);
+#pragma unroll
+                for (int v = 0; v < 4; ++v) o[v] = __fadd_rn(o[v], av[v]);
+            }
+            if (A.act == HG_ACT_RELU) {
+#pragma unroll
+                for (int v = 0; v < 4; ++v) o[v] = fmaxf(o[v], 0.f);
+            } else if (A.act == HG_ACT_ELU) {
+                // exp(x) - 1 for x <= 0 as one MUFU.EX2: equal to v6's __expf(x) - 1 (they differ only where exp(x) is
+                // denormal, and there both give -1)
+#pragma unroll
+                for (int v = 0; v < 4; ++v) o[v] = o[v] > 0.f ? o[v] : ex2_ftz(__fmul_rn(o[v], 1.4426950408889634f)) - 1.f;
+            }
+            st_vec<4>(outp + oc, o);
+        }
+    }
+}
+
+template <int HT, int RMAX>
+int launch_window(GatParams& P, cudaStream_t stream) {
+    constexpr int ROWB = HT * kWinC * 4;
+    P.tile_rows = kMaxTile;
+    P.hs = 4;
+    P.n_bias = kWinC;
+    P.cap = kWinEdges;
+    P.wrows = kWinBytes / ROWB;
+    const size_t smem = win_smem_bytes(P.wrows, ROWB, P.cap, RMAX);
+    HG_CUDA_TRY(cudaFuncSetAttribute(k_gat_window<HT, RMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    const int sms = sm_count() > 0 ? sm_count() : 148;
+    const int64_t need = ceil_div<int64_t>(P.a.n_dst, kMaxTile);
+    k_gat_window<HT, RMAX><<<static_cast<unsigned>(need < sms ? need : sms), kWinThreads, smem, stream>>>(P);  // persistent
+    return check_launch();
+}
+
+template <int RMAX>
+int dispatch_window(GatParams& P, cudaStream_t stream) {
+    switch (P.a.H) {
+        case 1: return launch_window<1, RMAX>(P, stream);
+        case 2: return launch_window<2, RMAX>(P, stream);
+        case 3: return launch_window<3, RMAX>(P, stream);
+        case 4: return launch_window<4, RMAX>(P, stream);
+        default: return HG_EUNSUPPORTED;
+    }
+}
+
+// HG_GAT_WINDOW=0 keeps the v6 kernel (A/B runs)
+bool window_enabled() {
+    static const bool on = [] {
+        const char* e = std::getenv("HG_GAT_WINDOW");
+        return !(e && e[0] == '0');
+    }();
+    return on;
+}
+
+// Aggregate-first over wide, 8-byte aligned source rows (the 306-d input features: 153 float2 chunks, 5 per lane).
+template <int HT>
+int dispatch_wide_shared(GatParams& P, cudaStream_t stream) {
+    const int nco = P.f_count / 2;
+    if (nco <= 96) return launch<2, 32, 3, 2, HT>(P, stream);
+    if (nco <= 128) return launch<2, 32, 4, 2, HT>(P, stream);
+    if (nco <= 160) return launch<2, 32, 5, 2, HT>(P, stream);
+    return HG_EUNSUPPORTED;
+}
+
 template <int MODE>
 int dispatch_heads(GatParams& P, cudaStream_t stream) {
     switch (P.a.H) {
@@ -577,12 +1054,35 @@ extern "C" int hg_gat_fused(const hg_gat_args* a, void* stream_) {
         P.a = *a;
         P.f_begin = 0;
         P.f_count = a->C;
+        P.wrows = 0;
+        if (head_mean && a->C == kWinC && a->n_rel <= kWinMaxRel && a->dropout_p == 0.f && window_enabled()) {
+            bool hint = true, plain = true;  // the caller gives windows only where they are short (ops.gat_fused)
+            for (int r = 0; r < a->n_rel; ++r) {
+                hint = hint && a->rel[r].tile_win != nullptr;
+                plain = plain && a->alpha_saved[r] == nullptr;
+            }
+            if (hint && plain) return a->n_rel <= 2 ? dispatch_window<2>(P, stream) : dispatch_window<4>(P, stream);
+        }
         return head_mean ? dispatch_heads<1>(P, stream) : dispatch_heads<2>(P, stream);
+    }
+    if (vec == 2 && a->src_shared && a->H <= 4 && a->C > 128 && a->C <= 320) {
+        GatParams P;
+        P.a = *a;
+        P.f_begin = 0;
+        P.f_count = a->C;
+        P.wrows = 0;
+        switch (a->H) {
+            case 1: return dispatch_wide_shared<1>(P, stream);
+            case 2: return dispatch_wide_shared<2>(P, stream);
+            case 3: return dispatch_wide_shared<3>(P, stream);
+            default: return dispatch_wide_shared<4>(P, stream);
+        }
     }
     const int block = 32 * 8 * vec;  // widest output block one launch covers
     for (int f0 = 0; f0 < width; f0 += block) {
         GatParams P;
         P.a = *a;
+        P.wrows = 0;
         P.f_begin = f0;
         P.f_count = (width - f0 < block) ? width - f0 : block;
         const int rc = vec == 4 ? dispatch<4>(P, stream) : (vec == 2 ? dispatch<2>(P, stream) : dispatch<1>(P, stream));

@@ -31,6 +31,7 @@ struct RelDev {
     int32_t* bsum;     // [n_scan_blocks]
     int32_t n_scan_blocks;
     int32_t pad;
+    int32_t* tile_win; // [ceil(n_dst / HG_TILE_ROWS)][2] or NULL
 };
 
 struct PlanParams {
@@ -179,6 +180,36 @@ __global__ void __launch_bounds__(kEdgeThreads) k_rank(const __grid_constant__ P
     }
 }
 
+// Source-row window of every tile of HG_TILE_ROWS destination rows: warp per tile, lanes over the tile's CSR entries.
+__global__ void __launch_bounds__(kEdgeThreads) k_tile_window(const __grid_constant__ PlanParams P) {
+    const RelDev& R = P.r[blockIdx.y];
+    if (!R.tile_win) return;
+    const int lane = threadIdx.x & 31;
+    constexpr int kWarps = kEdgeThreads / kWarp;
+    const int32_t n_tiles = ceil_div<int32_t>(R.n_dst, HG_TILE_ROWS);
+    for (int32_t tile = blockIdx.x * kWarps + (threadIdx.x >> 5); tile < n_tiles; tile += gridDim.x * kWarps) {
+        const int32_t r0 = tile * HG_TILE_ROWS;
+        const int32_t r1 = r0 + HG_TILE_ROWS < R.n_dst ? r0 + HG_TILE_ROWS : R.n_dst;
+        const int32_t beg = R.rowptr[r0], end = R.rowptr[r1];
+        int32_t lo = INT32_MAX, hi = -1;
+        for (int32_t e = beg + lane; e < end; e += 32) {
+            const int32_t c = R.col[e];
+            lo = c < lo ? c : lo;
+            hi = c > hi ? c : hi;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const int32_t l2 = __shfl_xor_sync(0xffffffffu, lo, o), h2 = __shfl_xor_sync(0xffffffffu, hi, o);
+            lo = l2 < lo ? l2 : lo;
+            hi = h2 > hi ? h2 : hi;
+        }
+        if (lane == 0) {
+            R.tile_win[2 * tile] = hi >= 0 ? lo : 0;
+            R.tile_win[2 * tile + 1] = hi >= 0 ? hi - lo + 1 : 0;
+        }
+    }
+}
+
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
@@ -234,7 +265,7 @@ extern "C" int hg_plan_build(const hg_plan_rel* rels, int n_rel, int32_t* status
     PlanParams P;
     P.status = status;
     int64_t max_edges = 0, max_total = 0;
-    int32_t max_blocks = 0;
+    int32_t max_blocks = 0, max_tiles = 0;
     for (int r = 0; r < n_rel; ++r) {
         const hg_plan_rel& h = rels[r];
         if (h.n_edges > 0 && (!h.src || !h.dst)) return HG_EINVAL;
@@ -249,6 +280,8 @@ extern "C" int hg_plan_build(const hg_plan_rel* rels, int n_rel, int32_t* status
         d.bsum = reinterpret_cast<int32_t*>(ws + L.bsum_off[r]);
         d.n_scan_blocks = static_cast<int32_t>(ceil_div<int64_t>(h.n_dst, kScanTile));
         d.pad = 0;
+        d.tile_win = h.tile_win;
+        max_tiles = (h.tile_win && ceil_div<int32_t>(h.n_dst, HG_TILE_ROWS) > max_tiles) ? ceil_div<int32_t>(h.n_dst, HG_TILE_ROWS) : max_tiles;
         max_edges = h.n_edges > max_edges ? h.n_edges : max_edges;
         max_total = h.n_edges + d.n_loop > max_total ? h.n_edges + d.n_loop : max_total;
         max_blocks = d.n_scan_blocks > max_blocks ? d.n_scan_blocks : max_blocks;
@@ -271,6 +304,8 @@ extern "C" int hg_plan_build(const hg_plan_rel* rels, int n_rel, int32_t* status
     if (max_blocks > 0) k_scan_c<<<dim3(max_blocks, n_rel), kScanThreads, 0, stream>>>(P);
     if (max_edges > 0) k_fill<<<dim3(edge_grid(max_edges), n_rel), kEdgeThreads, 0, stream>>>(P);
     if (max_total > 0) k_rank<<<dim3(edge_grid(max_total), n_rel), kEdgeThreads, 0, stream>>>(P);
+    if (max_tiles > 0)
+        k_tile_window<<<dim3(edge_grid(static_cast<int64_t>(max_tiles) * kWarp), n_rel), kEdgeThreads, 0, stream>>>(P);
     return check_launch();
 }
 

@@ -10,7 +10,7 @@
 
 namespace hg {
 
-// wgrad_tc.cu: the tcgen05 variant (opt-in, HG_WGRAD_TC=1)
+// wgrad_tc.cu: the tcgen05 variant (default for N * K >= 65536 and M >= 16384; HG_WGRAD_TC=1 / 0 forces it on / off)
 int wgrad_tc(const float* dy, int64_t lddy, const float* x, int64_t ldx, int32_t M, int32_t N, int32_t K, float* dw,
              int64_t lddw, cudaStream_t stream);
 
@@ -294,9 +294,13 @@ extern "C" int hg_linear_wgrad(const float* dy, int64_t lddy, const float* x, in
         k_zero_rows<<<static_cast<unsigned>(g < sms * 8 ? g : sms * 8), 256, 0, stream>>>(dw, lddw, N, K);
     }
     if (M > 0) {
-        // opt-in tcgen05 variant (not yet run on hardware, see wgrad_tc.cu); read per call so one process can A/B
+        // tcgen05 variant (wgrad_tc.cu): measured on a B200 at M = 488,696 -- [396 x 306] 1.35 ms against 2.26 ms for the
+        // mma.sync kernel below, but 454 / 180 / 465 us against 436 / 134 / 435 us at [396 x 64], [88 x 64], [64 x 396]
+        // (profiles/r02_wgrad_tc_first_run.txt) -- so it is the default only for large weight matrices over many rows.
+        // HG_WGRAD_TC=1 / 0 forces it on / off (read per call so one process can A/B).
         const char* tc_env = getenv("HG_WGRAD_TC");
-        if (tc_env && tc_env[0] == '1') {
+        const bool tc_auto = static_cast<int64_t>(N) * K >= 65536 && M >= 16384;
+        if (tc_env ? tc_env[0] == '1' : tc_auto) {
             const int rc = check_launch();  // the zeroing launch
             return rc != HG_OK ? rc : wgrad_tc(dy, lddy, x, ldx, M, N, K, dw, lddw, stream);
         }

@@ -1,8 +1,11 @@
 // hg_linear_wgrad on tcgen05 (sm_100a):  dW[N, K] += dY[M, N]^T X[M, K], the reduction running over the M rows.
 //
-// STATUS: opt-in (environment HG_WGRAD_TC=1), written at the end of round 1 without GPU time left -- it compiles for
-// sm_100a but has NOT run on hardware yet; tools/check_wgrad_tc.py is its first-run check (own process: a protocol
-// bug traps after ~2 s, it cannot hang the GPU).  The default path stays k_wgrad_mma (train_ops.cu).
+// STATUS: default for large weight matrices over many rows (N * K >= 65536, M >= 16384; HG_WGRAD_TC=1 / 0 forces it
+// on / off).  First run on a B200 in round 2 (tools/check_wgrad_tc.py, profiles/r02_wgrad_tc_first_run.txt): all 12
+// ragged shapes inside the 3-term TF32 bound against fp64 (error 0.02-0.26 of the bound, below the mma.sync kernel's),
+// [488,696 x 396 x 306] in 1.35 ms (87.9 TFLOP/s fp32-equivalent) against 2.26 ms; slower than mma.sync on the small
+// [396 x 64] / [88 x 64] / [64 x 396] products, which therefore stay on k_wgrad_mma (train_ops.cu).
+// tests/test_gpu_train.py::test_linear_wgrad_tcgen05 covers it.
 //
 // Both operands are row-major with the reduced index m as the ROW, so neither is in the K-major form the tensor
 // core reads and neither row pitch is TMA-legal (306 floats = 1224 B).  The loaders therefore read 32-row k-blocks

@@ -66,7 +66,8 @@ class HomogeneousNetwork(_Base):
     def _main_request(self, data) -> PlanRequest:
         n = data.x.size(0)
         if self.conv_block[:3] == "GAT":
-            return PlanRequest(_REL, data.edge_index, n, n, True, want_perm=self.conv_block == "GAT_edge")
+            return PlanRequest(_REL, data.edge_index, n, n, True, want_perm=self.conv_block == "GAT_edge",
+                               want_window=any(c.wants_window() for c in self.convs))
         if self.conv_block == "GCN":
             return PlanRequest(_REL, data.edge_index, n, n, True, want_norm=True)
         return PlanRequest(_REL, data.edge_index, n, n, False)

@@ -80,11 +80,13 @@ class GraphPlan:
 
 
 class PlanRequest:
-    __slots__ = ("key", "edge_index", "n_src", "n_dst", "self_loops", "want_perm", "want_norm")
+    __slots__ = ("key", "edge_index", "n_src", "n_dst", "self_loops", "want_perm", "want_norm", "want_window")
 
-    def __init__(self, key, edge_index, n_src, n_dst, self_loops=False, want_perm=False, want_norm=False):
+    def __init__(self, key, edge_index, n_src, n_dst, self_loops=False, want_perm=False, want_norm=False,
+                 want_window=False):
         self.key, self.edge_index, self.n_src, self.n_dst = key, edge_index, int(n_src), int(n_dst)
         self.self_loops, self.want_perm, self.want_norm = bool(self_loops), bool(want_perm), bool(want_norm)
+        self.want_window = bool(want_window)  # per-tile source windows for the shared-memory GAT gather
 
     def signature(self):
         """Shape / version part of the cache key.  The ADDRESS of ``edge_index`` only identifies a tensor while that
@@ -92,7 +94,7 @@ class PlanRequest:
         the plan was built from and compares storage identity against it (``same_tensor``)."""
         ei = self.edge_index
         return (self.key, tuple(ei.shape), tuple(ei.stride()), ei._version, self.n_src, self.n_dst, self.self_loops,
-                self.want_perm, self.want_norm)
+                self.want_perm, self.want_norm, self.want_window)
 
 
 def same_tensor(a: Tensor, b: Tensor) -> bool:
@@ -133,7 +135,8 @@ class PlanCache:
                 all(same_tensor(a, r.edge_index) for a, r in zip(self._built_from, requests)):
             return self._plan
         plan = GraphPlan()
-        specs = [CSRSpec(r.edge_index, r.n_src, r.n_dst, r.self_loops, r.want_perm, r.want_norm) for r in requests]
+        specs = [CSRSpec(r.edge_index, r.n_src, r.n_dst, r.self_loops, r.want_perm, r.want_norm,
+                         want_window=r.want_window) for r in requests]
         csrs, plan.status = ops.build_csr(specs, overlap=self.overlap)
         self._pending = csrs[0].join if csrs else None
         for r, c in zip(requests, csrs):
@@ -240,13 +243,18 @@ class GATConv(nn.Module):
                     "(the reference uses zeros(3), models/utils.py:125-126)")
         return cache[key]
 
+    def wants_window(self) -> bool:
+        """The shapes hg_gat_fused's shared-memory window kernel covers (head-mean, 64 channels, <= 4 heads)."""
+        return (not self.concat) and self.out_channels == 64 and self.heads <= 4
+
     def forward(self, x, edge_index: Tensor, edge_attr: Tensor = None, act: str = None) -> Tensor:
         """Stand-alone call (single relation).  ``x``: Tensor or ``(x_src, x_dst)``."""
         single = isinstance(x, Tensor)
         x_src, x_dst = (x, x) if single else x
         key = "_"
         req = [PlanRequest(key, edge_index, x_src.size(0), x_dst.size(0), self.add_self_loops,
-                           want_perm=self.lin_edge is not None and edge_attr is not None)]
+                           want_perm=self.lin_edge is not None and edge_attr is not None,
+                           want_window=self.wants_window())]
         plan = self._plans.get(req)
         types = {"s": x_src} if single else {"s": x_src, "d": x_dst}
         et = ("s", key, "s" if single else "d")
@@ -260,19 +268,29 @@ def _pad4(n: int) -> int:
 
 
 AGG_FIRST_RATIO = 4  # a relation aggregates first when it has >= 4x fewer destinations than sources
-AGG_FIRST_WIDTH = float(os.environ.get("HG_AGG_FIRST_WIDTH", "1"))  # ... and raw rows at most this x the projected width
+AGG_FIRST_WIDTH = float(os.environ.get("HG_AGG_FIRST_WIDTH", "1.6"))  # ... and raw rows at most this x the projected width
 
 
 def _gat_modes(convs, rels: Sequence[EdgeType], x: Dict[str, Tensor], group: str) -> Tuple[bool, ...]:
     """Per relation: True = aggregate-first (``out_h = W_h (sum_e w_eh x_j)``: gather the raw source
     rows with the H weight sets, project the few aggregated rows afterwards), False = project-first.
     Same value up to fp32 re-association.  Chosen by shapes only (host-known, no sync): far fewer
-    destinations than sources AND raw rows no wider than the projected ones (else the gather of the
-    raw rows costs more than the projection it saves -- the 306-d input layer stays project-first)."""
+    destinations than sources AND raw rows not much wider than the projected ones.  The 3-term TF32 projection runs at
+    the tensor pipe's limit, so dropping a relation's H*C output columns from the big per-type GEMM pays even when
+    the raw rows are somewhat wider (objects -> rooms at the 306-d input layer: 306 vs 192; the GEMM shrinks from 396
+    to 204 columns) -- as long as the rows are even (float2 gathers; the odd 303-d GAT_edge rows stay project-first
+    unless they are narrower than the projection)."""
     if group != "sum":
         return tuple(False for _ in rels)
-    return tuple(x[et[2]].size(0) * AGG_FIRST_RATIO <= x[et[0]].size(0)
-                 and x[et[0]].size(1) <= AGG_FIRST_WIDTH * convs[et].heads * convs[et].out_channels for et in rels)
+
+    def agg_first(et):
+        width, proj = x[et[0]].size(1), convs[et].heads * convs[et].out_channels
+        if x[et[2]].size(0) * AGG_FIRST_RATIO > x[et[0]].size(0):
+            return False
+        return width <= proj or (width <= AGG_FIRST_WIDTH * proj and width % 2 == 0 and width <= 320
+                                 and convs[et].heads <= 4)
+
+    return tuple(agg_first(et) for et in rels)
 
 
 class _GatPack:
@@ -624,7 +642,8 @@ class HeteroConv(nn.Module):
             c = self.conv_of(et)
             loops = bool(getattr(c, "add_self_loops", False)) and isinstance(c, GATConv)
             perm = isinstance(c, GATConv) and c.lin_edge is not None
-            reqs.append(PlanRequest(et, edge_index_dict[et], x_dict[et[0]].size(0), x_dict[et[2]].size(0), loops, perm))
+            reqs.append(PlanRequest(et, edge_index_dict[et], x_dict[et[0]].size(0), x_dict[et[2]].size(0), loops, perm,
+                                    want_window=isinstance(c, GATConv) and c.wants_window()))
         return reqs
 
     def run(self, x_dict, edge_index_dict, plan: GraphPlan, *, act: str = None, edge_attr_dict=None,

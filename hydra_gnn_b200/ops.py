@@ -23,6 +23,9 @@ TC_MIN_ROWS = 512
 _profile_sink = None
 
 
+USE_TILE_WINDOW = True  # pass the plan's per-tile source windows to hg_gat_fused (False: the v6 global-gather kernel)
+
+
 def set_profile_sink(sink):
     global _profile_sink
     _profile_sink = sink
@@ -178,6 +181,7 @@ class CSR:
     join: Optional[_Join] = None
     edge_index: Optional[Tensor] = None  # kept when perm was requested: the training side is built from it
     train: Optional["TrainCSR"] = None   # reversed CSR + position map (ensure_train_csr)
+    tile_win: Optional[Tensor] = None    # int32 [ceil(n_dst / 32), 2]: source-row window of every destination tile
 
     def ready(self) -> "CSR":
         """Call before handing the arrays to a kernel on the current stream."""
@@ -195,6 +199,7 @@ class CSRSpec:
     want_perm: bool = False
     want_norm: bool = False
     transpose: bool = False  # build the CSR of the reversed relation (rows = sources)
+    want_window: bool = False  # also record the source-row window of every 32-row destination tile (hg_gat_fused)
 
 
 def build_csr(specs: Sequence[CSRSpec], overlap: bool = False):
@@ -218,7 +223,7 @@ def build_csr(specs: Sequence[CSRSpec], overlap: bool = False):
         side.wait_stream(cur)  # the edge lists are ready on the current stream
         with torch.cuda.stream(side):
             out, status = build_csr(specs)
-        tensors = [t for c in out for t in (c.rowptr, c.col, c.perm, c.inv_sqrt_deg) if t is not None] + [status]
+        tensors = [t for c in out for t in (c.rowptr, c.col, c.perm, c.inv_sqrt_deg, c.tile_win) if t is not None] + [status]
         join = _Join(side, tensors)
         for c in out:
             c.join = join
@@ -246,15 +251,18 @@ def build_csr(specs: Sequence[CSRSpec], overlap: bool = False):
             col = torch.empty(max(cap, 1), dtype=torch.int32, device=device)
             perm = torch.empty(max(cap, 1), dtype=torch.int32, device=device) if s.want_perm else None
             norm = torch.empty(max(n_dst, 1), dtype=torch.float32, device=device) if s.want_norm else None
+            n_tiles = (n_dst + _lib.HG_TILE_ROWS - 1) // _lib.HG_TILE_ROWS
+            win = torch.empty(max(n_tiles, 1), 2, dtype=torch.int32, device=device) if s.want_window else None
             r = rels[k]
             src_row, dst_row = (1, 0) if s.transpose else (0, 1)
             r.src = ei.data_ptr() + src_row * E * 8
             r.dst = ei.data_ptr() + dst_row * E * 8
             r.n_edges, r.n_src, r.n_dst, r.self_loops = E, n_src, n_dst, int(s.self_loops)
             r.rowptr, r.col, r.perm, r.inv_sqrt_deg = ptr(rowptr), ptr(col), ptr(perm), ptr(norm)
+            r.tile_win = ptr(win)
             keep.append(ei)
             out.append(CSR(rowptr, col, perm, norm, n_src, n_dst, cap, s.self_loops,
-                           edge_index=ei if (s.want_perm and not s.transpose) else None))
+                           edge_index=ei if (s.want_perm and not s.transpose) else None, tile_win=win))
         nbytes = h.hg_plan_workspace_bytes(rels, len(chunk))
         if nbytes == 0:
             raise RuntimeError("hg_plan_workspace_bytes rejected the plan (sizes out of int32 range?)")
@@ -264,7 +272,7 @@ def build_csr(specs: Sequence[CSRSpec], overlap: bool = False):
                     n_dst=[int(r.n_dst) for r in rels], caps=[c.cap for c in out[lo:]])
         _call("hg_plan_build", meta,
               lambda: h.hg_plan_build(rels, len(chunk), ptr(st), ptr(ws), ws.numel(), stream_ptr()))
-        _lib.launch_count += 6
+        _lib.launch_count += 6 + int(any(s.want_window for s in chunk))
         if lo != 0:
             status += st
     return out, status
@@ -318,6 +326,15 @@ class GatRelation:
     alpha_out: Optional[Tensor] = None
 
 
+def window_applies(rels: Sequence["GatRelation"], n_dst: int) -> bool:
+    """Whether the plan's per-tile source windows are handed to ``hg_gat_fused`` (which then stages them in shared
+    memory).  Only where the windows are short: every relation carries one, has at most 14 edges per destination row on
+    average (the kernel's edge pool per 32-row tile) and no more than 4 source rows per destination row (a tile of rooms
+    spans hundreds of object rows: that relation stays on the global-gather kernel)."""
+    return USE_TILE_WINDOW and n_dst > 0 and all(
+        r.csr.tile_win is not None and r.csr.cap <= 14 * n_dst and r.csr.n_src <= 4 * n_dst for r in rels)
+
+
 def gat_fused(rels: Sequence[GatRelation], n_dst: int, H: int, Cc: int, concat: bool, *, group: str = "sum",
               act: str = None, neg_slope: float = 0.2, out: Tensor = None, addend: Tensor = None,
               src_shared: bool = False, dropout_p: float = 0.0, seed: int = 0, seed_dev: Tensor = None) -> Tensor:
@@ -336,6 +353,7 @@ def gat_fused(rels: Sequence[GatRelation], n_dst: int, H: int, Cc: int, concat: 
     if out is None:
         out = torch.empty(n_dst, width, dtype=torch.float32, device=device)
     a = _lib.GatArgs()
+    use_window = window_applies(rels, n_dst)
     for k, r in enumerate(rels):
         _require_no_grad(r.xs, r.a_src, r.a_dst, r.bias)
         for t, nm in ((r.xs, "xs"), (r.a_src, "a_src"), (r.a_dst, "a_dst")):
@@ -353,6 +371,7 @@ def gat_fused(rels: Sequence[GatRelation], n_dst: int, H: int, Cc: int, concat: 
         g.a_dst, g.lda_dst = ptr(r.a_dst), _ld(r.a_dst)
         g.a_edge = ptr(r.a_edge)
         g.rowptr, g.col, g.bias = ptr(r.csr.rowptr), ptr(r.csr.col), ptr(r.bias)
+        g.tile_win = ptr(r.csr.tile_win) if use_window else None
         a.alpha_saved[k] = ptr(r.alpha_out)
     a.n_rel, a.n_dst, a.H, a.C = len(rels), n_dst, H, Cc
     a.concat, a.group, a.act, a.neg_slope = int(concat), GROUP[group], ACT[act], float(neg_slope)

@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define HG_ABI_VERSION 1
+#define HG_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define HG_API __attribute__((visibility("default")))
@@ -59,6 +59,7 @@ enum { HG_PREC_FP32 = 0, HG_PREC_TF32X3 = 1 };
 #define HG_MAX_RELATIONS 8   /* relations fused per destination type (H-tree needs 4) */
 #define HG_MAX_SEGMENTS 8    /* K-segments of one fused projection */
 #define HG_MAX_PLAN_RELATIONS 16 /* relations per plan-build call (H-tree has 15) */
+#define HG_TILE_ROWS 32      /* destination rows per tile of hg_plan_rel.tile_win / hg_gat_fused */
 
 HG_API const char* hg_strerror(int code);
 HG_API int hg_abi_version(void);
@@ -99,6 +100,11 @@ typedef struct hg_plan_rel {
     int32_t* col;         /* out [E + loops] */
     int32_t* perm;        /* out [E + loops], may be NULL */
     float* inv_sqrt_deg;  /* out [n_dst] deg^-1/2 (0 when deg == 0), may be NULL (gcn_norm) */
+    int32_t* tile_win;    /* out [ceil(n_dst / HG_TILE_ROWS)][2], may be NULL: for every tile of HG_TILE_ROWS consecutive
+                             destination rows, {lowest source id, number of source rows spanned} over the tile's CSR
+                             entries ({0, 0} for a tile without edges).  A batch of scene graphs is a disjoint union in
+                             graph order, so the span of a tile is a few dozen rows: hg_gat_fused stages it in shared
+                             memory with bulk copies (hg_gat_rel.tile_win) */
 } hg_plan_rel;
 
 HG_API size_t hg_plan_workspace_bytes(const hg_plan_rel* rels_host, int n_rel);
@@ -178,6 +184,13 @@ typedef struct hg_gat_rel {
     const float* a_edge;                /* NULL | [E', H] contiguous, CSR order */
     const int32_t* rowptr; const int32_t* col;
     const float* bias;                  /* NULL | [H*C] (concat) or [C] */
+    const int32_t* tile_win;            /* NULL | [ceil(n_dst / HG_TILE_ROWS)][2] from hg_plan_build: source-row window of
+                                           every destination tile.  A hint: when EVERY relation of the call carries one
+                                           (head-mean, C = 64, H <= 4, n_rel <= 4, no alpha_saved / dropout) the kernel
+                                           bulk-copies the windows of xs into shared memory and gathers from there; sources
+                                           outside the staged rows are read from global memory, so any window that stays
+                                           inside [0, n_src) gives the same result.  Pass it for relations whose sources
+                                           are local (a few dozen rows per tile, <= ~14 edges per row) */
 } hg_gat_rel;
 
 typedef struct hg_gat_args {

@@ -239,6 +239,115 @@ def test_gat_fused_hub_rows_take_the_streaming_path():
         assert_close(got, want, f"hub concat={concat}", check_argmax=False)
 
 
+# ------------------------------------------------------------------------------ tile windows + the shared-memory window kernel
+def _tile_windows(rowptr, col, n_dst):
+    """{first source row, rows spanned} per tile of 32 destination rows, from the CSR (integer, exact)."""
+    rowptr, col = rowptr.cpu().long(), col.cpu().long()
+    out = torch.zeros((n_dst + 31) // 32, 2, dtype=torch.int32)
+    for t in range(out.size(0)):
+        c = col[rowptr[32 * t]: rowptr[min(32 * t + 32, n_dst)]]
+        if c.numel():
+            out[t, 0], out[t, 1] = int(c.min()), int(c.max() - c.min() + 1)
+    return out
+
+
+@pytest.mark.parametrize("n_src,n_dst,E,loops", [(50, 50, 400, True), (1000, 37, 5000, False), (37, 1000, 5000, True),
+                                                 (7, 7, 0, True), (0, 5, 0, False), (3000, 2999, 9000, False)])
+def test_plan_tile_windows_bit_exact(n_src, n_dst, E, loops):
+    g = torch.Generator().manual_seed(E + n_dst)
+    ei = torch.stack([torch.randint(0, max(n_src, 1), (E,), generator=g),
+                      torch.randint(0, max(n_dst, 1), (E,), generator=g)]) if E else torch.zeros(2, 0, dtype=torch.long)
+    (csr,), _ = ops.build_csr([CSRSpec(ei.cuda(), n_src, n_dst, loops, want_window=True)])
+    assert torch.equal(csr.tile_win.cpu(), _tile_windows(csr.rowptr, csr.col, n_dst))
+
+
+def _scene_batch_relations(graph_ids, H, g, a_edge=False):
+    """o->o (self loops) and r->o relations of a synthetic scene-graph batch with random projected rows / logits."""
+    b = synth.synth_mp3d_batch(graph_ids, device="cuda")
+    n_o, n_r = b["objects"].x.size(0), b["rooms"].x.size(0)
+    specs = [CSRSpec(b[("objects", "objects_to_objects", "objects")].edge_index, n_o, n_o, True, want_perm=True, want_window=True),
+             CSRSpec(b[("rooms", "rooms_to_objects", "objects")].edge_index, n_r, n_o, False, want_perm=True, want_window=True)]
+    csrs, _ = ops.build_csr(specs)
+    rels = []
+    for csr, n_src in zip(csrs, (n_o, n_r)):
+        Y = torch.randn(n_src, H * 64 + 12, generator=g).cuda()  # xs is a column slice of a wider projection output
+        ae = torch.randn(csr.cap, H, generator=g).cuda() if a_edge else None
+        rels.append(ops.GatRelation(Y[:, :H * 64], Y[:, H * 64: H * 64 + H], torch.randn(n_o, H, generator=g).cuda(), csr,
+                                    torch.randn(64, generator=g).cuda(), ae))
+    return rels, n_o
+
+
+def _fp64_gat(rels, n_dst, H, C):
+    """fp64 head-mean GAT over CSR relations (rows in CSR order), biases included."""
+    want = 0
+    for r in rels:
+        rowptr = r.csr.rowptr.cpu().long()
+        n_live = int(rowptr[-1])
+        col = r.csr.col.cpu().long()[:n_live]
+        dst = torch.repeat_interleave(torch.arange(n_dst), rowptr[1:] - rowptr[:-1])
+        a_src, a_dst = r.a_src.cpu(), r.a_dst.cpu()
+        if r.a_edge is not None:  # fold the edge term into a per-edge source logit
+            s = a_src.double()[col] + r.a_edge.cpu().double()[:n_live] + a_dst.double()[dst]
+            s = torch.nn.functional.leaky_relu(s, 0.2)
+            w = ou.softmax(s, dst, None, n_dst)
+            msg = w.unsqueeze(-1) * r.xs.cpu().double()[col].view(-1, H, C)
+            o = ou.scatter(msg, dst, 0, dim_size=n_dst, reduce="sum").mean(1)
+        else:
+            o, _ = gat_reference(r.xs.cpu(), a_src, a_dst, torch.stack([col, dst]), n_dst, H, C, False)
+        want = want + o + r.bias.cpu().double()
+    return want
+
+
+@pytest.mark.parametrize("H", [1, 2, 3, 4])
+@pytest.mark.parametrize("n_graphs,a_edge", [(37, False), (300, False), (64, True)])
+def test_gat_window_kernel_matches_fp64_and_the_global_gather_kernel_bitwise(H, n_graphs, a_edge):
+    g = torch.Generator().manual_seed(100 * H + n_graphs)
+    rels, n_o = _scene_batch_relations(range(n_graphs), H, g, a_edge)
+    addend = torch.randn(n_o, 64, generator=g).cuda()
+    assert ops.window_applies(rels, n_o)
+    got = ops.gat_fused(rels, n_o, H, 64, False, act="elu", addend=addend)
+    assert_close(got, torch.nn.functional.elu(_fp64_gat(rels, n_o, H, 64) + addend.cpu().double()), f"window H={H}",
+                 check_argmax=False)
+    try:
+        ops.USE_TILE_WINDOW = False
+        base = ops.gat_fused(rels, n_o, H, 64, False, act="elu", addend=addend)
+    finally:
+        ops.USE_TILE_WINDOW = True
+    assert torch.equal(got, base)  # same accumulation order: bit-identical
+    # one relation only, group mean over a repeated relation, ReLU
+    got1 = ops.gat_fused([rels[0], rels[0], rels[1]], n_o, H, 64, False, group="mean", act="relu")
+    want1 = torch.relu((2 * _fp64_gat(rels[:1], n_o, H, 64) + _fp64_gat(rels[1:], n_o, H, 64)) / 3)
+    assert_close(got1, want1, "window, 3 relations, group mean", check_argmax=False)
+
+
+def test_gat_window_kernel_any_graph_and_any_hint():
+    """Sources outside the staged window are gathered from global memory: random graphs (windows span everything),
+    windows that do not cover the tile's sources at all, and hub tiles (edge pool overflow) all give the same bits."""
+    g = torch.Generator().manual_seed(5)
+    H, C, n_src, n_dst = 3, 64, 4000, 1000 + 17
+    ei = torch.stack([torch.randint(0, n_src, (9000,), generator=g), torch.randint(0, n_dst, (9000,), generator=g)])
+    hub = torch.stack([torch.randint(0, n_src, (700,), generator=g), torch.full((700,), 40)])  # tile 1: 700 edges > pool
+    ei = torch.cat([ei, hub], dim=1)
+    (csr,), _ = ops.build_csr([CSRSpec(ei.cuda(), n_src, n_dst, False, want_window=True)])
+    xs, a_s, a_d = torch.randn(n_src, H * C, generator=g), torch.randn(n_src, H, generator=g), torch.randn(n_dst, H, generator=g)
+    rel = ops.GatRelation(xs.cuda(), a_s.cuda(), a_d.cuda(), csr)
+    want, _ = gat_reference(xs, a_s, a_d, ei, n_dst, H, C, False)
+    assert ops.window_applies([rel], n_dst)
+    got = ops.gat_fused([rel], n_dst, H, C, False)
+    assert_close(got, want, "window kernel, random graph", check_argmax=False)
+    win = csr.tile_win.clone()
+    for hint in (torch.zeros_like(win), torch.stack([torch.full_like(win[:, 0], n_src - 5), torch.full_like(win[:, 1], 5)], 1),
+                 torch.stack([win[:, 0] + 3, (win[:, 1] - 3).clamp(min=0)], 1)):
+        csr.tile_win = hint.contiguous()
+        assert torch.equal(ops.gat_fused([rel], n_dst, H, C, False), got)
+    csr.tile_win = None
+    base = ops.gat_fused([rel], n_dst, H, C, False)  # the global-gather kernel
+    hub_rows = torch.zeros(n_dst, dtype=torch.bool)
+    hub_rows[32:64] = True  # its staging pool holds this tile; the window kernel's does not (warp-per-row path: other rounding)
+    assert torch.equal(base[~hub_rows], got[~hub_rows])
+    assert_close(base[hub_rows], got[hub_rows], "hub tile", check_argmax=False)
+
+
 # ------------------------------------------------------------------------------ GPU collate (bit-exact, SURVEY.md a11 / f2)
 def _graph_list(n, hetero=True):
     from hydra_gnn_b200 import convert

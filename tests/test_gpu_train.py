@@ -137,6 +137,24 @@ def test_linear_wgrad(M, N, K):
     assert float((got.double() - 2 * want).abs().max()) <= 2e-5 * max(float(want.abs().max()), 1.0) + 1e-6
 
 
+@pytest.mark.parametrize("M,N,K", [(20000, 396, 306), (16385, 306, 396), (33000, 300, 219)])
+def test_linear_wgrad_tcgen05(M, N, K, monkeypatch):
+    """Large weight matrices take the tcgen05 kernel (csrc/wgrad_tc.cu) by default: 3-term TF32 bound against fp64,
+    ragged tails in every dimension, padded leading dimensions, accumulate on top; HG_WGRAD_TC=0 (mma.sync) agrees."""
+    torch.manual_seed(1)
+    dyb, xb = torch.randn(M, N + 3, device="cuda"), torch.randn(M, K + 1, device="cuda")
+    dy, x = dyb[:, 1:N + 1], xb[:, :K]
+    want = dy.double().t() @ x.double()
+    bound = 2e-6 * (dy.double().abs().t() @ x.double().abs()) + 1e-30
+    got = ops.linear_wgrad(dy, x)
+    assert float(((got.double() - want).abs() / bound).max()) <= 1.0
+    ops.linear_wgrad(dy, x, out=got, accumulate=True)
+    assert float(((got.double() - 2 * want).abs() / (2 * bound)).max()) <= 1.0
+    monkeypatch.setenv("HG_WGRAD_TC", "0")
+    base = ops.linear_wgrad(dy, x)
+    assert float(((base.double() - want).abs() / bound).max()) <= 1.0
+
+
 def test_adam_kernel_matches_torch():
     torch.manual_seed(0)
     p = torch.randn(10001)

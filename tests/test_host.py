@@ -34,7 +34,7 @@ def test_library_exports_every_declared_symbol():
     h = _lib.load_shared_object()  # dlopen, prototypes, struct-size check
     for name in declared:
         assert hasattr(h, name)
-    assert h.hg_abi_version() == 1
+    assert h.hg_abi_version() == 2
     assert h.hg_strerror(0) == b"ok" and b"workspace" in h.hg_strerror(-3)
     for which, st in enumerate(_lib._STRUCTS):
         import ctypes
