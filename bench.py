@@ -222,6 +222,46 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def extra_configs():
+    """BASELINE.json configs[2] (Neural Tree, heterogeneous GAT over H-trees of 4096 graphs) and configs[4] (M-GAT training
+    step, 8192 graphs) on this GPU, each in its own process (tools/bench_nt.py, tools/bench_train.py): a few steps,
+    summarised.  Not the headline metric; here so that the driver's bench record carries them."""
+    out = {}
+
+    def run(cmd, timeout):
+        try:
+            r = subprocess.run([sys.executable] + cmd, cwd=ROOT, capture_output=True, text=True, timeout=timeout)
+            lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+            return json.loads(lines[-1]) if r.returncode == 0 and lines else {"error": (r.stderr or "no output")[-300:]}
+        except (subprocess.TimeoutExpired, OSError, ValueError) as e:
+            return {"error": repr(e)[:300]}
+
+    nt = run(["tools/bench_nt.py", "--only", "nt_het_gat", "--check", "0", "--iters", "10"], 240)
+    if "error" in nt:
+        out["config3_neural_tree_hetero_gat"] = nt
+    else:
+        m = nt["models"]["nt_het_gat"]
+        top = m["kernels"][0]
+        out["config3_neural_tree_hetero_gat"] = {
+            "workload": "configs[2]: HeterogeneousNeuralTreeNetwork (GAT) forward over the H-trees of 4096 synthetic graphs, "
+                        "plan rebuilt every forward, CUDA-graph replay", "value": m["graphs_per_s"], "unit": UNIT,
+            "ms_per_step": m["ms_per_forward_graph"], "eager_ms_per_step": m["ms_per_forward_eager"],
+            "alg_gbs_whole_forward": m["alg_gbs_whole_forward"],
+            "dominant_kernel": {"kernel": top["kernel"], "mean_us": top["mean_us"], "gbs": top["gbs"], "frac": top["hbm_frac"]},
+            "htree_builder_graphs_per_s": nt["htree_builder"]["graphs_per_s"]}
+    tr = run(["tools/bench_train.py", "--no-cpu", "--steps", "10", "--warmup", "3"], 240)
+    if "error" in tr:
+        out["config5_training_step"] = tr
+    else:
+        top = tr["kernels"][0]
+        out["config5_training_step"] = {
+            "workload": tr["config"]["workload"], "value": tr["value"], "unit": UNIT, "ms_per_step": tr["ms_per_step"],
+            "cuda_graph": tr["config"]["cuda_graph"], "our_kernels_share_of_step": tr["our_kernels_share_of_step"],
+            "dominant_kernel": {"kernel": top["kernel"], "mean_us": top["mean_us"], "gbs": top["gbs"], "tflops": top["tflops"],
+                                "frac": top["hbm_frac"]}}
+    return out
+
+
 def _traffic_table():
     """ncu-measured DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum), committed
     under profiles/ by the round's ncu --set full capture; None when no capture matches."""
@@ -303,13 +343,25 @@ def run_ours(args, rank, world, local_rank):
         run(0)
     fence()
     with ClockSampler(local_rank) as clocks:
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(args.steps):
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+        marks[0].record()
+        for i in range(args.steps):
             run(0)
-        e1.record()
+            marks[i + 1].record()  # one event between back-to-back replays: per-step times for median / p10 / p90
         fence()
-    ms = e0.elapsed_time(e1)
+    ms = marks[0].elapsed_time(marks[-1])
+    per_step = sorted(marks[i].elapsed_time(marks[i + 1]) for i in range(args.steps))
+
+    # ---- the same K steps launched eagerly (no CUDA graph; side streams as in the value arm): SURVEY.md 8d reports both
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    step(bufs[0])
+    fence()
+    g0.record()
+    for _ in range(args.steps):
+        step(bufs[0])
+    g1.record()
+    fence()
+    ms_eager = g0.elapsed_time(g1)
 
     # ---- roofline leg: the same K steps launched eagerly with a CUDA-event pair around every launch
     # (stream concurrency off for this leg only, so an event pair brackets ONE kernel running alone: the value
@@ -366,9 +418,9 @@ def run_ours(args, rank, world, local_rank):
     ms_e2e = f0.elapsed_time(f1)
 
     if world > 1:  # max over ranks, measured on the device
-        t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+        t = torch.tensor([ms, ms_e2e, ms_eager], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, ms_e2e = float(t[0]), float(t[1])
+        ms, ms_e2e, ms_eager = float(t[0]), float(t[1]), float(t[2])
     if rank != 0:
         return
     peaks = _peaks()
@@ -382,12 +434,18 @@ def run_ours(args, rank, world, local_rank):
         "metric": METRIC, "value": total_graphs * args.steps / (ms / 1e3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD,
-                   "graphs_per_gpu": G, "objects": int(host["objects"].x.size(0)), "rooms": int(n_rooms),
-                   "edges": {et[1]: int(host[et].edge_index.size(1)) for et in host.edge_types},
+        "config": {"workload": WORKLOAD, "graphs_per_gpu": G},  # identical in both arms (--impl reference)
+        "detail": {"objects": int(host["objects"].x.size(0)), "rooms": int(n_rooms),
+                   "edges_objects_to_objects": int(host["objects", "objects_to_objects", "objects"].edge_index.size(1)),
+                   "edges_rooms_to_rooms": int(host["rooms", "rooms_to_rooms", "rooms"].edge_index.size(1)),
+                   "edges_objects_to_rooms": int(host["objects", "objects_to_rooms", "rooms"].edge_index.size(1)),
                    "l2": "inputs larger than L2 (object features 297 MB + ~190 MB of projections per layer vs 126 MB L2)",
                    "projection_precision": ops.DEFAULT_PRECISION, "cuda_graph": use_graph,
                    "collective": "all_gather_into_tensor(room logits)" if world > 1 else "none"},
+        "step_ms": {"median": statistics.median(per_step), "p10": per_step[len(per_step) // 10],
+                    "p90": per_step[min(len(per_step) - 1, (9 * len(per_step)) // 10)],
+                    "eager_ms_per_step": ms_eager / args.steps,
+                    "note": "per-step = CUDA events between back-to-back graph replays (max over ranks applies to ms_per_step only)"},
         "e2e": {"value": total_graphs * args.steps / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps,
                 "pipeline": "double-buffered: H2D of step k+1 overlaps the forward of step k"},
@@ -396,6 +454,15 @@ def run_ours(args, rank, world, local_rank):
         "roofline": roof,
         "kernels": table,
     }
+    agg_rows = [k for k in table if k["kernel"].startswith("hg_gat_fused")]
+    if agg_rows:  # the dominant AGGREGATION kernel (north_star's 60 % target is about these), whatever tops the step
+        k = agg_rows[0]
+        line["roofline_aggregation"] = dict(bound="hbm", kernel=k["kernel"], achieved=k["gbs"], peak=peaks["hbm_gbs"], unit="GB/s",
+                                            frac=round(k["gbs"] / peaks["hbm_gbs"], 4), mean_us=k["mean_us"],
+                                            alg_bytes_per_launch=k["alg_bytes"], share_of_step=k["share"],
+                                            traffic=traffic.get(k["kernel"]), peak_source=peaks["source"])
+    if world == 1 and not args.no_extra:
+        line["extra"] = extra_configs()
     if world == 1 and not args.no_cpu:
         rate, threads, secs, iters = cpu_forward_rate(G, args.cpu_seconds, 40)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
@@ -415,6 +482,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU-baseline sample: seconds of CPU work")
     ap.add_argument("--no-graph", action="store_true", help="launch every step eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--no-extra", action="store_true", help="skip the configs[2] / configs[4] summaries under `extra` (N = 1 only)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

@@ -43,7 +43,7 @@ class SegArgs(C.Structure):
 
 class GatRel(C.Structure):
     _fields_ = [("xs", vp), ("ldxs", i64), ("a_src", vp), ("lda_src", i64), ("a_dst", vp), ("lda_dst", i64),
-                ("a_edge", vp), ("rowptr", vp), ("col", vp), ("bias", vp), ("tile_win", vp)]
+                ("a_edge", vp), ("rowptr", vp), ("col", vp), ("bias", vp), ("tile_win", vp), ("n_src", i32), ("reserved", i32)]
 
 
 class GatArgs(C.Structure):

@@ -23,6 +23,8 @@
 // src_shared = 1 is the aggregate-first form: xs is [n_src, C] (ONE row shared by all heads) and the
 // output is [n_dst, H*C] with out[i, h, :] = sum_e w_eh xs[j, :]; the projection is applied afterwards
 // to the aggregated rows (used when a relation has far fewer destinations than sources).
+#include <cuda.h>
+
 #include <cstdlib>
 
 #include "tc_common.cuh"
@@ -560,9 +562,10 @@ int dispatch_special(GatParams& P, cudaStream_t stream) {
 constexpr int kWinConsumerWarps = 8, kWinProducerWarps = 6, kWinStages = 3;
 constexpr int kWinThreads = (kWinConsumerWarps + kWinProducerWarps + 1) * 32;  // 480
 constexpr int kWinC = 64;               // channels per head (8 threads x 2 float4 chunks)
-constexpr int kWinBytes = 43008;        // window pool of one stage: 56 rows at H = 3
-constexpr int kWinEdges = 448;          // edge pool of one stage (all relations of a tile)
+constexpr int kWinBytes = 55296;        // window pool of one stage: 72 rows at H = 3
+constexpr int kWinEdges = 320;          // edge pool of one stage (all relations of a tile)
 constexpr int kWinMaxRel = 4;
+constexpr int kWinBox = 4;             // source rows per TMA box
 constexpr int kWinBars = 2 * kWinProducerWarps + 2 * kWinStages;
 
 // one edge stage: weights float4[ecap] | destination logits float4[rmax][32] | offsets int[ecap] |
@@ -600,8 +603,9 @@ struct WinTile {
                 tot += ne[r];
                 if (Rl.tile_win) {
                     const int2 w = __ldg(reinterpret_cast<const int2*>(Rl.tile_win) + tile);
+                    const int need = (w.y + kWinBox - 1) / kWinBox * kWinBox;  // whole TMA boxes (wrows is a multiple too)
                     wlo[r] = w.x;
-                    wn[r] = w.y < wrows - used ? w.y : wrows - used;
+                    wn[r] = need < wrows - used ? need : wrows - used;
                     wb[r] = used * ROWB;
                     used += wn[r];
                 }
@@ -610,9 +614,30 @@ struct WinTile {
     }
 };
 
+struct WinParams : GatParams {
+    alignas(64) CUtensorMap tmap[kWinMaxRel];  // xs of relation r as a [n_src, H*C] fp32 tensor, box = kWinBox rows
+};
+
+// one box of kWinBox source rows -> shared memory, completing on `bar` (SASS: UTMALDG)
+__device__ __forceinline__ void tma_rows_g2s(uint32_t dst, const CUtensorMap* map, int row0, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+        ::"r"(dst), "l"(map), "r"(0), "r"(row0), "r"(bar)
+        : "memory");
+}
+// waits that may last a whole tile: back off so the spinning warp does not take issue slots from the gather warps
+__device__ __forceinline__ void mbar_wait_idle(uint32_t bar, uint32_t parity) {
+    if (tc::mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!tc::mbar_try_wait(bar, parity)) {
+        __nanosleep(128);
+        if (clock64() - t0 > tc::kWaitCycles) __trap();
+    }
+}
+
 template <int HT, int RMAX>
 __global__ void __launch_bounds__(kWinThreads, 1)
-k_gat_window(const __grid_constant__ GatParams P) {
+k_gat_window(const __grid_constant__ WinParams P) {
     extern __shared__ __align__(128) uint8_t s_raw[];
     constexpr int ROWB = HT * kWinC * 4;  // bytes of one window row
     const hg_gat_args& A = P.a;
@@ -658,25 +683,30 @@ k_gat_window(const __grid_constant__ GatParams P) {
         // ================================================================== window warp
         int ws = 0;
         uint32_t wph = 0;
+        WinTile<ROWB, RMAX> Tn;  // control of the NEXT tile: loaded one iteration ahead, so its DRAM round trip
+        {                        // overlaps the wait for a free stage and the copies of the current tile
+            const int64_t t0 = static_cast<int64_t>(blockIdx.x) * kMaxTile;
+            Tn.load(A, blockIdx.x, t0, (A.n_dst - t0 < kMaxTile) ? static_cast<int>(A.n_dst - t0) : kMaxTile, P.wrows);
+        }
         for (int k = 0; k < n_k; ++k) {
-            const int64_t tile = blockIdx.x + static_cast<int64_t>(k) * gridDim.x, t0 = tile * kMaxTile;
-            const int rows = (A.n_dst - t0 < kMaxTile) ? static_cast<int>(A.n_dst - t0) : kMaxTile;
-            WinTile<ROWB, RMAX> T;
-            T.load(A, tile, t0, rows, P.wrows);  // issued before the wait: in flight while the stage drains
-            tc::mbar_wait(win_empty + 8 * ws, wph ^ 1u);
-            if (T.tot > P.cap || T.used == 0) {  // hub tile / no window: complete the phase without bytes
-                if (lane == 0) tc::mbar_arrive(win_full + 8 * ws);
-            } else {
-                if (lane == 0) tc::mbar_arrive_expect_tx(win_full + 8 * ws, static_cast<uint32_t>(T.used) * ROWB);
-                __syncwarp();
-                const uint32_t win_a = tc::smem_u32(s_raw) + ws * win_bytes;
+            const WinTile<ROWB, RMAX> T = Tn;
+            if (k + 1 < n_k) {
+                const int64_t tile = blockIdx.x + static_cast<int64_t>(k + 1) * gridDim.x, t0 = tile * kMaxTile;
+                Tn.load(A, tile, t0, (A.n_dst - t0 < kMaxTile) ? static_cast<int>(A.n_dst - t0) : kMaxTile, P.wrows);
+            }
+            mbar_wait_idle(win_empty + 8 * ws, wph ^ 1u);
+            if (lane == 0) {
+                if (T.tot > P.cap || T.used == 0) {  // hub tile / no window: complete the phase without bytes
+                    tc::mbar_arrive(win_full + 8 * ws);
+                } else {
+                    tc::mbar_arrive_expect_tx(win_full + 8 * ws, static_cast<uint32_t>(T.used) * ROWB);
+                    const uint32_t win_a = tc::smem_u32(s_raw) + ws * win_bytes;
 #pragma unroll
-                for (int r = 0; r < RMAX; ++r) {
-                    if (r < R && T.wn[r] > 0) {
-                        const size_t pitch = static_cast<size_t>(A.rel[r].ldxs) * 4;
-                        const char* src = reinterpret_cast<const char*>(A.rel[r].xs) + static_cast<size_t>(T.wlo[r]) * pitch;
-                        for (int row = lane; row < T.wn[r]; row += 32)
-                            tc::bulk_g2s(win_a + T.wb[r] + row * ROWB, src + static_cast<size_t>(row) * pitch, ROWB, win_full + 8 * ws);
+                    for (int r = 0; r < RMAX; ++r) {
+                        if (r < R) {
+                            for (int row = 0; row < T.wn[r]; row += kWinBox)
+                                tma_rows_g2s(win_a + T.wb[r] + row * ROWB, &P.tmap[r], T.wlo[r] + row, win_full + 8 * ws);
+                        }
                     }
                 }
             }
@@ -696,12 +726,18 @@ k_gat_window(const __grid_constant__ GatParams P) {
         int32_t* const s_rp = reinterpret_cast<int32_t*>(st + o_rp);
         int32_t* const s_ctl = reinterpret_cast<int32_t*>(st + o_ctl);
         uint32_t eph = 0;
+        auto load_tile = [&](WinTile<ROWB, RMAX>& T, int k) {
+            const int64_t tile = blockIdx.x + static_cast<int64_t>(k) * gridDim.x, t0 = tile * kMaxTile;
+            T.load(A, tile, t0, (A.n_dst - t0 < kMaxTile) ? static_cast<int>(A.n_dst - t0) : kMaxTile, P.wrows);
+        };
+        WinTile<ROWB, RMAX> Tn;  // control of this warp's NEXT tile, loaded one tile ahead
+        if (p < n_k) load_tile(Tn, p);
         for (int k = p; k < n_k; k += kWinProducerWarps, eph ^= 1u) {
             const int64_t tile = blockIdx.x + static_cast<int64_t>(k) * gridDim.x, t0 = tile * kMaxTile;
             const int rows = (A.n_dst - t0 < kMaxTile) ? static_cast<int>(A.n_dst - t0) : kMaxTile;
-            WinTile<ROWB, RMAX> T;
-            T.load(A, tile, t0, rows, P.wrows);
-            tc::mbar_wait(edge_empty + 8 * p, eph ^ 1u);  // stage free (the first pass is on the fresh barrier)
+            const WinTile<ROWB, RMAX> T = Tn;
+            if (k + kWinProducerWarps < n_k) load_tile(Tn, k + kWinProducerWarps);
+            mbar_wait_idle(edge_empty + 8 * p, eph ^ 1u);  // stage free (the first pass is on the fresh barrier)
             if (T.tot > P.cap) {  // hub tile (uniform): the consumers stream it from global memory
                 if (lane == 0) {
                     s_ctl[0] = 1, s_ctl[1] = 0, s_ctl[2] = 0;
@@ -710,73 +746,97 @@ k_gat_window(const __grid_constant__ GatParams P) {
                 __syncwarp();
                 continue;
             }
-            // ---- stage: pool-relative rowptr slices, destination logits ...
-            for (int idx = lane; idx < R * (kMaxTile + 1); idx += 32) {
-                const int r = idx / (kMaxTile + 1), tt = idx - r * (kMaxTile + 1);
-                int d = 0;
+            // ---- stage.  Two DRAM round trips per tile, each with every load of the tile in flight at once:
+            //   trip 1  rowptr slices, destination logits and the neighbour ids (lanes = pool entries, 8 per lane);
+            //   trip 2  the source logits of those neighbours.
+            constexpr int kRpIt = (RMAX * (kMaxTile + 1) + 31) / 32;
+            int32_t rpv[kRpIt];
 #pragma unroll
-                for (int rr = 0; rr < RMAX; ++rr)
-                    if (rr == r) d = T.eb[rr] - T.e0[rr];
-                s_rp[idx] = __ldg(A.rel[r].rowptr + t0 + min(tt, rows)) + d;
+            for (int it = 0; it < kRpIt; ++it) {
+                const int idx = it * 32 + lane;
+                rpv[it] = 0;
+                if (idx < R * (kMaxTile + 1)) {
+                    const int r = idx / (kMaxTile + 1), tt = idx - r * (kMaxTile + 1);
+                    int d = 0;
+#pragma unroll
+                    for (int rr = 0; rr < RMAX; ++rr)
+                        if (rr == r) d = T.eb[rr] - T.e0[rr];
+                    rpv[it] = __ldg(A.rel[r].rowptr + t0 + min(tt, rows)) + d;
+                }
             }
+            float adv[RMAX][4];
 #pragma unroll
             for (int r = 0; r < RMAX; ++r) {
+#pragma unroll
+                for (int h = 0; h < 4; ++h) adv[r][h] = 0.f;
                 if (r < R && lane < rows) {
                     const hg_gat_rel& Rl = A.rel[r];
                     const float* ap = Rl.a_dst + (t0 + lane) * Rl.lda_dst;
-                    float v[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-                    for (int h = 0; h < HT; ++h) v[h] = __ldg(ap + h);
-                    s_ad[r * kMaxTile + lane] = make_float4(v[0], v[1], v[2], v[3]);
+                    for (int h = 0; h < HT; ++h) adv[r][h] = __ldg(ap + h);
                 }
             }
-            // ---- ... and, lanes = edges in batches of 4 x 32 (all neighbour ids of a batch in flight, then all logits)
             bool miss = false;
+            for (int base = 0; base < T.tot; base += 8 * 32) {
+                int32_t j[8];
+                int rel_of[8];
 #pragma unroll
-            for (int r = 0; r < RMAX; ++r) {
-                if (r < R) {
-                    const hg_gat_rel& Rl = A.rel[r];
-                    const float* __restrict__ a_src = Rl.a_src;
-                    const float* __restrict__ a_edge = Rl.a_edge;
-                    const int64_t lda = Rl.lda_src;
-                    const int n = T.ne[r];
-                    for (int base = 0; base < n; base += 128) {
-                        int32_t j[4];
+                for (int u = 0; u < 8; ++u) {
+                    const int e = base + u * 32 + lane;  // pool entry
+                    j[u] = -1;
+                    rel_of[u] = 0;
+                    if (e < T.tot) {
+                        const int32_t* colp = A.rel[0].col + T.e0[0];
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) {
+                        for (int r = 1; r < RMAX; ++r)
+                            if (r < R && e >= T.eb[r]) colp = A.rel[r].col + (T.e0[r] - T.eb[r]), rel_of[u] = r;
+                        j[u] = __ldg(colp + e);
+                    }
+                }
+                float v[8][4];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+#pragma unroll
+                    for (int h = 0; h < 4; ++h) v[u][h] = 0.f;
+                    if (j[u] >= 0) {
+                        const hg_gat_rel& Rl = A.rel[rel_of[u]];
+                        const float* src = Rl.a_src + static_cast<int64_t>(j[u]) * Rl.lda_src;
+#pragma unroll
+                        for (int h = 0; h < HT; ++h) v[u][h] = __ldg(src + h);
+                        if (Rl.a_edge) {
                             const int e = base + u * 32 + lane;
-                            j[u] = e < n ? __ldg(Rl.col + T.e0[r] + e) : -1;
-                        }
-                        float v[4][4];
+                            int d = 0;
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) {
+                            for (int rr = 0; rr < RMAX; ++rr)
+                                if (rr == rel_of[u]) d = T.e0[rr] - T.eb[rr];
+                            const float* ae = Rl.a_edge + static_cast<int64_t>(e + d) * HT;
 #pragma unroll
-                            for (int h = 0; h < 4; ++h) v[u][h] = 0.f;
-                            if (j[u] >= 0) {
-                                const float* src = a_src + static_cast<int64_t>(j[u]) * lda;
-#pragma unroll
-                                for (int h = 0; h < HT; ++h) v[u][h] = __ldg(src + h);
-                                if (a_edge) {
-                                    const float* ae = a_edge + static_cast<int64_t>(T.e0[r] + base + u * 32 + lane) * HT;
-#pragma unroll
-                                    for (int h = 0; h < HT; ++h) v[u][h] += __ldg(ae + h);
-                                }
-                            }
-                        }
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            if (j[u] >= 0) {
-                                const int e = T.eb[r] + base + u * 32 + lane;
-                                const uint32_t d = static_cast<uint32_t>(j[u] - T.wlo[r]);
-                                const bool in = d < static_cast<uint32_t>(T.wn[r]);
-                                miss = miss || !in;
-                                s_off[e] = in ? static_cast<int32_t>(T.wb[r] + d * ROWB) : -1 - j[u];
-                                s_w[e] = make_float4(v[u][0], v[u][1], v[u][2], v[u][3]);
-                            }
+                            for (int h = 0; h < HT; ++h) v[u][h] += __ldg(ae + h);
                         }
                     }
                 }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    if (j[u] >= 0) {
+                        const int e = base + u * 32 + lane;
+                        int wlo = 0, wn = 0, wb = 0;
+#pragma unroll
+                        for (int rr = 0; rr < RMAX; ++rr)
+                            if (rr == rel_of[u]) wlo = T.wlo[rr], wn = T.wn[rr], wb = T.wb[rr];
+                        const uint32_t d = static_cast<uint32_t>(j[u] - wlo);
+                        const bool in = d < static_cast<uint32_t>(wn);
+                        miss = miss || !in;
+                        s_off[e] = in ? static_cast<int32_t>(wb + d * ROWB) : -1 - j[u];
+                        s_w[e] = make_float4(v[u][0], v[u][1], v[u][2], v[u][3]);
+                    }
+                }
             }
+#pragma unroll
+            for (int it = 0; it < kRpIt; ++it)
+                if (it * 32 + lane < R * (kMaxTile + 1)) s_rp[it * 32 + lane] = rpv[it];
+#pragma unroll
+            for (int r = 0; r < RMAX; ++r)
+                if (r < R && lane < rows) s_ad[r * kMaxTile + lane] = make_float4(adv[r][0], adv[r][1], adv[r][2], adv[r][3]);
             const bool any_miss = __any_sync(0xffffffffu, miss);
             __syncwarp();  // the stores above are ordered before the reads below (other lanes' edges)
 
@@ -859,34 +919,64 @@ k_gat_window(const __grid_constant__ GatParams P) {
         for (int kk = 0; kk < 2; ++kk)
 #pragma unroll
             for (int v = 0; v < 4; ++v) acc[kk][v] = 0.f;
-        if (t < rows) {
+        if (t < rows && !any_miss) {
+            // Every source of the tile is in the window.  One software-pipelined pass over the row's edges of ALL
+            // relations (pool entries; offsets are absolute in the window): the loads of edge i + 1 are issued before the
+            // FFMAs of edge i, ping-ponging between two register sets, so a warp exposes one shared-memory latency per
+            // row instead of one per edge.  Edge order = relation by relation, CSR order: v6's accumulation order.
+            // i-th edge of the row -> pool entry i + delta[r], r = the relation whose cumulative range holds i (selects)
+            int cum[RMAX], delta[RMAX], n_edges = 0;
+#pragma unroll
+            for (int r = 0; r < RMAX; ++r) {
+                const int beg = r < R ? s_rp[r * (kMaxTile + 1) + t] : 0, end = r < R ? s_rp[r * (kMaxTile + 1) + t + 1] : 0;
+                cum[r] = n_edges;
+                delta[r] = beg - n_edges;
+                n_edges += end - beg;
+            }
+            auto fetch = [&](float4 (&val)[HT][2], float4& w, int i) {  // unconditional and branch-free: schedulable early
+                i = i < n_edges ? i : n_edges - 1;
+                int d = delta[0];
+#pragma unroll
+                for (int r = 1; r < RMAX; ++r)
+                    if (i >= cum[r]) d = delta[r];
+                const int32_t off = s_off[i + d];
+                w = s_w[i + d];
+#pragma unroll
+                for (int hh = 0; hh < HT; ++hh) {
+                    val[hh][0] = *reinterpret_cast<const float4*>(wq + off + hh * (kWinC * 4));
+                    val[hh][1] = *reinterpret_cast<const float4*>(wq + off + hh * (kWinC * 4) + 128);
+                }
+            };
+            auto fma_edge = [&](const float4 (&val)[HT][2], const float4& w) {
+                const float wv[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                for (int hh = 0; hh < HT; ++hh)
+#pragma unroll
+                    for (int kk = 0; kk < 2; ++kk) {
+                        acc[kk][0] = fmaf(wv[hh], val[hh][kk].x, acc[kk][0]);
+                        acc[kk][1] = fmaf(wv[hh], val[hh][kk].y, acc[kk][1]);
+                        acc[kk][2] = fmaf(wv[hh], val[hh][kk].z, acc[kk][2]);
+                        acc[kk][3] = fmaf(wv[hh], val[hh][kk].w, acc[kk][3]);
+                    }
+            };
+            if (n_edges > 0) {
+                float4 va[HT][2], vb[HT][2], wa, wb;
+                fetch(va, wa, 0);
+                for (int i = 0;; i += 2) {
+                    fetch(vb, wb, i + 1);
+                    fma_edge(va, wa);
+                    if (i + 1 >= n_edges) break;
+                    fetch(va, wa, i + 2);
+                    fma_edge(vb, wb);
+                    if (i + 2 >= n_edges) break;
+                }
+            }
+        } else if (t < rows) {
 #pragma unroll
             for (int r = 0; r < RMAX; ++r) {
                 if (r < R) {
                     const int beg = s_rp[r * (kMaxTile + 1) + t], end = s_rp[r * (kMaxTile + 1) + t + 1];
-                    if (!any_miss) {  // every source of the tile is in the window: no per-edge branch
-#pragma unroll 2
-                        for (int e = beg; e < end; ++e) {
-                            const int32_t off = s_off[e];
-                            const float4 wa = s_w[e];
-                            const float wv[4] = {wa.x, wa.y, wa.z, wa.w};
-                            float4 val[HT][2];
-#pragma unroll
-                            for (int hh = 0; hh < HT; ++hh) {
-                                val[hh][0] = *reinterpret_cast<const float4*>(wq + off + hh * (kWinC * 4));
-                                val[hh][1] = *reinterpret_cast<const float4*>(wq + off + hh * (kWinC * 4) + 128);
-                            }
-#pragma unroll
-                            for (int hh = 0; hh < HT; ++hh)
-#pragma unroll
-                                for (int kk = 0; kk < 2; ++kk) {
-                                    acc[kk][0] = fmaf(wv[hh], val[hh][kk].x, acc[kk][0]);
-                                    acc[kk][1] = fmaf(wv[hh], val[hh][kk].y, acc[kk][1]);
-                                    acc[kk][2] = fmaf(wv[hh], val[hh][kk].z, acc[kk][2]);
-                                    acc[kk][3] = fmaf(wv[hh], val[hh][kk].w, acc[kk][3]);
-                                }
-                        }
-                    } else {
+                    {
                         const char* xg = reinterpret_cast<const char*>(A.rel[r].xs) + q * 16;
                         const uint32_t pitch = static_cast<uint32_t>(A.rel[r].ldxs) * 4u;
                         for (int e = beg; e < end; ++e) {
@@ -958,14 +1048,55 @@ k_gat_window(const __grid_constant__ GatParams P) {
     }
 }
 
+constexpr int kWinFallback = 1;  // internal: the window kernel does not apply after all, use v6
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point: the library must not NEED libcuda.so.1 at load time
+// (it is dlopen'ed on machines without a driver to check its exports).
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled() {
+    static const EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess) {
+            (void)cudaGetLastError();
+            p = nullptr;
+        }
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
 template <int HT, int RMAX>
-int launch_window(GatParams& P, cudaStream_t stream) {
+int launch_window(GatParams& G, cudaStream_t stream) {
     constexpr int ROWB = HT * kWinC * 4;
+    WinParams P;
+    static_cast<GatParams&>(P) = G;
     P.tile_rows = kMaxTile;
     P.hs = 4;
     P.n_bias = kWinC;
     P.cap = kWinEdges;
-    P.wrows = kWinBytes / ROWB;
+    P.wrows = kWinBytes / ROWB / kWinBox * kWinBox;
+    const EncodeTiledFn encode = encode_tiled();
+    if (!encode) return kWinFallback;
+    for (int r = 0; r < kWinMaxRel; ++r) {
+        if (r >= P.a.n_rel) {
+            P.tmap[r] = P.tmap[0];
+            continue;
+        }
+        const hg_gat_rel& Rl = P.a.rel[r];
+        if (Rl.n_src <= 0 || !Rl.xs || !aligned(Rl.xs, 16) || (Rl.ldxs * 4) % 16 != 0) return kWinFallback;
+        const cuuint64_t dims[2] = {static_cast<cuuint64_t>(HT * kWinC), static_cast<cuuint64_t>(Rl.n_src)};
+        const cuuint64_t strides[1] = {static_cast<cuuint64_t>(Rl.ldxs) * 4};
+        const cuuint32_t box[2] = {static_cast<cuuint32_t>(HT * kWinC), kWinBox};
+        const cuuint32_t estr[2] = {1, 1};
+        const CUresult cr = encode(&P.tmap[r], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(Rl.xs), dims,
+                                                   strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (cr != CUDA_SUCCESS) return kWinFallback;
+    }
     const size_t smem = win_smem_bytes(P.wrows, ROWB, P.cap, RMAX);
     HG_CUDA_TRY(cudaFuncSetAttribute(k_gat_window<HT, RMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     const int sms = sm_count() > 0 ? sm_count() : 148;
@@ -1061,7 +1192,10 @@ extern "C" int hg_gat_fused(const hg_gat_args* a, void* stream_) {
                 hint = hint && a->rel[r].tile_win != nullptr;
                 plain = plain && a->alpha_saved[r] == nullptr;
             }
-            if (hint && plain) return a->n_rel <= 2 ? dispatch_window<2>(P, stream) : dispatch_window<4>(P, stream);
+            if (hint && plain) {
+                const int rc = a->n_rel <= 2 ? dispatch_window<2>(P, stream) : dispatch_window<4>(P, stream);
+                if (rc != kWinFallback) return rc;
+            }
         }
         return head_mean ? dispatch_heads<1>(P, stream) : dispatch_heads<2>(P, stream);
     }

@@ -328,11 +328,11 @@ class GatRelation:
 
 def window_applies(rels: Sequence["GatRelation"], n_dst: int) -> bool:
     """Whether the plan's per-tile source windows are handed to ``hg_gat_fused`` (which then stages them in shared
-    memory).  Only where the windows are short: every relation carries one, has at most 14 edges per destination row on
+    memory).  Only where the windows are short: every relation carries one, has at most 9 edges per destination row on
     average (the kernel's edge pool per 32-row tile) and no more than 4 source rows per destination row (a tile of rooms
     spans hundreds of object rows: that relation stays on the global-gather kernel)."""
     return USE_TILE_WINDOW and n_dst > 0 and all(
-        r.csr.tile_win is not None and r.csr.cap <= 14 * n_dst and r.csr.n_src <= 4 * n_dst for r in rels)
+        r.csr.tile_win is not None and r.csr.cap <= 9 * n_dst and r.csr.n_src <= 4 * n_dst for r in rels)
 
 
 def gat_fused(rels: Sequence[GatRelation], n_dst: int, H: int, Cc: int, concat: bool, *, group: str = "sum",
@@ -372,6 +372,7 @@ def gat_fused(rels: Sequence[GatRelation], n_dst: int, H: int, Cc: int, concat: 
         g.a_edge = ptr(r.a_edge)
         g.rowptr, g.col, g.bias = ptr(r.csr.rowptr), ptr(r.csr.col), ptr(r.bias)
         g.tile_win = ptr(r.csr.tile_win) if use_window else None
+        g.n_src = int(r.xs.size(0))
         a.alpha_saved[k] = ptr(r.alpha_out)
     a.n_rel, a.n_dst, a.H, a.C = len(rels), n_dst, H, Cc
     a.concat, a.group, a.act, a.neg_slope = int(concat), GROUP[group], ACT[act], float(neg_slope)

@@ -190,7 +190,11 @@ typedef struct hg_gat_rel {
                                            bulk-copies the windows of xs into shared memory and gathers from there; sources
                                            outside the staged rows are read from global memory, so any window that stays
                                            inside [0, n_src) gives the same result.  Pass it for relations whose sources
-                                           are local (a few dozen rows per tile, <= ~14 edges per row) */
+                                           are local (a few dozen rows per tile, <= ~9 edges per row) */
+    int32_t n_src;                      /* source rows of xs: required (> 0) with tile_win -- the window kernel describes xs
+                                           to the TMA unit as a [n_src, H*C] tensor so that a box reaching past the last row
+                                           is zero-filled instead of read; ignored otherwise */
+    int32_t reserved;
 } hg_gat_rel;
 
 typedef struct hg_gat_args {

@@ -325,7 +325,7 @@ def test_gat_window_kernel_any_graph_and_any_hint():
     windows that do not cover the tile's sources at all, and hub tiles (edge pool overflow) all give the same bits."""
     g = torch.Generator().manual_seed(5)
     H, C, n_src, n_dst = 3, 64, 4000, 1000 + 17
-    ei = torch.stack([torch.randint(0, n_src, (9000,), generator=g), torch.randint(0, n_dst, (9000,), generator=g)])
+    ei = torch.stack([torch.randint(0, n_src, (7000,), generator=g), torch.randint(0, n_dst, (7000,), generator=g)])
     hub = torch.stack([torch.randint(0, n_src, (700,), generator=g), torch.full((700,), 40)])  # tile 1: 700 edges > pool
     ei = torch.cat([ei, hub], dim=1)
     (csr,), _ = ops.build_csr([CSRSpec(ei.cuda(), n_src, n_dst, False, want_window=True)])
