@@ -298,12 +298,15 @@ def run_ours(args, rank, world, local_rank):
         return d
 
     n_rooms = host["rooms"].x.size(0)
-    gather = LogitGather(26).prepare(n_rooms, dev) if world > 1 else None
+    gather = LogitGather(26).prepare(n_rooms, dev, slots=2) if world > 1 else None
 
-    def step(data):
+    def step(data, slot=0):
+        # the only collective on the path is the gather of the room logits (config 4).  The step stages its logits in
+        # the slot's padded buffer (part of the captured graph); the all-gather itself is launched by run() on a side
+        # stream, so it overlaps the next step's forward (latency-bound: 8 x 2 MB)
         logits = net(data)
-        if gather is not None:  # the only collective on the path: gather of the room logits (config 4)
-            gather(logits)
+        if gather is not None:
+            gather.stage(logits, slot)
         return logits
 
     def fence():
@@ -314,8 +317,11 @@ def run_ours(args, rank, world, local_rank):
     # ---- static buffers + captured steps (CUDA graphs: the forward is 20-odd short kernels)
     bufs = [device_copy(), device_copy()]
     outs = [None, None]
-    for b in bufs:  # eager warm-up: packs weights, sizes workspaces
-        step(b)
+    for k, b in enumerate(bufs):  # eager warm-up: packs weights, sizes workspaces, primes NCCL
+        step(b, k)
+        if gather is not None:
+            gather.launch(k)
+            gather.wait(k)
     fence()
     graphs = [None, None]
     use_graph = not args.no_graph
@@ -323,42 +329,66 @@ def run_ours(args, rank, world, local_rank):
         cap_stream = torch.cuda.Stream(dev)
         with torch.cuda.stream(cap_stream):
             for k in range(2):
-                step(bufs[k])
+                step(bufs[k], k)
             cap_stream.synchronize()
             for k in range(2):
                 g = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g, stream=cap_stream):
-                    outs[k] = step(bufs[k])
+                    outs[k] = step(bufs[k], k)
                 graphs[k] = g
         fence()
 
     def run(k):
+        if gather is not None:
+            gather.wait(k)  # the gather that last used this slot (two steps ago) has drained
         if use_graph:
             graphs[k].replay()
-            return outs[k]
-        return step(bufs[k])
+            out = outs[k]
+        else:
+            out = step(bufs[k], k)
+        if gather is not None:
+            gather.launch(k)
+        return out
+
+    def drain():
+        if gather is not None:
+            gather.wait(0)
+            gather.wait(1)
 
     # ---- device-resident arm (value): inputs already in HBM
-    for _ in range(args.warmup):
-        run(0)
+    for i in range(args.warmup):
+        run(i & 1)
+    drain()
     fence()
     with ClockSampler(local_rank) as clocks:
         marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+        last = torch.cuda.Event(enable_timing=True)
         marks[0].record()
         for i in range(args.steps):
-            run(0)
+            run(i & 1)  # the two slots hold the same batch; alternating them lets gather i overlap forward i + 1
             marks[i + 1].record()  # one event between back-to-back replays: per-step times for median / p10 / p90
+        drain()  # every gather has landed before the clock stops
+        last.record()
         fence()
-    ms = marks[0].elapsed_time(marks[-1])
+    ms = marks[0].elapsed_time(last)
     per_step = sorted(marks[i].elapsed_time(marks[i + 1]) for i in range(args.steps))
 
     # ---- the same K steps launched eagerly (no CUDA graph; side streams as in the value arm): SURVEY.md 8d reports both
+    def eager(k):
+        if gather is not None:
+            gather.wait(k)
+        step(bufs[k], k)
+        if gather is not None:
+            gather.launch(k)
+
     g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    step(bufs[0])
+    eager(0)
+    drain()
     fence()
     g0.record()
-    for _ in range(args.steps):
-        step(bufs[0])
+    for i in range(args.steps):
+        eager(i & 1)
+    drain()
     g1.record()
     fence()
     ms_eager = g0.elapsed_time(g1)
@@ -372,7 +402,8 @@ def run_ours(args, rank, world, local_rank):
     saved = ops.PARALLEL_BRANCHES, net.plan_cache.overlap
     ops.PARALLEL_BRANCHES, net.plan_cache.overlap = False, False
     for _ in range(args.steps):
-        step(bufs[0])
+        eager(0)
+        drain()
     fence()
     ops.PARALLEL_BRANCHES, net.plan_cache.overlap = saved
     ops.set_profile_sink(None)
@@ -405,6 +436,7 @@ def run_ours(args, rank, world, local_rank):
             main.wait_event(loaded[k])
             out_host[k].copy_(run(k), non_blocking=True)
             freed[k].record(main)
+        drain()
 
     h2d = sum(host[t].x.numel() * 4 for t in host.node_types) + sum(host[t].edge_index.numel() * 8 for t in host.edge_types)
     d2h = out_host[0].numel() * 4
@@ -441,7 +473,7 @@ def run_ours(args, rank, world, local_rank):
                    "edges_objects_to_rooms": int(host["objects", "objects_to_rooms", "rooms"].edge_index.size(1)),
                    "l2": "inputs larger than L2 (object features 297 MB + ~190 MB of projections per layer vs 126 MB L2)",
                    "projection_precision": ops.DEFAULT_PRECISION, "cuda_graph": use_graph,
-                   "collective": "all_gather_into_tensor(room logits)" if world > 1 else "none"},
+                   "collective": "all_gather_into_tensor(room logits), on a side stream, overlapping the next step" if world > 1 else "none"},
         "step_ms": {"median": statistics.median(per_step), "p10": per_step[len(per_step) // 10],
                     "p90": per_step[min(len(per_step) - 1, (9 * len(per_step)) // 10)],
                     "eager_ms_per_step": ms_eager / args.steps,

@@ -77,7 +77,24 @@ class GatTrainArgs(C.Structure):
                 ("g", vp), ("ldg", i64), ("dbias", vp)]
 
 
-_STRUCTS = [PlanRel, SegArgs, GatRel, GatArgs, LinSeg, LinearArgs, GatTrainRel, GatTrainArgs]
+HG_MAX_HTREE_TYPES = 8
+
+
+class HtreeType(C.Structure):
+    _fields_ = [("ptr", vp), ("n_nodes", i64), ("place", vp), ("is_room_virtual", i32), ("is_object_virtual", i32)]
+
+
+class HtreeRel(C.Structure):
+    _fields_ = [("src", vp), ("dst", vp), ("n_edges", i64), ("src_type", i32), ("dst_type", i32)]
+
+
+class HtreeSplitArgs(C.Structure):
+    _fields_ = [("type", HtreeType * HG_MAX_HTREE_TYPES), ("rel", HtreeRel * HG_MAX_PLAN_RELATIONS), ("n_types", i32),
+                ("n_rel", i32), ("n_graphs", i32), ("reserved", i32), ("ptr", vp), ("node_type", vp), ("batch", vp),
+                ("room_mask", vp), ("object_mask", vp), ("edges", vp * 3), ("status", vp)]
+
+
+_STRUCTS = [PlanRel, SegArgs, GatRel, GatArgs, LinSeg, LinearArgs, GatTrainRel, GatTrainArgs, HtreeSplitArgs]
 
 # name -> (restype, argtypes); every symbol declared in include/hydra_gnn_b200.h
 SYMBOLS = {
@@ -99,6 +116,8 @@ SYMBOLS = {
     "hg_gather_rows": (C.c_int, [vp, i64, vp, i64, i32, i32, vp, i64, vp]),
     "hg_collate_offsets": (C.c_int, [vp, i64, vp, vp, vp, i32, vp]),
     "hg_batch_vector": (C.c_int, [vp, i64, vp, i32, vp]),
+    "hg_htree_split_workspace_bytes": (C.c_size_t, [C.POINTER(HtreeSplitArgs)]),
+    "hg_htree_split": (C.c_int, [C.POINTER(HtreeSplitArgs), vp, C.c_size_t, vp]),
     "hg_gat_train_fwd": (C.c_int, [C.POINTER(GatTrainArgs), vp]),
     "hg_gat_train_bwd": (C.c_int, [C.POINTER(GatTrainArgs), vp]),
     "hg_csr_transpose_map": (C.c_int, [vp, vp, vp, i64, vp, vp, vp, i64, i32, vp, vp, vp]),

@@ -122,6 +122,10 @@ def batched_htree_to_homogeneous(batch: HeteroData) -> Data:
     node_types = [t for t in batch.node_types if "x" in batch[t]]
     assert "object_virtual" in node_types and "room_virtual" in node_types
     dev = batch[node_types[0]].x.device
+    if dev.type == "cuda" and USE_SPLIT_KERNEL:
+        out = _batched_htree_to_homogeneous_device(batch, node_types)
+        if out is not None:
+            return out
     ptrs = {}
     for t in node_types:
         st = batch[t]
@@ -208,6 +212,120 @@ def batched_htree_to_homogeneous(batch: HeteroData) -> Data:
     out.object_mask = node_type == node_types.index("object_virtual")
     out.batch = torch.repeat_interleave(torch.arange(G, device=dev), ptr[1:] - ptr[:-1], output_size=N)
     out.ptr = ptr
+    out.num_graphs = G
+    return out
+
+
+last_split_status = None  # status word of the most recent hg_htree_split call (device int32[1])
+USE_SPLIT_KERNEL = True  # device-resident batches: the integer half runs in hg_htree_split (False: the tensor-op pass)
+
+
+def _batched_htree_to_homogeneous_device(batch: HeteroData, node_types: List[str]):
+    """``batched_htree_to_homogeneous`` for a CUDA-resident batch: node placement, ``node_type`` / ``batch`` / ``ptr`` /
+    masks and the tree / init / pool edge lists come from ONE ``hg_htree_split`` call (six launches, no host
+    synchronisation: every output size is host-known); only the feature rows are moved with tensor indexing.
+    Returns None for the shapes the kernel does not cover (edge attributes, a virtual -> virtual relation)."""
+    import ctypes as C
+
+    from . import _lib
+    from .ops import _call, _workspace
+
+    rels = [et for et in batch.edge_types if "edge_index" in batch[et]]
+    virtual = ("object_virtual", "room_virtual")
+    if len(node_types) > _lib.HG_MAX_HTREE_TYPES or len(rels) > _lib.HG_MAX_PLAN_RELATIONS:
+        return None
+    if any("edge_attr" in batch[et] for et in rels) or any(et[0] in virtual and et[2] in virtual for et in rels):
+        return None
+    if any(et[0] not in node_types or et[2] not in node_types for et in rels):
+        return None
+    h = _lib.lib()
+    dev = batch[node_types[0]].x.device
+    a = _lib.HtreeSplitArgs()
+    keep, place, N = [], {}, 0
+    G = None
+    for i, t in enumerate(node_types):
+        st = batch[t]
+        n = int(st.x.size(0))
+        ptr_t = st.ptr.long().to(dev).contiguous() if "ptr" in st else torch.tensor([0, n], dtype=torch.long, device=dev)
+        if G is None:
+            G = int(ptr_t.numel()) - 1
+        elif int(ptr_t.numel()) - 1 != G:
+            return None
+        place[t] = torch.empty(n, dtype=torch.long, device=dev)
+        keep.append(ptr_t)
+        a.type[i].ptr, a.type[i].n_nodes, a.type[i].place = ptr_t.data_ptr(), n, place[t].data_ptr()
+        a.type[i].is_room_virtual, a.type[i].is_object_virtual = int(t == "room_virtual"), int(t == "object_virtual")
+        N += n
+    sizes = [0, 0, 0]
+    for k, et in enumerate(rels):
+        ei = batch[et].edge_index
+        if ei.dtype != torch.int64 or not ei.is_contiguous():
+            ei = ei.long().contiguous()
+        keep.append(ei)
+        E = int(ei.size(1))
+        a.rel[k].src, a.rel[k].dst, a.rel[k].n_edges = ei.data_ptr(), ei.data_ptr() + 8 * E, E
+        a.rel[k].src_type, a.rel[k].dst_type = node_types.index(et[0]), node_types.index(et[2])
+        sizes[1 if et[0] in virtual else (2 if et[2] in virtual else 0)] += E
+    a.n_types, a.n_rel, a.n_graphs = len(node_types), len(rels), G
+    out = Data()
+    out.ptr = torch.empty(G + 1, dtype=torch.long, device=dev)
+    out.node_type = torch.empty(N, dtype=torch.long, device=dev)
+    out.batch = torch.empty(N, dtype=torch.long, device=dev)
+    out.room_mask = torch.empty(N, dtype=torch.bool, device=dev)
+    out.object_mask = torch.empty(N, dtype=torch.bool, device=dev)
+    edges = [torch.empty(2, n, dtype=torch.long, device=dev) for n in sizes]
+    status = torch.empty(1, dtype=torch.int32, device=dev)
+    a.ptr, a.node_type, a.batch = out.ptr.data_ptr(), out.node_type.data_ptr(), out.batch.data_ptr()
+    a.room_mask, a.object_mask, a.status = out.room_mask.data_ptr(), out.object_mask.data_ptr(), status.data_ptr()
+    for c in range(3):
+        a.edges[c] = edges[c].data_ptr()
+    nbytes = h.hg_htree_split_workspace_bytes(C.byref(a))
+    if nbytes == 0:
+        return None
+    ws = _workspace(dev, nbytes)
+    rc = [0]
+
+    def run():
+        rc[0] = h.hg_htree_split(C.byref(a), ws.data_ptr(), ws.numel(), _lib.stream_ptr())
+        return 0 if rc[0] == -6 else rc[0]  # HG_EUNSUPPORTED: the caller takes the tensor-op pass
+
+    _call("hg_htree_split", dict(n_graphs=G, nodes=N, edges=sizes), run)
+    if rc[0] == -6:
+        return None
+    _lib.launch_count += 6
+    global last_split_status
+    last_split_status = status  # device int32[1]: edges out of graph order / range (0 for collated batches)
+    if rels:
+        out.edge_index, out.init_edge_index, out.pool_edge_index = edges
+    # ---- node attributes present in every store with one trailing shape (x zero-padded to the widest)
+    width = max(int(batch[t].x.size(1)) for t in node_types)
+    first = batch[node_types[0]]
+    names = [k for k, v in first.items() if torch.is_tensor(v) and v.dim() >= 1 and k not in ("batch", "ptr")]
+    if "y" in batch["room_virtual"] and "y" not in names:
+        names.append("y")
+    for key in names:
+        vals = []
+        for t in node_types:
+            w = batch[t].get(key)
+            if key == "y" and w is None and "y" in batch["room_virtual"]:
+                y = batch["room_virtual"].y
+                w = -torch.ones(int(batch[t].x.size(0)), dtype=y.dtype, device=dev)
+            if not torch.is_tensor(w):
+                vals = None
+                break
+            vals.append(w)
+        if vals is None:
+            continue
+        trail = (width,) if key == "x" else tuple(vals[0].shape[1:])
+        if key != "x" and any(tuple(w.shape[1:]) != trail for w in vals):
+            continue
+        buf = torch.zeros((N,) + trail, dtype=vals[0].dtype, device=dev)
+        for t, w in zip(node_types, vals):
+            if key == "x":
+                buf[place[t], : w.size(1)] = w
+            else:
+                buf[place[t]] = w
+        out[key] = buf
     out.num_graphs = G
     return out
 

@@ -559,14 +559,45 @@ int dispatch_special(GatParams& P, cudaStream_t stream) {
 // All relations of a tile share one edge pool and one window pool (packed per tile).
 // Tiles whose edges exceed the pool (hub rows) take v6's warp-per-row path in the consumer warps.
 // ---------------------------------------------------------------------------------------------------
-constexpr int kWinConsumerWarps = 8, kWinProducerWarps = 6, kWinStages = 3;
-constexpr int kWinThreads = (kWinConsumerWarps + kWinProducerWarps + 1) * 32;  // 480
+#ifndef HG_WIN_PRODUCERS
+#define HG_WIN_PRODUCERS 6
+#endif
+#ifndef HG_WIN_STAGES
+#define HG_WIN_STAGES 3
+#endif
+#ifndef HG_WIN_BYTES
+#define HG_WIN_BYTES 49152  // 64 rows at H = 3 (98.5 % of the 32-row tiles of an MP3D-shaped batch fit)
+#endif
+#ifndef HG_WIN_PREDICATE
+#define HG_WIN_PREDICATE 1   // gather loads predicated on i < n_edges (0: clamped index, unconditional loads)
+#endif
+#ifndef HG_WIN_SLEEP
+#define HG_WIN_SLEEP 128    // ns of back-off in the producers' stage waits (0: plain spin)
+#endif
+#ifndef HG_WIN_KC
+#define HG_WIN_KC 2  // float4 chunks per gather thread: 1 = 16 threads per row, 16 gather warps; 2 = 8 and 8
+#endif
+#ifndef HG_WIN_GROUPS
+#define HG_WIN_GROUPS 1  // gather warps form this many groups that take alternate tiles (each tile in 32 / rows-per-pass passes)
+#endif
+constexpr int kWinKC = HG_WIN_KC, kWinTPR = 16 / kWinKC, kWinGroups = HG_WIN_GROUPS;
+#ifndef HG_WIN_ESTAGES
+#define HG_WIN_ESTAGES 8  // edge stages: more than producer warps, so a producer never waits for the gather of its last tile
+#endif
+constexpr int kWinConsumerWarps = kWinTPR, kWinProducerWarps = HG_WIN_PRODUCERS, kWinStages = HG_WIN_STAGES;
+constexpr int kWinEdgeStages = HG_WIN_ESTAGES;
+constexpr int kWinThreads = (kWinConsumerWarps + kWinProducerWarps + 1) * 32;  // 736 (KC = 1) or 480
+constexpr int kWinMaxRegs = 65536 / kWinThreads / 8 * 8 > 128 ? 128 : 65536 / kWinThreads / 8 * 8;  // one CTA per SM
 constexpr int kWinC = 64;               // channels per head (8 threads x 2 float4 chunks)
-constexpr int kWinBytes = 55296;        // window pool of one stage: 72 rows at H = 3
+constexpr int kWinBytes = HG_WIN_BYTES;   // window pool of one stage
 constexpr int kWinEdges = 320;          // edge pool of one stage (all relations of a tile)
 constexpr int kWinMaxRel = 4;
 constexpr int kWinBox = 4;             // source rows per TMA box
-constexpr int kWinBars = 2 * kWinProducerWarps + 2 * kWinStages;
+constexpr int kWinBars = 2 * kWinEdgeStages + 2 * kWinStages;
+constexpr int kWinGroupWarps = kWinConsumerWarps / kWinGroups;     // gather warps per group
+constexpr int kWinPassRows = kWinGroupWarps * 32 / kWinTPR;        // destination rows a group gathers at a time
+constexpr int kWinPasses = kMaxTile / kWinPassRows;
+static_assert(kWinConsumerWarps % kWinGroups == 0 && kMaxTile % kWinPassRows == 0, "groups must tile the 32-row tile");
 
 // one edge stage: weights float4[ecap] | destination logits float4[rmax][32] | offsets int[ecap] |
 // pool-relative rowptr int[rmax][33] (padded to 16 B) | control int[4] {hub, window rows, any source outside}
@@ -574,7 +605,7 @@ __host__ __device__ inline uint32_t win_edge_stage_bytes(int ecap, int rmax) {
     return static_cast<uint32_t>(ecap * 16 + rmax * kMaxTile * 16 + ecap * 4 + (rmax * (kMaxTile + 1) * 4 + 15) / 16 * 16 + 16);
 }
 __host__ __device__ inline size_t win_smem_bytes(int wrows, int rowb, int ecap, int rmax) {
-    return static_cast<size_t>(kWinStages) * wrows * rowb + static_cast<size_t>(kWinProducerWarps) * win_edge_stage_bytes(ecap, rmax) +
+    return static_cast<size_t>(kWinStages) * wrows * rowb + static_cast<size_t>(kWinEdgeStages) * win_edge_stage_bytes(ecap, rmax) +
            kWinC * 4 + kWinBars * 8 + 16;
 }
 
@@ -630,10 +661,19 @@ __device__ __forceinline__ void mbar_wait_idle(uint32_t bar, uint32_t parity) {
     if (tc::mbar_try_wait(bar, parity)) return;
     const long long t0 = clock64();
     while (!tc::mbar_try_wait(bar, parity)) {
-        __nanosleep(128);
+        if (HG_WIN_SLEEP > 0) __nanosleep(HG_WIN_SLEEP);
         if (clock64() - t0 > tc::kWaitCycles) __trap();
     }
 }
+
+#ifdef HG_WIN_TRACE
+// debug build only (tools/ab_build.sh ... -DHG_WIN_TRACE): clock64 stamps of CTA 0's roles, per tile
+constexpr int kTraceTiles = 64, kTraceEv = 12;
+__device__ long long g_win_trace[kTraceTiles * kTraceEv];
+#define WIN_STAMP(k, ev) do { if (blockIdx.x == 0 && (threadIdx.x & 31) == 0 && (k) < kTraceTiles) g_win_trace[(k) * kTraceEv + (ev)] = clock64(); } while (0)
+#else
+#define WIN_STAMP(k, ev) do { } while (0)
+#endif
 
 template <int HT, int RMAX>
 __global__ void __launch_bounds__(kWinThreads, 1)
@@ -646,12 +686,12 @@ k_gat_window(const __grid_constant__ WinParams P) {
     const uint32_t win_bytes = static_cast<uint32_t>(P.wrows) * ROWB;
     const uint32_t est_bytes = win_edge_stage_bytes(P.cap, RMAX);
     uint8_t* const edge0 = s_raw + static_cast<size_t>(kWinStages) * win_bytes;
-    uint8_t* const tail = edge0 + static_cast<size_t>(kWinProducerWarps) * est_bytes;
+    uint8_t* const tail = edge0 + static_cast<size_t>(kWinEdgeStages) * est_bytes;
     float* const s_bias = reinterpret_cast<float*>(tail);
     uint64_t* const s_bar = reinterpret_cast<uint64_t*>(tail + kWinC * 4);
     const uint32_t bar_a = tc::smem_u32(s_bar);
-    const uint32_t edge_full = bar_a, edge_empty = bar_a + 8 * kWinProducerWarps;
-    const uint32_t win_full = bar_a + 16 * kWinProducerWarps, win_empty = win_full + 8 * kWinStages;
+    const uint32_t edge_full = bar_a, edge_empty = bar_a + 8 * kWinEdgeStages;
+    const uint32_t win_full = bar_a + 16 * kWinEdgeStages, win_empty = win_full + 8 * kWinStages;
     // offsets inside an edge stage
     const uint32_t o_ad = static_cast<uint32_t>(P.cap) * 16;
     const uint32_t o_off = o_ad + RMAX * kMaxTile * 16;
@@ -665,13 +705,13 @@ k_gat_window(const __grid_constant__ WinParams P) {
         s_bias[tid] = b;
     }
     if (tid == 0) {
-        for (int s = 0; s < kWinProducerWarps; ++s) {
+        for (int s = 0; s < kWinEdgeStages; ++s) {
             tc::mbar_init(s_bar + s, 1);                                        // edge_full: lane 0 of the producer warp
-            tc::mbar_init(s_bar + kWinProducerWarps + s, kWinConsumerWarps);    // edge_empty: one lane per consumer warp
+            tc::mbar_init(s_bar + kWinEdgeStages + s, kWinGroupWarps);          // edge_empty: one lane per warp of the owning group
         }
         for (int s = 0; s < kWinStages; ++s) {
-            tc::mbar_init(s_bar + 2 * kWinProducerWarps + s, 1);                // win_full: one arrive (+ the copies' bytes)
-            tc::mbar_init(s_bar + 2 * kWinProducerWarps + kWinStages + s, kWinConsumerWarps);  // win_empty
+            tc::mbar_init(s_bar + 2 * kWinEdgeStages + s, 1);                // win_full: one arrive (+ the copies' bytes)
+            tc::mbar_init(s_bar + 2 * kWinEdgeStages + kWinStages + s, kWinGroupWarps);  // win_empty
         }
         tc::fence_barrier_init();
     }
@@ -694,7 +734,9 @@ k_gat_window(const __grid_constant__ WinParams P) {
                 const int64_t tile = blockIdx.x + static_cast<int64_t>(k + 1) * gridDim.x, t0 = tile * kMaxTile;
                 Tn.load(A, tile, t0, (A.n_dst - t0 < kMaxTile) ? static_cast<int>(A.n_dst - t0) : kMaxTile, P.wrows);
             }
+            WIN_STAMP(k, 0);
             mbar_wait_idle(win_empty + 8 * ws, wph ^ 1u);
+            WIN_STAMP(k, 1);
             if (lane == 0) {
                 if (T.tot > P.cap || T.used == 0) {  // hub tile / no window: complete the phase without bytes
                     tc::mbar_arrive(win_full + 8 * ws);
@@ -719,36 +761,64 @@ k_gat_window(const __grid_constant__ WinParams P) {
     if (warp >= kWinConsumerWarps) {
         // ================================================================== edge producers: warp p, tiles k = p, p + 6, ...
         const int p = warp - kWinConsumerWarps;
-        uint8_t* const st = edge0 + static_cast<size_t>(p) * est_bytes;
-        float4* const s_w = reinterpret_cast<float4*>(st);
-        float4* const s_ad = reinterpret_cast<float4*>(st + o_ad);
-        int32_t* const s_off = reinterpret_cast<int32_t*>(st + o_off);
-        int32_t* const s_rp = reinterpret_cast<int32_t*>(st + o_rp);
-        int32_t* const s_ctl = reinterpret_cast<int32_t*>(st + o_ctl);
-        uint32_t eph = 0;
         auto load_tile = [&](WinTile<ROWB, RMAX>& T, int k) {
             const int64_t tile = blockIdx.x + static_cast<int64_t>(k) * gridDim.x, t0 = tile * kMaxTile;
             T.load(A, tile, t0, (A.n_dst - t0 < kMaxTile) ? static_cast<int>(A.n_dst - t0) : kMaxTile, P.wrows);
         };
-        WinTile<ROWB, RMAX> Tn;  // control of this warp's NEXT tile, loaded one tile ahead
-        if (p < n_k) load_tile(Tn, p);
-        for (int k = p; k < n_k; k += kWinProducerWarps, eph ^= 1u) {
+        // neighbour ids of pool entries base + u * 32 + lane, u < 8 (-1 past the end): all eight loads in flight at once
+        auto load_cols = [&](const WinTile<ROWB, RMAX>& T, int base, int32_t (&j)[8]) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int e = base + u * 32 + lane;
+                j[u] = -1;
+                if (e < T.tot && T.tot <= P.cap) {
+                    const int32_t* colp = A.rel[0].col + T.e0[0];
+#pragma unroll
+                    for (int r = 1; r < RMAX; ++r)
+                        if (r < R && e >= T.eb[r]) colp = A.rel[r].col + (T.e0[r] - T.eb[r]);
+                    j[u] = __ldg(colp + e);
+                }
+            }
+        };
+        WinTile<ROWB, RMAX> Tn;  // control of this warp's NEXT tile, loaded one tile ahead ...
+        int32_t jn[8];           // ... and the first 256 neighbour ids of it (one DRAM round trip less per tile)
+        if (p < n_k) {
+            load_tile(Tn, p);
+            load_cols(Tn, 0, jn);
+        }
+        for (int k = p; k < n_k; k += kWinProducerWarps) {
+            const int es = k % kWinEdgeStages;  // the tile's edge stage (a ring longer than the number of producer warps)
+            const uint32_t eph = (k / kWinEdgeStages) & 1;
+            uint8_t* const st = edge0 + static_cast<size_t>(es) * est_bytes;
+            float4* const s_w = reinterpret_cast<float4*>(st);
+            float4* const s_ad = reinterpret_cast<float4*>(st + o_ad);
+            int32_t* const s_off = reinterpret_cast<int32_t*>(st + o_off);
+            int32_t* const s_rp = reinterpret_cast<int32_t*>(st + o_rp);
+            int32_t* const s_ctl = reinterpret_cast<int32_t*>(st + o_ctl);
             const int64_t tile = blockIdx.x + static_cast<int64_t>(k) * gridDim.x, t0 = tile * kMaxTile;
             const int rows = (A.n_dst - t0 < kMaxTile) ? static_cast<int>(A.n_dst - t0) : kMaxTile;
             const WinTile<ROWB, RMAX> T = Tn;
-            if (k + kWinProducerWarps < n_k) load_tile(Tn, k + kWinProducerWarps);
-            mbar_wait_idle(edge_empty + 8 * p, eph ^ 1u);  // stage free (the first pass is on the fresh barrier)
+            int32_t jc[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) jc[u] = jn[u];
+            const bool has_next = k + kWinProducerWarps < n_k;
+            if (has_next) load_tile(Tn, k + kWinProducerWarps);
+            WIN_STAMP(k, 2);
+            mbar_wait_idle(edge_empty + 8 * es, eph ^ 1u);  // stage free (the first pass is on the fresh barrier)
+            WIN_STAMP(k, 3);
             if (T.tot > P.cap) {  // hub tile (uniform): the consumers stream it from global memory
                 if (lane == 0) {
                     s_ctl[0] = 1, s_ctl[1] = 0, s_ctl[2] = 0;
-                    tc::mbar_arrive(edge_full + 8 * p);
+                    tc::mbar_arrive(edge_full + 8 * es);
                 }
                 __syncwarp();
+                if (has_next) load_cols(Tn, 0, jn);
                 continue;
             }
-            // ---- stage.  Two DRAM round trips per tile, each with every load of the tile in flight at once:
-            //   trip 1  rowptr slices, destination logits and the neighbour ids (lanes = pool entries, 8 per lane);
-            //   trip 2  the source logits of those neighbours.
+            // ---- stage.  One DRAM round trip per tile on the critical path, every load of the tile in flight at once:
+            //   (prefetched during the previous tile of this warp: tile control and the neighbour ids, lanes = pool
+            //   entries, 8 per lane)
+            //   trip    rowptr slices, destination logits and the source logits of those neighbours.
             constexpr int kRpIt = (RMAX * (kMaxTile + 1) + 31) / 32;
             int32_t rpv[kRpIt];
 #pragma unroll
@@ -780,24 +850,25 @@ k_gat_window(const __grid_constant__ WinParams P) {
             for (int base = 0; base < T.tot; base += 8 * 32) {
                 int32_t j[8];
                 int rel_of[8];
+                if (base == 0) {
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) j[u] = jc[u];
+                } else {
+                    load_cols(T, base, j);
+                }
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
                     const int e = base + u * 32 + lane;  // pool entry
-                    j[u] = -1;
                     rel_of[u] = 0;
-                    if (e < T.tot) {
-                        const int32_t* colp = A.rel[0].col + T.e0[0];
 #pragma unroll
-                        for (int r = 1; r < RMAX; ++r)
-                            if (r < R && e >= T.eb[r]) colp = A.rel[r].col + (T.e0[r] - T.eb[r]), rel_of[u] = r;
-                        j[u] = __ldg(colp + e);
-                    }
+                    for (int r = 1; r < RMAX; ++r)
+                        if (r < R && e >= T.eb[r]) rel_of[u] = r;
                 }
-                float v[8][4];
+                float v[8][HT];
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
 #pragma unroll
-                    for (int h = 0; h < 4; ++h) v[u][h] = 0.f;
+                    for (int h = 0; h < HT; ++h) v[u][h] = 0.f;
                     if (j[u] >= 0) {
                         const hg_gat_rel& Rl = A.rel[rel_of[u]];
                         const float* src = Rl.a_src + static_cast<int64_t>(j[u]) * Rl.lda_src;
@@ -827,7 +898,8 @@ k_gat_window(const __grid_constant__ WinParams P) {
                         const bool in = d < static_cast<uint32_t>(wn);
                         miss = miss || !in;
                         s_off[e] = in ? static_cast<int32_t>(wb + d * ROWB) : -1 - j[u];
-                        s_w[e] = make_float4(v[u][0], v[u][1], v[u][2], v[u][3]);
+                        s_w[e] = make_float4(v[u][0], HT > 1 ? v[u][HT > 1 ? 1 : 0] : 0.f, HT > 2 ? v[u][HT > 2 ? 2 : 0] : 0.f,
+                                             HT > 3 ? v[u][HT > 3 ? 3 : 0] : 0.f);
                     }
                 }
             }
@@ -837,62 +909,79 @@ k_gat_window(const __grid_constant__ WinParams P) {
 #pragma unroll
             for (int r = 0; r < RMAX; ++r)
                 if (r < R && lane < rows) s_ad[r * kMaxTile + lane] = make_float4(adv[r][0], adv[r][1], adv[r][2], adv[r][3]);
+            if (has_next) load_cols(Tn, 0, jn);  // in flight during the softmax below
+            WIN_STAMP(k, 4);
             const bool any_miss = __any_sync(0xffffffffu, miss);
             __syncwarp();  // the stores above are ordered before the reads below (other lanes' edges)
 
-            // ---- softmax in place: lanes = rows, relation by relation; all heads of an edge are one float4
+            // ---- softmax in place: lanes = rows, relation by relation; all heads of an edge are one float4.
+            // Each pass handles the row's edges in pairs (both loads first), halving the serialised shared-memory latency.
 #pragma unroll
             for (int r = 0; r < RMAX; ++r) {
                 if (r < R && lane < rows) {
                     const int beg = s_rp[r * (kMaxTile + 1) + lane], end = s_rp[r * (kMaxTile + 1) + lane + 1];
                     const float4 ad4 = s_ad[r * kMaxTile + lane];
                     const float ad[4] = {ad4.x, ad4.y, ad4.z, ad4.w};
-                    float m[HT], l[HT];
+                    float m[HT], l[HT], inv[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
                     for (int h = 0; h < HT; ++h) m[h] = -INFINITY, l[h] = 0.f;
-                    for (int e = beg; e < end; ++e) {
-                        float4 w4 = s_w[e];
-                        float v[4] = {w4.x, w4.y, w4.z, w4.w};
+                    auto sweep = [&](auto&& fn) {  // fn(float (&v)[4]) on every edge of the row, in order, two at a time
+                        int e = beg;
+                        for (; e + 1 < end; e += 2) {
+                            const float4 a4 = s_w[e], b4 = s_w[e + 1];
+                            float va[4] = {a4.x, a4.y, a4.z, a4.w}, vb[4] = {b4.x, b4.y, b4.z, b4.w};
+                            fn(va);
+                            fn(vb);
+                            s_w[e] = make_float4(va[0], va[1], va[2], va[3]);
+                            s_w[e + 1] = make_float4(vb[0], vb[1], vb[2], vb[3]);
+                        }
+                        if (e < end) {
+                            const float4 a4 = s_w[e];
+                            float va[4] = {a4.x, a4.y, a4.z, a4.w};
+                            fn(va);
+                            s_w[e] = make_float4(va[0], va[1], va[2], va[3]);
+                        }
+                    };
+                    sweep([&](float (&v)[4]) {
 #pragma unroll
                         for (int h = 0; h < HT; ++h) {
                             v[h] = leaky(v[h] + ad[h], A.neg_slope);
                             m[h] = fmaxf(m[h], v[h]);
                         }
-                        s_w[e] = make_float4(v[0], v[1], v[2], v[3]);
-                    }
-                    for (int e = beg; e < end; ++e) {
-                        float4 w4 = s_w[e];
-                        float v[4] = {w4.x, w4.y, w4.z, w4.w};
+                    });
+                    sweep([&](float (&v)[4]) {
 #pragma unroll
                         for (int h = 0; h < HT; ++h) {
                             v[h] = __expf(v[h] - m[h]);
                             l[h] += v[h];
                         }
-                        s_w[e] = make_float4(v[0], v[1], v[2], v[3]);
-                    }
-                    float inv[4] = {0.f, 0.f, 0.f, 0.f};
+                    });
 #pragma unroll
                     for (int h = 0; h < HT; ++h) inv[h] = 1.f / (l[h] + 1e-16f);
-                    for (int e = beg; e < end; ++e) {
-                        float4 w4 = s_w[e];
-                        s_w[e] = make_float4(w4.x * inv[0], w4.y * inv[1], w4.z * inv[2], w4.w * inv[3]);
-                    }
+                    sweep([&](float (&v)[4]) {
+#pragma unroll
+                        for (int h = 0; h < 4; ++h) v[h] *= inv[h];
+                    });
                 }
             }
+            WIN_STAMP(k, 5);
             if (lane == 0) s_ctl[0] = 0, s_ctl[1] = T.used, s_ctl[2] = any_miss ? 1 : 0;
             __syncwarp();  // every lane's stage writes are ordered before lane 0's releasing arrive
-            if (lane == 0) tc::mbar_arrive(edge_full + 8 * p);
+            if (lane == 0) tc::mbar_arrive(edge_full + 8 * es);
         }
         return;
     }
 
     // ====================================================================== consumers
-    const int q = tid & 7, t = tid >> 3;  // chunk pair / destination row of the tile
+    // Groups of gather warps take alternate tiles, so one group's epilogue / barrier waits overlap the other group's
+    // gather and the shared-memory port (the bound of the gather: 768 B per edge) never idles between tiles.
+    const int grp = warp / kWinGroupWarps, wi = warp % kWinGroupWarps;
+    const int q = lane % kWinTPR, row_in_pass = wi * (32 / kWinTPR) + lane / kWinTPR;  // first chunk / row within a pass
     const float gscale = (A.group == HG_GROUP_MEAN) ? 1.f / static_cast<float>(R) : 1.f;
     const float hscale = 1.f / static_cast<float>(HT);
-    int es = 0, ws = 0;
-    uint32_t eph = 0, wph = 0;
-    for (int k = 0; k < n_k; ++k) {
+    for (int k = grp; k < n_k; k += kWinGroups) {
+        const int es = k % kWinEdgeStages, ws = k % kWinStages;
+        const uint32_t eph = (k / kWinEdgeStages) & 1, wph = (k / kWinStages) & 1;
         const int64_t tile = blockIdx.x + static_cast<int64_t>(k) * gridDim.x, t0 = tile * kMaxTile;
         const int rows = (A.n_dst - t0 < kMaxTile) ? static_cast<int>(A.n_dst - t0) : kMaxTile;
         const uint8_t* const st = edge0 + static_cast<size_t>(es) * est_bytes;
@@ -903,20 +992,23 @@ k_gat_window(const __grid_constant__ WinParams P) {
         const uint32_t b_ef = edge_full + 8 * es, b_ee = edge_empty + 8 * es, b_wf = win_full + 8 * ws, b_we = win_empty + 8 * ws;
         const uint8_t* const wq = s_raw + static_cast<size_t>(ws) * win_bytes + q * 16;
 
+        if (warp == 0) WIN_STAMP(k, 6);
         tc::mbar_wait(b_ef, eph);
+        if (warp == 0) WIN_STAMP(k, 7);
         tc::mbar_wait(b_wf, wph);
+        if (warp == 0) WIN_STAMP(k, 8);
         const int hub = s_ctl[0], any_miss = s_ctl[2];
-        if (++es == kWinProducerWarps) es = 0, eph ^= 1u;
-        if (++ws == kWinStages) ws = 0, wph ^= 1u;
         if (hub) {  // uniform: warp per row straight from global memory
-            for (int tt = warp; tt < rows; tt += kWinConsumerWarps) slow_row<4>(P, t0 + tt, lane, 0, kWinC);
+            for (int tt = wi; tt < rows; tt += kWinGroupWarps) slow_row<4>(P, t0 + tt, lane, 0, kWinC);
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(b_ee), tc::mbar_arrive(b_we);
             continue;
         }
-        float acc[2][4];
+        for (int pass = 0; pass < kWinPasses; ++pass) {
+        const int t = pass * kWinPassRows + row_in_pass;
+        float acc[kWinKC][4];
 #pragma unroll
-        for (int kk = 0; kk < 2; ++kk)
+        for (int kk = 0; kk < kWinKC; ++kk)
 #pragma unroll
             for (int v = 0; v < 4; ++v) acc[kk][v] = 0.f;
         if (t < rows && !any_miss) {
@@ -933,26 +1025,44 @@ k_gat_window(const __grid_constant__ WinParams P) {
                 delta[r] = beg - n_edges;
                 n_edges += end - beg;
             }
-            auto fetch = [&](float4 (&val)[HT][2], float4& w, int i) {  // unconditional and branch-free: schedulable early
-                i = i < n_edges ? i : n_edges - 1;
+            // Three-deep: while the FFMAs of edge i run, the source rows of edge i + 1 are in flight and the
+            // offset / weights of edge i + 2 are being read -- no load waits on another load inside an iteration.
+            // Loads are predicated on i < n_edges (a finished row = a whole quarter-warp: its LDS.128 requests cost no
+            // shared-memory wavefronts); the index math is branch-free.
+            auto fetch_ow = [&](int32_t& off, float4& w, int i) {
                 int d = delta[0];
 #pragma unroll
                 for (int r = 1; r < RMAX; ++r)
                     if (i >= cum[r]) d = delta[r];
-                const int32_t off = s_off[i + d];
-                w = s_w[i + d];
+                if (!HG_WIN_PREDICATE) {
+                    const int ic = i < n_edges ? i : n_edges - 1;
+                    int dc = delta[0];
 #pragma unroll
-                for (int hh = 0; hh < HT; ++hh) {
-                    val[hh][0] = *reinterpret_cast<const float4*>(wq + off + hh * (kWinC * 4));
-                    val[hh][1] = *reinterpret_cast<const float4*>(wq + off + hh * (kWinC * 4) + 128);
+                    for (int r = 1; r < RMAX; ++r)
+                        if (ic >= cum[r]) dc = delta[r];
+                    off = s_off[ic + dc];
+                    w = s_w[ic + dc];
+                } else if (i < n_edges) {
+                    off = s_off[i + d];
+                    w = s_w[i + d];
                 }
             };
-            auto fma_edge = [&](const float4 (&val)[HT][2], const float4& w) {
+            auto fetch_xs = [&](float4 (&val)[HT][kWinKC], int32_t off, bool on) {
+                if (on || !HG_WIN_PREDICATE) {
+#pragma unroll
+                    for (int hh = 0; hh < HT; ++hh) {
+#pragma unroll
+                        for (int kk = 0; kk < kWinKC; ++kk)
+                            val[hh][kk] = *reinterpret_cast<const float4*>(wq + off + hh * (kWinC * 4) + kk * (kWinTPR * 16));
+                    }
+                }
+            };
+            auto fma_edge = [&](const float4 (&val)[HT][kWinKC], const float4& w) {
                 const float wv[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
                 for (int hh = 0; hh < HT; ++hh)
 #pragma unroll
-                    for (int kk = 0; kk < 2; ++kk) {
+                    for (int kk = 0; kk < kWinKC; ++kk) {
                         acc[kk][0] = fmaf(wv[hh], val[hh][kk].x, acc[kk][0]);
                         acc[kk][1] = fmaf(wv[hh], val[hh][kk].y, acc[kk][1]);
                         acc[kk][2] = fmaf(wv[hh], val[hh][kk].z, acc[kk][2]);
@@ -960,13 +1070,21 @@ k_gat_window(const __grid_constant__ WinParams P) {
                     }
             };
             if (n_edges > 0) {
-                float4 va[HT][2], vb[HT][2], wa, wb;
-                fetch(va, wa, 0);
+                float4 va[HT][kWinKC], vb[HT][kWinKC], wa, wb, wn = make_float4(0.f, 0.f, 0.f, 0.f);
+                int32_t offn = 0;
+                fetch_ow(offn, wn, 0);
+                fetch_xs(va, offn, true);
+                wa = wn;
+                fetch_ow(offn, wn, 1);
                 for (int i = 0;; i += 2) {
-                    fetch(vb, wb, i + 1);
+                    fetch_xs(vb, offn, i + 1 < n_edges);
+                    wb = wn;
+                    fetch_ow(offn, wn, i + 2);
                     fma_edge(va, wa);
                     if (i + 1 >= n_edges) break;
-                    fetch(va, wa, i + 2);
+                    fetch_xs(va, offn, i + 2 < n_edges);
+                    wa = wn;
+                    fetch_ow(offn, wn, i + 3);
                     fma_edge(vb, wb);
                     if (i + 2 >= n_edges) break;
                 }
@@ -983,25 +1101,27 @@ k_gat_window(const __grid_constant__ WinParams P) {
                             const int32_t off = s_off[e];
                             const float4 wa = s_w[e];
                             const float wv[4] = {wa.x, wa.y, wa.z, wa.w};
-                            float4 val[HT][2];
+                            float4 val[HT][kWinKC];
                             if (off >= 0) {
 #pragma unroll
                                 for (int hh = 0; hh < HT; ++hh) {
-                                    val[hh][0] = *reinterpret_cast<const float4*>(wq + off + hh * (kWinC * 4));
-                                    val[hh][1] = *reinterpret_cast<const float4*>(wq + off + hh * (kWinC * 4) + 128);
+#pragma unroll
+                                    for (int kk = 0; kk < kWinKC; ++kk)
+                                        val[hh][kk] = *reinterpret_cast<const float4*>(wq + off + hh * (kWinC * 4) + kk * (kWinTPR * 16));
                                 }
                             } else {  // source outside the staged window
                                 const char* row = xg + static_cast<uint64_t>(static_cast<uint32_t>(-1 - off)) * pitch;
 #pragma unroll
                                 for (int hh = 0; hh < HT; ++hh) {
-                                    val[hh][0] = __ldg(reinterpret_cast<const float4*>(row + hh * (kWinC * 4)));
-                                    val[hh][1] = __ldg(reinterpret_cast<const float4*>(row + hh * (kWinC * 4) + 128));
+#pragma unroll
+                                    for (int kk = 0; kk < kWinKC; ++kk)
+                                        val[hh][kk] = __ldg(reinterpret_cast<const float4*>(row + hh * (kWinC * 4) + kk * (kWinTPR * 16)));
                                 }
                             }
 #pragma unroll
                             for (int hh = 0; hh < HT; ++hh)
 #pragma unroll
-                                for (int kk = 0; kk < 2; ++kk) {
+                                for (int kk = 0; kk < kWinKC; ++kk) {
                                     acc[kk][0] = fmaf(wv[hh], val[hh][kk].x, acc[kk][0]);
                                     acc[kk][1] = fmaf(wv[hh], val[hh][kk].y, acc[kk][1]);
                                     acc[kk][2] = fmaf(wv[hh], val[hh][kk].z, acc[kk][2]);
@@ -1012,8 +1132,11 @@ k_gat_window(const __grid_constant__ WinParams P) {
                 }
             }
         }
-        __syncwarp();
-        if (lane == 0) tc::mbar_arrive(b_ee), tc::mbar_arrive(b_we);  // release: this warp no longer reads the stages
+        if (pass == kWinPasses - 1) {
+            __syncwarp();
+            if (warp == 0) WIN_STAMP(k, 9);
+            if (lane == 0) tc::mbar_arrive(b_ee), tc::mbar_arrive(b_we);  // release: this warp no longer reads the stages
+        }
         if (t >= rows) continue;
         // ---- epilogue: head mean, summed biases, group mean, addend, activation, one store per chunk
         // (FMUL then FADD like v6's SASS, so the two kernels round identically)
@@ -1021,8 +1144,8 @@ k_gat_window(const __grid_constant__ WinParams P) {
         const float* __restrict__ addp = A.addend ? A.addend + i * A.ldadd : nullptr;
         float* __restrict__ outp = A.out + i * A.ldout;
 #pragma unroll
-        for (int kk = 0; kk < 2; ++kk) {
-            const int oc = (q + kk * 8) * 4;
+        for (int kk = 0; kk < kWinKC; ++kk) {
+            const int oc = (q + kk * kWinTPR) * 4;
             const float4 b4 = *reinterpret_cast<const float4*>(s_bias + oc);
             const float bv[4] = {b4.x, b4.y, b4.z, b4.w};
             float o[4];
@@ -1045,8 +1168,20 @@ k_gat_window(const __grid_constant__ WinParams P) {
             }
             st_vec<4>(outp + oc, o);
         }
+        }  // pass
+        if (warp == 0) WIN_STAMP(k, 10);
     }
 }
+
+#ifdef HG_WIN_TRACE
+}  // namespace
+}  // namespace hg
+extern "C" __attribute__((visibility("default"))) int hg_debug_win_trace(long long* host, int n) {
+    return static_cast<int>(cudaMemcpyFromSymbol(host, hg::g_win_trace, sizeof(long long) * n));
+}
+namespace hg {
+namespace {
+#endif
 
 constexpr int kWinFallback = 1;  // internal: the window kernel does not apply after all, use v6
 

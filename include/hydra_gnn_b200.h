@@ -68,7 +68,7 @@ HG_API int hg_last_cuda_error(void);
 /* 0 if no usable device / kernel image for it; otherwise SM count of the current device */
 HG_API int hg_device_sm_count(void);
 /* sizeof of ABI struct #which (0 plan_rel, 1 seg_args, 2 gat_rel, 3 gat_args, 4 lin_seg, 5 linear_args,
- * 6 gat_train_rel, 7 gat_train_args) */
+ * 6 gat_train_rel, 7 gat_train_args, 8 htree_split_args) */
 HG_API int hg_sizeof(int which);
 
 /* ------------------------------------------------------------------------------------
@@ -299,6 +299,53 @@ HG_API int hg_collate_offsets(int64_t* index, int64_t n_edges, const int64_t* ed
 
 /* batch[n] = g for ptr[g] <= n < ptr[g+1]: the `batch` vector of a collated node type (device int64). */
 HG_API int hg_batch_vector(int64_t* batch, int64_t n_nodes, const int64_t* ptr, int32_t n_graphs, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * hg_htree_split -- the integer half of `heterogeneous_htree_to_homogeneous` (mp3d_dataset.py:72-119) applied to every
+ * graph of a batched heterogeneous H-tree and collated (PyG `Batch.from_data_list`, base_training_job.py:164-178), as
+ * one pass on the device: per graph the node types in store order (PyG `to_homogeneous`), every node's homogeneous
+ * index (`place`), `node_type`, `batch`, the homogeneous `ptr`, `room_mask` / `object_mask`, and the edges of all relations
+ * -- per graph in relation store order, endpoints mapped to homogeneous ids -- split by endpoint type into
+ * init (source is a virtual node), pool (target is a virtual node, source is not) and tree (neither) lists.
+ * Integer work, bit-exact with the reference's per-graph conversion + collate (tests/golden/convert_golden.npz).
+ * Every relation's edge list must be grouped by graph in graph order (what collate produces); edges that are not, or
+ * whose endpoints lie outside their graph's node range, are counted in status[0] and their slots hold -1.
+ * Output sizes are host-known: N = sum of the types' node counts; the three edge lists hold the summed edge counts of
+ * the relations of each class.
+ * ---------------------------------------------------------------------------------- */
+#define HG_MAX_HTREE_TYPES 8
+enum { HG_EDGE_TREE = 0, HG_EDGE_INIT = 1, HG_EDGE_POOL = 2 };
+
+typedef struct hg_htree_type {
+    const int64_t* ptr;      /* [n_graphs + 1] first node of every graph within this type (PyG Batch `ptr`) */
+    int64_t n_nodes;         /* = ptr[n_graphs] */
+    int64_t* place;          /* out, may be NULL: [n_nodes] homogeneous index of every node of this type */
+    int32_t is_room_virtual; /* 1: nodes of this type set room_mask */
+    int32_t is_object_virtual;
+} hg_htree_type;
+
+typedef struct hg_htree_rel {
+    const int64_t* src;      /* [n_edges] ids within src_type (batched) */
+    const int64_t* dst;      /* [n_edges] ids within dst_type */
+    int64_t n_edges;
+    int32_t src_type, dst_type; /* indices into type[] */
+} hg_htree_rel;
+
+typedef struct hg_htree_split_args {
+    hg_htree_type type[HG_MAX_HTREE_TYPES];
+    hg_htree_rel rel[HG_MAX_PLAN_RELATIONS];
+    int32_t n_types, n_rel, n_graphs, reserved;
+    int64_t* ptr;            /* out [n_graphs + 1] homogeneous node offsets */
+    int64_t* node_type;      /* out [N] index into type[] */
+    int64_t* batch;          /* out [N] graph of every node */
+    uint8_t* room_mask;      /* out [N] 0 / 1 (torch.bool storage) */
+    uint8_t* object_mask;    /* out [N] */
+    int64_t* edges[3];       /* out, by HG_EDGE_*: [2, n_class] row-major (row 0 = sources), n_class = summed n_edges */
+    int32_t* status;         /* [1], zeroed by the call */
+} hg_htree_split_args;
+
+HG_API size_t hg_htree_split_workspace_bytes(const hg_htree_split_args* args_host);
+HG_API int hg_htree_split(const hg_htree_split_args* args_host, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ====================================================================================
  * Training step (BASELINE.json configs[4]; reference: base_training_job.py:203-219 --

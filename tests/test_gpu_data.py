@@ -89,6 +89,43 @@ def test_batched_htree_conversion_on_the_device_equals_the_per_graph_host_route(
         assert torch.equal(got[key].cpu(), want[key]), key
 
 
+def test_htree_split_kernel_matches_the_tensor_op_pass_and_the_fixture():
+    """hg_htree_split (the device form of mp3d_dataset.py:72-119 + collate): every integer output equals the tensor-op
+    pass on a 300-tree batch, the per-graph slices of a fixture batch equal tests/golden/convert_golden.npz (written by
+    the reference's own function), and edges out of graph order are counted, not misplaced."""
+    het = htree.generate_htree_batch(synth.synth_mp3d_batch(range(300)))
+    dev = _to_cuda(het)
+    got = convert.batched_htree_to_homogeneous(dev)
+    assert int(convert.last_split_status.item()) == 0
+    try:
+        convert.USE_SPLIT_KERNEL = False
+        want = convert.batched_htree_to_homogeneous(_to_cuda(het))
+    finally:
+        convert.USE_SPLIT_KERNEL = True
+    for key in ("x", "edge_index", "init_edge_index", "pool_edge_index", "room_mask", "object_mask", "node_type", "batch", "ptr"):
+        assert got[key].dtype == want[key].dtype and torch.equal(got[key], want[key]), key
+    assert got.num_graphs == want.num_graphs == 300
+    # reference-generated fixture: graph k of the collated batch, shifted back by its node offset
+    z = np.load(os.path.join(ROOT, "tests", "golden", "convert_golden.npz"))
+    trees = cases.load_htrees("htree_synth")[:3]
+    hom = convert.batched_htree_to_homogeneous(_to_cuda(Batch.from_data_list([clone_data(t) for t in trees])))
+    ptr = hom.ptr.cpu()
+    for k in range(3):
+        lo, hi = int(ptr[k]), int(ptr[k + 1])
+        for key in ("edge_index", "init_edge_index", "pool_edge_index"):
+            ei = hom[key].cpu()
+            mine = ei[:, (ei[0] >= lo) & (ei[0] < hi)] - lo
+            assert np.array_equal(mine.numpy(), z[f"htree{k}|{key}"]), (k, key)
+        for key in ("room_mask", "object_mask", "node_type"):
+            assert np.array_equal(hom[key].cpu()[lo:hi].numpy(), z[f"htree{k}|{key}"]), (k, key)
+    # a relation whose edges are not grouped by graph: counted in the status word
+    bad = _to_cuda(het)
+    et = bad.edge_types[0]
+    bad[et].edge_index = bad[et].edge_index.flip(1).contiguous()
+    convert.batched_htree_to_homogeneous(bad)
+    assert int(convert.last_split_status.item()) > 0
+
+
 # ------------------------------------------------------------------------------ a9 at the configs[2] size
 HT_DIMS = {"object": 306, "room": 6, "object-room": 6, "room-room": 6, "object_virtual": 306, "room_virtual": 6}
 _NT = {}

@@ -324,7 +324,7 @@ def test_gat_window_kernel_any_graph_and_any_hint():
     """Sources outside the staged window are gathered from global memory: random graphs (windows span everything),
     windows that do not cover the tile's sources at all, and hub tiles (edge pool overflow) all give the same bits."""
     g = torch.Generator().manual_seed(5)
-    H, C, n_src, n_dst = 3, 64, 4000, 1000 + 17
+    H, C, n_src, n_dst = 3, 64, 1500, 1000 + 17
     ei = torch.stack([torch.randint(0, n_src, (7000,), generator=g), torch.randint(0, n_dst, (7000,), generator=g)])
     hub = torch.stack([torch.randint(0, n_src, (700,), generator=g), torch.full((700,), 40)])  # tile 1: 700 edges > pool
     ei = torch.cat([ei, hub], dim=1)
