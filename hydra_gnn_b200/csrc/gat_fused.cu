@@ -467,7 +467,19 @@ int launch(GatParams& P, cudaStream_t stream) {
     // short grids (the rooms side of a scene-graph batch) take smaller tiles: more CTAs in flight per SM
     const int sms0 = sm_count() > 0 ? sm_count() : 148;
     P.tile_rows = kMaxTile;
-    while (P.tile_rows > HG_GAT_MIN_TILE && ceil_div<int64_t>(A.n_dst, P.tile_rows) < static_cast<int64_t>(sms0) * 6) P.tile_rows >>= 1;
+    // wide aggregate-first rows (5 float2 chunks per lane: the 306-d input layer) do long, latency-bound rows on a grid of
+    // ~1 wave: 16-row tiles balance the tail (measured 134 -> 115 us at 20,277 rows; 8-row tiles the same; a warp-per-row
+    // streaming kernel without shared memory 114-130 us: dropped).  HG_GAT_WIDE_TILE overrides, for A/B.
+    static const int wide_tile = [] {
+        const char* e = std::getenv("HG_GAT_WIDE_TILE");
+        const int v = e ? std::atoi(e) : 16;
+        return v == 8 || v == 16 || v == 32 ? v : 16;
+    }();
+    if (MODE == 2 && VEC == 2) {
+        if (ceil_div<int64_t>(A.n_dst, kMaxTile) < static_cast<int64_t>(sms0) * 6) P.tile_rows = wide_tile;
+    } else {
+        while (P.tile_rows > HG_GAT_MIN_TILE && ceil_div<int64_t>(A.n_dst, P.tile_rows) < static_cast<int64_t>(sms0) * 6) P.tile_rows >>= 1;
+    }
     P.hs = A.H <= 4 ? 4 : 8;
     P.n_bias = MODE == 2 ? A.H * P.f_count : P.f_count;
     // staging capacity: what the shared-memory budget holds, 128..2048 edges per relation per tile

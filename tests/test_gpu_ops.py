@@ -224,6 +224,41 @@ def test_gat_fused_group_mean_and_aggregate_first():
     assert_close(got, torch.relu(want + 1.0), "group mean", check_argmax=False)
 
 
+@pytest.mark.parametrize("H,C,pad", [(3, 306, 0), (3, 306, 2), (1, 306, 0), (4, 256, 0), (2, 130, 0), (3, 384, 4)])
+def test_gat_aggregate_first_wide_rows(H, C, pad):
+    """Aggregate-first over wide source rows (objects -> rooms at the 306-d input layer; float2 / float4 chunks, up to 5
+    per lane): rows longer than a tile's share, empty rows, strided sources, a bias, edge logits."""
+    g = torch.Generator().manual_seed(7 * H + C)
+    n_src, n_dst = 3000, 257
+    deg = torch.randint(0, 25, (n_dst,), generator=g)
+    deg[5], deg[6], deg[100] = 0, 77, 33
+    dst = torch.repeat_interleave(torch.arange(n_dst), deg)
+    E = int(dst.numel())
+    ei = torch.stack([torch.randint(0, n_src, (E,), generator=g), dst])[:, torch.randperm(E, generator=g)]
+    xb = torch.randn(n_src, C + pad, generator=g)
+    x = xb[:, :C]
+    a_s, a_d = torch.randn(n_src, H, generator=g), torch.randn(n_dst, H, generator=g)
+    (csr,), _ = ops.build_csr([CSRSpec(ei.cuda(), n_src, n_dst, want_perm=True)])
+    want, _ = gat_reference(x, a_s, a_d, ei, n_dst, H, C, True, src_shared=True)
+    rel = ops.GatRelation(xb.cuda()[:, :C], a_s.cuda(), a_d.cuda(), csr)
+    got = ops.gat_fused([rel], n_dst, H, C, True, src_shared=True)
+    assert_close(got, want, f"aggregate-first H={H} C={C}", check_argmax=False)
+    assert float(got[5].abs().max()) == 0.0  # a row without edges
+    bias = torch.randn(H * C, generator=g)
+    rel_b = ops.GatRelation(xb.cuda()[:, :C], a_s.cuda(), a_d.cuda(), csr, bias.cuda())
+    assert_close(ops.gat_fused([rel_b], n_dst, H, C, True, src_shared=True), want + bias.double(), "with bias", check_argmax=False)
+    # GAT_edge: per-edge logits in CSR order
+    a_e = torch.randn(csr.cap, H, generator=g)
+    perm = csr.perm.cpu().long()[:E]
+    j, i = ei[0][perm], ei[1][perm]
+    sc = torch.nn.functional.leaky_relu(a_s.double()[j] + a_d.double()[i] + a_e.double()[:E], 0.2)
+    w = ou.softmax(sc, i, None, n_dst)
+    want_e = ou.scatter(w.unsqueeze(-1) * x.double()[j].unsqueeze(1), i, 0, dim_size=n_dst, reduce="sum").reshape(n_dst, H * C)
+    rel_e = ops.GatRelation(xb.cuda()[:, :C], a_s.cuda(), a_d.cuda(), csr, None, a_e.cuda())
+    assert_close(ops.gat_fused([rel_e], n_dst, H, C, True, src_shared=True), want_e, "aggregate-first + edge logits",
+                 check_argmax=False)
+
+
 def test_gat_fused_hub_rows_take_the_streaming_path():
     g = torch.Generator().manual_seed(12)
     n_src, n_dst, H, C = 5000, 70, 3, 64
