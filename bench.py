@@ -127,7 +127,8 @@ def kernel_key(name, m):
     if name == "hg_linear":
         return f"hg_linear[M={m['M']},N={m['N']},K={'+'.join(map(str, m['K']))},{m['precision']}]"
     if name == "hg_gat_fused":
-        return f"hg_gat_fused[n_dst={m['n_dst']},H={m['H']},C={m['C']},rels={len(m['rels'])}]"
+        agg = ",aggregate-first" if m.get("src_width", m["H"] * m["C"]) != m["H"] * m["C"] else ""
+        return f"hg_gat_fused[n_dst={m['n_dst']},H={m['H']},C={m['C']},rels={len(m['rels'])}{agg}]"
     if name == "hg_seg_reduce":
         return f"hg_seg_reduce[n_out={m['n_out']},F={m['F']}]"
     return name
@@ -299,6 +300,8 @@ def run_ours(args, rank, world, local_rank):
 
     n_rooms = host["rooms"].x.size(0)
     gather = LogitGather(26).prepare(n_rooms, dev, slots=2) if world > 1 else None
+    if os.environ.get("HG_BENCH_NO_GATHER"):  # diagnosis only: N independent replicas, no collective
+        gather = None
 
     def step(data, slot=0):
         # the only collective on the path is the gather of the room logits (config 4).  The step stages its logits in
@@ -360,16 +363,19 @@ def run_ours(args, rank, world, local_rank):
         run(i & 1)
     drain()
     fence()
-    with ClockSampler(local_rank) as clocks:
-        marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
-        last = torch.cuda.Event(enable_timing=True)
-        marks[0].record()
-        for i in range(args.steps):
-            run(i & 1)  # the two slots hold the same batch; alternating them lets gather i overlap forward i + 1
-            marks[i + 1].record()  # one event between back-to-back replays: per-step times for median / p10 / p90
-        drain()  # every gather has landed before the clock stops
-        last.record()
-        fence()
+    # clocks / throttle reasons are sampled (nvidia-smi, every 100 ms) from here to the end of the e2e arm: the K replays of
+    # the value arm alone last ~16 ms, less than one sampling period
+    clocks = ClockSampler(local_rank)
+    clocks.__enter__()
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    last = torch.cuda.Event(enable_timing=True)
+    marks[0].record()
+    for i in range(args.steps):
+        run(i & 1)  # the two slots hold the same batch; alternating them lets gather i overlap forward i + 1
+        marks[i + 1].record()  # one event between back-to-back replays: per-step times for median / p10 / p90
+    drain()  # every gather has landed before the clock stops
+    last.record()
+    fence()
     ms = marks[0].elapsed_time(last)
     per_step = sorted(marks[i].elapsed_time(marks[i + 1]) for i in range(args.steps))
 
@@ -448,6 +454,7 @@ def run_ours(args, rank, world, local_rank):
     f1.record()
     fence()
     ms_e2e = f0.elapsed_time(f1)
+    clocks.__exit__(None, None, None)
 
     if world > 1:  # max over ranks, measured on the device
         t = torch.tensor([ms, ms_e2e, ms_eager], device=dev, dtype=torch.float64)
@@ -462,6 +469,13 @@ def run_ours(args, rank, world, local_rank):
     roof["timing"] = ("eager pass of the same K steps, one CUDA-event pair per launch, launches serialised on one stream "
                       "(the value arm replays CUDA graphs with the plan and the rooms-side chain on side streams)")
     total_graphs = G * world
+    if world == 1:
+        collective = "none"
+    elif gather is None:
+        collective = "none (HG_BENCH_NO_GATHER: independent replicas, diagnosis only)"
+    else:
+        collective = ("copy-engine pulls of the room logits over NVLink peer memory" if gather._peer is not None
+                      else "all_gather_into_tensor(room logits)") + ", on a side stream, overlapping the next step"
     line = {
         "metric": METRIC, "value": total_graphs * args.steps / (ms / 1e3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
@@ -473,7 +487,7 @@ def run_ours(args, rank, world, local_rank):
                    "edges_objects_to_rooms": int(host["objects", "objects_to_rooms", "rooms"].edge_index.size(1)),
                    "l2": "inputs larger than L2 (object features 297 MB + ~190 MB of projections per layer vs 126 MB L2)",
                    "projection_precision": ops.DEFAULT_PRECISION, "cuda_graph": use_graph,
-                   "collective": "all_gather_into_tensor(room logits), on a side stream, overlapping the next step" if world > 1 else "none"},
+                   "collective": collective},
         "step_ms": {"median": statistics.median(per_step), "p10": per_step[len(per_step) // 10],
                     "p90": per_step[min(len(per_step) - 1, (9 * len(per_step)) // 10)],
                     "eager_ms_per_step": ms_eager / args.steps,

@@ -7,6 +7,7 @@ process group's backend -- NCCL over NVLink on the GPU box, gloo in the CPU test
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional, Tuple
 
 import torch
@@ -21,6 +22,9 @@ def shard_range(n_graphs: int, rank: int, world: int) -> Tuple[int, int]:
     base, rem = divmod(n_graphs, world)
     lo = rank * base + min(rank, rem)
     return lo, lo + base + (1 if rank < rem else 0)
+
+
+USE_PEER_COPIES = os.environ.get("HG_PEER_GATHER", "0") == "1"  # opt-in: pipelined gather by copy-engine pulls over symmetric (peer) memory instead of the NCCL kernel (measured on 8 x B200: 0.887-0.896 vs 0.878-0.881 ms per step, so NCCL stays the default)
 
 
 class LogitGather:
@@ -52,12 +56,38 @@ class LogitGather:
         self._pads = [torch.zeros(self.max_rows, self.width, dtype=torch.float32, device=device) for _ in range(slots)]
         self._bufs = [torch.empty(self.world * self.max_rows, self.width, dtype=torch.float32, device=device)
                       for _ in range(slots)]
+        self._peer = None
+        if device.type == "cuda" and slots > 1 and self.world > 1 and USE_PEER_COPIES:
+            self._peer = self._peer_setup(device, slots)
         if device.type == "cuda":
             self._side = torch.cuda.Stream(device)
             self._done = [torch.cuda.Event() for _ in range(slots)]
             self._staged = [torch.cuda.Event() for _ in range(slots)]
         self._last = 0
         return self
+
+    def _peer_setup(self, device, slots):
+        """Pipelined form over NVLink peer memory: the padded staging buffers live in symmetric memory, and the gather is
+        `barrier -> one copy-engine copy per peer (pull) -> barrier` on the side stream -- no SM is taken from the
+        persistent one-CTA-per-SM kernels of the forward it overlaps (an NCCL all-gather kernel occupies SMs for the
+        whole exchange).  Returns None (NCCL is used) when symmetric memory cannot be set up on this system."""
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+
+            group = self.group if self.group is not None else dist.group.WORLD
+            pads, handles = [], []
+            for _ in range(slots):
+                t = symm_mem.empty(self.max_rows, self.width, dtype=torch.float32, device=device)
+                t.zero_()
+                handles.append(symm_mem.rendezvous(t, group.group_name))
+                pads.append(t)
+            self._pads = pads
+            return handles
+        except Exception as e:  # noqa: BLE001 -- any failure here means "no peer memory": fall back to NCCL
+            import warnings
+
+            warnings.warn(f"LogitGather: symmetric memory unavailable ({type(e).__name__}: {e}); using NCCL all_gather")
+            return None
 
     def __call__(self, logits: torch.Tensor) -> torch.Tensor:
         self.stage(logits, 0)
@@ -77,7 +107,17 @@ class LogitGather:
         self._staged[slot].record(cur)
         with torch.cuda.stream(self._side):
             self._side.wait_event(self._staged[slot])
-            dist.all_gather_into_tensor(self._bufs[slot], self._pads[slot], group=self.group)
+            if self._peer is not None:
+                h = self._peer[slot]
+                shape = (self.max_rows, self.width)
+                chunks = self._bufs[slot].view(self.world, self.max_rows, self.width)
+                h.barrier()  # every rank has staged this slot
+                for step in range(self.world):
+                    r = (h.rank - step) % self.world
+                    chunks[r].copy_(h.get_buffer(r, shape, torch.float32))  # device-to-device copy engine, pull over NVLink
+                h.barrier()  # every rank has read this rank's slot: it may be staged again
+            else:
+                dist.all_gather_into_tensor(self._bufs[slot], self._pads[slot], group=self.group)
             self._done[slot].record(self._side)
         self._last = slot
 

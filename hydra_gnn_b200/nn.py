@@ -267,6 +267,7 @@ def _pad4(n: int) -> int:
     return (n + 3) // 4 * 4
 
 
+AGG_FIRST_WIDE_MIN_ROWS = 32768  # source rows from which the wide aggregate-first form (raw rows wider than the projection) is used
 AGG_FIRST_RATIO = 4  # a relation aggregates first when it has >= 4x fewer destinations than sources
 AGG_FIRST_WIDTH = float(os.environ.get("HG_AGG_FIRST_WIDTH", "1.6"))  # ... and raw rows at most this x the projected width
 
@@ -287,8 +288,10 @@ def _gat_modes(convs, rels: Sequence[EdgeType], x: Dict[str, Tensor], group: str
         width, proj = x[et[0]].size(1), convs[et].heads * convs[et].out_channels
         if x[et[2]].size(0) * AGG_FIRST_RATIO > x[et[0]].size(0):
             return False
+        # the wide form pays through the smaller big GEMM: only for batches (at batch 1 its extra K = H * width post-projection
+        # is 29 serial k-blocks of latency: 285 vs 184 us per forward)
         return width <= proj or (width <= AGG_FIRST_WIDTH * proj and width % 2 == 0 and width <= 320
-                                 and convs[et].heads <= 4)
+                                 and convs[et].heads <= 4 and x[et[0]].size(0) >= AGG_FIRST_WIDE_MIN_ROWS)
 
     return tuple(agg_first(et) for et in rels)
 

@@ -334,7 +334,7 @@ def _fp64_gat(rels, n_dst, H, C):
 
 
 @pytest.mark.parametrize("H", [1, 2, 3, 4])
-@pytest.mark.parametrize("n_graphs,a_edge", [(37, False), (300, False), (64, True)])
+@pytest.mark.parametrize("n_graphs,a_edge", [(37, False), (300, False), (64, True), (1200, False), (1150, True)])
 def test_gat_window_kernel_matches_fp64_and_the_global_gather_kernel_bitwise(H, n_graphs, a_edge):
     g = torch.Generator().manual_seed(100 * H + n_graphs)
     rels, n_o = _scene_batch_relations(range(n_graphs), H, g, a_edge)
@@ -343,12 +343,20 @@ def test_gat_window_kernel_matches_fp64_and_the_global_gather_kernel_bitwise(H, 
     got = ops.gat_fused(rels, n_o, H, 64, False, act="elu", addend=addend)
     assert_close(got, torch.nn.functional.elu(_fp64_gat(rels, n_o, H, 64) + addend.cpu().double()), f"window H={H}",
                  check_argmax=False)
+    # <= 65,536 rows: the small-destination row kernel; more: the window kernel (n_graphs >= 1150).  Either must equal
+    # the v6 tile kernel bit for bit (same accumulation order, same rounding); asking for the saved softmax weights
+    # forces v6, and so does dropping the window hint above 65,536 rows
+    for r in rels:
+        r.alpha_out = torch.empty(r.csr.cap, H, device="cuda")
+    base = ops.gat_fused(rels, n_o, H, 64, False, act="elu", addend=addend)
+    for r in rels:
+        r.alpha_out = None
+    assert torch.equal(got, base)
     try:
         ops.USE_TILE_WINDOW = False
-        base = ops.gat_fused(rels, n_o, H, 64, False, act="elu", addend=addend)
+        assert torch.equal(ops.gat_fused(rels, n_o, H, 64, False, act="elu", addend=addend), base)
     finally:
         ops.USE_TILE_WINDOW = True
-    assert torch.equal(got, base)  # same accumulation order: bit-identical
     # one relation only, group mean over a repeated relation, ReLU
     got1 = ops.gat_fused([rels[0], rels[0], rels[1]], n_o, H, 64, False, group="mean", act="relu")
     want1 = torch.relu((2 * _fp64_gat(rels[:1], n_o, H, 64) + _fp64_gat(rels[1:], n_o, H, 64)) / 3)
@@ -359,8 +367,8 @@ def test_gat_window_kernel_any_graph_and_any_hint():
     """Sources outside the staged window are gathered from global memory: random graphs (windows span everything),
     windows that do not cover the tile's sources at all, and hub tiles (edge pool overflow) all give the same bits."""
     g = torch.Generator().manual_seed(5)
-    H, C, n_src, n_dst = 3, 64, 1500, 1000 + 17
-    ei = torch.stack([torch.randint(0, n_src, (7000,), generator=g), torch.randint(0, n_dst, (7000,), generator=g)])
+    H, C, n_src, n_dst = 3, 64, 100000, 70000 + 17
+    ei = torch.stack([torch.randint(0, n_src, (400000,), generator=g), torch.randint(0, n_dst, (400000,), generator=g)])
     hub = torch.stack([torch.randint(0, n_src, (700,), generator=g), torch.full((700,), 40)])  # tile 1: 700 edges > pool
     ei = torch.cat([ei, hub], dim=1)
     (csr,), _ = ops.build_csr([CSRSpec(ei.cuda(), n_src, n_dst, False, want_window=True)])
