@@ -1292,11 +1292,12 @@ int dispatch_wide_shared(GatParams& P, cudaStream_t stream) {
 // ---------------------------------------------------------------------------------------------------
 constexpr int kRowsKernelMax = 65536;
 
-// SHARED = aggregate-first form: xs is [n_src, 64] (one row for all heads), out[i, h, :] = sum_e w_eh xs[j, :], width H * 64.
-template <int HT, bool SHARED>
+// VEC = 4 covers C <= 64 in multiples of 4 (the hidden layers: C = 64), VEC = 2 even C <= 32 (the output layer: C = 26):
+// thread q of a row owns chunks q and q + 8 of the C / VEC vector chunks.
+template <int HT, int VEC>
 __global__ void __launch_bounds__(256) k_gat_rows(const __grid_constant__ GatParams P) {
     const hg_gat_args& A = P.a;
-    const int R = A.n_rel;
+    const int R = A.n_rel, C = A.C;
     const int tid = threadIdx.x, lane = tid & 31, q = tid & 7;
     const int64_t i = static_cast<int64_t>(blockIdx.x) * 32 + (tid >> 3);
     const bool valid = i < A.n_dst;
@@ -1309,25 +1310,17 @@ __global__ void __launch_bounds__(256) k_gat_rows(const __grid_constant__ GatPar
     if (__any_sync(0xffffffffu, maxdeg > 64)) {  // warp-uniform
         for (int rr = 0; rr < 4; ++rr) {
             const int64_t ii = static_cast<int64_t>(blockIdx.x) * 32 + (tid >> 5) * 4 + rr;
-            if (ii < A.n_dst) {
-                if (SHARED) {
-                    for (int h = 0; h < HT; ++h) slow_row<4>(P, ii, lane, h * kWinC, kWinC);
-                } else {
-                    slow_row<4>(P, ii, lane, 0, kWinC);
-                }
-            }
+            if (ii < A.n_dst) slow_row<VEC>(P, ii, lane, 0, C);
         }
         return;
     }
     if (!valid) return;
-    constexpr int NA = SHARED ? HT : 1;  // accumulator sets: one per head (aggregate-first) or one (head mean)
-    float acc[NA][2][4];
+    const bool live[2] = {q * VEC < C, (q + 8) * VEC < C};
+    float acc[2][VEC];
 #pragma unroll
-    for (int a = 0; a < NA; ++a)
+    for (int k = 0; k < 2; ++k)
 #pragma unroll
-        for (int k = 0; k < 2; ++k)
-#pragma unroll
-            for (int v = 0; v < 4; ++v) acc[a][k][v] = 0.f;
+        for (int v = 0; v < VEC; ++v) acc[k][v] = 0.f;
     for (int r = 0; r < R; ++r) {
         const hg_gat_rel& Rl = A.rel[r];
         const int32_t beg = __ldg(Rl.rowptr + i), end = __ldg(Rl.rowptr + i + 1);
@@ -1357,19 +1350,24 @@ __global__ void __launch_bounds__(256) k_gat_rows(const __grid_constant__ GatPar
         }
 #pragma unroll
         for (int h = 0; h < HT; ++h) inv[h] = 1.f / (l[h] + 1e-16f);
-        const char* xg = reinterpret_cast<const char*>(Rl.xs) + q * 16;
-        const uint32_t pitch = static_cast<uint32_t>(Rl.ldxs) * 4u;
+        const float* __restrict__ xg = Rl.xs + q * VEC;
+        const int64_t ld = Rl.ldxs;
 #pragma unroll 2
         for (int32_t e = beg; e < end; ++e) {
             const int32_t j = __ldg(Rl.col + e);
-            const char* row = xg + static_cast<uint64_t>(static_cast<uint32_t>(j)) * pitch;
-            constexpr int NV = SHARED ? 1 : HT;  // source slices read per edge
-            float4 val[NV][2];
+            const float* __restrict__ row = xg + static_cast<int64_t>(j) * ld;
+            float val[HT][2][VEC];
 #pragma unroll
-            for (int hh = 0; hh < NV; ++hh) {
-                val[hh][0] = __ldg(reinterpret_cast<const float4*>(row + hh * (kWinC * 4)));
-                val[hh][1] = __ldg(reinterpret_cast<const float4*>(row + hh * (kWinC * 4) + 128));
-            }
+            for (int hh = 0; hh < HT; ++hh)
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    if (live[k]) {
+                        ldg_vec<VEC>(row + hh * C + 8 * k * VEC, val[hh][k]);
+                    } else {
+#pragma unroll
+                        for (int v = 0; v < VEC; ++v) val[hh][k][v] = 0.f;
+                    }
+                }
             float sc[HT], wv[HT];
             score(e, j, sc);
 #pragma unroll
@@ -1377,61 +1375,57 @@ __global__ void __launch_bounds__(256) k_gat_rows(const __grid_constant__ GatPar
 #pragma unroll
             for (int hh = 0; hh < HT; ++hh)
 #pragma unroll
-                for (int k = 0; k < 2; ++k) {
-                    const float4 x4 = val[SHARED ? 0 : hh][k];
-                    float (&ac)[4] = acc[SHARED ? hh : 0][k];
-                    ac[0] = fmaf(wv[hh], x4.x, ac[0]);
-                    ac[1] = fmaf(wv[hh], x4.y, ac[1]);
-                    ac[2] = fmaf(wv[hh], x4.z, ac[2]);
-                    ac[3] = fmaf(wv[hh], x4.w, ac[3]);
-                }
+                for (int k = 0; k < 2; ++k)
+#pragma unroll
+                    for (int v = 0; v < VEC; ++v) acc[k][v] = fmaf(wv[hh], val[hh][k][v], acc[k][v]);
         }
     }
     const float gscale = (A.group == HG_GROUP_MEAN) ? 1.f / static_cast<float>(R) : 1.f;
-    const float hscale = SHARED ? 1.f : 1.f / static_cast<float>(HT);
+    const float hscale = 1.f / static_cast<float>(HT);
     const float* __restrict__ addp = A.addend ? A.addend + i * A.ldadd : nullptr;
     float* __restrict__ outp = A.out + i * A.ldout;
 #pragma unroll
-    for (int a = 0; a < NA; ++a)
-#pragma unroll
     for (int k = 0; k < 2; ++k) {
-        const int oc = a * kWinC + (q + 8 * k) * 4;
-        float bs[4] = {0.f, 0.f, 0.f, 0.f};  // summed biases of the relations, in relation order (as the tile kernels stage them)
+        if (!live[k]) continue;
+        const int oc = (q + 8 * k) * VEC;
+        float bs[VEC];  // summed biases of the relations, in relation order (as the tile kernels stage them)
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) bs[v] = 0.f;
         for (int r = 0; r < R; ++r)
             if (A.rel[r].bias) {
-                float b[4];
-                ldg_vec<4>(A.rel[r].bias + oc, b);
+                float b[VEC];
+                ldg_vec<VEC>(A.rel[r].bias + oc, b);
 #pragma unroll
-                for (int v = 0; v < 4; ++v) bs[v] += b[v];
+                for (int v = 0; v < VEC; ++v) bs[v] += b[v];
             }
-        float o[4];
+        float o[VEC];
 #pragma unroll
-        for (int v = 0; v < 4; ++v) o[v] = __fmul_rn(__fadd_rn(__fmul_rn(acc[a][k][v], hscale), bs[v]), gscale);
+        for (int v = 0; v < VEC; ++v) o[v] = __fmul_rn(__fadd_rn(__fmul_rn(acc[k][v], hscale), bs[v]), gscale);
         if (addp) {
-            float av[4];
-            ldg_vec<4>(addp + oc, av);
+            float av[VEC];
+            ldg_vec<VEC>(addp + oc, av);
 #pragma unroll
-            for (int v = 0; v < 4; ++v) o[v] = __fadd_rn(o[v], av[v]);
+            for (int v = 0; v < VEC; ++v) o[v] = __fadd_rn(o[v], av[v]);
         }
         if (A.act == HG_ACT_RELU) {
 #pragma unroll
-            for (int v = 0; v < 4; ++v) o[v] = fmaxf(o[v], 0.f);
+            for (int v = 0; v < VEC; ++v) o[v] = fmaxf(o[v], 0.f);
         } else if (A.act == HG_ACT_ELU) {
 #pragma unroll
-            for (int v = 0; v < 4; ++v) o[v] = o[v] > 0.f ? o[v] : ex2_ftz(__fmul_rn(o[v], 1.4426950408889634f)) - 1.f;
+            for (int v = 0; v < VEC; ++v) o[v] = o[v] > 0.f ? o[v] : ex2_ftz(__fmul_rn(o[v], 1.4426950408889634f)) - 1.f;
         }
-        st_vec<4>(outp + oc, o);
+        st_vec<VEC>(outp + oc, o);
     }
 }
 
-template <bool SHARED>
+template <int VEC>
 int launch_rows(GatParams& P, cudaStream_t stream) {
     const unsigned grid = static_cast<unsigned>(ceil_div<int64_t>(P.a.n_dst, 32));
     switch (P.a.H) {
-        case 1: k_gat_rows<1, SHARED><<<grid, 256, 0, stream>>>(P); break;
-        case 2: k_gat_rows<2, SHARED><<<grid, 256, 0, stream>>>(P); break;
-        case 3: k_gat_rows<3, SHARED><<<grid, 256, 0, stream>>>(P); break;
-        default: k_gat_rows<4, SHARED><<<grid, 256, 0, stream>>>(P); break;
+        case 1: k_gat_rows<1, VEC><<<grid, 256, 0, stream>>>(P); break;
+        case 2: k_gat_rows<2, VEC><<<grid, 256, 0, stream>>>(P); break;
+        case 3: k_gat_rows<3, VEC><<<grid, 256, 0, stream>>>(P); break;
+        default: k_gat_rows<4, VEC><<<grid, 256, 0, stream>>>(P); break;
     }
     return check_launch();
 }
@@ -1481,19 +1475,27 @@ extern "C" int hg_gat_fused(const hg_gat_args* a, void* stream_) {
         return true;
     };
     const int vec = ok(4) ? 4 : (ok(2) ? 2 : 1);
+    // small head-mean destination sets: the row kernel (an aggregate-first form of it -- ~12 edges of DRAM-resident source rows
+    // per row -- measured 56 us against 29 us for the tile kernel and was dropped)
+    if (head_mean && a->H <= 4 && a->n_dst <= kRowsKernelMax && a->dropout_p == 0.f &&
+        ((vec == 4 && a->C <= 64) || (vec >= 2 && a->C % 2 == 0 && a->C <= 32))) {
+        bool plain = true;
+        for (int r = 0; r < a->n_rel; ++r) plain = plain && a->alpha_saved[r] == nullptr;
+        if (plain) {
+            GatParams P;
+            P.a = *a;
+            P.f_begin = 0;
+            P.f_count = a->C;
+            P.wrows = 0;
+            return (vec == 4 && a->C % 4 == 0) ? launch_rows<4>(P, stream) : launch_rows<2>(P, stream);
+        }
+    }
     if (vec == 4 && a->H <= 4 && ((head_mean && a->C <= 128) || (a->src_shared && a->C <= 256))) {
         GatParams P;
         P.a = *a;
         P.f_begin = 0;
         P.f_count = a->C;
         P.wrows = 0;
-        // (the aggregate-first instantiation of the row kernel, SHARED = true, is NOT used: its rows have ~12 edges of
-        // DRAM-resident source rows and the per-lane edge walk measured 56 us against 29 us for the tile kernel)
-        if (head_mean && a->C == kWinC && a->n_dst <= kRowsKernelMax && a->dropout_p == 0.f) {
-            bool plain = true;
-            for (int r = 0; r < a->n_rel; ++r) plain = plain && a->alpha_saved[r] == nullptr;
-            if (plain) return launch_rows<false>(P, stream);
-        }
         if (head_mean && a->C == kWinC && a->n_rel <= kWinMaxRel && a->dropout_p == 0.f && window_enabled()) {
             bool hint = true, plain = true;  // the caller gives windows only where they are short (ops.gat_fused)
             for (int r = 0; r < a->n_rel; ++r) {

@@ -363,6 +363,37 @@ def test_gat_window_kernel_matches_fp64_and_the_global_gather_kernel_bitwise(H, 
     assert_close(got1, want1, "window, 3 relations, group mean", check_argmax=False)
 
 
+@pytest.mark.parametrize("H,C", [(3, 26), (3, 64), (1, 32), (4, 12), (2, 60)])
+def test_gat_row_kernel_small_destination_sets(H, C):
+    """<= 65,536 destination rows, head-mean, C <= 64: the row kernel (8 threads own a row; the output layer's C = 26 takes
+    float2 chunks).  Against fp64, and bit for bit against the tile kernel (asking for the saved weights forces it): two
+    relations, bias, addend, ELU, an empty row and a 100-edge row (warp-per-row path)."""
+    g = torch.Generator().manual_seed(31 * H + C)
+    n_dst, rels, want = 3001, [], 0
+    for n_src, E in ((3001, 9000), (411, 3001)):
+        dst = torch.randint(0, n_dst, (E,), generator=g)
+        dst[dst == 7] = 8          # row 7 has no edges
+        dst[:100] = 1500           # row 1500: 100 edges from this relation
+        ei = torch.stack([torch.randint(0, n_src, (E,), generator=g), dst])
+        xs = torch.randn(n_src, H * C + 4, generator=g)
+        a_s, a_d = torch.randn(n_src, H, generator=g), torch.randn(n_dst, H, generator=g)
+        bias = torch.randn(C, generator=g)
+        (csr,), _ = ops.build_csr([CSRSpec(ei.cuda(), n_src, n_dst, want_perm=True)])
+        rels.append(ops.GatRelation(xs.cuda()[:, :H * C], a_s.cuda(), a_d.cuda(), csr, bias.cuda()))
+        o, _ = gat_reference(xs[:, :H * C], a_s, a_d, ei, n_dst, H, C, False)
+        want = want + o + bias.double()
+    addend = torch.randn(n_dst, C, generator=g)
+    got = ops.gat_fused(rels, n_dst, H, C, False, act="elu", addend=addend.cuda())
+    assert_close(got, torch.nn.functional.elu(want + addend.double()), f"row kernel H={H} C={C}", check_argmax=False)
+    for r in rels:
+        r.alpha_out = torch.empty(r.csr.cap, H, device="cuda")
+    tile = ops.gat_fused(rels, n_dst, H, C, False, act="elu", addend=addend.cuda())
+    rows_1500 = torch.zeros(n_dst, dtype=torch.bool)
+    rows_1500[1500 // 4 * 4: 1500 // 4 * 4 + 4] = True  # the warp holding the long row takes the warp-per-row path
+    assert torch.equal(got.cpu()[~rows_1500], tile.cpu()[~rows_1500])
+    assert_close(got.cpu()[rows_1500], tile.cpu()[rows_1500], "long row", check_argmax=False)
+
+
 def test_gat_window_kernel_any_graph_and_any_hint():
     """Sources outside the staged window are gathered from global memory: random graphs (windows span everything),
     windows that do not cover the tile's sources at all, and hub tiles (edge pool overflow) all give the same bits."""
