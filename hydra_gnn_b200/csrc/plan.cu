@@ -1,10 +1,15 @@
-// K1 -- graph plan: CSR-by-destination for up to 16 relations in six launches.
+// K1 -- graph plan: CSR-by-destination for up to 16 relations in four launches.
 //
 // Integer work, bit-exact with a stable sort by destination of the (self-loop adjusted) edge
 // list.  Stability without a radix sort: count -> scan -> unordered atomic fill of edge ids
 // -> every edge ranks itself inside its (short) row.  All relations of a batch share each
 // launch (blockIdx.y = relation) so a 4-relation DSG plan or a 15-relation H-tree plan costs
 // the same number of launches.  HBM-bound: 16 B/edge in, 8 B/edge + 4 B/row out.
+//   k_count  histogram of the kept edges + (for relations that ask for tile windows) the min / max source row of
+//            every 32-row destination tile, warp-aggregated (match_any + reduce) before the two atomics
+//   k_scan   ONE pass: chained scan with decoupled look-back (ticketed tiles of 2048 rows, a warp looks back 32
+//            predecessors at a time); writes rowptr, the GCN degree^-1/2, the tile windows, clears the cursors
+//   k_fill   unordered atomic fill of edge ids;   k_rank   stable rank inside the row, col / perm
 #include <mutex>
 
 #include "hg_common.cuh"
@@ -28,10 +33,11 @@ struct RelDev {
     float* inv_sqrt_deg;
     int32_t* cnt;      // [n_dst]  histogram, then fill cursor
     int32_t* ids_tmp;  // [E + n_loop] edge ids, row-bucketed, unordered inside a row
-    int32_t* bsum;     // [n_scan_blocks]
+    unsigned long long* scan_state;  // [n_scan_blocks] (flag << 32 | value) + [1] ticket counter; zeroed by the plan
     int32_t n_scan_blocks;
     int32_t pad;
     int32_t* tile_win; // [ceil(n_dst / HG_TILE_ROWS)][2] or NULL
+    int32_t* tw_tmp;   // [ceil(n_dst / HG_TILE_ROWS)][2] {max(INT32_MAX - src), max(src + 1)}, 0 = no edge; zeroed by the plan
 };
 
 struct PlanParams {
@@ -53,14 +59,26 @@ __device__ __forceinline__ bool edge_kept(const RelDev& R, int64_t e, int32_t& s
 __global__ void __launch_bounds__(kEdgeThreads) k_count(const __grid_constant__ PlanParams P) {
     const RelDev& R = P.r[blockIdx.y];
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-    for (int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; e < R.n_edges; e += stride) {
-        int32_t s, d;
-        if (edge_kept(R, e, s, d, P.status)) atomicAdd(&R.cnt[d], 1);
+    const int lane = threadIdx.x & 31;
+    // warp-uniform trip count: the tile-window part uses warp collectives
+    for (int64_t b = static_cast<int64_t>(blockIdx.x) * blockDim.x + (threadIdx.x - lane); b < R.n_edges; b += stride) {
+        const int64_t e = b + lane;
+        int32_t s = 0, d = 0;
+        const bool kept = e < R.n_edges && edge_kept(R, e, s, d, P.status);
+        if (kept) atomicAdd(&R.cnt[d], 1);
+        if (R.tw_tmp) {  // edges of one graph are neighbours in the list: a warp usually touches one or two tiles
+            const unsigned live = __ballot_sync(0xffffffffu, kept);
+            if (kept) {
+                const int32_t tile = d / HG_TILE_ROWS;
+                const unsigned grp = __match_any_sync(live, tile);
+                const int32_t lo = __reduce_min_sync(grp, s), hi = __reduce_max_sync(grp, s);
+                if (lane == __ffs(grp) - 1) {
+                    atomicMax(&R.tw_tmp[2 * tile], INT32_MAX - lo);
+                    atomicMax(&R.tw_tmp[2 * tile + 1], hi + 1);
+                }
+            }
+        }
     }
-}
-
-__device__ __forceinline__ int32_t row_count(const RelDev& R, int32_t k) {
-    return k < R.n_dst ? R.cnt[k] + (k < R.n_loop ? 1 : 0) : 0;
 }
 
 // Block-wide exclusive scan of one int per thread; returns the exclusive prefix, total in `total`.
@@ -91,55 +109,104 @@ __device__ __forceinline__ int32_t block_exclusive_scan(int32_t v, int32_t& tota
     return warp_off + inc - v;
 }
 
-__global__ void __launch_bounds__(kScanThreads) k_scan_a(const __grid_constant__ PlanParams P) {
-    const RelDev& R = P.r[blockIdx.y];
-    if (static_cast<int>(blockIdx.x) >= R.n_scan_blocks) return;
-    const int32_t base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
-    int32_t v = 0;
+constexpr unsigned long long kAggregate = 1ull << 32, kInclusive = 2ull << 32;
+
+__device__ __forceinline__ unsigned long long ld_state(const unsigned long long* p) {
+    return *reinterpret_cast<const volatile unsigned long long*>(p);
+}
+__device__ __forceinline__ void st_state(unsigned long long* p, unsigned long long v) {
+    *reinterpret_cast<volatile unsigned long long*>(p) = v;
+}
+
+// Sum of the totals of tiles [0, tile): warp 0 walks back 32 predecessors at a time until it meets an inclusive prefix.
+// A predecessor holds a smaller TICKET, so it is running or done: the wait ends.
+__device__ __forceinline__ int32_t look_back(const unsigned long long* state, int32_t tile, int lane) {
+    int32_t prefix = 0;
+    for (int32_t p = tile - 1; p >= 0; p -= 32) {
+        const int32_t q = p - lane;
+        unsigned long long w = kInclusive;  // lanes before tile 0 read as "inclusive prefix 0"
+        if (q >= 0) {
+            do { w = ld_state(state + q); } while ((w >> 32) == 0);
+        }
+        const unsigned inc = __ballot_sync(0xffffffffu, (w >> 32) == 2);
+        const int stop = inc ? __ffs(inc) - 1 : 31;  // nearest inclusive prefix ends the walk
+        int32_t v = lane <= stop ? static_cast<int32_t>(static_cast<uint32_t>(w)) : 0;
 #pragma unroll
-    for (int t = 0; t < kScanItems; ++t) v += row_count(R, base + t);
-    int32_t total;
-    block_exclusive_scan(v, total);
-    if (threadIdx.x == 0) R.bsum[blockIdx.x] = total;
-}
-
-// One block per relation: in-place exclusive scan of the per-block sums.
-__global__ void __launch_bounds__(kScanThreads) k_scan_b(const __grid_constant__ PlanParams P) {
-    const RelDev& R = P.r[blockIdx.x];
-    int32_t carry = 0;
-    for (int32_t b0 = 0; b0 < R.n_scan_blocks; b0 += kScanThreads) {
-        const int32_t b = b0 + threadIdx.x;
-        const int32_t v = b < R.n_scan_blocks ? R.bsum[b] : 0;
-        int32_t total;
-        const int32_t ex = block_exclusive_scan(v, total);
-        if (b < R.n_scan_blocks) R.bsum[b] = carry + ex;
-        carry += total;
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        prefix += v;
+        if (inc) break;
     }
-    if (threadIdx.x == 0) R.rowptr[R.n_dst] = carry;  // E'
+    return prefix;
 }
 
-__global__ void __launch_bounds__(kScanThreads) k_scan_c(const __grid_constant__ PlanParams P) {
+__global__ void __launch_bounds__(kScanThreads) k_scan(const __grid_constant__ PlanParams P) {
     const RelDev& R = P.r[blockIdx.y];
+    if (R.n_scan_blocks == 0) {  // no destination rows: rowptr = [0]
+        if (blockIdx.x == 0 && threadIdx.x == 0 && R.rowptr) R.rowptr[0] = 0;
+        return;
+    }
     if (static_cast<int>(blockIdx.x) >= R.n_scan_blocks) return;
-    const int32_t base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+    __shared__ int32_t s_tile, s_prefix;
+    __shared__ int32_t s_out[kScanTile + 1];
+    if (threadIdx.x == 0) s_tile = static_cast<int32_t>(atomicAdd(R.scan_state + R.n_scan_blocks, 1ull));  // ticket
+    __syncthreads();
+    const int32_t tile = s_tile;
+    const int32_t base = tile * kScanTile + threadIdx.x * kScanItems;
     int32_t c[kScanItems];
-    int32_t v = 0;
-#pragma unroll
-    for (int t = 0; t < kScanItems; ++t) {
-        c[t] = row_count(R, base + t);
-        v += c[t];
+    if (base < R.n_dst) {  // cnt is 256-byte aligned and padded to 256 bytes: whole groups of 8 are readable
+        const int4 lo = *reinterpret_cast<const int4*>(R.cnt + base), hi = *reinterpret_cast<const int4*>(R.cnt + base + 4);
+        c[0] = lo.x; c[1] = lo.y; c[2] = lo.z; c[3] = lo.w; c[4] = hi.x; c[5] = hi.y; c[6] = hi.z; c[7] = hi.w;
     }
-    int32_t total;
-    int32_t run = block_exclusive_scan(v, total) + R.bsum[blockIdx.x];
+    int32_t v = 0;
 #pragma unroll
     for (int t = 0; t < kScanItems; ++t) {
         const int32_t k = base + t;
-        if (k < R.n_dst) {
-            R.rowptr[k] = run;
-            R.cnt[k] = 0;  // becomes the fill cursor
-            if (R.inv_sqrt_deg) R.inv_sqrt_deg[k] = c[t] > 0 ? 1.0f / sqrtf(static_cast<float>(c[t])) : 0.f;
+        c[t] = k < R.n_dst ? c[t] + (k < R.n_loop ? 1 : 0) : 0;
+        v += c[t];
+    }
+    int32_t total;
+    int32_t run = block_exclusive_scan(v, total);
+    if (threadIdx.x < 32) {
+        if (threadIdx.x == 0) st_state(R.scan_state + tile, (tile == 0 ? kInclusive : kAggregate) | static_cast<uint32_t>(total));
+        const int32_t prefix = tile == 0 ? 0 : look_back(R.scan_state, tile, threadIdx.x);
+        if (threadIdx.x == 0) {
+            if (tile != 0) st_state(R.scan_state + tile, kInclusive | static_cast<uint32_t>(prefix + total));
+            s_prefix = prefix;
+            s_out[kScanTile] = prefix + total;
+            if (tile == R.n_scan_blocks - 1) R.rowptr[R.n_dst] = prefix + total;  // E'
         }
+    }
+    __syncthreads();
+    run += s_prefix;
+#pragma unroll
+    for (int t = 0; t < kScanItems; ++t) {
+        s_out[threadIdx.x * kScanItems + t] = run;
         run += c[t];
+    }
+    __syncthreads();
+    const int32_t k0 = tile * kScanTile;
+    for (int i = threadIdx.x; i < kScanTile; i += kScanThreads) {
+        const int32_t k = k0 + i;
+        if (k >= R.n_dst) break;
+        R.rowptr[k] = s_out[i];
+        R.cnt[k] = 0;  // becomes the fill cursor
+        if (R.inv_sqrt_deg) {
+            const int32_t deg = s_out[i + 1] - s_out[i];
+            R.inv_sqrt_deg[k] = deg > 0 ? 1.0f / sqrtf(static_cast<float>(deg)) : 0.f;
+        }
+        if (R.tile_win && (i % HG_TILE_ROWS) == 0) {  // kScanTile is a multiple of the tile: tiles do not straddle blocks
+            const int32_t t = k / HG_TILE_ROWS;
+            const int32_t enc_lo = R.tw_tmp[2 * t], enc_hi = R.tw_tmp[2 * t + 1];
+            int32_t lo = enc_hi ? INT32_MAX - enc_lo : INT32_MAX, hi = enc_hi - 1;
+            if (k < R.n_loop) {  // appended self loops (j, j) of this tile's rows
+                const int32_t r1 = k + HG_TILE_ROWS < R.n_dst ? k + HG_TILE_ROWS : R.n_dst;
+                const int32_t last = (r1 < R.n_loop ? r1 : R.n_loop) - 1;
+                lo = k < lo ? k : lo;
+                hi = last > hi ? last : hi;
+            }
+            R.tile_win[2 * t] = hi >= 0 ? lo : 0;
+            R.tile_win[2 * t + 1] = hi >= 0 ? hi - lo + 1 : 0;
+        }
     }
 }
 
@@ -180,41 +247,12 @@ __global__ void __launch_bounds__(kEdgeThreads) k_rank(const __grid_constant__ P
     }
 }
 
-// Source-row window of every tile of HG_TILE_ROWS destination rows: warp per tile, lanes over the tile's CSR entries.
-__global__ void __launch_bounds__(kEdgeThreads) k_tile_window(const __grid_constant__ PlanParams P) {
-    const RelDev& R = P.r[blockIdx.y];
-    if (!R.tile_win) return;
-    const int lane = threadIdx.x & 31;
-    constexpr int kWarps = kEdgeThreads / kWarp;
-    const int32_t n_tiles = ceil_div<int32_t>(R.n_dst, HG_TILE_ROWS);
-    for (int32_t tile = blockIdx.x * kWarps + (threadIdx.x >> 5); tile < n_tiles; tile += gridDim.x * kWarps) {
-        const int32_t r0 = tile * HG_TILE_ROWS;
-        const int32_t r1 = r0 + HG_TILE_ROWS < R.n_dst ? r0 + HG_TILE_ROWS : R.n_dst;
-        const int32_t beg = R.rowptr[r0], end = R.rowptr[r1];
-        int32_t lo = INT32_MAX, hi = -1;
-        for (int32_t e = beg + lane; e < end; e += 32) {
-            const int32_t c = R.col[e];
-            lo = c < lo ? c : lo;
-            hi = c > hi ? c : hi;
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const int32_t l2 = __shfl_xor_sync(0xffffffffu, lo, o), h2 = __shfl_xor_sync(0xffffffffu, hi, o);
-            lo = l2 < lo ? l2 : lo;
-            hi = h2 > hi ? h2 : hi;
-        }
-        if (lane == 0) {
-            R.tile_win[2 * tile] = hi >= 0 ? lo : 0;
-            R.tile_win[2 * tile + 1] = hi >= 0 ? hi - lo + 1 : 0;
-        }
-    }
-}
-
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
-    size_t cnt_off[HG_MAX_PLAN_RELATIONS], ids_off[HG_MAX_PLAN_RELATIONS], bsum_off[HG_MAX_PLAN_RELATIONS];
-    size_t cnt_total;  // bytes of the leading region that must be zeroed
+    size_t cnt_off[HG_MAX_PLAN_RELATIONS], ids_off[HG_MAX_PLAN_RELATIONS], state_off[HG_MAX_PLAN_RELATIONS],
+        tw_off[HG_MAX_PLAN_RELATIONS];
+    size_t cnt_total;  // bytes of the leading region that must be zeroed: histograms, scan states + tickets, window scratch
     size_t total;
 };
 
@@ -227,14 +265,17 @@ int layout(const hg_plan_rel* rels, int n_rel, WsLayout& L) {
         if (rels[r].n_edges + loops >= (int64_t(1) << 31)) return HG_ERANGE;
         L.cnt_off[r] = off;
         off = align_up(off + sizeof(int32_t) * static_cast<size_t>(rels[r].n_dst), 256);
+        L.state_off[r] = off;
+        off = align_up(off + sizeof(unsigned long long) * static_cast<size_t>(ceil_div<int64_t>(rels[r].n_dst, kScanTile) + 1), 256);
+        L.tw_off[r] = off;
+        if (rels[r].tile_win)
+            off = align_up(off + 2 * sizeof(int32_t) * static_cast<size_t>(ceil_div<int64_t>(rels[r].n_dst, HG_TILE_ROWS)), 256);
     }
     L.cnt_total = off;
     for (int r = 0; r < n_rel; ++r) {
         const int64_t loops = rels[r].self_loops ? (rels[r].n_src < rels[r].n_dst ? rels[r].n_src : rels[r].n_dst) : 0;
         L.ids_off[r] = off;
         off = align_up(off + sizeof(int32_t) * static_cast<size_t>(rels[r].n_edges + loops), 256);
-        L.bsum_off[r] = off;
-        off = align_up(off + sizeof(int32_t) * static_cast<size_t>(ceil_div<int64_t>(rels[r].n_dst, kScanTile) + 1), 256);
     }
     L.total = off;
     return HG_OK;
@@ -265,7 +306,7 @@ extern "C" int hg_plan_build(const hg_plan_rel* rels, int n_rel, int32_t* status
     PlanParams P;
     P.status = status;
     int64_t max_edges = 0, max_total = 0;
-    int32_t max_blocks = 0, max_tiles = 0;
+    int32_t max_blocks = 0;
     for (int r = 0; r < n_rel; ++r) {
         const hg_plan_rel& h = rels[r];
         if (h.n_edges > 0 && (!h.src || !h.dst)) return HG_EINVAL;
@@ -277,11 +318,11 @@ extern "C" int hg_plan_build(const hg_plan_rel* rels, int n_rel, int32_t* status
         d.rowptr = h.rowptr; d.col = h.col; d.perm = h.perm; d.inv_sqrt_deg = h.inv_sqrt_deg;
         d.cnt = reinterpret_cast<int32_t*>(ws + L.cnt_off[r]);
         d.ids_tmp = reinterpret_cast<int32_t*>(ws + L.ids_off[r]);
-        d.bsum = reinterpret_cast<int32_t*>(ws + L.bsum_off[r]);
+        d.scan_state = reinterpret_cast<unsigned long long*>(ws + L.state_off[r]);
         d.n_scan_blocks = static_cast<int32_t>(ceil_div<int64_t>(h.n_dst, kScanTile));
         d.pad = 0;
         d.tile_win = h.tile_win;
-        max_tiles = (h.tile_win && ceil_div<int32_t>(h.n_dst, HG_TILE_ROWS) > max_tiles) ? ceil_div<int32_t>(h.n_dst, HG_TILE_ROWS) : max_tiles;
+        d.tw_tmp = h.tile_win ? reinterpret_cast<int32_t*>(ws + L.tw_off[r]) : nullptr;
         max_edges = h.n_edges > max_edges ? h.n_edges : max_edges;
         max_total = h.n_edges + d.n_loop > max_total ? h.n_edges + d.n_loop : max_total;
         max_blocks = d.n_scan_blocks > max_blocks ? d.n_scan_blocks : max_blocks;
@@ -299,13 +340,9 @@ extern "C" int hg_plan_build(const hg_plan_rel* rels, int n_rel, int32_t* status
         return static_cast<unsigned>(g < cap ? g : cap);
     };
     if (max_edges > 0) k_count<<<dim3(edge_grid(max_edges), n_rel), kEdgeThreads, 0, stream>>>(P);
-    if (max_blocks > 0) k_scan_a<<<dim3(max_blocks, n_rel), kScanThreads, 0, stream>>>(P);
-    k_scan_b<<<dim3(n_rel), kScanThreads, 0, stream>>>(P);
-    if (max_blocks > 0) k_scan_c<<<dim3(max_blocks, n_rel), kScanThreads, 0, stream>>>(P);
+    k_scan<<<dim3(max_blocks > 0 ? max_blocks : 1, n_rel), kScanThreads, 0, stream>>>(P);
     if (max_edges > 0) k_fill<<<dim3(edge_grid(max_edges), n_rel), kEdgeThreads, 0, stream>>>(P);
     if (max_total > 0) k_rank<<<dim3(edge_grid(max_total), n_rel), kEdgeThreads, 0, stream>>>(P);
-    if (max_tiles > 0)
-        k_tile_window<<<dim3(edge_grid(static_cast<int64_t>(max_tiles) * kWarp), n_rel), kEdgeThreads, 0, stream>>>(P);
     return check_launch();
 }
 

@@ -203,7 +203,7 @@ class CSRSpec:
 
 
 def build_csr(specs: Sequence[CSRSpec], overlap: bool = False):
-    """All relations of a batch in one ``hg_plan_build`` call (six launches in total).
+    """All relations of a batch in one ``hg_plan_build`` call (four launches in total).
 
     ``overlap=True`` launches the plan on a side stream forked from the current one; the current
     stream joins it at the first ``CSR.ready()`` (every op below calls it), so independent work

@@ -296,6 +296,31 @@ def test_plan_tile_windows_bit_exact(n_src, n_dst, E, loops):
     assert torch.equal(csr.tile_win.cpu(), _tile_windows(csr.rowptr, csr.col, n_dst))
 
 
+@pytest.mark.parametrize("loops", [True, False])
+def test_plan_single_pass_scan_many_tiles(loops):
+    """147 scan tiles of 2048 rows chained by look-back, two relations of different size in one call, windows + perm +
+    degree^-1/2; one relation's edges grouped by destination block (the batch layout), the other's random."""
+    g = torch.Generator().manual_seed(5)
+    n, E = 300001, 1500000
+    blk = torch.randint(0, n // 50, (E,), generator=g).sort().values * 50
+    local = torch.stack([blk + torch.randint(0, 50, (E,), generator=g), blk + torch.randint(0, 50, (E,), generator=g)])
+    rand = torch.stack([torch.randint(0, 70000, (E // 3,), generator=g), torch.randint(0, 4097, (E // 3,), generator=g)])
+    specs = [CSRSpec(local.cuda(), n, n, loops, want_perm=True, want_norm=True, want_window=True),
+             CSRSpec(rand.cuda(), 70000, 4097, False, want_perm=True, want_window=True)]
+    for _ in range(2):  # the second call reuses a warm workspace
+        csrs, status = ops.build_csr(specs)
+        assert int(status.item()) == 0
+        for csr, (ei, ns, nd, lp) in zip(csrs, [(local, n, n, loops), (rand, 70000, 4097, False)]):
+            rowptr, col, perm = csr_oracle(ei, ns, nd, lp)
+            m = int(rowptr[-1])
+            assert torch.equal(csr.rowptr.cpu(), rowptr)
+            assert torch.equal(csr.col.cpu()[:m], col) and torch.equal(csr.perm.cpu()[:m], perm)
+            assert torch.equal(csr.tile_win.cpu(), _tile_windows(csr.rowptr, csr.col, nd))
+    deg = (csrs[0].rowptr[1:] - csrs[0].rowptr[:-1]).float()
+    assert torch.equal(csrs[0].inv_sqrt_deg[:n], torch.where(deg > 0, deg.pow(-0.5), torch.zeros_like(deg))) or \
+        torch.allclose(csrs[0].inv_sqrt_deg[:n], torch.where(deg > 0, deg.pow(-0.5), torch.zeros_like(deg)), rtol=1e-6, atol=0)
+
+
 def _scene_batch_relations(graph_ids, H, g, a_edge=False):
     """o->o (self loops) and r->o relations of a synthetic scene-graph batch with random projected rows / logits."""
     b = synth.synth_mp3d_batch(graph_ids, device="cuda")
