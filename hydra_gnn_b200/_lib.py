@@ -94,7 +94,15 @@ class HtreeSplitArgs(C.Structure):
                 ("room_mask", vp), ("object_mask", vp), ("edges", vp * 3), ("status", vp)]
 
 
-_STRUCTS = [PlanRel, SegArgs, GatRel, GatArgs, LinSeg, LinearArgs, GatTrainRel, GatTrainArgs, HtreeSplitArgs]
+class SynthArgs(C.Structure):
+    _fields_ = [("graph_id0", i64), ("n_graphs", i32), ("reserved", i32), ("seed", C.c_uint64), ("cdf_rooms", vp),
+                ("cdf_objects", vp), ("prefix", vp), ("n_rooms", i64), ("n_objects", i64), ("n_rr_pairs", i64),
+                ("n_oo_pairs", i64), ("word2vec", vp), ("x_rooms", vp), ("x_objects", vp), ("ld_objects", i64),
+                ("rooms_to_rooms", vp), ("objects_to_objects", vp), ("objects_to_rooms", vp), ("rooms_to_objects", vp),
+                ("room_label", vp), ("object_label", vp), ("room_batch", vp), ("object_batch", vp), ("status", vp)]
+
+
+_STRUCTS = [PlanRel, SegArgs, GatRel, GatArgs, LinSeg, LinearArgs, GatTrainRel, GatTrainArgs, HtreeSplitArgs, SynthArgs]
 
 # name -> (restype, argtypes); every symbol declared in include/hydra_gnn_b200.h
 SYMBOLS = {
@@ -118,6 +126,8 @@ SYMBOLS = {
     "hg_batch_vector": (C.c_int, [vp, i64, vp, i32, vp]),
     "hg_htree_split_workspace_bytes": (C.c_size_t, [C.POINTER(HtreeSplitArgs)]),
     "hg_htree_split": (C.c_int, [C.POINTER(HtreeSplitArgs), vp, C.c_size_t, vp]),
+    "hg_synth_mp3d_counts": (C.c_int, [C.POINTER(SynthArgs), vp]),
+    "hg_synth_mp3d_fill": (C.c_int, [C.POINTER(SynthArgs), vp]),
     "hg_gat_train_fwd": (C.c_int, [C.POINTER(GatTrainArgs), vp]),
     "hg_gat_train_bwd": (C.c_int, [C.POINTER(GatTrainArgs), vp]),
     "hg_csr_transpose_map": (C.c_int, [vp, vp, vp, i64, vp, vp, vp, i64, i32, vp, vp, vp]),

@@ -67,6 +67,7 @@ extern "C" int hg_sizeof(int which) {
         case 6: return static_cast<int>(sizeof(hg_gat_train_rel));
         case 7: return static_cast<int>(sizeof(hg_gat_train_args));
         case 8: return static_cast<int>(sizeof(hg_htree_split_args));
+        case 9: return static_cast<int>(sizeof(hg_synth_args));
         default: return -1;
     }
 }

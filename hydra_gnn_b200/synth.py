@@ -44,11 +44,15 @@ def _u01(seed: int, gid: np.ndarray, stream: int, idx: np.ndarray) -> np.ndarray
     return (k >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
 
 
-def _poisson_icdf(u: np.ndarray, lam: float, kmax: int) -> np.ndarray:
+def _poisson_cdf(lam: float, kmax: int) -> np.ndarray:
+    """Cumulative Poisson(lam) table over 0..kmax in float64 (the device generator is handed the same array)."""
     k = np.arange(kmax + 1)
     logp = -lam + k * np.log(lam) - np.cumsum(np.concatenate([[0.0], np.log(np.arange(1, kmax + 1))]))
-    cdf = np.cumsum(np.exp(logp))
-    return np.searchsorted(cdf, u, side="right")
+    return np.cumsum(np.exp(logp))
+
+
+def _poisson_icdf(u: np.ndarray, lam: float, kmax: int) -> np.ndarray:
+    return np.searchsorted(_poisson_cdf(lam, kmax), u, side="right")
 
 
 def _normal(seed, gid, stream, idx):
@@ -168,6 +172,101 @@ def synth_mp3d_batch(graph_ids, seed: int = SEED, with_word2vec: bool = True, re
         if relative_pos:  # the batch lives on the device: hg_relative_pos, bit-identical to the host expression
             rel_pos()
     return data
+
+
+class DeviceSynth:
+    """``synth_mp3d_batch`` generated on the GPU by ``hg_synth_mp3d_counts`` / ``hg_synth_mp3d_fill`` (csrc/synth.cu):
+    same counter hash, same tables -- counts, edge lists, labels and batch vectors are bit-identical to the host
+    generator, features too except that the Box-Muller object positions may differ in the last float32 bit where
+    libm and CUDA round a double differently.
+
+    ``sizes(first, n)`` launches the counting pass of a range of graph ids and returns its totals (ONE host sync;
+    call it for every micro-batch of a job up front), ``batch(first, n)`` then fills a ``HeteroData`` without any
+    further synchronisation."""
+
+    def __init__(self, device, seed: int = SEED, with_word2vec: bool = True):
+        self.device, self.seed, self.with_word2vec = torch.device(device), seed, with_word2vec
+        self.cdf_rooms = torch.from_numpy(_poisson_cdf(5.0, 64)).to(self.device)
+        self.cdf_objects = torch.from_numpy(_poisson_cdf(12.0, 128)).to(self.device)
+        self.w2v = torch.from_numpy(word2vec_table(seed)).to(self.device) if with_word2vec else None
+        self._prefix = {}
+
+    def _args(self, first: int, n: int, prefix: torch.Tensor):
+        from . import _lib
+
+        a = _lib.SynthArgs()
+        a.graph_id0, a.n_graphs, a.seed = first, n, self.seed
+        a.cdf_rooms, a.cdf_objects, a.prefix = self.cdf_rooms.data_ptr(), self.cdf_objects.data_ptr(), prefix.data_ptr()
+        return a
+
+    def counts_async(self, first: int, n: int) -> torch.Tensor:
+        """Launch the counting pass; returns the device tensor ``[n + 1, 4]`` of exclusive prefix sums (+ totals)."""
+        import ctypes as C
+
+        from . import _lib
+        from .ops import _call
+
+        h = _lib.lib()
+        prefix = torch.empty(n + 1, 4, dtype=torch.int64, device=self.device)
+        a = self._args(first, n, prefix)
+        with torch.cuda.device(self.device):
+            _call("hg_synth_mp3d_counts", dict(n_graphs=n), lambda: h.hg_synth_mp3d_counts(C.byref(a), _lib.stream_ptr()))
+        _lib.launch_count += 2
+        self._prefix[(first, n)] = prefix
+        return prefix
+
+    def sizes(self, first: int, n: int):
+        """Totals ``(rooms, objects, room pairs, object pairs)`` of graphs ``first .. first + n - 1`` (host sync)."""
+        prefix = self._prefix.get((first, n))
+        if prefix is None:
+            prefix = self.counts_async(first, n)
+        return tuple(int(v) for v in prefix[n].tolist())
+
+    def batch(self, first: int, n: int, sizes=None, labels: bool = True) -> HeteroData:
+        import ctypes as C
+
+        from . import _lib
+        from .ops import _call
+
+        h = _lib.lib()
+        if sizes is None:
+            sizes = self.sizes(first, n)
+        prefix = self._prefix.pop((first, n), None)
+        if prefix is None:
+            prefix = self.counts_async(first, n)
+            self._prefix.pop((first, n), None)
+        NR, NO, Prr, Poo = sizes
+        dev, i64 = self.device, torch.int64
+        width = 6 + (W2V_DIM if self.with_word2vec else 0)
+        data = HeteroData()
+        x_room = torch.empty(NR, 6, dtype=torch.float32, device=dev)
+        x_obj = torch.empty(NO, width, dtype=torch.float32, device=dev)
+        rr, oo = torch.empty(2, 2 * Prr, dtype=i64, device=dev), torch.empty(2, 2 * Poo, dtype=i64, device=dev)
+        o2r, r2o = torch.empty(2, NO, dtype=i64, device=dev), torch.empty(2, NO, dtype=i64, device=dev)
+        status = torch.empty(1, dtype=torch.int32, device=dev)
+        a = self._args(first, n, prefix)
+        a.n_rooms, a.n_objects, a.n_rr_pairs, a.n_oo_pairs = NR, NO, Prr, Poo
+        a.word2vec = self.w2v.data_ptr() if self.with_word2vec else None
+        a.x_rooms, a.x_objects, a.ld_objects = x_room.data_ptr(), x_obj.data_ptr(), width
+        a.rooms_to_rooms, a.objects_to_objects = rr.data_ptr(), oo.data_ptr()
+        a.objects_to_rooms, a.rooms_to_objects, a.status = o2r.data_ptr(), r2o.data_ptr(), status.data_ptr()
+        if labels:
+            data["rooms"].y = torch.empty(NR, dtype=i64, device=dev)
+            data["objects"].y = torch.empty(NO, dtype=i64, device=dev)
+            data["rooms"].batch = torch.empty(NR, dtype=i64, device=dev)
+            data["objects"].batch = torch.empty(NO, dtype=i64, device=dev)
+            a.room_label, a.object_label = data["rooms"].y.data_ptr(), data["objects"].y.data_ptr()
+            a.room_batch, a.object_batch = data["rooms"].batch.data_ptr(), data["objects"].batch.data_ptr()
+        with torch.cuda.device(dev):
+            _call("hg_synth_mp3d_fill", dict(n_graphs=n, objects=NO), lambda: h.hg_synth_mp3d_fill(C.byref(a), _lib.stream_ptr()))
+        _lib.launch_count += 1
+        data["objects"].x, data["rooms"].x = x_obj, x_room
+        data["objects"].pos, data["rooms"].pos = x_obj[:, :3], x_room[:, :3]
+        for et, ei in zip(EDGE_TYPES, (oo, rr, o2r, r2o)):
+            data[et].edge_index = ei
+        data.num_graphs = n
+        data.synth_status = status  # device int32[1]: 1 when `sizes` disagree with the counting pass
+        return data
 
 
 def random_state_dict_(model: torch.nn.Module, seed: int = 0, bias_std: float = 0.1) -> torch.nn.Module:

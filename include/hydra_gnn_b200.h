@@ -442,6 +442,60 @@ HG_API int hg_adam_step(float* param, const float* grad, float* exp_avg, float* 
 HG_API int hg_act_bwd(const float* dy, int64_t lddy, const float* y, int64_t ldy, int64_t M, int32_t N, int32_t act,
                       float* g, int64_t ldg, float* dbias /* NULL | [N], accumulated (caller zeroes) */, void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * hg_synth_mp3d_* -- the synthetic "MP3D-shaped" scene-graph batch of hydra_gnn_b200/synth.py generated on the
+ * device (BASELINE.json configs[3] streams 1 M graphs in micro-batches of 16,384 that are
+ * generated where they are consumed -- ~75 GB of fp32 inputs do not fit host memory).  No counterpart in the
+ * reference, whose inputs are preprocessed Matterport3D pickles (mp3d_dataset.py:135-296); the node / edge layout
+ * is that of its HeteroData (EDGE_TYPES order, objects grouped by room).  Every draw is the counter hash
+ * splitmix64(seed, graph id, stream, index) of synth.py, so graph g is the same whichever rank, micro-batch or side
+ * (host / device) generates it: the integer structure (counts, edge lists, labels, batch vectors) and every feature
+ * that is an affine map of a uniform draw are BIT-IDENTICAL to the host generator; the object positions go through
+ * log / cos / sqrt in double (Box-Muller) and agree to the last float32 bit except where libm and CUDA round the
+ * double differently (~1 value in 2^29).
+ *
+ *   hg_synth_mp3d_counts: prefix[g] = exclusive prefix sums over the graphs of {rooms, objects, room-room pairs,
+ *                         object-object pairs}, prefix[n_graphs] = totals (the caller reads them to size the outputs:
+ *                         one host sync per micro-batch, or ONE for all micro-batches of a job).
+ *   hg_synth_mp3d_fill:   features, labels, batch vectors and the four edge lists ([2, E] int64, row 0 = source);
+ *                         every undirected pair gives the two directed edges a->b, b->a next to each other.
+ * ---------------------------------------------------------------------------------- */
+#define HG_SYNTH_MAX_ROOMS 12
+#define HG_SYNTH_MAX_OBJECTS 40
+#define HG_SYNTH_W2V_DIM 300
+#define HG_SYNTH_OBJECT_LABELS 28
+#define HG_SYNTH_ROOM_LABELS 26
+#define HG_SYNTH_CDF_ROOMS 65      /* entries of the Poisson(5) cdf table */
+#define HG_SYNTH_CDF_OBJECTS 129   /* entries of the Poisson(12) cdf table */
+
+typedef struct hg_synth_args {
+    int64_t graph_id0;          /* the batch is graphs graph_id0 .. graph_id0 + n_graphs - 1 */
+    int32_t n_graphs;
+    int32_t reserved;
+    uint64_t seed;
+    const double* cdf_rooms;    /* device [HG_SYNTH_CDF_ROOMS]:   cumulative Poisson(5) table of synth._poisson_icdf */
+    const double* cdf_objects;  /* device [HG_SYNTH_CDF_OBJECTS]: cumulative Poisson(12) table */
+    int64_t* prefix;            /* device [n_graphs + 1][4]: written by _counts, read by _fill */
+    /* ---- _fill only; sizes are the totals read from prefix[n_graphs] */
+    int64_t n_rooms, n_objects, n_rr_pairs, n_oo_pairs;
+    const float* word2vec;      /* NULL | device [HG_SYNTH_OBJECT_LABELS, HG_SYNTH_W2V_DIM] */
+    float* x_rooms;             /* [n_rooms, 6]  position | size */
+    float* x_objects; int64_t ld_objects; /* [n_objects, 6 (+ 300 with word2vec)] position | size | word2vec[label] */
+    int64_t* rooms_to_rooms;    /* [2, 2 * n_rr_pairs] */
+    int64_t* objects_to_objects;/* [2, 2 * n_oo_pairs] */
+    int64_t* objects_to_rooms;  /* [2, n_objects] */
+    int64_t* rooms_to_objects;  /* [2, n_objects] */
+    int64_t* room_label;        /* NULL | [n_rooms] */
+    int64_t* object_label;      /* NULL | [n_objects] */
+    int64_t* room_batch;        /* NULL | [n_rooms]   graph slot (0 .. n_graphs - 1) of every room */
+    int64_t* object_batch;      /* NULL | [n_objects] */
+    int32_t* status;            /* device scalar, set to 1 when the sizes above disagree with prefix[n_graphs] (nothing
+                                   is written outside the declared sizes) */
+} hg_synth_args;
+
+HG_API int hg_synth_mp3d_counts(const hg_synth_args* args_host, void* stream);
+HG_API int hg_synth_mp3d_fill(const hg_synth_args* args_host, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -177,3 +177,50 @@ def test_heterogeneous_neural_tree_gat_at_config3_size_vs_oracle(pre_mp):
         want = ref(clone_data(het))
     got = prod(clone_data(het, "cuda"))
     assert_close(got, want, f"NT heterogeneous GAT (4096 trees, pre_mp={pre_mp})")
+
+
+# ------------------------------------------------------------------------------ device generator (configs[3] streaming)
+@pytest.mark.parametrize("first,n", [(0, 1), (0, 64), (12345, 257), (999_000, 1500)])
+def test_device_generator_reproduces_the_host_generator(first, n):
+    """hg_synth_mp3d_counts / _fill vs synth.synth_mp3d_batch on the same graph ids: every integer output and every
+    feature that is an affine map of a uniform draw bit-identical; Box-Muller positions to the last float32 bit or two."""
+    host = synth.synth_mp3d_batch(range(first, first + n))
+    gen = synth.DeviceSynth("cuda")
+    sizes = gen.sizes(first, n)
+    assert sizes[0] == host["rooms"].x.size(0) and sizes[1] == host["objects"].x.size(0)
+    dev = gen.batch(first, n, sizes)
+    assert int(dev.synth_status.item()) == 0
+    for et in dev.edge_types:
+        assert torch.equal(dev[et].edge_index.cpu(), host[et].edge_index), et
+    for t in ("rooms", "objects"):
+        assert torch.equal(dev[t].y.cpu(), host[t].y) and torch.equal(dev[t].batch.cpu(), host[t].batch), t
+    assert torch.equal(dev["rooms"].x.cpu(), host["rooms"].x)
+    xo, want = dev["objects"].x.cpu(), host["objects"].x
+    assert torch.equal(xo[:, 3:], want[:, 3:])  # sizes + word2vec rows
+    # positions: room position + 1.5 * Box-Muller normal, log / cos / sqrt in double on both sides
+    diff = (xo[:, :3] - want[:, :3]).abs()
+    assert float(diff.max()) <= 4e-6 and float((diff > 0).float().mean()) < 1e-3
+
+
+def test_device_generator_prefix_sums_and_size_check():
+    gen = synth.DeviceSynth("cuda", with_word2vec=False)
+    prefix = gen.counts_async(7, 3000).cpu()
+    host = synth.synth_mp3d_batch(range(7, 3007), with_word2vec=False)
+    rooms = torch.bincount(host["rooms"].batch, minlength=3000)
+    objects = torch.bincount(host["objects"].batch, minlength=3000)
+    assert torch.equal(prefix[1:, 0] - prefix[:-1, 0], rooms) and torch.equal(prefix[1:, 1] - prefix[:-1, 1], objects)
+    assert int(prefix[-1, 2]) * 2 == host["rooms", "rooms_to_rooms", "rooms"].edge_index.size(1)
+    assert int(prefix[-1, 3]) * 2 == host["objects", "objects_to_objects", "objects"].edge_index.size(1)
+    sizes = gen.sizes(7, 3000)
+    bad = gen.batch(7, 3000, (sizes[0], sizes[1] + 1, sizes[2], sizes[3]))  # wrong declared size: flagged, nothing written
+    assert int(bad.synth_status.item()) == 1
+
+
+def test_forward_on_a_device_generated_batch_matches_the_host_generated_one():
+    net = synth.random_state_dict_(hg.HeterogeneousNetwork(**cases.CASES["mgat"][1]), seed=0).eval().cuda()
+    host = synth.synth_mp3d_batch(range(500, 564), device="cuda")
+    dev = synth.DeviceSynth("cuda").batch(500, 64)
+    with torch.no_grad():
+        a, b = net(host), net(dev)
+    assert a.shape == b.shape
+    assert_close(b, a.double().cpu(), "forward on the device-generated batch")

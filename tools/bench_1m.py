@@ -4,9 +4,14 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/bench_1m.py \
         [--total 1000000] [--micro 16384] [--repeat 3]
 
-Rank r owns graph ids [r T/W, (r+1) T/W) (dist.shard_range); its micro-batches are generated once (host, untimed) and
-kept resident in HBM.  Timed region (CUDA events between two barriers, max over ranks): every micro-batch forward
-(plan rebuilt per micro-batch) + the ragged logit gather.  One JSON line on rank 0.
+Rank r owns graph ids [r T/W, (r+1) T/W) (dist.shard_range).  Two forms:
+  default    the micro-batches are generated once (host, untimed) and kept resident in HBM; the local pass is one CUDA graph
+  --stream   every micro-batch is GENERATED ON THE DEVICE inside the timed region (hg_synth_mp3d_*: same graphs, bit for
+             bit, as the host generator), consumed by the forward and dropped: nothing but one micro-batch is resident,
+             which is the only form a 1 M-graph job (~75 GB of inputs) has on a host that cannot hold it.  The counting
+             pass of all micro-batches (output sizes) runs once up front with one host sync.
+Timed region (CUDA events between two barriers, max over ranks): [generation +] every micro-batch forward (plan rebuilt
+per micro-batch) + the ragged logit gather.  One JSON line on rank 0.
 """
 import argparse, json, os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -23,6 +28,7 @@ def main():
     ap.add_argument("--micro", type=int, default=16384)
     ap.add_argument("--repeat", type=int, default=10)
     ap.add_argument("--no-graph", action="store_true", help="launch every micro-batch eagerly")
+    ap.add_argument("--stream", action="store_true", help="generate every micro-batch on the device inside the timed region")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -40,7 +46,16 @@ def main():
     lo, hi = shard_range(args.total, rank, world)
     t0 = time.perf_counter()
     micro, rooms = [], 0
-    for a in range(lo, hi, args.micro):
+    gen = synth.DeviceSynth(dev) if args.stream else None
+    if gen is not None:
+        ranges = [(a, min(a + args.micro, hi) - a) for a in range(lo, hi, args.micro)]
+        for a, n in ranges:
+            gen.counts_async(a, n)  # all counting passes queued, then ONE sync reads the totals
+        for a, n in ranges:
+            sz = gen.sizes(a, n)
+            micro.append(((a, n, sz), rooms, sz[0]))
+            rooms += sz[0]
+    for a in ([] if gen is not None else range(lo, hi, args.micro)):
         host = synth.synth_mp3d_batch(range(a, min(a + args.micro, hi)))
         d = hg.data.HeteroData()
         for t in host.node_types:
@@ -57,10 +72,13 @@ def main():
 
     def forward_all():
         for d, off, n in micro:
+            if gen is not None:  # (first id, graphs, sizes): generate, consume, drop
+                gen.counts_async(d[0], d[1])
+                d = gen.batch(d[0], d[1], d[2], labels=False)
             logits[off:off + n].copy_(net(d))
 
     graph = None
-    if not args.no_graph:
+    if not args.no_graph and gen is None:
         # the micro-batches have fixed shapes: the whole local pass (plans included) is captured once and replayed, so the
         # job is bound by the device, not by ~340 eager launches per pass on a host shared by eight ranks (round 1: 26-50 ms)
         side = torch.cuda.Stream(dev)
@@ -119,7 +137,10 @@ def main():
                        "total_graphs": args.total, "micro_batch": args.micro, "micro_batches_per_rank": len(micro),
                        "rooms_total": n_rooms_all, "gathered_bytes": n_rooms_all * 26 * 4,
                        "collective": "all_gather_into_tensor(max-padded room logits)" if world > 1 else "none",
-                       "cuda_graph": graph is not None, "host_generation_s_per_rank": round(t_gen, 1)},
+                       "cuda_graph": graph is not None,
+                       "inputs": ("generated on the device inside the timed region, one micro-batch resident"
+                                  if gen is not None else "generated on the host (untimed), resident in HBM"),
+                       "setup_s_per_rank": round(t_gen, 1)},
             "gpu_launches": launches, "clocks": clocks.summary()}), flush=True)
     graph = None
     torch.cuda.synchronize(dev)
