@@ -78,7 +78,7 @@ def main():
             logits[off:off + n].copy_(net(d))
 
     graph = None
-    if not args.no_graph and gen is None:
+    if not args.no_graph:  # --stream too: generation is sync-free once the sizes are known, and every replay regenerates
         # the micro-batches have fixed shapes: the whole local pass (plans included) is captured once and replayed, so the
         # job is bound by the device, not by ~340 eager launches per pass on a host shared by eight ranks (round 1: 26-50 ms)
         side = torch.cuda.Stream(dev)
