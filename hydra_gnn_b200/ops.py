@@ -6,6 +6,7 @@ is used only to own device memory.  No function here has a CPU or eager fallback
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence
 
@@ -45,7 +46,28 @@ def bump_param_generation() -> None:
     _param_generation += 1
 
 
+# NVTX ranges around every ABI call (HG_NVTX=1 or set_nvtx(True)): `ncu --nvtx --nvtx-include "hg_gat_fused/"` then
+# selects the launches of one operator; off by default (a push / pop pair per call on the launch path).
+_nvtx = os.environ.get("HG_NVTX", "0") == "1"
+
+
+def set_nvtx(on: bool) -> None:
+    global _nvtx
+    _nvtx = bool(on)
+
+
 def _call(name: str, meta, fn):
+    if _nvtx:
+        torch.cuda.nvtx.range_push(name)
+        try:
+            _call_inner(name, meta, fn)
+        finally:
+            torch.cuda.nvtx.range_pop()
+        return
+    _call_inner(name, meta, fn)
+
+
+def _call_inner(name: str, meta, fn):
     if _profile_sink is None:
         check(fn(), name)
         return

@@ -497,3 +497,18 @@ def test_collate_offsets_with_empty_graphs():
     assert torch.equal(got.cpu(), want)
     bv = ops.batch_vector(sp.cuda(), int(sp[-1]))
     assert torch.equal(bv.cpu(), torch.repeat_interleave(torch.arange(len(src_counts)), torch.tensor(src_counts)))
+
+
+def test_nvtx_ranges_around_abi_calls_do_not_change_results():
+    g = torch.Generator().manual_seed(2)
+    ei = torch.stack([torch.randint(0, 300, (2000,), generator=g), torch.randint(0, 200, (2000,), generator=g)])
+    x = torch.randn(300, 64, generator=g).cuda()
+    (csr,), _ = ops.build_csr([CSRSpec(ei.cuda(), 300, 200)])
+    want = ops.seg_reduce(x, csr, "sum")
+    ops.set_nvtx(True)
+    try:
+        (csr2,), _ = ops.build_csr([CSRSpec(ei.cuda(), 300, 200)])
+        got = ops.seg_reduce(x, csr2, "sum")
+    finally:
+        ops.set_nvtx(False)
+    assert torch.equal(got, want)
