@@ -18,6 +18,8 @@ from ._lib import ACT, GROUP, PREC, REDUCE, check, lib, ptr, stream_ptr
 
 DEFAULT_PRECISION = "auto"  # "auto": tcgen05 TF32x3 for M >= TC_MIN_ROWS, fp32 CUDA cores below
 TC_MIN_ROWS = 512
+FP32_SMALL_ROWS = int(os.environ.get("HG_FP32_SMALL_ROWS", "0"))  # A/B knob, off by default
+FP32_SMALL_K = int(os.environ.get("HG_FP32_SMALL_K", "64"))
 
 # Optional per-launch timing (bench.py's roofline leg): a list that receives
 # (abi_name, meta dict, start_event, end_event) for every ABI call while it is set.
@@ -152,7 +154,7 @@ def _side_stream(device, k: int = 0) -> "torch.cuda.Stream":
     short ones that fill the gaps of the long kernel on the main stream."""
     s = _side_streams.get((device.index, k))
     if s is None:
-        s = _side_streams[(device.index, k)] = torch.cuda.Stream(device, priority=-1)
+        s = _side_streams[(device.index, k)] = torch.cuda.Stream(device, priority=int(os.environ.get("HG_SIDE_PRIORITY", "-1")))
     return s
 
 
@@ -455,6 +457,8 @@ def linear(segments: Sequence, N: int, *, bias: Tensor = None, scale: Tensor = N
     precision = precision or DEFAULT_PRECISION
     if precision == "auto":
         precision = "tf32x3" if M >= TC_MIN_ROWS else "fp32"
+        if FP32_SMALL_ROWS and M < FP32_SMALL_ROWS and sum(x.size(1) for x, _ in keep) <= FP32_SMALL_K:
+            precision = "fp32"  # A/B: short, shallow projections on the CUDA cores (no TMEM / barrier set-up)
     a.precision = PREC[precision]
     a.y, a.ldy = ptr(out), _ld(out)
     meta = dict(M=M, N=N, K=[x.size(1) for x, _ in keep], precision=precision)
