@@ -5,7 +5,7 @@
 // builds, pair selection by exact float64 compares, ordered edge lists by ballot compaction in the host's
 // enumeration order.  Double arithmetic that the host does as separate numpy operations is written with
 // __dmul_rn / __dadd_rn so that no fused multiply-add changes a rounding.
-//   k_counts  thread per graph: rooms, objects, selected room pairs, selected object pairs
+//   k_counts  warp per graph: rooms, objects, selected room pairs, selected object pairs
 //   k_prefix  one CTA: exclusive prefix sums of the four counts over the graphs (+ totals)
 //   k_fill    warp per graph: room rows, object rows (6 computed columns + the label's word2vec row), labels,
 //             batch vectors, rooms<->rooms, objects<->objects, objects<->rooms edge lists
@@ -68,37 +68,64 @@ __device__ __forceinline__ double pair_prob(int n) {
     return q < 1.0 ? q : 1.0;
 }
 
-__global__ void __launch_bounds__(128) k_counts(const __grid_constant__ hg_synth_args A) {
-    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+// Warp per graph.  Counting needs no order, so the lanes stride over the flattened a x b grid of a room (the hash is
+// evaluated for a < b only): ~5 iterations per 12-object room instead of 11 partly filled ones.
+__global__ void __launch_bounds__(256) k_counts(const __grid_constant__ hg_synth_args A) {
+    const int lane = threadIdx.x & 31;
+    const int g = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (g >= A.n_graphs) return;
     const uint64_t gkey = graph_key(A.seed, A.graph_id0 + g);
     const int R = n_rooms_of(A, gkey);
-    int64_t objects = 0, oo = 0, rr = 0;
-    for (int r = 0; r < R; ++r) {
-        const int n = n_objects_of(A, gkey, r);
-        objects += n;
-        const double p = pair_prob(n);
-        for (int a = 0; a < n; ++a)
-            for (int b = a + 1; b < n; ++b) oo += object_pair(gkey, r, a, b, p) ? 1 : 0;
+    const int n_mine = lane < R ? n_objects_of(A, gkey, lane) : 0;
+    int objects = n_mine, rr = 0, oo = 0;
+    for (int k = lane; k < R * R; k += 32) {
+        const int a = k / R, b = k - a * R;
+        rr += (a < b && room_pair(gkey, a, b)) ? 1 : 0;
     }
-    for (int a = 0; a < R; ++a)
-        for (int b = a + 1; b < R; ++b) rr += room_pair(gkey, a, b) ? 1 : 0;
-    int64_t* out = A.prefix + 4 * static_cast<int64_t>(g);
-    out[0] = R; out[1] = objects; out[2] = rr; out[3] = oo;
+    for (int r = 0; r < R; ++r) {
+        const int n = __shfl_sync(0xffffffffu, n_mine, r);
+        const double p = pair_prob(n);
+        for (int k = lane; k < n * n; k += 32) {
+            const int a = k / n, b = k - a * n;
+            oo += (a < b && object_pair(gkey, r, a, b, p)) ? 1 : 0;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        objects += __shfl_xor_sync(0xffffffffu, objects, o);
+        rr += __shfl_xor_sync(0xffffffffu, rr, o);
+        oo += __shfl_xor_sync(0xffffffffu, oo, o);
+    }
+    if (lane == 0) {
+        int64_t* out = A.prefix + 4 * static_cast<int64_t>(g);
+        out[0] = R; out[1] = objects; out[2] = rr; out[3] = oo;
+    }
 }
 
-// In-place exclusive prefix sums of the four columns, one CTA of 1024 threads, chunks of 1024 graphs with a carry.
-__global__ void __launch_bounds__(1024) k_prefix(const __grid_constant__ hg_synth_args A) {
+// In-place exclusive prefix sums of the four columns: one CTA of 512 threads, 8 consecutive graphs per thread (4,096
+// graphs per pass, all loads of a pass in flight together; the per-graph counts fit 32 bits), a carry between passes.
+constexpr int kPrefixItems = 8, kPrefixThreads = 512;
+__global__ void __launch_bounds__(kPrefixThreads) k_prefix(const __grid_constant__ hg_synth_args A) {
+    constexpr int kWarps = kPrefixThreads / 32;
     __shared__ int64_t warp_tot[32][4];
     __shared__ int64_t carry[4];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (threadIdx.x < 4) carry[threadIdx.x] = 0;
     __syncthreads();
-    for (int g0 = 0; g0 < A.n_graphs; g0 += 1024) {
-        const int g = g0 + threadIdx.x;
-        int64_t v[4], inc[4];
+    for (int64_t g0 = 0; g0 < A.n_graphs; g0 += kPrefixThreads * kPrefixItems) {
+        const int64_t base = g0 + static_cast<int64_t>(threadIdx.x) * kPrefixItems;
+        int4 v[kPrefixItems];
+        int64_t tot[4] = {0, 0, 0, 0};
 #pragma unroll
-        for (int c = 0; c < 4; ++c) v[c] = g < A.n_graphs ? A.prefix[4 * static_cast<int64_t>(g) + c] : 0, inc[c] = v[c];
+        for (int t = 0; t < kPrefixItems; ++t) {
+            v[t] = make_int4(0, 0, 0, 0);
+            if (base + t < A.n_graphs) {
+                const longlong4 w = *reinterpret_cast<const longlong4*>(A.prefix + 4 * (base + t));
+                v[t] = make_int4(static_cast<int>(w.x), static_cast<int>(w.y), static_cast<int>(w.z), static_cast<int>(w.w));
+            }
+            tot[0] += v[t].x; tot[1] += v[t].y; tot[2] += v[t].z; tot[3] += v[t].w;
+        }
+        int64_t inc[4] = {tot[0], tot[1], tot[2], tot[3]};
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
 #pragma unroll
@@ -115,7 +142,7 @@ __global__ void __launch_bounds__(1024) k_prefix(const __grid_constant__ hg_synt
         if (wid == 0) {
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-                int64_t w = warp_tot[lane][c];
+                int64_t w = lane < kWarps ? warp_tot[lane][c] : 0;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
                     const int64_t t = __shfl_up_sync(0xffffffffu, w, o);
@@ -125,13 +152,17 @@ __global__ void __launch_bounds__(1024) k_prefix(const __grid_constant__ hg_synt
             }
         }
         __syncthreads();
+        int64_t run[4];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const int64_t ex = carry[c] + (wid ? warp_tot[wid - 1][c] : 0) + inc[c] - v[c];
-            if (g < A.n_graphs) A.prefix[4 * static_cast<int64_t>(g) + c] = ex;
+        for (int c = 0; c < 4; ++c) run[c] = carry[c] + (wid ? warp_tot[wid - 1][c] : 0) + inc[c] - tot[c];
+#pragma unroll
+        for (int t = 0; t < kPrefixItems; ++t) {
+            if (base + t < A.n_graphs)
+                *reinterpret_cast<longlong4*>(A.prefix + 4 * (base + t)) = make_longlong4(run[0], run[1], run[2], run[3]);
+            run[0] += v[t].x; run[1] += v[t].y; run[2] += v[t].z; run[3] += v[t].w;
         }
         __syncthreads();
-        if (threadIdx.x < 4) carry[threadIdx.x] += warp_tot[31][threadIdx.x];
+        if (threadIdx.x < 4) carry[threadIdx.x] += warp_tot[31][threadIdx.x];  // lanes >= kWarps scanned zeros: row 31 = the total
         __syncthreads();
     }
     if (threadIdx.x < 4) A.prefix[4 * static_cast<int64_t>(A.n_graphs) + threadIdx.x] = carry[threadIdx.x];
@@ -148,6 +179,16 @@ __device__ __forceinline__ void put_pair(int64_t* list, int64_t n_edges, int64_t
     list[2 * k + 1] = b;
     list[n_edges + 2 * k] = b;     // row 1 (targets): b, a
     list[n_edges + 2 * k + 1] = a;
+}
+
+// Pair q of the row-major upper triangle of an n x n grid (row a holds the n - 1 - a pairs (a, a + 1 .. n - 1)).
+__device__ __forceinline__ void pair_of(int q, int n, int& a, int& b) {
+    const float t = static_cast<float>(2 * n - 1);
+    a = static_cast<int>((t - sqrtf(t * t - 8.f * static_cast<float>(q))) * 0.5f);
+    a = a < 0 ? 0 : (a > n - 2 ? n - 2 : a);
+    while (a > 0 && a * (2 * n - a - 1) / 2 > q) --a;           // the float estimate is off by at most one row
+    while ((a + 1) * (2 * n - a - 2) / 2 <= q) ++a;
+    b = a + 1 + (q - a * (2 * n - a - 1) / 2);
 }
 
 __global__ void __launch_bounds__(256) k_fill(const __grid_constant__ hg_synth_args A) {
@@ -187,6 +228,8 @@ __global__ void __launch_bounds__(256) k_fill(const __grid_constant__ hg_synth_a
         if (A.room_batch) A.room_batch[room0 + lane] = g;
     }
 
+    const bool vec2 = (A.ld_objects % 2 == 0) && (reinterpret_cast<uintptr_t>(A.x_objects) % 8 == 0) &&
+                      (reinterpret_cast<uintptr_t>(A.word2vec) % 8 == 0);
     // ---- objects, room by room (objects of a room are consecutive rows)
     for (int r = 0; r < R; ++r) {
         const int n = __shfl_sync(0xffffffffu, n_mine, r), s = __shfl_sync(0xffffffffu, start_mine, r);
@@ -220,19 +263,28 @@ __global__ void __launch_bounds__(256) k_fill(const __grid_constant__ hg_synth_a
                     const int lbl = __shfl_sync(0xffffffffu, label, t);
                     const float* src = A.word2vec + lbl * HG_SYNTH_W2V_DIM;
                     float* dst = A.x_objects + (obj0 + s + o0 + t) * A.ld_objects + 6;
-                    for (int c = lane; c < HG_SYNTH_W2V_DIM; c += 32) dst[c] = __ldg(src + c);
+                    if (vec2) {  // rows of 306 floats: column 6 of every row is 8-byte aligned, and so are the table rows
+#pragma unroll
+                        for (int c = lane; c < HG_SYNTH_W2V_DIM / 2; c += 32)
+                            reinterpret_cast<float2*>(dst)[c] = __ldg(reinterpret_cast<const float2*>(src) + c);
+                    } else {
+                        for (int c = lane; c < HG_SYNTH_W2V_DIM; c += 32) dst[c] = __ldg(src + c);
+                    }
                 }
             }
         }
     }
 
-    // ---- rooms <-> rooms: pairs in (a, b) order, a < b < R <= 12 (one chunk of lanes per a)
+    // ---- rooms <-> rooms: pairs in (a, b) order -- the lanes take 32 consecutive pairs of the row-major upper triangle
     {
         const int64_t n_edges = 2 * A.n_rr_pairs;
         int64_t k = rr0;
-        for (int a = 0; a + 1 < R; ++a) {
-            const int b = a + 1 + lane;
-            const bool hit = b < R && room_pair(gkey, a, b);
+        const int total = R * (R - 1) / 2;
+        for (int q0 = 0; q0 < total; q0 += 32) {
+            int a = 0, b = 0;
+            const bool valid = q0 + lane < total;
+            if (valid) pair_of(q0 + lane, R, a, b);
+            const bool hit = valid && room_pair(gkey, a, b);
             const unsigned m = __ballot_sync(0xffffffffu, hit);
             if (hit) put_pair(A.rooms_to_rooms, n_edges, k + __popc(m & ((1u << lane) - 1)), room0 + a, room0 + b);
             k += __popc(m);
@@ -247,14 +299,16 @@ __global__ void __launch_bounds__(256) k_fill(const __grid_constant__ hg_synth_a
             const int n = __shfl_sync(0xffffffffu, n_mine, r), s = __shfl_sync(0xffffffffu, start_mine, r);
             const double p = pair_prob(n);
             const int64_t base = obj0 + s;
-            for (int a = 0; a + 1 < n; ++a)
-                for (int b0 = a + 1; b0 < n; b0 += 32) {
-                    const int b = b0 + lane;
-                    const bool hit = b < n && object_pair(gkey, r, a, b, p);
-                    const unsigned m = __ballot_sync(0xffffffffu, hit);
-                    if (hit) put_pair(A.objects_to_objects, n_edges, k + __popc(m & ((1u << lane) - 1)), base + a, base + b);
-                    k += __popc(m);
-                }
+            const int total = n * (n - 1) / 2;
+            for (int q0 = 0; q0 < total; q0 += 32) {
+                int a = 0, b = 0;
+                const bool valid = q0 + lane < total;
+                if (valid) pair_of(q0 + lane, n, a, b);
+                const bool hit = valid && object_pair(gkey, r, a, b, p);
+                const unsigned m = __ballot_sync(0xffffffffu, hit);
+                if (hit) put_pair(A.objects_to_objects, n_edges, k + __popc(m & ((1u << lane) - 1)), base + a, base + b);
+                k += __popc(m);
+            }
         }
     }
 }
@@ -273,9 +327,9 @@ extern "C" int hg_synth_mp3d_counts(const hg_synth_args* a, void* stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const int rc = check_common(a);
     if (rc != HG_OK) return rc;
-    if (!a->prefix) return HG_EINVAL;
-    if (a->n_graphs > 0) k_counts<<<ceil_div(a->n_graphs, 128), 128, 0, stream>>>(*a);
-    k_prefix<<<1, 1024, 0, stream>>>(*a);
+    if (!a->prefix || !aligned(a->prefix, 32)) return HG_EINVAL;  // rows of four int64 are read as one 32-byte vector
+    if (a->n_graphs > 0) k_counts<<<ceil_div(a->n_graphs, 8), 256, 0, stream>>>(*a);
+    k_prefix<<<1, kPrefixThreads, 0, stream>>>(*a);
     return check_launch();
 }
 

@@ -180,7 +180,7 @@ def test_heterogeneous_neural_tree_gat_at_config3_size_vs_oracle(pre_mp):
 
 
 # ------------------------------------------------------------------------------ device generator (configs[3] streaming)
-@pytest.mark.parametrize("first,n", [(0, 1), (0, 64), (12345, 257), (999_000, 1500)])
+@pytest.mark.parametrize("first,n", [(0, 1), (0, 64), (12345, 257), (999_000, 1500), (5, 10_000)])
 def test_device_generator_reproduces_the_host_generator(first, n):
     """hg_synth_mp3d_counts / _fill vs synth.synth_mp3d_batch on the same graph ids: every integer output and every
     feature that is an affine map of a uniform draw bit-identical; Box-Muller positions to the last float32 bit or two."""
