@@ -404,6 +404,9 @@ def run_ours(args, rank, world, local_rank):
     # and e2e arms overlap the plan and the per-node-type chains on side streams)
     sink = []
     ops.set_profile_sink(sink)
+    # ~50 us of device-side delay before every timed launch: the event pair then brackets the kernel alone (the host
+    # enqueues it while the GPU is still busy) instead of kernel + the host's launch path on an idle GPU
+    ops.PROFILE_PRESLEEP_CYCLES = int(os.environ.get("HG_PROFILE_PRESLEEP", "100000"))
     launches0 = _lib.launch_count
     saved = ops.PARALLEL_BRANCHES, net.plan_cache.overlap
     ops.PARALLEL_BRANCHES, net.plan_cache.overlap = False, False
@@ -413,6 +416,7 @@ def run_ours(args, rank, world, local_rank):
     fence()
     ops.PARALLEL_BRANCHES, net.plan_cache.overlap = saved
     ops.set_profile_sink(None)
+    ops.PROFILE_PRESLEEP_CYCLES = 0
     launches = _lib.launch_count - launches0
 
     # ---- end-to-end arm (e2e): pinned host buffers -> H2D -> forward -> D2H of the logits, double-buffered:
@@ -466,7 +470,8 @@ def run_ours(args, rank, world, local_rank):
     roof, table = roofline_from(sink, args.steps, peaks)
     traffic = _traffic_table()
     roof["traffic"] = traffic.get(roof["kernel"])
-    roof["timing"] = ("eager pass of the same K steps, one CUDA-event pair per launch, launches serialised on one stream "
+    roof["timing"] = ("eager pass of the same K steps, one CUDA-event pair per launch behind a ~50 us device-side delay (the pair "
+                      "brackets the kernel, not the host launch path on an idle GPU), launches serialised on one stream "
                       "(the value arm replays CUDA graphs with the plan and the rooms-side chain on side streams)")
     total_graphs = G * world
     if world == 1:

@@ -69,10 +69,18 @@ def _call(name: str, meta, fn):
     _call_inner(name, meta, fn)
 
 
+# While a profile sink is set, every timed call is preceded by a device-side delay of this many clock cycles (outside the
+# event pair): the host then enqueues start event, launch and end event while the GPU is still busy, so the pair brackets
+# the kernel alone and not the host's launch path (ctypes marshalling, tensor-map encoding) on an idle GPU.
+PROFILE_PRESLEEP_CYCLES = 0
+
+
 def _call_inner(name: str, meta, fn):
     if _profile_sink is None:
         check(fn(), name)
         return
+    if PROFILE_PRESLEEP_CYCLES > 0:
+        torch.cuda._sleep(PROFILE_PRESLEEP_CYCLES)
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     start.record()
     check(fn(), name)
