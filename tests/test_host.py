@@ -376,3 +376,70 @@ def test_plan_cache_keys_hold_their_tensors_so_recycled_addresses_cannot_alias()
     assert pc.mask_rows("room_rows", m).tolist() == [0, 1, 2]
     e = torch.zeros(2, 3, dtype=torch.long)
     assert same_tensor(e, e) and same_tensor(e, e.view(2, 3)) and not same_tensor(e, e.clone())
+
+
+# ------------------------------------------------------------------------------ device generator (host-side checks)
+def test_synth_entry_points_reject_bad_arguments_on_the_host():
+    import ctypes as C
+
+    h = _lib.load_shared_object()
+    EINVAL = -1
+    assert h.hg_synth_mp3d_counts(None, None) == EINVAL and h.hg_synth_mp3d_fill(None, None) == EINVAL
+    a = _lib.SynthArgs()
+    a.n_graphs = -1
+    assert h.hg_synth_mp3d_counts(C.byref(a), None) == EINVAL
+    a.n_graphs, a.graph_id0 = 4, -3
+    assert h.hg_synth_mp3d_counts(C.byref(a), None) == EINVAL
+    a.graph_id0 = 0  # tables / prefix missing
+    assert h.hg_synth_mp3d_counts(C.byref(a), None) == EINVAL and h.hg_synth_mp3d_fill(C.byref(a), None) == EINVAL
+
+
+def test_generator_enumeration_order_restated_per_graph():
+    """The device generator (csrc/synth.cu) walks one graph at a time: rooms, then per room the object pairs in (a, b)
+    order, both directions next to each other.  The same walk written as scalar Python over the same counter hash must
+    reproduce the vectorised host generator -- this pins the ORDER the kernel relies on without a GPU."""
+    import math
+
+    M = (1 << 64) - 1
+
+    def mix(z):
+        z = (z + 0x9E3779B97F4A7C15) & M
+        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & M
+        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & M
+        return z ^ (z >> 31)
+
+    def u01(k, stream, idx):
+        k = mix(k ^ ((stream * 0xD1B54A32D192ED03) & M))
+        return float(mix(k ^ mix(idx)) >> 11) * (1.0 / 9007199254740992.0)
+
+    cr, co = synth._poisson_cdf(5.0, 64), synth._poisson_cdf(12.0, 128)
+    first, n = 4242, 48
+    host = synth.synth_mp3d_batch(range(first, first + n))
+    rr, oo, o2r, labels = [[], []], [[], []], [], []
+    room0 = obj0 = 0
+    for g in range(n):
+        k = mix(synth.SEED ^ mix(first + g))
+        R = min(max(int(np.searchsorted(cr, u01(k, 1, 0), side="right")), 1), synth.MAX_ROOMS)
+        nobj = [min(max(int(np.searchsorted(co, u01(k, 2, r), side="right")), 1), synth.MAX_OBJ) for r in range(R)]
+        for a in range(R):
+            for b in range(a + 1, R):
+                tree = u01(k, 4, b) < 0.8 and a == int(math.floor(u01(k, 3, b) * b))
+                if tree or u01(k, 5, a * synth.MAX_ROOMS + b) < 0.05:
+                    rr[0] += [room0 + a, room0 + b]
+                    rr[1] += [room0 + b, room0 + a]
+        s = 0
+        for r in range(R):
+            p = min(1.0, 4.0 / max(nobj[r] - 1, 1))
+            for a in range(nobj[r]):
+                for b in range(a + 1, nobj[r]):
+                    if u01(k, 6, (r * synth.MAX_OBJ + a) * synth.MAX_OBJ + b) < p:
+                        oo[0] += [obj0 + s + a, obj0 + s + b]
+                        oo[1] += [obj0 + s + b, obj0 + s + a]
+            o2r += [room0 + r] * nobj[r]
+            labels += [int(math.floor(u01(k, 11, s + o) * synth.N_OBJECT_LABELS)) for o in range(nobj[r])]
+            s += nobj[r]
+        room0, obj0 = room0 + R, obj0 + s
+    assert torch.equal(torch.tensor(rr), host["rooms", "rooms_to_rooms", "rooms"].edge_index)
+    assert torch.equal(torch.tensor(oo), host["objects", "objects_to_objects", "objects"].edge_index)
+    assert torch.equal(torch.tensor(o2r), host["objects", "objects_to_rooms", "rooms"].edge_index[1])
+    assert torch.equal(torch.tensor(labels), host["objects"].y)
