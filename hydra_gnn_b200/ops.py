@@ -304,7 +304,7 @@ def build_csr(specs: Sequence[CSRSpec], overlap: bool = False):
                     n_dst=[int(r.n_dst) for r in rels], caps=[c.cap for c in out[lo:]])
         _call("hg_plan_build", meta,
               lambda: h.hg_plan_build(rels, len(chunk), ptr(st), ptr(ws), ws.numel(), stream_ptr()))
-        _lib.launch_count += 6 + int(any(s.want_window for s in chunk))
+        _lib.launch_count += 4  # count, scan, fill, rank (the tile windows ride on the count and scan passes)
         if lo != 0:
             status += st
     return out, status
