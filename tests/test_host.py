@@ -253,7 +253,7 @@ def test_gloo_world2_shard_and_gather_equals_single_process():
     procs = [ctx.Process(target=_gloo_worker, args=(r, world, port, n_graphs, q)) for r in range(world)]
     for p in procs:
         p.start()
-    counts, gathered = q.get(timeout=120)
+    counts, gathered = q.get(timeout=300)
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
@@ -336,11 +336,11 @@ def _gloo_grad_worker(rank, world, port, out):
 def test_gloo_world2_gradient_all_reduce_gives_the_global_mean():
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
-    q, world, port = ctx.Queue(), 2, 29611
+    q, world, port = ctx.Queue(), 2, _free_port()
     procs = [ctx.Process(target=_gloo_grad_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
-    got = sorted([q.get(timeout=120) for _ in range(world)], key=lambda t: t[0])
+    got = sorted([q.get(timeout=300) for _ in range(world)], key=lambda t: t[0])
     for p in procs:
         p.join(timeout=60)
     torch.manual_seed(0)
