@@ -141,6 +141,10 @@ class LogitGather:
     def launch(self, slot: int = 0) -> None:
         """All-gather of the slot's staged logits on the side stream, ordered after everything queued so far on the
         current stream (the step that staged them)."""
+        if self._side is None:  # CPU process group (gloo, the host-side tests): no streams, the exchange is synchronous
+            dist.all_gather_into_tensor(self._bufs[slot], self._pads[slot], group=self.group)
+            self._last = slot
+            return
         cur = torch.cuda.current_stream()
         self._staged[slot].record(cur)
         with torch.cuda.stream(self._side):
@@ -163,7 +167,8 @@ class LogitGather:
 
     def wait(self, slot: int = 0) -> torch.Tensor:
         """The current stream waits for the slot's gather (before its buffers are overwritten or read)."""
-        torch.cuda.current_stream().wait_event(self._done[slot])
+        if self._side is not None:
+            torch.cuda.current_stream().wait_event(self._done[slot])
         return self._bufs[slot]
 
     def unpad(self, slot: Optional[int] = None) -> torch.Tensor:

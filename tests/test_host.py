@@ -238,8 +238,19 @@ def _gloo_worker(rank, world, port, n_graphs, out):
         logits = torch.cat([rooms, rooms.sum(1, keepdim=True)], dim=1)
         gather = hdist.LogitGather(7).prepare(logits.size(0), logits.device)
         gather(logits)
+        first = gather.unpad().clone()
+        # the pipelined form of bench.py's N > 1 loop: two slots, step k staged while step k - 1 is in flight
+        piped = hdist.LogitGather(7).prepare(logits.size(0), logits.device, slots=2)
+        steps = []
+        for k in range(3):
+            slot = k % 2
+            piped.wait(slot)
+            piped.stage(logits * (k + 1), slot)
+            piped.launch(slot)
+            piped.wait(slot)
+            steps.append(piped.unpad(slot).clone())
         if rank == 0:
-            out.put((gather.counts, gather.unpad().clone()))
+            out.put((gather.counts, first, steps))
         dist.barrier()
     finally:
         dist.destroy_process_group()
@@ -253,7 +264,7 @@ def test_gloo_world2_shard_and_gather_equals_single_process():
     procs = [ctx.Process(target=_gloo_worker, args=(r, world, port, n_graphs, q)) for r in range(world)]
     for p in procs:
         p.start()
-    counts, gathered = q.get(timeout=300)
+    counts, gathered, steps = q.get(timeout=300)
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
@@ -261,6 +272,8 @@ def test_gloo_world2_shard_and_gather_equals_single_process():
     want = torch.cat([rooms, rooms.sum(1, keepdim=True)], dim=1)
     assert sum(counts) == want.size(0)
     assert torch.equal(gathered, want)
+    for k, got in enumerate(steps):  # every step of the two-slot pipeline lands in graph order with its own values
+        assert torch.equal(got, want * (k + 1))
 
 
 def test_checkpoint_keys_of_newer_pyg_are_accepted():
