@@ -17,7 +17,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
 import cases  # noqa: E402
 import hydra_gnn_b200 as hg  # noqa: E402
-from hydra_gnn_b200 import _lib, convert, synth  # noqa: E402
+from hydra_gnn_b200 import _lib, convert, ops, synth  # noqa: E402
 from hydra_gnn_b200 import dist as hdist  # noqa: E402
 from hydra_gnn_b200 import nn as hnn  # noqa: E402
 from hydra_gnn_b200.data import Batch, HeteroData  # noqa: E402
@@ -456,3 +456,45 @@ def test_generator_enumeration_order_restated_per_graph():
     assert torch.equal(torch.tensor(oo), host["objects", "objects_to_objects", "objects"].edge_index)
     assert torch.equal(torch.tensor(o2r), host["objects", "objects_to_rooms", "rooms"].edge_index[1])
     assert torch.equal(torch.tensor(labels), host["objects"].y)
+
+
+# ------------------------------------------------------------------------------ shape heuristics (host-known sizes only)
+def test_gat_mode_choice_from_shapes():
+    """nn._gat_modes: aggregate-first only for far fewer destinations than sources; wide raw rows (306 vs 192) only for
+    batches, even widths and <= 4 heads; never under a HeteroConv mean group."""
+    from types import SimpleNamespace as NS
+
+    o2r, o2o = ("objects", "objects_to_rooms", "rooms"), ("objects", "objects_to_objects", "objects")
+    conv = NS(heads=3, out_channels=64)
+    convs = {o2r: conv, o2o: conv}
+
+    def modes(n_obj, n_room, width, group="sum", c=conv):
+        x = {"objects": torch.empty(n_obj, width), "rooms": torch.empty(n_room, 6)}
+        return hnn._gat_modes({o2r: c, o2o: c}, [o2r, o2o], x, group)
+
+    assert modes(242968, 20277, 306) == (True, False)      # the bench's input layer: wide rows, a batch
+    assert modes(242968, 20277, 64) == (True, False)       # hidden layers: raw rows narrower than the projection
+    assert modes(59, 5, 306) == (False, False)             # batch 1 (serving): the wide form costs latency
+    assert modes(59, 5, 64) == (True, False)
+    assert modes(242968, 20277, 303) == (False, False)     # odd width (GAT_edge input): float2 gathers impossible
+    assert modes(242968, 100000, 64) == (False, False)     # not 4x fewer destinations
+    assert modes(242968, 20277, 306, group="mean") == (False, False)
+    assert modes(242968, 20277, 306, c=NS(heads=6, out_channels=64)) == (True, False)  # 306 <= 384: narrower than the projection
+    assert modes(242968, 20277, 400) == (False, False)     # wider than 1.6 x 192 and than 320
+    assert convs  # (silence linters: both relations share the conv stand-in)
+
+
+def test_window_hint_is_given_only_for_short_windows():
+    """ops.window_applies: every relation has a window, <= 9 edges per destination row, <= 1.5 source rows per destination."""
+    from types import SimpleNamespace as NS
+
+    def rel(n_src, cap, win=True):
+        return NS(csr=NS(tile_win=object() if win else None, cap=cap, n_src=n_src))
+
+    n_o, n_r = 242968, 20277
+    assert ops.window_applies([rel(n_o, 971518 + n_o), rel(n_r, n_o)], n_o)            # objects <- objects (+ loops), <- rooms
+    assert ops.window_applies([rel(n_r, 29294 + n_r)], n_r)                          # rooms <- rooms
+    assert not ops.window_applies([rel(n_o, n_o)], n_r)                              # rooms <- objects: 12 source rows per row
+    assert not ops.window_applies([rel(n_o, 971518 + n_o), rel(n_r, n_o, win=False)], n_o)
+    assert not ops.window_applies([rel(n_o, 10 * n_o)], n_o)                         # too many edges per row for the pool
+    assert not ops.window_applies([], 0)
