@@ -250,7 +250,7 @@ def _gloo_worker(rank, world, port, n_graphs, out):
             piped.wait(slot)
             steps.append(piped.unpad(slot).clone())
         if rank == 0:
-            out.put((gather.counts, first, steps))
+            out.put((gather.counts, first.numpy(), [t.numpy() for t in steps]))  # by value: no fd passing from a process about to exit
         dist.barrier()
     finally:
         dist.destroy_process_group()
@@ -265,6 +265,7 @@ def test_gloo_world2_shard_and_gather_equals_single_process():
     for p in procs:
         p.start()
     counts, gathered, steps = q.get(timeout=300)
+    gathered, steps = torch.from_numpy(gathered), [torch.from_numpy(t) for t in steps]
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
@@ -341,7 +342,7 @@ def _gloo_grad_worker(rank, world, port, out):
         ((x @ w.t() + b).sum() / n_global).backward()  # local sum / global count
         opt.flatten()
         dist.all_reduce(opt.flat_grad)  # the one collective of the training step
-        out.put((rank, opt.flat_grad.clone(), w.grad.clone()))
+        out.put((rank, opt.flat_grad.detach().numpy().copy(), w.grad.detach().numpy().copy()))  # by value (see above)
     finally:
         dist.destroy_process_group()
 
@@ -363,6 +364,7 @@ def test_gloo_world2_gradient_all_reduce_gives_the_global_mean():
     ((x @ w.t() + b).sum() / x.size(0)).backward()
     want = torch.cat([w.grad.reshape(-1), b.grad.reshape(-1)])
     for _, flat, wg in got:
+        flat, wg = torch.from_numpy(flat), torch.from_numpy(wg)
         assert torch.allclose(flat, want, rtol=1e-6, atol=1e-6)
         assert torch.allclose(wg, w.grad, rtol=1e-6, atol=1e-6)  # the parameter's .grad is a view of the reduced buffer
 
